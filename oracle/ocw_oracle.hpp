@@ -20,11 +20,22 @@
 //
 // The only intended deviation from the reference: per-source O(n) resets are replaced by
 // touched-list resets (same values, same semantics, lets the oracle run on 1M-node graphs).
+//
+// Two tie modes (constructor flag `canonical`):
+//   canonical=false : ties resolved exactly as the reference does (tlx binary heap sift rules, std::sort).
+//                     Bitwise equal to oracle/_ref on every input, ties included.
+//   canonical=true  : the CANONICAL tie-breaking the CUDA path implements (BASELINE.json north_star:
+//                     "identical after canonical tie-breaking"): the priority queue pops by the strict
+//                     total order (dist, hops, doubled id); the intermediate list and the chord list are
+//                     sorted stably.  Identical to the reference whenever no two queue entries share
+//                     (dist, hops) -- e.g. iid U(0,1) x* -- which tests/test_oracle_vs_reference.py checks.
 #pragma once
 #include <algorithm>
 #include <array>
 #include <cstdint>
 #include <optional>
+#include <set>
+#include <tuple>
 #include <stdexcept>
 #include <vector>
 
@@ -286,12 +297,13 @@ struct SourceStats {
     int64_t heapMax = 0;      // max heap size
     int64_t intermediates = 0;
     int64_t maxWalkLen = 0;
+    double finalBestDist = 0;
 };
 
 class OcwOracle {
 public:
-    explicit OcwOracle(const Csr &g)
-        : n_(g.n), g_(g), weights_(g.m, 0.), currentSource_(-1), blacklist_(g.n, 0) { // :9-23
+    explicit OcwOracle(const Csr &g, bool canonical = false)
+        : n_(g.n), g_(g), canonical_(canonical), weights_(g.m, 0.), currentSource_(-1), blacklist_(g.n, 0) { // :9-23
         distances_.assign(2 * n_ + 1, kInfDist_);
         hopDistances_.assign(2 * n_ + 1, static_cast<int>(2 * n_ + 2));
         previous_.assign(2 * n_ + 1, -1);
@@ -409,7 +421,10 @@ public:
                 }
             }
         }
-        std::sort(goodChords.begin(), goodChords.end(), [](auto &a, auto &b) { return a.length < b.length; });
+        if (canonical_)
+            std::stable_sort(goodChords.begin(), goodChords.end(), [](auto &a, auto &b) { return a.length < b.length; });
+        else
+            std::sort(goodChords.begin(), goodChords.end(), [](auto &a, auto &b) { return a.length < b.length; });
         // coveredNodes: vector<bool>(n_) indexed by POSITION when read and by NODE ID when written (quirk A.7.3)
         std::vector<int64_t> covered;
         auto isCovered = [&](int64_t k) { return std::find(covered.begin(), covered.end(), k) != covered.end(); };
@@ -463,6 +478,25 @@ private:
                                                   : distances_[u] < distances_[v];
         };
         TlxBinaryHeap<decltype(distSmaller)> heap(distSmaller, handles_);
+        // canonical queue: strict total order (dist, hops, doubled id); handles_[v] >= 0 marks membership
+        using CKey = std::tuple<double, int, int64_t>;
+        std::set<CKey> cq;
+        size_t cqMax = 0;
+        auto qEmpty = [&] { return canonical_ ? cq.empty() : heap.empty(); };
+        auto qTop = [&]() -> int64_t { return canonical_ ? std::get<2>(*cq.begin()) : heap.top(); };
+        auto qPop = [&]() -> int64_t {
+            if (!canonical_) return heap.extractTop();
+            int64_t v = std::get<2>(*cq.begin());
+            cq.erase(cq.begin());
+            handles_[v] = -1;
+            return v;
+        };
+        auto qPush = [&](int64_t v) {
+            if (!canonical_) return heap.push(v);
+            cq.emplace(distances_[v], hopDistances_[v], v);
+            handles_[v] = 0;
+            cqMax = std::max(cqMax, cq.size());
+        };
 
         double bestDist = 1.0 - 1e-6;
         double bestHopDist = 0;
@@ -473,15 +507,18 @@ private:
         touch(currentSource_);
         distances_[currentSource_] = 0.;
         hopDistances_[currentSource_] = 0;
-        heap.push(currentSource_);
+        qPush(currentSource_);
 
         auto updatePaths = [&](int64_t t, double newDist, double newHopDist, int64_t pred) { // :59-84
             if (distances_[t] == newDist ? newHopDist < hopDistances_[t] : newDist < distances_[t]) {
                 touch(t);
+                if (canonical_ && handles_[t] >= 0) cq.erase(CKey(distances_[t], hopDistances_[t], t));
                 distances_[t] = newDist;
                 hopDistances_[t] = static_cast<int>(newHopDist);
                 previous_[t] = pred;
-                if (heap.contains(t))
+                if (canonical_)
+                    qPush(t);
+                else if (heap.contains(t))
                     heap.update(t);
                 else
                     heap.push(t);
@@ -498,8 +535,8 @@ private:
             }
         };
 
-        while (!heap.empty() && heap.top() != target && (2 * distances_[heap.top()] <= bestDist)) { // :88-90
-            int64_t current = heap.extractTop();
+        while (!qEmpty() && qTop() != target && (2 * distances_[qTop()] <= bestDist)) { // :88-90
+            int64_t current = qPop();
             int64_t cur = originalId(current);
             last_.settled++;
             for (int64_t a = g_.rowptr[cur]; a < g_.rowptr[cur + 1]; ++a) { // :96-111
@@ -513,15 +550,21 @@ private:
                 updatePaths(toSide(nb, !side(current)), distances_[current] + crossW, newHopDist, current);
             }
         }
-        last_.heapMax = static_cast<int64_t>(heap.maxSize);
+        for (auto &k : cq) handles_[std::get<2>(k)] = -1;
+        last_.finalBestDist = bestDist;
+        last_.heapMax = static_cast<int64_t>(canonical_ ? cqMax : heap.maxSize);
         heap.clear();
         last_.labelled = static_cast<int64_t>(touched_.size());
         last_.intermediates = static_cast<int64_t>(intermediateVertices_.size());
         if (intermediateVertices_.empty()) blacklistIntReachable(originalId(currentSource_)); // :113-114
-        std::sort(intermediateVertices_.begin(), intermediateVertices_.end(), [this](auto u, auto v) { // :115-117
+        auto byFinalLabel = [this](auto u, auto v) { // :115-117
             return distances_[u] == distances_[v] ? hopDistances_[u] < hopDistances_[v]
                                                   : distances_[u] < distances_[v];
-        });
+        };
+        if (canonical_)
+            std::stable_sort(intermediateVertices_.begin(), intermediateVertices_.end(), byFinalLabel);
+        else
+            std::sort(intermediateVertices_.begin(), intermediateVertices_.end(), byFinalLabel);
     }
 
     struct ParityEdge {
@@ -581,6 +624,7 @@ private:
 
     const int64_t n_;
     const Csr &g_;
+    const bool canonical_;
     std::vector<double> weights_;
     std::vector<double> distances_;
     std::vector<int> hopDistances_;

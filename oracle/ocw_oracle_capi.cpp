@@ -9,7 +9,8 @@ struct OrcEngine {
     orc::Csr g;
     orc::OcwOracle sep;
     std::vector<int64_t> mutated;
-    OrcEngine(int64_t n, int64_t m, const int32_t *eu, const int32_t *ev) : g(orc::csrFromEdgeList(n, m, eu, ev)), sep(g) {}
+    OrcEngine(int64_t n, int64_t m, const int32_t *eu, const int32_t *ev, bool canonical = false)
+        : g(orc::csrFromEdgeList(n, m, eu, ev)), sep(g, canonical) {}
     void updateEdgeWeight(int64_t e, double w) { sep.updateEdgeWeight(e, w); }
     void resetBlacklist(const uint8_t *bl0) {
         for (int64_t u = 0; u < g.n; ++u) sep.updateBlacklist(u, bl0[u] != 0);
@@ -79,8 +80,9 @@ void orc_csr(int64_t n, int64_t m, const int32_t *eu, const int32_t *ev, int64_t
 
 void *orc_sweep(int64_t n, int64_t m, const int32_t *eu, const int32_t *ev, const double *x, const uint8_t *bl0,
                 const int32_t *sources, int64_t nsrc, int mode, int wantLabels, int wantCuts) {
-    OrcEngineFast eng(n, m, eu, ev);
-    return sweep::run(eng, n, x, m, bl0, sources, nsrc, mode, wantLabels, wantCuts);
+    // mode bit 0: 0 = I (independent sources), 1 = V (verbatim sequential); bit 1: canonical tie-breaking
+    OrcEngineFast eng(n, m, eu, ev, (mode & 2) != 0);
+    return sweep::run(eng, n, x, m, bl0, sources, nsrc, mode & 1, wantLabels, wantCuts);
 }
 void orc_sizes(void *h, int64_t *out) { sweep::sizes(static_cast<sweep::Result *>(h), out); }
 double orc_seconds(void *h) { return static_cast<sweep::Result *>(h)->seconds; }

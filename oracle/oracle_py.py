@@ -124,11 +124,16 @@ class _Lib:
         self._f("free")(h)
         return Sweep(cut_off, cut_src, node, stay, lo, ln, ld, lh, stats.reshape(-1, 6), secs, int(sz[4]), int(sz[5]))
 
-    def sweep(self, inst, x, blacklist=None, sources=None, mode="I", want_labels=False, want_cuts=True) -> Sweep:
+    def sweep(self, inst, x, blacklist=None, sources=None, mode="I", want_labels=False, want_cuts=True,
+              canonical=False) -> Sweep:
+        """mode "I": blacklist re-initialised before every source; "V": verbatim sequential sweep.
+        canonical=True (restatement only): canonical tie-breaking, the contract of the CUDA path."""
+        if canonical and self.p != "orc":
+            raise ValueError("the unmodified reference has no canonical tie mode")
         bl = inst.root_blacklist() if blacklist is None else _c(blacklist, np.uint8)
         src = inst.handler_sources() if sources is None else _c(sources, np.int32)
         h = self._f("sweep")(inst.n, inst.m, inst.eu, inst.ev, _c(x, np.float64), bl, src, len(src),
-                             {"I": 0, "V": 1}[mode], int(want_labels), int(want_cuts))
+                             {"I": 0, "V": 1}[mode] | (2 if canonical else 0), int(want_labels), int(want_cuts))
         return self._unpack(h, len(src), want_labels)
 
     def _walk_call(self, name, inst, x, nodes, stay):
