@@ -1,0 +1,349 @@
+#!/usr/bin/env python
+"""bench.py -- odd-cycle separation rounds/s (+ GTEPS) on synthetic instances of the BASELINE.json shapes.
+
+    python bench.py --gpus N --steps K --warmup W [--workload random1m|torus100|torus3d20|random20k] [--impl reference]
+
+A "step" is one root-node separation round: the round's x* and blacklist -> K1 arc records -> K2-K4 bounded
+shortest paths + walk extraction + chord repair for every source 0..n-1 -> K5 canonical dedup
+(-> NCCL all-gather + global dedup when N > 1).  N > 1 shards the SOURCES of the same round block-cyclically over
+the ranks (each GPU holds a graph replica), so total work is fixed: "scaling": "strong".
+
+  value    rounds/s with x*/blacklist already resident in HBM, result left on the device
+  e2e      rounds/s through the C ABI with HOST buffers: H2D of x* + blacklist and D2H of the cut list inside
+           the timed region
+  roofline of the search kernel: algorithmic bytes = 12 B per arc scan + 8 B per settled node
+  cpu_baseline / --impl reference: the UNMODIFIED reference separator (oracle/_ref, built from /root/reference)
+           on the box's host cores over a bounded, seeded sample of the same round's sources, extrapolated
+           linearly to the full round (sources are independent in mode I).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from sms_b200 import instances as I  # noqa: E402
+
+WORKLOADS = {
+    # name: (builder, description)
+    "random1m": (lambda: I.random_graph(1_000_000, 4_000_000, seed=7),
+                 "config 5: sparse random graph 1M nodes / 4M edges, iid U(0,1) x*, sources 0..n-1"),
+    "torus100": (lambda: I.torus2d(100), "config 2: 100x100 toroidal grid (10k nodes, 20k edges), iid U(0,1) x*"),
+    "torus3d20": (lambda: I.torus3d(20), "config 3: 20x20x20 toroidal grid (8k nodes, 24k edges), iid U(0,1) x*"),
+    "random20k": (lambda: I.random_graph(20_000, 80_000, seed=7), "config 4: random graph 20k nodes / 80k edges, iid U(0,1) x*"),
+}
+# sources the reference arm times per step (bounded sample; the reference costs O(n) per source)
+REF_SAMPLE = {"random1m": 256, "torus100": 10_000, "torus3d20": 8_000, "random20k": 4_000}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device_index: int):
+        self.idx = device_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(self.idx)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self) -> dict:
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [t.strip() for t in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# reference arm / cpu baseline: the unmodified reference on host cores
+# ------------------------------------------------------------------------------------------------------------------
+def _ref_worker(args):
+    name, srcs, seed = args
+    from oracle import oracle_py  # checker library, executed here as the timed CPU baseline only
+    inst = WORKLOADS[name][0]()
+    x = I.xstar_uniform(inst.m, seed=seed)
+    eng = oracle_py.ref() if oracle_py.have_ref() else oracle_py.orc()
+    # mode "V": the verbatim loop of ConshdlrOscw::sepaOddCycles (conshdlr_oscw.cpp:188-195) -- what the reference
+    # actually executes per round; no per-source blacklist re-initialisation is charged to it
+    s = eng.sweep(inst, x, sources=np.asarray(srcs, np.int32), mode="V", want_cuts=False)
+    return s.seconds, s.n_walks
+
+
+def reference_round_seconds(name: str, sample: int, procs: int, pool=None):
+    """Seconds the reference needs for `sample` seeded sources with `procs` processes (each its own separator
+    over a contiguous slice, the reference's verbatim sweep).  Returns (seconds for the sample, n sources, kind)."""
+    from oracle import oracle_py
+    kind = "reference" if oracle_py.have_ref() else "port"
+    n = WORKLOADS[name][0]().n if name != "random1m" else 1_000_000
+    sample = min(sample, n)
+    rng = np.random.default_rng(12345)
+    srcs = np.sort(rng.choice(n, sample, replace=False)) if sample < n else np.arange(n)
+    chunks = [c for c in np.array_split(srcs, procs) if len(c)]
+    t0 = time.perf_counter()
+    if pool is None or procs == 1:
+        res = [_ref_worker((name, c, 1)) for c in chunks]
+        wall = sum(r[0] for r in res)
+    else:
+        res = pool.map(_ref_worker, [(name, c, 1) for c in chunks])
+        wall = max(r[0] for r in res)  # separation time of the slowest worker (graph build excluded)
+    _ = time.perf_counter() - t0
+    return wall, sample, n, kind
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    import multiprocessing as mp
+    procs = os.cpu_count() or 1
+    sample = REF_SAMPLE[args.workload]
+    ctx = mp.get_context("spawn")
+    times = []
+    with ctx.Pool(procs) as pool:
+        pool.map(_ref_worker, [(args.workload, np.arange(2), 1)] * procs)  # page in / build graphs once per worker
+        for it in range(args.warmup + args.steps):
+            wall, sample_n, n, kind = reference_round_seconds(args.workload, sample, procs, pool)
+            if it >= args.warmup:
+                times.append(wall * (n / sample_n))
+    sec = statistics.mean(times)
+    val = 1.0 / sec
+    line = {
+        "impl": "reference", "metric": "odd-cycle separation rounds/sec", "value": val, "unit": "rounds/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": WORKLOADS[args.workload][1], "name": args.workload, "mode": "V (the reference's own sequential sweep) per process slice"},
+        "cpu_baseline": {"value": val, "unit": "rounds/s", "cores": procs, "kind": kind,
+                         "sample": f"{sample_n} seeded sources of {n} per step, one separator per process over a slice, "
+                                   f"time of the slowest process extrapolated x{n / sample_n:.1f}"},
+        "e2e": {"value": val, "unit": "rounds/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# own arm
+# ------------------------------------------------------------------------------------------------------------------
+def time_rounds(ctx, torch, dist, world, steps, warmup, step_fn, flush):
+    for _ in range(warmup):
+        step_fn()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    per = []
+    for _ in range(steps):
+        flush()
+        per.append(step_fn())
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([dt], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dt = float(t.item())
+    return dt, per
+
+
+def measure_workload(name, args, torch, dist, rank, world, device, full=True):
+    from sms_b200 import capi
+    inst = WORKLOADS[name][0]()
+    x = I.xstar_uniform(inst.m, seed=1)
+    bl = inst.root_blacklist()
+    ctx = capi.Context(inst.n, inst.rowptr, inst.col, inst.eid, device=device)
+    if world > 1:
+        uid = [ctx.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        ctx.comm_init(uid[0], rank, world)
+    ctx.set_sources(None, rank, world)
+    p = ctx.params(dedup=1)
+    import ctypes as C
+    lib = ctx.lib
+    # L2 flush buffer (> 126 MB), written between timed iterations
+    flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+
+    def flush():
+        flush_buf.zero_()
+
+    # ---- value leg: inputs resident in HBM, result left on the device ----
+    dx = torch.from_numpy(x).cuda()
+    dbl = torch.from_numpy(bl).cuda()
+    torch.cuda.synchronize()
+    agg = {"ms_search": 0.0, "arcs": 0, "settled": 0, "launches": 0, "search_launches": 0, "n": 0, "ms_dev": 0.0,
+           "ms_weights": 0.0, "ms_dedup": 0.0}
+
+    def step_dev():
+        ctx.set_round_input_device(dx.data_ptr(), dbl.data_ptr())
+        ctx._check(lib.smsgpu_separate_async(ctx.h, C.byref(p)))
+        return None
+
+    sampler = ClockSampler(device)
+    # warm-up (allocations, tier scratch) happens inside time_rounds
+    for _ in range(max(args.warmup, 3)):
+        step_dev()
+    torch.cuda.synchronize()
+    sampler.start()
+    dt, _ = time_rounds(ctx, torch, dist, world, args.steps, 0, step_dev, flush)
+    clocks = sampler.stop()
+    # per-round device stats of the last round (events on the library's own stream)
+    ctx.fetch()
+    st = ctx.stats()
+    ncuts, nnodes = ctx.cut_counts()
+    res = {"dt": dt, "stats": st, "ncuts": ncuts, "nnodes": nnodes, "clocks": clocks, "n": inst.n, "m": inst.m}
+    # aggregate algorithmic work over ranks (each rank searched its share of the sources)
+    work = torch.tensor([st["arcs_scanned"], st["settled"], st["sources_run"], st["raw_walks"]], dtype=torch.float64, device="cuda")
+    ms = torch.tensor([st["ms_search"], st["ms_weights"], st["ms_dedup"], st["ms_total_device"]], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(work, op=dist.ReduceOp.SUM)
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    res["arcs"], res["settled"], res["sources_run"], res["raw_walks"] = (int(v) for v in work.tolist())
+    res["ms_search"], res["ms_weights"], res["ms_dedup"], res["ms_total_device"] = ms.tolist()
+
+    # ---- e2e leg: host buffers through the C ABI, H2D and D2H inside the timed region ----
+    if full:
+        def step_host():
+            ctx.set_round_input(x, bl)
+            ctx.separate_nocopy(p)
+            return None
+        dt2, _ = time_rounds(ctx, torch, dist, world, args.steps, max(1, args.warmup // 2), step_host, flush)
+        ncuts2, nnodes2 = ctx.cut_counts()
+        res["e2e_dt"] = dt2
+        res["h2d"] = inst.m * 8 + inst.n
+        res["d2h"] = (ncuts2 + 1) * 8 + nnodes2 * 9 + ncuts2 * 16
+    ctx.close()
+    return res
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default="random1m", choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="skip the secondary torus100 measurement")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference_arm(args)
+
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the separation engine has no CPU fallback")
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE {world}")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    args.warmup = max(args.warmup, 3)
+
+    from sms_b200 import build
+    build.build()
+    res = measure_workload(args.workload, args, torch, dist, rank, world, local, full=True)
+    extra = {}
+    if world == 1 and not args.no_extra and args.workload != "torus100":
+        r2 = measure_workload("torus100", argparse.Namespace(steps=50, warmup=5), torch, dist, rank, world, local, full=True)
+        extra["torus100"] = {"rounds_per_s_device": 50 / r2["dt"], "rounds_per_s_e2e": 50 / r2["e2e_dt"],
+                             "ms_search": r2["ms_search"], "unique_cuts": r2["ncuts"], "arcs_scanned": r2["arcs"]}
+    if rank == 0:
+        peak, peak_src = peaks()
+        sec = res["dt"] / args.steps
+        alg_bytes = 12.0 * res["arcs"] + 8.0 * res["settled"]
+        # the search kernels of all ranks run concurrently: aggregate bytes / slowest rank's kernel time / N GPUs
+        ach = alg_bytes / (res["ms_search"] * 1e-3) / 1e9 / world if res["ms_search"] > 0 else 0.0
+        line = {
+            "metric": "odd-cycle separation rounds/sec", "value": 1.0 / sec, "unit": "rounds/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": WORKLOADS[args.workload][1], "name": args.workload, "n": res["n"], "m": res["m"],
+                       "sources": res["n"], "mode": "I (independent sources), canonical ties, dedup on",
+                       "l2": "256 MiB buffer rewritten between timed iterations; arc array alone is 16 B x 2m",
+                       "parallelism": f"sources block-cyclic over {world} GPU(s), graph replicated"},
+            "gteps": res["arcs"] / sec / 1e9,
+            "arcs_scanned_per_round": res["arcs"], "settled_per_round": res["settled"], "raw_walks": res["raw_walks"],
+            "unique_cuts": res["ncuts"],
+            "kernel_ms": {"weights": res["ms_weights"], "search": res["ms_search"], "dedup_and_merge": res["ms_dedup"],
+                          "device_total": res["ms_total_device"]},
+            "tier_sources": res["stats"]["tier_sources"],
+            "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                         "traffic": None, "peak_source": peak_src, "kernel": "ocwSearchKernel",
+                         "algorithmic_bytes": alg_bytes, "per_gpu": True},
+            "e2e": {"value": args.steps / res["e2e_dt"], "unit": "rounds/s", "h2d_bytes_per_step": res["h2d"],
+                    "d2h_bytes_per_step": res["d2h"]},
+            "gpu_launches": int(res["stats"]["total_launches"]) * args.steps,
+            "clocks": res["clocks"],
+            "extra": extra,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            wall, sample_n, n, kind = reference_round_seconds(args.workload, max(64, REF_SAMPLE[args.workload] // 4), 1)
+            est = wall * (n / sample_n)
+            line["cpu_baseline"] = {"value": 1.0 / est, "unit": "rounds/s", "cores": 1, "kind": kind,
+                                    "sample": f"{sample_n} seeded sources of {n}, 1 thread (the reference is single-threaded), "
+                                              f"{wall:.2f} s extrapolated x{n / sample_n:.1f}"}
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,161 @@
+// Kernels of the separation round that touch the graph:
+//   dcWeightsKernel  (K1)      per-round arc records: clamp(x*[eid]) + blacklist bit, CSR order
+//   ocwSearchKernel  (K2-K4)   persistent tiles pulling sources from an atomic cursor
+//   initTablesKernel           one-time clearing of the HBM label tables of tiers 1 / 2
+#pragma once
+#include "ocw_walks.cuh"
+
+namespace smsgpu {
+
+// ---- K1 ------------------------------------------------------------------------------------------------------
+// Replaces the m calls of OcwSeparator::updateWeights (ocw_seperator.cpp:25-31; clamp = std::min(std::max(0., w), 1.))
+// and folds the round's blacklist (ocw_seperator.hpp:25-28) into the arc.  One thread per 4 consecutive arcs:
+// 128-bit loads of col / eid, four 128-bit stores.
+__global__ void __launch_bounds__(256) dcWeightsKernel(const long long narcs, const int32_t *__restrict__ col,
+                                                       const int32_t *__restrict__ eid, const double *__restrict__ x,
+                                                       const uint8_t *__restrict__ bl, Arc *__restrict__ arcs) {
+    const long long nquads = narcs >> 2;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < nquads; q += stride) {
+        const int4 c = reinterpret_cast<const int4 *>(col)[q];
+        const int4 e = reinterpret_cast<const int4 *>(eid)[q];
+        const int cs[4] = {c.x, c.y, c.z, c.w};
+        const int es[4] = {e.x, e.y, e.z, e.w};
+        double ws[4];
+        int bs[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            ws[k] = __ldg(x + es[k]);
+            bs[k] = __ldg(bl + cs[k]);
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            Arc a;
+            a.nbr = cs[k] | (bs[k] ? (int32_t)0x80000000 : 0);
+            a.eid = es[k];
+            a.w = clamp01(ws[k]);
+            arcs[4 * q + k] = a;
+        }
+    }
+    // tail
+    const long long t = 4 * nquads + (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < narcs) {
+        Arc a;
+        const int c = col[t];
+        a.nbr = c | (bl[c] ? (int32_t)0x80000000 : 0);
+        a.eid = eid[t];
+        a.w = clamp01(x[a.eid]);
+        arcs[t] = a;
+    }
+}
+
+__global__ void initTablesKernel(unsigned char *scratch, const size_t tileStride, const long long ntiles,
+                                 const unsigned tabCap) {
+    const long long total = ntiles * (long long)tabCap;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+        const long long t = i / tabCap, s = i % tabCap;
+        storeEntry(reinterpret_cast<Entry *>(scratch + t * tileStride) + s, emptyEntry());
+    }
+}
+
+// ---- K2-K4 ---------------------------------------------------------------------------------------------------
+template <int TW, bool SMEM>
+__global__ void __launch_bounds__(128) ocwSearchKernel(const GraphDev G, const SearchParams P, const RawOut R,
+                                                        const TileCaps caps, unsigned char *scratch) {
+    extern __shared__ __align__(32) unsigned char smem[];
+    const Tile<TW> T;
+    const int tilesPerCta = blockDim.x / TW;
+    const int tileInCta = threadIdx.x / TW;
+    const size_t tb = tileBytes(caps);
+    TileMem M;
+    carveTileMem(M, SMEM ? smem + (size_t)tileInCta * tb
+                         : scratch + ((size_t)blockIdx.x * tilesPerCta + tileInCta) * tb,
+                 caps);
+    if (SMEM) {
+        for (uint32_t i = T.lane; i < caps.tabCap; i += TW) storeEntry(&M.tab[i], emptyEntry());
+        T.sync();
+    }
+    const long long total = P.worklist ? P.nwork : P.nsrc;
+    long long accArcs = 0, accSettled = 0, accSources = 0;
+    uint32_t sel[16];
+    const int maxInter = min(P.maxInter, 16);
+
+    while (true) {
+        long long wi = 0;
+        if (T.lane == 0) wi = (long long)atomicAdd(P.queueCounter, 1ull);
+        wi = T.shfl(wi, 0);
+        if (wi >= total) break;
+        const int32_t srcIdx = P.worklist ? P.worklist[wi] : (int32_t)wi;
+        const uint32_t src = P.sources ? (uint32_t)P.sources[srcIdx] : (uint32_t)(P.srcBegin + srcIdx * P.srcStride);
+        // `if (blacklist_[currentSource_]) return {}` -- indexed with the DOUBLED id (ocw_seperator.cpp:334, quirk A.7.1)
+        if ((long long)src < G.n && P.blacklist[src]) continue;
+        if ((long long)(src >> 1) >= G.n) continue; // not a node of the double cover
+
+        SrcState S;
+        searchSource<TW>(T, G, M, S, src, P.bestInit);
+        if (!S.overflow && S.histN > 0) {
+            const int nsel = selectIntermediates<TW>(T, M, S, maxInter, sel);
+            if (!S.overflow && T.lane == 0) {
+                Emitter E;
+                E.R = &R;
+                E.srcIdx = srcIdx;
+                E.seq = 0;
+                E.tier = P.tier;
+                for (int r = 0; r < nsel; ++r) {
+                    const int W = buildWalk(M, sel[r], src);
+                    if (W < 0) {
+                        S.overflow = 1;
+                        break;
+                    }
+                    simpleOddCyclesAndExtract(G, M, S, E, W);
+                    if (S.overflow) break;
+                }
+            }
+            S.overflow = T.shfl(S.overflow, 0);
+        }
+        if (!S.overflow) {
+            if (P.exportLabels) {
+                for (uint32_t i = T.lane; i < S.touchedN; i += TW) {
+                    const Entry e = loadEntry(&M.tab[M.touched[i]]);
+#pragma unroll
+                    for (int sd = 0; sd < 2; ++sd) {
+                        const double d = sd ? e.d1 : e.d0;
+                        if (d >= kUnlabelled) continue;
+                        const long long li = (long long)atomicAdd(&R.counters[5], 1ull);
+                        if (li < R.labCap) {
+                            R.labSrc[li] = srcIdx;
+                            R.labNode[li] = (int32_t)(2 * e.key + sd);
+                            R.labDist[li] = d;
+                            R.labHops[li] = (int32_t)(sd ? e.h1 : e.h0);
+                        }
+                    }
+                }
+            }
+            if (T.lane == 0) {
+                R.srcTier[srcIdx] = (int8_t)P.tier;
+                if (R.srcArcs) {
+                    R.srcArcs[srcIdx] = S.arcs;
+                    R.srcSettled[srcIdx] = S.settled;
+                }
+            }
+            accArcs += S.arcs;
+            accSettled += S.settled;
+            accSources++;
+        } else if (T.lane == 0) {
+            const unsigned long long k = atomicAdd(P.ovfCount, 1ull);
+            P.ovfList[k] = srcIdx;
+        }
+        // leave the table clean for the next source
+        T.sync();
+        for (uint32_t i = T.lane; i < S.touchedN; i += TW) storeEntry(&M.tab[M.touched[i]], emptyEntry());
+        T.sync();
+    }
+    if (T.lane == 0 && accSources) {
+        atomicAdd(&R.counters[2], (unsigned long long)accArcs);
+        atomicAdd(&R.counters[3], (unsigned long long)accSettled);
+        atomicAdd(&R.counters[4], (unsigned long long)accSources);
+    }
+}
+
+} // namespace smsgpu

@@ -1,0 +1,118 @@
+// Shared device/host types of the odd-cycle separation engine (libsmsgpu.so).
+// Product code: nothing under oracle/ is included or linked here.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace smsgpu {
+
+// One CSR adjacency entry in HBM, rebuilt every round by K1 (dc_weights): 16 B, one 128-bit load per arc scan.
+//   nbr : neighbour's original vertex id, bit 31 set when the neighbour is blacklisted this round
+//         (folds the `if (blacklist_[neighbor]) continue` of ocw_seperator.cpp:98-99 into the arc)
+//   eid : NetworKit edge id
+//   w   : stay weight = clamp(x*[eid], 0, 1) (ocw_seperator.cpp:25-35); the cross weight 1.0 - w is computed
+struct __align__(16) Arc {
+    int32_t nbr;
+    int32_t eid;
+    double w;
+};
+
+// Label-table entry: both double-cover copies (v,0) and (v,1) of one original vertex share one 32-byte
+// entry (one HBM sector), so the twin test dist[t] + dist[t^1] of ocw_seperator.cpp:72-74 costs no probe.
+struct __align__(16) Entry {
+    double d0, d1;     // distances_ of side 0 / side 1; kUnlabelled when the side has no label
+    uint32_t key;      // original vertex id, kEmptyKey when the slot is free
+    uint32_t h0, h1;   // hopDistances_
+    uint32_t flags;    // bit s: side s settled (extracted from the queue)
+};
+static_assert(sizeof(Entry) == 32, "Entry must be one 32-byte sector");
+
+// Priority-queue entry; (hi, lo) compared as one 128-bit unsigned number = the canonical strict order
+// (dist, hops, doubled id).  dist >= +0.0, so the IEEE bit pattern is order preserving.
+struct __align__(16) HeapEnt {
+    unsigned long long hi; // __double_as_longlong(dist)
+    unsigned long long lo; // hops << 32 | doubled id
+};
+
+constexpr uint32_t kEmptyKey = 0xFFFFFFFFu;
+constexpr double kUnlabelled = 4.0;       // > any reachable distance (< 1.5); never compares as an improvement
+constexpr uint32_t kUnlabelledHops = 0x3FFFFFFFu;
+constexpr double kInfDist = 1.0 + 10e-4;  // kInfDist_, include/sms/graph/ocw_seperator.hpp:45: offers >= this are never labelled
+
+// std::min(std::max(0., w), 1.) exactly as the reference evaluates it (ocw_seperator.cpp:28,34)
+__host__ __device__ __forceinline__ double clamp01(double w) {
+    const double a = (0. < w) ? w : 0.; // std::max(0., w)
+    return (1. < a) ? 1. : a;           // std::min(a, 1.)
+}
+
+struct GraphDev {
+    int64_t n, m;
+    const int64_t *rowptr; // n+1
+    const Arc *arcs;       // 2m, adjacency order of the reference graph
+};
+
+// Capacities of one tile's private working memory (shared memory in tier 0, HBM in tiers 1 and 2).
+struct TileCaps {
+    uint32_t tabCap;     // label-table slots (power of two unless dense)
+    uint32_t tabShift;   // 32 - log2(tabCap)
+    uint32_t dense;      // 1: slot = vertex id, no hashing (tier 2)
+    uint32_t touchedCap; // max entries a source may create (<= tabCap / 2 unless dense)
+    uint32_t heapCap;    // queue entries
+    uint32_t histCap;    // intermediate-vertex history entries
+    uint32_t walkCap;    // max edges of one path / walk
+    uint32_t chordCap;   // max good chords of one cycle
+};
+
+// bytes of one tile's working memory
+__host__ __device__ inline size_t tileBytes(const TileCaps &c) {
+    size_t b = 0;
+    b += (size_t)c.tabCap * sizeof(Entry);         // table
+    b += (size_t)c.tabCap * 2 * sizeof(uint32_t);  // pred per (slot, side)
+    b += (size_t)c.touchedCap * sizeof(uint32_t);  // touched slots
+    b += (size_t)c.heapCap * sizeof(HeapEnt);      // queue (re-used as sort scratch after the search)
+    b += (size_t)c.histCap * sizeof(uint32_t);     // history of intermediates
+    // walk scratch: pa, pb (walkCap+2 each), wn (2*walkCap+2), ws (2*walkCap+2), warc (2*walkCap+2), crs (2*walkCap+2)
+    b += (size_t)(2 * (c.walkCap + 2) + 4 * (2 * c.walkCap + 2)) * sizeof(int32_t);
+    b += (size_t)(2 * c.walkCap + 2) * sizeof(double); // plen
+    b += (size_t)c.chordCap * 4 * sizeof(int32_t);     // chords
+    b += (size_t)c.chordCap * 0 + (size_t)(4 * c.walkCap + 8) * sizeof(int32_t); // covered list
+    return (b + 31) & ~(size_t)31;
+}
+
+// Raw (pre-dedup) output arena, filled by the search kernel with atomic bump allocation.
+struct RawOut {
+    int32_t *node, *eid;   // [nodeCap]
+    uint8_t *stay;         // [nodeCap]
+    int32_t *cutOff;       // [cutCap]
+    int32_t *cutLen;       // [cutCap]
+    int32_t *cutSrc;       // [cutCap] local source index
+    int32_t *cutSeq;       // [cutCap] emission index within the source
+    int8_t *cutTier;       // [cutCap] tier that emitted it (valid iff == srcTier[src])
+    unsigned long long *counters; // [0] cuts, [1] nodes, [2] arcs scanned, [3] settled, [4] sources run, [5] labels
+    long long cutCap, nodeCap;
+    // label export (parity tests)
+    int32_t *labSrc, *labNode, *labHops;
+    double *labDist;
+    long long labCap;
+    // per-source
+    int8_t *srcTier;       // [nsrc] tier the source finished in, -1 = not finished / skipped
+    long long *srcArcs, *srcSettled; // nullable
+};
+
+struct SearchParams {
+    const int32_t *sources; // doubled ids; nullptr -> srcBegin + i*srcStride
+    long long nsrc;         // local number of sources
+    long long srcBegin, srcStride;
+    const int32_t *worklist; // nullptr in the first tier, else local source indices that overflowed
+    long long nwork;
+    unsigned long long *queueCounter; // work-stealing cursor
+    int32_t *ovfList;       // overflowed local source indices
+    unsigned long long *ovfCount;
+    const uint8_t *blacklist; // [n] the round's initial blacklist (source skip test, ocw_seperator.cpp:334)
+    double bestInit;
+    int32_t maxInter;
+    int32_t tier;
+    int32_t exportLabels;
+};
+
+} // namespace smsgpu

@@ -1,0 +1,315 @@
+// K3/K4: candidate selection, walk extraction, simple-cycle split and chord repair for one source, run by the
+// tile right after its search while the label table is still hot.
+//   selectIntermediates  <- std::sort of intermediateVertices_ + "first 10" (ocw_seperator.cpp:115-117, 343-346)
+//   buildWalk            <- getShortestPath + intermediateVertexToOcw      (ocw_seperator.cpp:120-188)
+//   simpleOddCycles      <- OcwSeparator::simpleOddCycles                  (ocw_seperator.cpp:202-227)
+//   extractCycles        <- OcwSeparator::extractCycles + OddClosedWalk::splitOnChord
+//                                                   (ocw_seperator.cpp:229-328, odd_closed_walk.cpp:67-90)
+// Walks are a handful of edges long, so everything after the selection is plain sequential code on lane 0;
+// the reference's O(n) scratch vectors (prevPos[n_], coveredNodes(n_)) become scans over the walk itself.
+#pragma once
+#include "ocw_search.cuh"
+
+namespace smsgpu {
+
+struct Emitter {
+    const RawOut *R;
+    int32_t srcIdx;
+    int32_t seq;
+    int32_t tier;
+};
+
+// reserve room for one cut; returns false (and still counts) when the arena is full
+__device__ __forceinline__ bool emitReserve(Emitter &E, int len, long long &cut, long long &off) {
+    cut = (long long)atomicAdd(&E.R->counters[0], 1ull);
+    off = (long long)atomicAdd(&E.R->counters[1], (unsigned long long)len);
+    const bool ok = cut < E.R->cutCap && off + len <= E.R->nodeCap;
+    if (ok) {
+        E.R->cutOff[cut] = (int32_t)off;
+        E.R->cutLen[cut] = len;
+        E.R->cutSrc[cut] = E.srcIdx;
+        E.R->cutSeq[cut] = E.seq;
+        E.R->cutTier[cut] = (int8_t)E.tier;
+    }
+    E.seq++;
+    return ok;
+}
+
+// ---- selection of the first maxInter intermediates by final (dist, hops), stable --------------------------------
+// Writes the selected doubled ids to sel[0..nsel).  Uses the (now idle) queue memory as key scratch.
+template <int TW>
+__device__ int selectIntermediates(const Tile<TW> &T, TileMem &M, SrcState &S, int maxInter, uint32_t *sel) {
+    const uint32_t H = S.histN;
+    if (H > M.caps.heapCap) {
+        S.overflow = 1;
+        return 0;
+    }
+    for (uint32_t i = T.lane; i < H; i += TW) {
+        const uint32_t t = M.hist[i];
+        const int slot = findSlot(M, t >> 1);
+        const Entry e = loadEntry(&M.tab[slot]);
+        HeapEnt k;
+        k.hi = (unsigned long long)__double_as_longlong((t & 1u) ? e.d1 : e.d0);
+        k.lo = ((unsigned long long)((t & 1u) ? e.h1 : e.h0) << 32) | i; // history index: stable order
+        M.heap[i] = k;
+    }
+    T.sync();
+    const int nsel = (int)min((uint32_t)maxInter, H);
+    for (int r = 0; r < nsel; ++r) {
+        unsigned long long mhi = ~0ull, mlo = ~0ull;
+        for (uint32_t i = T.lane; i < H; i += TW) {
+            const HeapEnt k = M.heap[i];
+            if (keyLess(k.hi, k.lo, mhi, mlo)) {
+                mhi = k.hi;
+                mlo = k.lo;
+            }
+        }
+#pragma unroll
+        for (int off = TW / 2; off > 0; off >>= 1) {
+            const unsigned long long ohi = T.shflXor(mhi, off), olo = T.shflXor(mlo, off);
+            if (keyLess(ohi, olo, mhi, mlo)) {
+                mhi = ohi;
+                mlo = olo;
+            }
+        }
+        const uint32_t idx = (uint32_t)(mlo & 0xFFFFFFFFull);
+        if (T.lane == 0) {
+            sel[r] = M.hist[idx];
+            HeapEnt k;
+            k.hi = ~0ull;
+            k.lo = ~0ull;
+            M.heap[idx] = k;
+        }
+        T.sync();
+    }
+    return nsel;
+}
+
+// ---- sequential helpers (lane 0) ------------------------------------------------------------------------------
+// Graph::indexInOutEdgeArray (NetworKit Graph.cpp:119-127): first adjacency position of u holding v
+__device__ __forceinline__ long long findArc(const GraphDev &G, int32_t u, int32_t v) {
+    for (long long a = G.rowptr[u]; a < G.rowptr[u + 1]; ++a)
+        if ((G.arcs[a].nbr & 0x7FFFFFFF) == v) return a;
+    return -1;
+}
+
+// getShortestPath (:120-136): doubled ids t = p[0], previous_[p[0]] = p[1], ..., p[len] = source.  -1 on overflow.
+__device__ inline int tracePath(const TileMem &M, uint32_t t, uint32_t src, int32_t *p) {
+    int len = 0;
+    uint32_t cur = t;
+    p[0] = (int32_t)cur;
+    while (cur != src) {
+        if (len >= (int)M.caps.walkCap) return -1;
+        const int slot = findSlot(M, cur >> 1);
+        cur = M.pred[2 * slot + (cur & 1u)];
+        p[++len] = (int32_t)cur;
+    }
+    return len;
+}
+
+// extractCycles (:229-328) on the closed walk c[0..len] (c[len] == c[0]) with stay flags st[0..len).
+__device__ inline void extractCycles(const GraphDev &G, TileMem &M, SrcState &S, Emitter &E, const int32_t *c,
+                                     const int32_t *st, const int len) {
+    int32_t *warc = M.warc; // warc[i]: arc (in the row of c[i]) of the edge c[i-1] - c[i], i = 1..len
+    int32_t *crs = M.crs;
+    double *plen = M.plen;
+    // prefix sums (:242-250)
+    int numCross = 0;
+    double pathLength = 0.;
+    crs[0] = 0;
+    plen[0] = 0.;
+    for (int i = 1; i <= len; ++i) {
+        numCross += st[i - 1] ? 0 : 1;
+        const long long a = findArc(G, c[i], c[i - 1]);
+        warc[i] = (int32_t)a;
+        const double w = G.arcs[a].w;
+        pathLength += st[i - 1] ? w : 1 - w;
+        crs[i] = numCross;
+        plen[i] = pathLength;
+    }
+    // good chords (:254-306)
+    int nch = 0;
+    for (int i = 2; i < len; ++i) {
+        const int32_t cur = c[i];
+        for (long long a = G.rowptr[cur]; a < G.rowptr[cur + 1]; ++a) {
+            const Arc arc = G.arcs[a];
+            const int32_t nb = arc.nbr & 0x7FFFFFFF;
+            if (nb == c[i - 1] || nb == c[i + 1]) continue;
+            int j = -1;
+            for (int k = 0; k < i; ++k)
+                if (c[k] == nb) {
+                    j = k;
+                    break;
+                }
+            if (j < 0) continue;
+            const int innerCrossingDif = crs[i] - crs[j];
+            const double innerLen = plen[i] - plen[j];
+            const double outerLen = plen[len] - innerLen;
+            // weights_[edgeId(c[i], c[j])]: first arc of c[i] towards c[j]
+            const long long ca = findArc(G, cur, nb);
+            const double x = G.arcs[ca].w;
+            int f0 = -1, l0 = 0, f1 = -1, l1 = 0; // flags: bit0 crossing, bit1 inner
+            if ((innerCrossingDif % 2) == 0) {
+                if (innerLen - x < 0) {
+                    f0 = 1 | 2;
+                    l0 = i - j + 1;
+                }
+                if (outerLen + x < 1) {
+                    f1 = 0;
+                    l1 = len - i + j + 1;
+                }
+            } else {
+                if (innerLen + x < 1) {
+                    f0 = 2;
+                    l0 = i - j + 1;
+                }
+                if (outerLen - x < 0) {
+                    f1 = 1;
+                    l1 = len - i + j + 1;
+                }
+            }
+            for (int q = 0; q < 2; ++q) {
+                const int f = q ? f1 : f0;
+                if (f < 0) continue;
+                if (nch >= (int)M.caps.chordCap) {
+                    S.overflow = 1;
+                    return;
+                }
+                int32_t *ch = M.chords + 4 * nch++;
+                ch[0] = j;
+                ch[1] = i;
+                ch[2] = q ? l1 : l0;
+                ch[3] = (int32_t)((uint32_t)f | ((uint32_t)ca << 2)); // 2m < 2^30 checked at create
+            }
+        }
+    }
+    // stable sort by resulting length (:309; canonical: stable)
+    for (int a = 1; a < nch; ++a) {
+        int32_t t0 = M.chords[4 * a], t1 = M.chords[4 * a + 1], t2 = M.chords[4 * a + 2], t3 = M.chords[4 * a + 3];
+        int b = a - 1;
+        while (b >= 0 && M.chords[4 * b + 2] > t2) {
+            for (int q = 0; q < 4; ++q) M.chords[4 * (b + 1) + q] = M.chords[4 * b + q];
+            --b;
+        }
+        M.chords[4 * (b + 1)] = t0;
+        M.chords[4 * (b + 1) + 1] = t1;
+        M.chords[4 * (b + 1) + 2] = t2;
+        M.chords[4 * (b + 1) + 3] = t3;
+    }
+    // greedy, non-overlapping (:312-323).  coveredNodes is READ by position and WRITTEN by node id (quirk A.7.3)
+    int ncov = 0, emitted = 0;
+    const int covCap = 4 * (int)M.caps.walkCap + 8;
+    for (int q = 0; q < nch; ++q) {
+        const int32_t *ch = M.chords + 4 * q;
+        const int start = ch[0], end = ch[1];
+        bool cs = false, ce = false;
+        for (int k = 0; k < ncov; ++k) {
+            cs |= M.covered[k] == start;
+            ce |= M.covered[k] == end;
+        }
+        if (cs || ce) continue;
+        const bool crossing = ch[3] & 1, inner = (ch[3] & 2) != 0;
+        const long long ca = (long long)((uint32_t)ch[3] >> 2);
+        const int32_t chordEid = G.arcs[ca].eid;
+        const int wlen = ch[2];
+        long long cut, off;
+        const bool ok = emitReserve(E, wlen, cut, off);
+        // splitOnChord (odd_closed_walk.cpp:67-90)
+        int pos = 0;
+        auto put = [&](int32_t node, int32_t eid, int32_t stay) {
+            if (ok) {
+                E.R->node[off + pos] = node;
+                E.R->eid[off + pos] = eid;
+                E.R->stay[off + pos] = (uint8_t)stay;
+            }
+            // covered: positions 1 .. size-2 of the new walk, by node id
+            if (pos >= 1 && pos <= wlen - 2) {
+                if (ncov < covCap) M.covered[ncov] = node;
+                ncov++;
+            }
+            pos++;
+        };
+        if (inner) {
+            for (int k = start; k < end; ++k) put(c[k], G.arcs[warc[k + 1]].eid, st[k]);
+            put(c[end], chordEid, crossing ? 0 : 1);
+        } else {
+            for (int k = 0; k < start; ++k) put(c[k], G.arcs[warc[k + 1]].eid, st[k]);
+            put(c[start], chordEid, crossing ? 0 : 1);
+            for (int k = end; k < len; ++k) put(c[k], G.arcs[warc[k + 1]].eid, st[k]);
+        }
+        if (ncov > covCap) {
+            S.overflow = 1;
+            return;
+        }
+        emitted++;
+    }
+    if (emitted == 0) { // :325-326: no chord cycle -> the cycle itself
+        long long cut, off;
+        if (emitReserve(E, len, cut, off))
+            for (int k = 0; k < len; ++k) {
+                E.R->node[off + k] = c[k];
+                E.R->eid[off + k] = G.arcs[warc[k + 1]].eid;
+                E.R->stay[off + k] = (uint8_t)st[k];
+            }
+    }
+}
+
+// simpleOddCycles (:202-227) on the closed walk wn[0..W], then extractCycles on every piece
+__device__ inline void simpleOddCyclesAndExtract(const GraphDev &G, TileMem &M, SrcState &S, Emitter &E, const int W) {
+    const int32_t *wn = M.wn, *ws = M.ws;
+    int lastLeft = -1;
+    bool any = false;
+    for (int i = 0; i <= W; ++i) {
+        const int32_t v = wn[i];
+        int pp = -1; // prevPos[v]: last earlier position of v
+        for (int k = i - 1; k >= 0; --k)
+            if (wn[k] == v) {
+                pp = k;
+                break;
+            }
+        if (lastLeft < pp) {
+            lastLeft = pp;
+            if (i - lastLeft > 2) {
+                extractCycles(G, M, S, E, wn + lastLeft, ws + lastLeft, i - lastLeft);
+                if (S.overflow) return;
+                any = true;
+            }
+        }
+    }
+    if (!any) extractCycles(G, M, S, E, wn, ws, W);
+}
+
+// intermediateVertexToOcw (:138-188) into M.wn / M.ws; returns the number of edges, -1 on overflow.
+// The stem blacklisting side effect (:164-169) has no reader in independent-source mode and is not performed.
+__device__ inline int buildWalk(const TileMem &M, uint32_t t, uint32_t src) {
+    int32_t *pa = M.pa, *pb = M.pb;
+    const int P = tracePath(M, t, src, pa);
+    if (P < 0) return -1;
+    const int Q = tracePath(M, t ^ 1u, src, pb);
+    if (Q < 0) return -1;
+    // path[i] = {u = orig(pa[i]), v = orig(pa[i+1]), stay = same side}, i < P; twinPath likewise from pb
+    int W = 0;
+    M.wn[0] = pa[0] >> 1;
+    auto addEdge = [&](int32_t next, bool stay) {
+        M.ws[W] = stay ? 1 : 0;
+        M.wn[++W] = next;
+    };
+    if (Q == 0) {
+        for (int i = 0; i < P; ++i) addEdge(pa[i + 1] >> 1, ((pa[i] ^ pa[i + 1]) & 1) == 0);
+        return W;
+    }
+    int endPath = P - 1, endTwin = Q - 1;
+    while (((pa[endPath + 1] >> 1) == (pb[endTwin + 1] >> 1)) && endPath > 0 && endTwin > 0) {
+        endPath--;
+        endTwin--;
+    }
+    if ((pa[endPath + 1] >> 1) != (pb[endTwin + 1] >> 1)) {
+        endPath++;
+        endTwin++;
+    }
+    for (int i = 0; i <= endPath; ++i) addEdge(pa[i + 1] >> 1, ((pa[i] ^ pa[i + 1]) & 1) == 0);
+    for (int i = endTwin; i >= 0; --i) addEdge(pb[i] >> 1, ((pb[i] ^ pb[i + 1]) & 1) == 0);
+    return W;
+}
+
+} // namespace smsgpu

@@ -1,0 +1,1275 @@
+// libsmsgpu.so -- C ABI (include/smsgpu.h) over the sm_100a kernels.  Host side of the separation round:
+// uploads the CSR once (the ConshdlrOscw constructor's job in the reference, conshdlr_oscw.cpp:33-45 ->
+// OcwSeparator::OcwSeparator), ships x* / blacklist per round, runs K1 -> K2-K4 (tier 0, 1, 2) -> K5 on one
+// stream and returns the cut list in pinned host memory.
+// Product code: no oracle, no CPU fallback -- every entry point fails with SMSGPU_ERR_CUDA without a device.
+#include "../../include/smsgpu.h"
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "dedup_kernels.cuh"
+#include "ocw_kernels.cuh"
+#include "small_cycles.cuh"
+
+using namespace smsgpu;
+
+namespace {
+
+thread_local std::string g_createError;
+
+struct DevBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        size_t want = bytes + bytes / 4 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e != cudaSuccess) {
+            (void)cudaGetLastError();
+            want = bytes;
+            e = cudaMalloc(&p, want);
+        }
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+    template <class T>
+    T *as() const {
+        return static_cast<T *>(p);
+    }
+};
+struct PinBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        cap = 0;
+        const size_t want = bytes + bytes / 4 + 256;
+        cudaError_t e = cudaMallocHost(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() {
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        cap = 0;
+    }
+    template <class T>
+    T *as() const {
+        return static_cast<T *>(p);
+    }
+};
+
+struct TierCfg {
+    TileCaps caps{};
+    long long ntiles = 0;   // tiles that own HBM working memory (tiers 1, 2)
+    int ctas = 0;           // grid size
+    size_t smemBytes = 0;   // tier 0
+    DevBuf scratch;
+    bool ready = false;
+};
+
+// host mirror of a cut list (pinned) + device copy
+struct CutListDev {
+    DevBuf off, node, eid, stay, ncross, src, seq, viol;
+    long long ncuts = 0, nnodes = 0;
+};
+struct CutListHost {
+    PinBuf off, node, eid, stay, ncross, src, viol;
+    long long ncuts = 0, nnodes = 0;
+};
+
+} // namespace
+
+struct smsgpu_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[8]{};
+    int smCount = 148;
+    long long n = 0, m = 0;
+    std::string err;
+
+    // graph (uploaded once)
+    DevBuf dRowptr, dCol, dEid, dArcs;
+    // round input
+    DevBuf dX, dBl;
+    const double *xPtr = nullptr;   // device pointer in use (own buffer or caller's)
+    const uint8_t *blPtr = nullptr;
+    PinBuf hX, hBl;
+    bool haveInput = false, arcsDirty = true;
+    // sources
+    DevBuf dSources;
+    bool explicitSources = false;
+    long long nsrcGlobal = 0, nsrcLocal = 0;
+    int rank = 0, nranks = 1;
+
+    int tileWidth = 0; // resolved
+    TierCfg tier[3];
+
+    // raw arena
+    DevBuf rNode, rEid, rStay, rCutOff, rCutLen, rCutSrc, rCutSeq, rCutTier, rValid;
+    DevBuf labSrc, labNode, labHops, labDist;
+    DevBuf srcTier, srcArcs, srcSettled;
+    long long cutCap = 0, nodeCap = 0, labCap = 0;
+    DevBuf counters; // 16 x u64: see RawOut::counters; [8] queue cursor, [9] ovf count A, [10] ovf count B, [11] collisions
+    PinBuf hCounters;
+    DevBuf ovfA, ovfB;
+
+    // dedup work
+    DevBuf wCnode, wCeid, wCstay, wHash, wRank, wSlot, wKeep, wNcross, wViol, wTabKey, wTabRank, wTabIdx;
+    DevBuf wCnt, wCursor, wBase, wOrder, wOutLen, wBlockSums;
+    CutListDev fin;
+    CutListHost host;
+    bool fetched = false;
+
+    // labels / per-source stats on the host
+    PinBuf hLabOff, hLabNode, hLabDist, hLabHops, hSrcArcs, hSrcSettled, hSrcTier;
+    long long nLabels = 0;
+    bool haveLabels = false, haveSrcStats = false;
+
+    // small cycles (k = 3, 4)
+    DevBuf scNodes[2], scEids[2], scFlag[2], scStay[2];
+    long long scCount[2] = {0, 0};
+    CutListHost scHost[2];
+    CutListDev scFin;
+    PinBuf scTmp;
+
+    smsgpu_params lastParams{};
+    smsgpu_stats stats{};
+
+    // multi-GPU
+    void *ncclComm = nullptr;
+    int commRank = 0, commSize = 1;
+    DevBuf gCounts, pLen, pSrc, pSeq, pOff, pNode, pEid, pStay;
+    PinBuf hGCounts;
+    DevBuf mNode, mEid, mStay, mOff, mLen, mSrc, mSeq, mValid;
+};
+
+namespace {
+
+int fail(smsgpu_ctx *c, int code, const char *fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (c)
+        c->err = buf;
+    else
+        g_createError = buf;
+    return code;
+}
+
+#define CU(call)                                                                                           \
+    do {                                                                                                   \
+        cudaError_t e_ = (call);                                                                           \
+        if (e_ != cudaSuccess) {                                                                           \
+            (void)cudaGetLastError();                                                                      \
+            return fail(ctx, e_ == cudaErrorMemoryAllocation ? SMSGPU_ERR_NOMEM : SMSGPU_ERR_CUDA,         \
+                        "%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_));                \
+        }                                                                                                  \
+    } while (0)
+
+inline unsigned gridFor(long long n, int block) { return (unsigned)std::max<long long>(1, (n + block - 1) / block); }
+
+uint32_t log2ceil(uint64_t v) {
+    uint32_t l = 0;
+    while ((1ull << l) < v) ++l;
+    return l;
+}
+
+} // namespace
+
+// =====================================================================================================================
+// life cycle
+// =====================================================================================================================
+namespace {
+
+template <int TW, bool SMEM>
+cudaError_t launchSearchT(smsgpu_ctx *c, const TierCfg &t, const GraphDev &G, const SearchParams &P, const RawOut &R) {
+    auto kern = ocwSearchKernel<TW, SMEM>;
+    if (SMEM) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t.smemBytes);
+        if (e != cudaSuccess) return e;
+    }
+    kern<<<t.ctas, 128, SMEM ? t.smemBytes : 0, c->stream>>>(G, P, R, t.caps, t.scratch.as<unsigned char>());
+    return cudaGetLastError();
+}
+cudaError_t launchSearch(smsgpu_ctx *c, int tierIdx, const GraphDev &G, const SearchParams &P, const RawOut &R) {
+    const TierCfg &t = c->tier[tierIdx];
+    const bool smem = tierIdx == 0;
+    switch (c->tileWidth) {
+    case 8: return smem ? launchSearchT<8, true>(c, t, G, P, R) : launchSearchT<8, false>(c, t, G, P, R);
+    case 16: return smem ? launchSearchT<16, true>(c, t, G, P, R) : launchSearchT<16, false>(c, t, G, P, R);
+    default: return smem ? launchSearchT<32, true>(c, t, G, P, R) : launchSearchT<32, false>(c, t, G, P, R);
+    }
+}
+template <int TW, bool SMEM>
+int occupancyT(size_t smemBytes) {
+    int nb = 0;
+    auto kern = ocwSearchKernel<TW, SMEM>;
+    if (SMEM) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, 128, SMEM ? smemBytes : 0) != cudaSuccess) {
+        (void)cudaGetLastError();
+        nb = 1;
+    }
+    return std::max(nb, 1);
+}
+int occupancy(int tw, bool smem, size_t smemBytes) {
+    switch (tw) {
+    case 8: return smem ? occupancyT<8, true>(smemBytes) : occupancyT<8, false>(0);
+    case 16: return smem ? occupancyT<16, true>(smemBytes) : occupancyT<16, false>(0);
+    default: return smem ? occupancyT<32, true>(smemBytes) : occupancyT<32, false>(0);
+    }
+}
+
+// Working-memory capacities of the three tiers (DESIGN.md "tiers").
+void configureTiers(smsgpu_ctx *c) {
+    const int tw = c->tileWidth;
+    const int tilesPerCta = 128 / tw;
+    // tier 0: everything in shared memory; sized for the balls of sparse lattices with fractional x*
+    {
+        TierCfg &t = c->tier[0];
+        t.caps = TileCaps{128, 32 - 7, 0, 64 + (uint32_t)tw, 64 + 2 * (uint32_t)tw, 32, 16, 16};
+        t.smemBytes = tileBytes(t.caps) * tilesPerCta;
+        t.ctas = c->smCount * occupancy(tw, true, t.smemBytes);
+        t.ready = true;
+    }
+    // tier 1: per-tile working memory in HBM (L2-resident while hot); hashed table
+    {
+        TierCfg &t = c->tier[1];
+        t.caps = TileCaps{1u << 14, 32 - 14, 0, 1u << 13, 1u << 13, 1u << 12, 256, 1024};
+        t.ctas = c->smCount * occupancy(tw, false, 0);
+        t.ntiles = (long long)t.ctas * tilesPerCta;
+    }
+    // tier 2: dense table indexed by vertex, capacities that cannot overflow before the graph is exhausted
+    {
+        TierCfg &t = c->tier[2];
+        const uint64_t n = (uint64_t)c->n, m = (uint64_t)c->m;
+        const uint32_t big = (uint32_t)std::min<uint64_t>(4 * m + 64 + 2 * tw, 1u << 30);
+        t.caps = TileCaps{(uint32_t)n, 0, 1, (uint32_t)n + (uint32_t)tw, big, big,
+                          (uint32_t)std::min<uint64_t>(2 * n + 2, 1u << 28),
+                          (uint32_t)std::min<uint64_t>(4 * m + 16, 1u << 22)};
+    }
+}
+
+int ensureTierScratch(smsgpu_ctx *ctx, int ti) {
+    TierCfg &t = ctx->tier[ti];
+    if (t.ready) return 0;
+    const size_t tb = tileBytes(t.caps);
+    if (ti == 2) {
+        size_t freeB = 0, totalB = 0;
+        CU(cudaMemGetInfo(&freeB, &totalB));
+        long long nt = (long long)((freeB / 4) / tb);
+        const int tilesPerCta = 128 / ctx->tileWidth;
+        nt = std::min<long long>(nt, (long long)ctx->smCount * 2 * tilesPerCta);
+        if (nt < 1) return fail(ctx, SMSGPU_ERR_NOMEM, "dense tier needs %zu bytes per tile, %zu free", tb, freeB);
+        t.ctas = (int)std::max<long long>(1, nt / tilesPerCta);
+        t.ntiles = (long long)t.ctas * tilesPerCta;
+    }
+    CU(t.scratch.ensure((size_t)t.ntiles * tb));
+    initTablesKernel<<<ctx->smCount * 8, 256, 0, ctx->stream>>>(t.scratch.as<unsigned char>(), tb, t.ntiles, t.caps.tabCap);
+    CU(cudaGetLastError());
+    t.ready = true;
+    return 0;
+}
+
+} // namespace
+
+extern "C" {
+
+int smsgpu_abi_version(void) { return SMSGPU_ABI_VERSION; }
+
+void smsgpu_default_params(smsgpu_params *p) {
+    if (!p) return;
+    std::memset(p, 0, sizeof *p);
+    p->max_intermediates = 10;
+    p->best_dist_init = 1.0 - 1e-6;
+    p->dedup = 1;
+}
+
+const char *smsgpu_last_error(const smsgpu_ctx *ctx) { return ctx ? ctx->err.c_str() : g_createError.c_str(); }
+
+int smsgpu_create(smsgpu_ctx **out, int64_t n, int64_t m, const int64_t *rowptr, const int32_t *col, const int32_t *eid,
+                  int device) {
+    smsgpu_ctx *ctx = nullptr; // errors before the context exists go to the thread-local slot
+    if (!out) return fail(ctx, SMSGPU_ERR_ARG, "out is null");
+    *out = nullptr;
+    if (n <= 0 || m < 0 || !rowptr || (m > 0 && (!col || !eid))) return fail(ctx, SMSGPU_ERR_ARG, "null or empty graph");
+    if (n >= (1ll << 30) || 2 * m >= (1ll << 30)) return fail(ctx, SMSGPU_ERR_ARG, "graph too large for 32-bit arc ids");
+    // the reference rejects non-compact / un-indexed graphs (ocw_seperator.cpp:16-19); here: a malformed CSR
+    if (rowptr[0] != 0 || rowptr[n] != 2 * m) return fail(ctx, SMSGPU_ERR_ARG, "rowptr[0] != 0 or rowptr[n] != 2m");
+    {
+        std::vector<int32_t> seen(n, -1);
+        std::vector<uint8_t> eidCount(m, 0);
+        for (int64_t u = 0; u < n; ++u) {
+            if (rowptr[u + 1] < rowptr[u]) return fail(ctx, SMSGPU_ERR_ARG, "rowptr not monotone at %lld", (long long)u);
+            for (int64_t a = rowptr[u]; a < rowptr[u + 1]; ++a) {
+                const int32_t v = col[a];
+                if (v < 0 || v >= n) return fail(ctx, SMSGPU_ERR_ARG, "neighbour out of range at arc %lld", (long long)a);
+                if (v == u) return fail(ctx, SMSGPU_ERR_ARG, "self loop at vertex %lld", (long long)u);
+                if (seen[v] == (int32_t)u) return fail(ctx, SMSGPU_ERR_ARG, "multi-edge %lld-%d", (long long)u, v);
+                seen[v] = (int32_t)u;
+                if (eid[a] < 0 || eid[a] >= m) return fail(ctx, SMSGPU_ERR_ARG, "edge id out of range at arc %lld", (long long)a);
+                if (++eidCount[eid[a]] > 2) return fail(ctx, SMSGPU_ERR_ARG, "edge id %d used more than twice", eid[a]);
+            }
+        }
+    }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        (void)cudaGetLastError();
+        return fail(ctx, SMSGPU_ERR_CUDA, "no CUDA device (libsmsgpu has no CPU fallback)");
+    }
+    if (device < 0 || device >= ndev) return fail(ctx, SMSGPU_ERR_ARG, "device %d out of range (%d devices)", device, ndev);
+    ctx = new smsgpu_ctx();
+    ctx->device = device;
+    ctx->n = n;
+    ctx->m = m;
+    auto bail = [&](int code) {
+        g_createError = ctx->err;
+        smsgpu_destroy(ctx);
+        return code;
+    };
+#define CUB(call)                                                                                          \
+    do {                                                                                                   \
+        cudaError_t e_ = (call);                                                                           \
+        if (e_ != cudaSuccess) {                                                                           \
+            (void)cudaGetLastError();                                                                      \
+            fail(ctx, SMSGPU_ERR_CUDA, "%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+            return bail(e_ == cudaErrorMemoryAllocation ? SMSGPU_ERR_NOMEM : SMSGPU_ERR_CUDA);             \
+        }                                                                                                  \
+    } while (0)
+    CUB(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CUB(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10) {
+        fail(ctx, SMSGPU_ERR_CUDA, "device %d is sm_%d%d; libsmsgpu is built for sm_100a only", device, prop.major, prop.minor);
+        return bail(SMSGPU_ERR_CUDA);
+    }
+    ctx->smCount = prop.multiProcessorCount;
+    CUB(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    for (auto &e : ctx->ev) CUB(cudaEventCreate(&e));
+    CUB(ctx->dRowptr.ensure((size_t)(n + 1) * sizeof(int64_t)));
+    CUB(ctx->dCol.ensure((size_t)std::max<int64_t>(2 * m, 4) * sizeof(int32_t)));
+    CUB(ctx->dEid.ensure((size_t)std::max<int64_t>(2 * m, 4) * sizeof(int32_t)));
+    CUB(ctx->dArcs.ensure((size_t)std::max<int64_t>(2 * m, 4) * sizeof(Arc)));
+    CUB(cudaMemcpyAsync(ctx->dRowptr.p, rowptr, (size_t)(n + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, ctx->stream));
+    if (m > 0) {
+        CUB(cudaMemcpyAsync(ctx->dCol.p, col, (size_t)2 * m * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
+        CUB(cudaMemcpyAsync(ctx->dEid.p, eid, (size_t)2 * m * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
+    }
+    CUB(ctx->dX.ensure((size_t)std::max<int64_t>(m, 1) * sizeof(double)));
+    CUB(ctx->dBl.ensure((size_t)n));
+    CUB(ctx->hX.ensure((size_t)std::max<int64_t>(m, 1) * sizeof(double)));
+    CUB(ctx->hBl.ensure((size_t)n));
+    CUB(ctx->counters.ensure(16 * sizeof(unsigned long long)));
+    CUB(ctx->hCounters.ensure(16 * sizeof(unsigned long long)));
+    CUB(cudaStreamSynchronize(ctx->stream));
+    // tile width by average degree: one lane per arc of a typical row
+    const double avgDeg = n ? 2.0 * (double)m / (double)n : 0.0;
+    ctx->tileWidth = avgDeg <= 6.5 ? 8 : (avgDeg <= 14.0 ? 16 : 32);
+    configureTiers(ctx);
+    ctx->nsrcGlobal = ctx->nsrcLocal = n; // default source list 0..n-1 (conshdlr_oscw.cpp:188-195)
+    ctx->rank = 0;
+    ctx->nranks = 1;
+    *out = ctx;
+    return SMSGPU_OK;
+#undef CUB
+}
+
+void smsgpu_destroy(smsgpu_ctx *ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    smsgpu_comm_destroy(ctx);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    DevBuf *dev[] = {&ctx->dRowptr, &ctx->dCol, &ctx->dEid, &ctx->dArcs, &ctx->dX, &ctx->dBl, &ctx->dSources,
+                     &ctx->tier[0].scratch, &ctx->tier[1].scratch, &ctx->tier[2].scratch, &ctx->rNode, &ctx->rEid,
+                     &ctx->rStay, &ctx->rCutOff, &ctx->rCutLen, &ctx->rCutSrc, &ctx->rCutSeq, &ctx->rCutTier, &ctx->rValid,
+                     &ctx->labSrc, &ctx->labNode, &ctx->labHops, &ctx->labDist, &ctx->srcTier, &ctx->srcArcs,
+                     &ctx->srcSettled, &ctx->counters, &ctx->ovfA, &ctx->ovfB, &ctx->wCnode, &ctx->wCeid, &ctx->wCstay,
+                     &ctx->wHash, &ctx->wRank, &ctx->wSlot, &ctx->wKeep, &ctx->wNcross, &ctx->wViol, &ctx->wTabKey,
+                     &ctx->wTabRank, &ctx->wTabIdx, &ctx->wCnt, &ctx->wCursor, &ctx->wBase, &ctx->wOrder, &ctx->wOutLen,
+                     &ctx->wBlockSums, &ctx->fin.off, &ctx->fin.node, &ctx->fin.eid, &ctx->fin.stay, &ctx->fin.ncross,
+                     &ctx->fin.src, &ctx->fin.seq, &ctx->fin.viol, &ctx->scFin.off, &ctx->scFin.node, &ctx->scFin.eid,
+                     &ctx->scFin.stay, &ctx->scFin.ncross, &ctx->scFin.src, &ctx->scFin.viol, &ctx->scNodes[0], &ctx->scNodes[1], &ctx->scEids[0],
+                     &ctx->scEids[1], &ctx->scFlag[0], &ctx->scFlag[1], &ctx->scStay[0], &ctx->scStay[1], &ctx->gCounts,
+                     &ctx->pLen, &ctx->pSrc, &ctx->pSeq, &ctx->pOff, &ctx->pNode, &ctx->pEid, &ctx->pStay, &ctx->mNode, &ctx->mEid, &ctx->mStay, &ctx->mOff, &ctx->mLen, &ctx->mSrc,
+                     &ctx->mSeq, &ctx->mValid};
+    for (auto *b : dev) b->release();
+    PinBuf *pin[] = {&ctx->hX, &ctx->hBl, &ctx->hCounters, &ctx->host.off, &ctx->host.node, &ctx->host.eid,
+                     &ctx->host.stay, &ctx->host.ncross, &ctx->host.src, &ctx->host.viol, &ctx->hLabOff, &ctx->hLabNode,
+                     &ctx->hLabDist, &ctx->hLabHops, &ctx->hSrcArcs, &ctx->hSrcSettled, &ctx->hSrcTier, &ctx->scTmp,
+                     &ctx->hGCounts};
+    for (auto *b : pin) b->release();
+    for (int k = 0; k < 2; ++k) {
+        PinBuf *sc[] = {&ctx->scHost[k].off, &ctx->scHost[k].node, &ctx->scHost[k].eid, &ctx->scHost[k].stay,
+                        &ctx->scHost[k].ncross, &ctx->scHost[k].src, &ctx->scHost[k].viol};
+        for (auto *b : sc) b->release();
+    }
+    for (auto &e : ctx->ev)
+        if (e) cudaEventDestroy(e);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+// ---- per round input ----------------------------------------------------------------------------------------
+int smsgpu_set_round_input(smsgpu_ctx *ctx, const double *x, const uint8_t *bl) {
+    if (!ctx) return SMSGPU_ERR_ARG;
+    if (!x || !bl) return fail(ctx, SMSGPU_ERR_ARG, "x_by_eid or blacklist is null");
+    CU(cudaSetDevice(ctx->device));
+    // pageable -> pinned staging -> device, all on the context's stream
+    std::memcpy(ctx->hX.p, x, (size_t)ctx->m * sizeof(double));
+    std::memcpy(ctx->hBl.p, bl, (size_t)ctx->n);
+    CU(cudaEventRecord(ctx->ev[6], ctx->stream));
+    if (ctx->m) CU(cudaMemcpyAsync(ctx->dX.p, ctx->hX.p, (size_t)ctx->m * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaMemcpyAsync(ctx->dBl.p, ctx->hBl.p, (size_t)ctx->n, cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaEventRecord(ctx->ev[7], ctx->stream));
+    ctx->xPtr = ctx->dX.as<double>();
+    ctx->blPtr = ctx->dBl.as<uint8_t>();
+    ctx->haveInput = true;
+    ctx->arcsDirty = true;
+    return SMSGPU_OK;
+}
+
+int smsgpu_set_round_input_device(smsgpu_ctx *ctx, const double *dx, const uint8_t *dbl) {
+    if (!ctx) return SMSGPU_ERR_ARG;
+    if (!dx || !dbl) return fail(ctx, SMSGPU_ERR_ARG, "device x or blacklist is null");
+    ctx->xPtr = dx;
+    ctx->blPtr = dbl;
+    ctx->haveInput = true;
+    ctx->arcsDirty = true;
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaEventRecord(ctx->ev[6], ctx->stream));
+    CU(cudaEventRecord(ctx->ev[7], ctx->stream));
+    return SMSGPU_OK;
+}
+
+int smsgpu_set_sources(smsgpu_ctx *ctx, const int32_t *sources, int64_t nsrc, int rank, int nranks) {
+    if (!ctx) return SMSGPU_ERR_ARG;
+    if (nranks < 1 || rank < 0 || rank >= nranks) return fail(ctx, SMSGPU_ERR_ARG, "bad rank %d / %d", rank, nranks);
+    if (sources && nsrc < 0) return fail(ctx, SMSGPU_ERR_ARG, "negative source count");
+    CU(cudaSetDevice(ctx->device));
+    ctx->rank = rank;
+    ctx->nranks = nranks;
+    ctx->nsrcGlobal = sources ? nsrc : ctx->n;
+    // block-cyclic deal: local index j <-> global index j * nranks + rank
+    ctx->nsrcLocal = ctx->nsrcGlobal > rank ? (ctx->nsrcGlobal - rank + nranks - 1) / nranks : 0;
+    ctx->explicitSources = sources != nullptr;
+    if (sources) {
+        std::vector<int32_t> mine((size_t)ctx->nsrcLocal);
+        for (int64_t j = 0; j < ctx->nsrcLocal; ++j) {
+            mine[j] = sources[j * nranks + rank];
+            if (mine[j] < 0) return fail(ctx, SMSGPU_ERR_ARG, "negative source id");
+        }
+        CU(ctx->dSources.ensure(std::max<size_t>(mine.size(), 1) * sizeof(int32_t)));
+        CU(cudaMemcpyAsync(ctx->dSources.p, mine.data(), mine.size() * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
+        CU(cudaStreamSynchronize(ctx->stream));
+    }
+    return SMSGPU_OK;
+}
+
+} // extern "C"
+
+// =====================================================================================================================
+// one separation round
+// =====================================================================================================================
+namespace {
+
+int exclusiveScan(smsgpu_ctx *ctx, const int32_t *in, long long n, long long *out) {
+    if (n == 0) {
+        CU(cudaMemsetAsync(out, 0, sizeof(long long), ctx->stream));
+        return 0;
+    }
+    const long long nb = (n + kScanTile - 1) / kScanTile;
+    CU(ctx->wBlockSums.ensure((size_t)(nb + 1) * sizeof(long long)));
+    scanReduceKernel<<<(unsigned)nb, kScanBlock, 0, ctx->stream>>>(in, n, ctx->wBlockSums.as<long long>());
+    scanBlockSumsKernel<<<1, kScanBlock, 0, ctx->stream>>>(ctx->wBlockSums.as<long long>(), nb);
+    scanFinalKernel<<<(unsigned)nb, kScanBlock, 0, ctx->stream>>>(in, n, ctx->wBlockSums.as<long long>(), out);
+    CU(cudaGetLastError());
+    ctx->stats.total_launches += 3;
+    return 0;
+}
+
+__global__ void validKernel(const long long n, const int8_t *cutTier, const int32_t *cutSrc, const int8_t *srcTier,
+                            uint8_t *valid) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) valid[i] = cutTier[i] == srcTier[cutSrc[i]];
+}
+
+int ensureRawArena(smsgpu_ctx *ctx, long long cutCap, long long nodeCap) {
+    if (cutCap > ctx->cutCap) {
+        CU(ctx->rCutOff.ensure((size_t)cutCap * 4));
+        CU(ctx->rCutLen.ensure((size_t)cutCap * 4));
+        CU(ctx->rCutSrc.ensure((size_t)cutCap * 4));
+        CU(ctx->rCutSeq.ensure((size_t)cutCap * 4));
+        CU(ctx->rCutTier.ensure((size_t)cutCap));
+        CU(ctx->rValid.ensure((size_t)cutCap));
+        ctx->cutCap = cutCap;
+    }
+    if (nodeCap > ctx->nodeCap) {
+        CU(ctx->rNode.ensure((size_t)nodeCap * 4));
+        CU(ctx->rEid.ensure((size_t)nodeCap * 4));
+        CU(ctx->rStay.ensure((size_t)nodeCap));
+        ctx->nodeCap = nodeCap;
+    }
+    return 0;
+}
+
+// K5 on an arbitrary cut view; result in ctx->fin.  srcMul/srcAdd map the view's source index to the global one.
+int runDedup(smsgpu_ctx *ctx, const CutView &V, long long totalNodes, bool canonicalise, bool dedup, int srcMul,
+             int srcAdd, long long nsrcGlobal) {
+    const long long R = V.n;
+    cudaStream_t st = ctx->stream;
+    CutListDev &F = ctx->fin;
+    if (R == 0) {
+        F.ncuts = F.nnodes = 0;
+        CU(F.off.ensure(sizeof(long long)));
+        CU(cudaMemsetAsync(F.off.p, 0, sizeof(long long), st));
+        return 0;
+    }
+    CU(ctx->wCnode.ensure((size_t)totalNodes * 4));
+    CU(ctx->wCeid.ensure((size_t)totalNodes * 4));
+    CU(ctx->wCstay.ensure((size_t)totalNodes));
+    CU(ctx->wHash.ensure((size_t)R * 8));
+    CU(ctx->wRank.ensure((size_t)R * 8));
+    CU(ctx->wSlot.ensure((size_t)R * 4));
+    CU(ctx->wKeep.ensure((size_t)R));
+    CU(ctx->wNcross.ensure((size_t)R * 4));
+    CU(ctx->wViol.ensure((size_t)R * 8));
+    DedupWork D{};
+    D.cnode = ctx->wCnode.as<int32_t>();
+    D.ceid = ctx->wCeid.as<int32_t>();
+    D.cstay = ctx->wCstay.as<uint8_t>();
+    D.hash = ctx->wHash.as<unsigned long long>();
+    D.rank = ctx->wRank.as<unsigned long long>();
+    D.slot = ctx->wSlot.as<int32_t>();
+    D.keep = ctx->wKeep.as<uint8_t>();
+    D.ncross = ctx->wNcross.as<int32_t>();
+    D.viol = ctx->wViol.as<double>();
+    D.collisions = ctx->counters.as<unsigned long long>() + 11;
+    canonKernel<<<gridFor(R, 128), 128, 0, st>>>(V, D, ctx->xPtr, canonicalise ? 1 : 0, srcMul, srcAdd);
+    ctx->stats.total_launches += 1;
+    if (dedup) {
+        const uint64_t tabCap = 1ull << log2ceil((uint64_t)2 * R + 16);
+        CU(ctx->wTabKey.ensure(tabCap * 8));
+        CU(ctx->wTabRank.ensure(tabCap * 8));
+        CU(ctx->wTabIdx.ensure(tabCap * 4));
+        D.tabKey = ctx->wTabKey.as<unsigned long long>();
+        D.tabRank = ctx->wTabRank.as<unsigned long long>();
+        D.tabIdx = ctx->wTabIdx.as<int32_t>();
+        D.tabMask = tabCap - 1;
+        CU(cudaMemsetAsync(D.tabKey, 0, tabCap * 8, st));
+        CU(cudaMemsetAsync(D.tabRank, 0xFF, tabCap * 8, st));
+        dedupInsertKernel<<<gridFor(R, 256), 256, 0, st>>>(R, D);
+        dedupMarkKernel<<<gridFor(R, 256), 256, 0, st>>>(R, D);
+        dedupVerifyKernel<<<gridFor(R, 256), 256, 0, st>>>(V, D);
+        ctx->stats.total_launches += 3;
+    }
+    // order by (global source index, emission index)
+    CU(ctx->wCnt.ensure((size_t)(nsrcGlobal + 1) * 4));
+    CU(ctx->wCursor.ensure((size_t)(nsrcGlobal + 1) * 4));
+    CU(ctx->wBase.ensure((size_t)(nsrcGlobal + 2) * 8));
+    CU(ctx->wOrder.ensure((size_t)R * 4));
+    CU(ctx->wOutLen.ensure((size_t)R * 4));
+    CU(cudaMemsetAsync(ctx->wCnt.p, 0, (size_t)(nsrcGlobal + 1) * 4, st));
+    CU(cudaMemsetAsync(ctx->wCursor.p, 0, (size_t)(nsrcGlobal + 1) * 4, st));
+    countPerSrcKernel<<<gridFor(R, 256), 256, 0, st>>>(R, D, ctx->wCnt.as<int32_t>());
+    ctx->stats.total_launches += 1;
+    if (int rc = exclusiveScan(ctx, ctx->wCnt.as<int32_t>(), nsrcGlobal, ctx->wBase.as<long long>())) return rc;
+    scatterPerSrcKernel<<<gridFor(R, 256), 256, 0, st>>>(R, D, ctx->wBase.as<long long>(), ctx->wCursor.as<int32_t>(),
+                                                        ctx->wOrder.as<int32_t>());
+    sortSegmentsKernel<<<gridFor(nsrcGlobal, 256), 256, 0, st>>>(nsrcGlobal, D, ctx->wBase.as<long long>(),
+                                                                ctx->wOrder.as<int32_t>(), ctx->wOutLen.as<int32_t>(), V.len);
+    ctx->stats.total_launches += 2;
+    CU(cudaGetLastError());
+    // number of unique cuts -> host (sizes the final arrays)
+    unsigned long long *hc = ctx->hCounters.as<unsigned long long>();
+    CU(cudaMemcpyAsync(hc + 12, ctx->wBase.as<long long>() + nsrcGlobal, 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(hc + 11, ctx->counters.as<unsigned long long>() + 11, 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    const long long U = (long long)hc[12];
+    F.ncuts = U;
+    CU(F.off.ensure((size_t)(U + 1) * 8));
+    if (int rc = exclusiveScan(ctx, ctx->wOutLen.as<int32_t>(), U, F.off.as<long long>())) return rc;
+    CU(cudaMemcpyAsync(hc + 13, F.off.as<long long>() + U, 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    F.nnodes = (long long)hc[13];
+    CU(F.node.ensure((size_t)std::max<long long>(F.nnodes, 1) * 4));
+    CU(F.eid.ensure((size_t)std::max<long long>(F.nnodes, 1) * 4));
+    CU(F.stay.ensure((size_t)std::max<long long>(F.nnodes, 1)));
+    CU(F.ncross.ensure((size_t)std::max<long long>(U, 1) * 4));
+    CU(F.src.ensure((size_t)std::max<long long>(U, 1) * 4));
+    CU(F.seq.ensure((size_t)std::max<long long>(U, 1) * 4));
+    CU(F.viol.ensure((size_t)std::max<long long>(U, 1) * 8));
+    if (U > 0) {
+        FinalCuts fc{F.off.as<long long>(), F.node.as<int32_t>(), F.eid.as<int32_t>(), F.stay.as<uint8_t>(),
+                     F.ncross.as<int32_t>(), F.src.as<int32_t>(), F.seq.as<int32_t>(), F.viol.as<double>()};
+        gatherFinalKernel<<<gridFor(U, 256), 256, 0, st>>>(U, V, D, ctx->wOrder.as<int32_t>(), fc);
+        ctx->stats.total_launches += 1;
+        CU(cudaGetLastError());
+    }
+    return 0;
+}
+
+int mergeAcrossRanks(smsgpu_ctx *ctx, bool dedup); // multi-GPU part below
+
+} // namespace
+
+extern "C" {
+
+int smsgpu_separate_async(smsgpu_ctx *ctx, const smsgpu_params *params) {
+    if (!ctx) return SMSGPU_ERR_ARG;
+    if (!ctx->haveInput) return fail(ctx, SMSGPU_ERR_STATE, "smsgpu_separate before smsgpu_set_round_input");
+    smsgpu_params P;
+    if (params)
+        P = *params;
+    else
+        smsgpu_default_params(&P);
+    if (P.max_intermediates < 0 || P.max_intermediates > 16) return fail(ctx, SMSGPU_ERR_ARG, "max_intermediates must be 0..16");
+    if (P.tile_width != 0 && P.tile_width != 8 && P.tile_width != 16 && P.tile_width != 32)
+        return fail(ctx, SMSGPU_ERR_ARG, "tile_width must be 0, 8, 16 or 32");
+    if (P.start_tier < 0 || P.start_tier > 2) return fail(ctx, SMSGPU_ERR_ARG, "start_tier must be 0..2");
+    CU(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    if (P.tile_width != 0 && P.tile_width != ctx->tileWidth) {
+        CU(cudaStreamSynchronize(st));
+        for (auto &t : ctx->tier) {
+            t.scratch.release();
+            t.ready = false;
+        }
+        ctx->tileWidth = P.tile_width;
+        configureTiers(ctx);
+    }
+    ctx->lastParams = P;
+    ctx->fetched = false;
+    ctx->haveLabels = ctx->haveSrcStats = false;
+    const long long keepH2dStats = 0;
+    (void)keepH2dStats;
+    std::memset(&ctx->stats, 0, sizeof ctx->stats);
+    const long long nsrc = ctx->nsrcLocal;
+    unsigned long long *dc = ctx->counters.as<unsigned long long>();
+    unsigned long long *hc = ctx->hCounters.as<unsigned long long>();
+
+    CU(cudaEventRecord(ctx->ev[0], st));
+    // ---- K1 ----
+    if (ctx->arcsDirty && ctx->m > 0) {
+        dcWeightsKernel<<<std::min<unsigned>(gridFor((2 * ctx->m + 3) / 4, 256), (unsigned)ctx->smCount * 16), 256, 0, st>>>(
+            2 * ctx->m, ctx->dCol.as<int32_t>(), ctx->dEid.as<int32_t>(), ctx->xPtr, ctx->blPtr, ctx->dArcs.as<Arc>());
+        CU(cudaGetLastError());
+        ctx->stats.total_launches += 1;
+    }
+    ctx->arcsDirty = false;
+    CU(cudaEventRecord(ctx->ev[1], st));
+
+    // ---- K2-K4: tiers ----
+    CU(ctx->srcTier.ensure((size_t)std::max<long long>(nsrc, 1)));
+    CU(ctx->ovfA.ensure((size_t)std::max<long long>(nsrc, 1) * 4));
+    CU(ctx->ovfB.ensure((size_t)std::max<long long>(nsrc, 1) * 4));
+    if (P.export_src_stats) {
+        CU(ctx->srcArcs.ensure((size_t)std::max<long long>(nsrc, 1) * 8));
+        CU(ctx->srcSettled.ensure((size_t)std::max<long long>(nsrc, 1) * 8));
+        CU(cudaMemsetAsync(ctx->srcArcs.p, 0, (size_t)std::max<long long>(nsrc, 1) * 8, st));
+        CU(cudaMemsetAsync(ctx->srcSettled.p, 0, (size_t)std::max<long long>(nsrc, 1) * 8, st));
+    }
+    if (ctx->cutCap == 0) {
+        const long long cc = 4 * nsrc + 1024;
+        if (int rc = ensureRawArena(ctx, cc, 8 * cc)) return rc;
+    }
+    if (P.export_labels && ctx->labCap == 0) {
+        ctx->labCap = 64 * nsrc + 1024;
+        CU(ctx->labSrc.ensure((size_t)ctx->labCap * 4));
+        CU(ctx->labNode.ensure((size_t)ctx->labCap * 4));
+        CU(ctx->labHops.ensure((size_t)ctx->labCap * 4));
+        CU(ctx->labDist.ensure((size_t)ctx->labCap * 8));
+    }
+    GraphDev G{ctx->n, ctx->m, ctx->dRowptr.as<int64_t>(), ctx->dArcs.as<Arc>()};
+    long long rawCuts = 0, rawNodes = 0;
+    for (int attempt = 0;; ++attempt) {
+        if (attempt > 4) return fail(ctx, SMSGPU_ERR_INTERNAL, "raw arena kept overflowing");
+        CU(cudaMemsetAsync(dc, 0, 16 * sizeof(unsigned long long), st));
+        CU(cudaMemsetAsync(ctx->srcTier.p, 0xFF, (size_t)std::max<long long>(nsrc, 1), st));
+        RawOut R{};
+        R.node = ctx->rNode.as<int32_t>();
+        R.eid = ctx->rEid.as<int32_t>();
+        R.stay = ctx->rStay.as<uint8_t>();
+        R.cutOff = ctx->rCutOff.as<int32_t>();
+        R.cutLen = ctx->rCutLen.as<int32_t>();
+        R.cutSrc = ctx->rCutSrc.as<int32_t>();
+        R.cutSeq = ctx->rCutSeq.as<int32_t>();
+        R.cutTier = ctx->rCutTier.as<int8_t>();
+        R.counters = dc;
+        R.cutCap = ctx->cutCap;
+        R.nodeCap = std::min<long long>(ctx->nodeCap, 0x7FFFFFFFll);
+        R.labSrc = ctx->labSrc.as<int32_t>();
+        R.labNode = ctx->labNode.as<int32_t>();
+        R.labHops = ctx->labHops.as<int32_t>();
+        R.labDist = ctx->labDist.as<double>();
+        R.labCap = P.export_labels ? ctx->labCap : 0;
+        R.srcTier = ctx->srcTier.as<int8_t>();
+        R.srcArcs = P.export_src_stats ? ctx->srcArcs.as<long long>() : nullptr;
+        R.srcSettled = P.export_src_stats ? ctx->srcSettled.as<long long>() : nullptr;
+
+        SearchParams SP{};
+        SP.sources = ctx->explicitSources ? ctx->dSources.as<int32_t>() : nullptr;
+        SP.nsrc = nsrc;
+        SP.srcBegin = ctx->rank;
+        SP.srcStride = ctx->nranks;
+        SP.blacklist = ctx->blPtr;
+        SP.bestInit = P.best_dist_init;
+        SP.maxInter = P.max_intermediates;
+        SP.exportLabels = P.export_labels;
+        SP.queueCounter = dc + 8;
+        long long nwork = nsrc;
+        const int32_t *worklist = nullptr;
+        int32_t *ovfBufs[2] = {ctx->ovfA.as<int32_t>(), ctx->ovfB.as<int32_t>()};
+        long long done[3] = {0, 0, 0};
+        long long prevRun = 0;
+        for (int ti = P.start_tier; ti < 3 && nwork > 0; ++ti) {
+            if (int rc = ensureTierScratch(ctx, ti)) return rc;
+            const int which = ti & 1;
+            SP.tier = ti;
+            SP.worklist = worklist;
+            SP.nwork = nwork;
+            SP.ovfList = ovfBufs[which];
+            SP.ovfCount = dc + 9 + which;
+            CU(cudaMemsetAsync(dc + 8, 0, 8, st));
+            CU(cudaMemsetAsync(dc + 9 + which, 0, 8, st));
+            CU(launchSearch(ctx, ti, G, SP, R));
+            ctx->stats.search_launches += 1;
+            ctx->stats.total_launches += 1;
+            CU(cudaMemcpyAsync(hc, dc, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+            CU(cudaStreamSynchronize(st));
+            done[ti] = (long long)hc[4] - prevRun;
+            prevRun = (long long)hc[4];
+            nwork = (long long)hc[9 + which];
+            worklist = ovfBufs[which];
+        }
+        if (nwork > 0)
+            return fail(ctx, SMSGPU_ERR_INTERNAL, "%lld sources exceeded the capacities of the dense tier", nwork);
+        rawCuts = (long long)hc[0];
+        rawNodes = (long long)hc[1];
+        const long long nlab = (long long)hc[5];
+        bool redo = false;
+        if (rawCuts > ctx->cutCap || rawNodes > std::min<long long>(ctx->nodeCap, 0x7FFFFFFFll)) {
+            if (rawNodes > 0x7FFFFFFFll) return fail(ctx, SMSGPU_ERR_INTERNAL, "more than 2^31 walk nodes in one round");
+            if (int rc = ensureRawArena(ctx, std::max(ctx->cutCap, rawCuts + rawCuts / 4), std::max(ctx->nodeCap, rawNodes + rawNodes / 4)))
+                return rc;
+            redo = true;
+        }
+        if (P.export_labels && nlab > ctx->labCap) {
+            ctx->labCap = nlab + nlab / 4;
+            CU(ctx->labSrc.ensure((size_t)ctx->labCap * 4));
+            CU(ctx->labNode.ensure((size_t)ctx->labCap * 4));
+            CU(ctx->labHops.ensure((size_t)ctx->labCap * 4));
+            CU(ctx->labDist.ensure((size_t)ctx->labCap * 8));
+            redo = true;
+        }
+        if (redo) continue;
+        ctx->stats.sources_run = (long long)hc[4];
+        ctx->stats.arcs_scanned = (long long)hc[2];
+        ctx->stats.settled = (long long)hc[3];
+        ctx->stats.raw_walks = rawCuts;
+        ctx->nLabels = nlab;
+        for (int k = 0; k < 3; ++k) ctx->stats.tier_sources[k] = done[k];
+        break;
+    }
+    CU(cudaEventRecord(ctx->ev[2], st));
+
+    // ---- K5 ----
+    if (rawCuts > 0) {
+        validKernel<<<gridFor(rawCuts, 256), 256, 0, st>>>(rawCuts, ctx->rCutTier.as<int8_t>(), ctx->rCutSrc.as<int32_t>(),
+                                                           ctx->srcTier.as<int8_t>(), ctx->rValid.as<uint8_t>());
+        ctx->stats.total_launches += 1;
+    }
+    CutView V{ctx->rNode.as<int32_t>(), ctx->rEid.as<int32_t>(), ctx->rStay.as<uint8_t>(), ctx->rCutOff.as<int32_t>(),
+              ctx->rCutLen.as<int32_t>(), ctx->rCutSrc.as<int32_t>(), ctx->rCutSeq.as<int32_t>(), ctx->rValid.as<uint8_t>(),
+              rawCuts};
+    if (int rc = runDedup(ctx, V, rawNodes, P.dedup != 0, P.dedup != 0, ctx->nranks, ctx->rank, ctx->nsrcGlobal)) return rc;
+    if (ctx->ncclComm && ctx->commSize > 1)
+        if (int rc = mergeAcrossRanks(ctx, P.dedup != 0)) return rc;
+    ctx->stats.unique_cuts = ctx->fin.ncuts;
+    CU(cudaEventRecord(ctx->ev[3], st));
+    return SMSGPU_OK;
+}
+
+int smsgpu_fetch_cuts(smsgpu_ctx *ctx) {
+    if (!ctx) return SMSGPU_ERR_ARG;
+    CU(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    CutListDev &F = ctx->fin;
+    CutListHost &H = ctx->host;
+    const long long U = F.ncuts, N = F.nnodes;
+    CU(H.off.ensure((size_t)(U + 1) * 8));
+    CU(H.node.ensure((size_t)std::max<long long>(N, 1) * 4));
+    CU(H.eid.ensure((size_t)std::max<long long>(N, 1) * 4));
+    CU(H.stay.ensure((size_t)std::max<long long>(N, 1)));
+    CU(H.ncross.ensure((size_t)std::max<long long>(U, 1) * 4));
+    CU(H.src.ensure((size_t)std::max<long long>(U, 1) * 4));
+    CU(H.viol.ensure((size_t)std::max<long long>(U, 1) * 8));
+    CU(cudaEventRecord(ctx->ev[4], st));
+    CU(cudaMemcpyAsync(H.off.p, F.off.p, (size_t)(U + 1) * 8, cudaMemcpyDeviceToHost, st));
+    if (U > 0) {
+        CU(cudaMemcpyAsync(H.node.p, F.node.p, (size_t)N * 4, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(H.eid.p, F.eid.p, (size_t)N * 4, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(H.stay.p, F.stay.p, (size_t)N, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(H.ncross.p, F.ncross.p, (size_t)U * 4, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(H.src.p, F.src.p, (size_t)U * 4, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(H.viol.p, F.viol.p, (size_t)U * 8, cudaMemcpyDeviceToHost, st));
+    }
+    CU(cudaEventRecord(ctx->ev[5], st));
+    CU(cudaStreamSynchronize(st));
+    H.ncuts = U;
+    H.nnodes = N;
+    ctx->fetched = true;
+    float ms = 0;
+    cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]);
+    ctx->stats.ms_weights = ms;
+    cudaEventElapsedTime(&ms, ctx->ev[1], ctx->ev[2]);
+    ctx->stats.ms_search = ms;
+    cudaEventElapsedTime(&ms, ctx->ev[2], ctx->ev[3]);
+    ctx->stats.ms_dedup = ms;
+    cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[3]);
+    ctx->stats.ms_total_device = ms;
+    cudaEventElapsedTime(&ms, ctx->ev[4], ctx->ev[5]);
+    ctx->stats.ms_d2h = ms;
+    if (cudaEventElapsedTime(&ms, ctx->ev[6], ctx->ev[7]) == cudaSuccess) ctx->stats.ms_h2d = ms;
+    (void)cudaGetLastError();
+    return SMSGPU_OK;
+}
+
+int smsgpu_separate(smsgpu_ctx *ctx, const smsgpu_params *params) {
+    if (int rc = smsgpu_separate_async(ctx, params)) return rc;
+    return smsgpu_fetch_cuts(ctx);
+}
+
+int smsgpu_get_cuts(smsgpu_ctx *ctx, smsgpu_cuts *out) {
+    if (!ctx || !out) return SMSGPU_ERR_ARG;
+    if (!ctx->fetched) return fail(ctx, SMSGPU_ERR_STATE, "no fetched result: call smsgpu_separate or smsgpu_fetch_cuts first");
+    const CutListHost &H = ctx->host;
+    out->ncuts = H.ncuts;
+    out->nnodes = H.nnodes;
+    out->off = H.off.as<int64_t>();
+    out->node = H.node.as<int32_t>();
+    out->eid = H.eid.as<int32_t>();
+    out->is_stay = H.stay.as<uint8_t>();
+    out->n_cross = H.ncross.as<int32_t>();
+    out->src = H.src.as<int32_t>();
+    out->violation = H.viol.as<double>();
+    return SMSGPU_OK;
+}
+
+int smsgpu_get_stats(smsgpu_ctx *ctx, smsgpu_stats *out) {
+    if (!ctx || !out) return SMSGPU_ERR_ARG;
+    *out = ctx->stats;
+    return SMSGPU_OK;
+}
+
+} // extern "C"
+
+// =====================================================================================================================
+// parity instrumentation
+// =====================================================================================================================
+extern "C" {
+
+int smsgpu_get_labels(smsgpu_ctx *ctx, int64_t *nlabels, const int64_t **label_off, const int32_t **label_node,
+                      const double **label_dist, const int32_t **label_hops) {
+    if (!ctx || !nlabels || !label_off || !label_node || !label_dist || !label_hops) return SMSGPU_ERR_ARG;
+    if (!ctx->lastParams.export_labels) return fail(ctx, SMSGPU_ERR_STATE, "last round ran without export_labels");
+    CU(cudaSetDevice(ctx->device));
+    const long long L = ctx->nLabels, nsrc = ctx->nsrcLocal;
+    if (!ctx->haveLabels) {
+        std::vector<int32_t> src((size_t)L), node((size_t)L), hops((size_t)L);
+        std::vector<double> dist((size_t)L);
+        if (L > 0) {
+            CU(cudaMemcpy(src.data(), ctx->labSrc.p, (size_t)L * 4, cudaMemcpyDeviceToHost));
+            CU(cudaMemcpy(node.data(), ctx->labNode.p, (size_t)L * 4, cudaMemcpyDeviceToHost));
+            CU(cudaMemcpy(hops.data(), ctx->labHops.p, (size_t)L * 4, cudaMemcpyDeviceToHost));
+            CU(cudaMemcpy(dist.data(), ctx->labDist.p, (size_t)L * 8, cudaMemcpyDeviceToHost));
+        }
+        std::vector<long long> order((size_t)L);
+        for (long long i = 0; i < L; ++i) order[i] = i;
+        std::sort(order.begin(), order.end(), [&](long long a, long long b) {
+            return src[a] != src[b] ? src[a] < src[b] : node[a] < node[b];
+        });
+        CU(ctx->hLabOff.ensure((size_t)(nsrc + 1) * 8));
+        CU(ctx->hLabNode.ensure((size_t)std::max<long long>(L, 1) * 4));
+        CU(ctx->hLabDist.ensure((size_t)std::max<long long>(L, 1) * 8));
+        CU(ctx->hLabHops.ensure((size_t)std::max<long long>(L, 1) * 4));
+        int64_t *off = ctx->hLabOff.as<int64_t>();
+        std::fill(off, off + nsrc + 1, 0);
+        for (long long i = 0; i < L; ++i) {
+            const long long o = order[i];
+            off[src[o] + 1]++;
+            ctx->hLabNode.as<int32_t>()[i] = node[o];
+            ctx->hLabDist.as<double>()[i] = dist[o];
+            ctx->hLabHops.as<int32_t>()[i] = hops[o];
+        }
+        for (long long s = 0; s < nsrc; ++s) off[s + 1] += off[s];
+        ctx->haveLabels = true;
+    }
+    *nlabels = L;
+    *label_off = ctx->hLabOff.as<int64_t>();
+    *label_node = ctx->hLabNode.as<int32_t>();
+    *label_dist = ctx->hLabDist.as<double>();
+    *label_hops = ctx->hLabHops.as<int32_t>();
+    return SMSGPU_OK;
+}
+
+int smsgpu_get_src_stats(smsgpu_ctx *ctx, int64_t *nsrcOut, const int64_t **arcs, const int64_t **settled,
+                         const int32_t **tier) {
+    if (!ctx || !nsrcOut || !arcs || !settled || !tier) return SMSGPU_ERR_ARG;
+    if (!ctx->lastParams.export_src_stats) return fail(ctx, SMSGPU_ERR_STATE, "last round ran without export_src_stats");
+    CU(cudaSetDevice(ctx->device));
+    const long long nsrc = ctx->nsrcLocal;
+    if (!ctx->haveSrcStats) {
+        CU(ctx->hSrcArcs.ensure((size_t)std::max<long long>(nsrc, 1) * 8));
+        CU(ctx->hSrcSettled.ensure((size_t)std::max<long long>(nsrc, 1) * 8));
+        CU(ctx->hSrcTier.ensure((size_t)std::max<long long>(nsrc, 1) * 4));
+        std::vector<int8_t> t8((size_t)nsrc);
+        if (nsrc > 0) {
+            CU(cudaMemcpy(ctx->hSrcArcs.p, ctx->srcArcs.p, (size_t)nsrc * 8, cudaMemcpyDeviceToHost));
+            CU(cudaMemcpy(ctx->hSrcSettled.p, ctx->srcSettled.p, (size_t)nsrc * 8, cudaMemcpyDeviceToHost));
+            CU(cudaMemcpy(t8.data(), ctx->srcTier.p, (size_t)nsrc, cudaMemcpyDeviceToHost));
+        }
+        for (long long s = 0; s < nsrc; ++s) ctx->hSrcTier.as<int32_t>()[s] = t8[s];
+        ctx->haveSrcStats = true;
+    }
+    *nsrcOut = nsrc;
+    *arcs = ctx->hSrcArcs.as<int64_t>();
+    *settled = ctx->hSrcSettled.as<int64_t>();
+    *tier = ctx->hSrcTier.as<int32_t>();
+    return SMSGPU_OK;
+}
+
+// =====================================================================================================================
+// K6: small-cycle scan
+// =====================================================================================================================
+int smsgpu_small_cycles_set(smsgpu_ctx *ctx, int k, int64_t T, const int32_t *cycles) {
+    if (!ctx) return SMSGPU_ERR_ARG;
+    if ((k != 3 && k != 4) || T < 0 || (T > 0 && !cycles)) return fail(ctx, SMSGPU_ERR_ARG, "k must be 3 or 4, cycles non-null");
+    if (T * k >= (1ll << 31)) return fail(ctx, SMSGPU_ERR_ARG, "cycle list too long");
+    CU(cudaSetDevice(ctx->device));
+    const int s = k - 3;
+    for (int64_t i = 0; i < T * k; ++i)
+        if (cycles[i] < 0 || cycles[i] >= ctx->n) return fail(ctx, SMSGPU_ERR_ARG, "cycle vertex out of range");
+    ctx->scCount[s] = T;
+    CU(ctx->scNodes[s].ensure((size_t)std::max<int64_t>(T * k, 4) * 4));
+    CU(ctx->scEids[s].ensure((size_t)std::max<int64_t>(T * k, 4) * 4));
+    CU(ctx->scFlag[s].ensure((size_t)std::max<int64_t>(T, 1) * 4));
+    CU(ctx->scStay[s].ensure((size_t)std::max<int64_t>(T, 1)));
+    if (T == 0) return SMSGPU_OK;
+    CU(cudaMemcpyAsync(ctx->scNodes[s].p, cycles, (size_t)T * k * 4, cudaMemcpyHostToDevice, ctx->stream));
+    unsigned long long *dc = ctx->counters.as<unsigned long long>();
+    CU(cudaMemsetAsync(dc + 14, 0, 8, ctx->stream));
+    int *missing = reinterpret_cast<int *>(dc + 14);
+    if (k == 3)
+        resolveCycleEidsKernel<3><<<gridFor(T, 256), 256, 0, ctx->stream>>>(T, ctx->scNodes[s].as<int32_t>(), ctx->dRowptr.as<long long>(),
+                                                                           ctx->dCol.as<int32_t>(), ctx->dEid.as<int32_t>(),
+                                                                           ctx->scEids[s].as<int32_t>(), missing);
+    else
+        resolveCycleEidsKernel<4><<<gridFor(T, 256), 256, 0, ctx->stream>>>(T, ctx->scNodes[s].as<int32_t>(), ctx->dRowptr.as<long long>(),
+                                                                           ctx->dCol.as<int32_t>(), ctx->dEid.as<int32_t>(),
+                                                                           ctx->scEids[s].as<int32_t>(), missing);
+    CU(cudaGetLastError());
+    int hm = 0;
+    CU(cudaMemcpyAsync(&hm, missing, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    if (hm) {
+        ctx->scCount[s] = 0;
+        return fail(ctx, SMSGPU_ERR_ARG, "%d cycle edges are not edges of the graph", hm);
+    }
+    return SMSGPU_OK;
+}
+
+int smsgpu_small_cycles_scan(smsgpu_ctx *ctx, int k) {
+    if (!ctx) return SMSGPU_ERR_ARG;
+    if (k != 3 && k != 4) return fail(ctx, SMSGPU_ERR_ARG, "k must be 3 or 4");
+    if (!ctx->haveInput) return fail(ctx, SMSGPU_ERR_STATE, "small_cycles_scan before set_round_input");
+    CU(cudaSetDevice(ctx->device));
+    const int s = k - 3;
+    const long long T = ctx->scCount[s];
+    cudaStream_t st = ctx->stream;
+    CutListHost &H = ctx->scHost[s];
+    H.ncuts = H.nnodes = 0;
+    CU(H.off.ensure(8));
+    H.off.as<int64_t>()[0] = 0;
+    if (T == 0) return SMSGPU_OK;
+    CU(ctx->wViol.ensure((size_t)T * 8));
+    CU(ctx->wBase.ensure((size_t)(T + 2) * 8));
+    if (k == 3)
+        smallCycleScanKernel<3><<<gridFor(T, 256), 256, 0, st>>>(T, ctx->scEids[s].as<int32_t>(), ctx->xPtr, ctx->scFlag[s].as<int32_t>(),
+                                                                ctx->scStay[s].as<uint8_t>(), ctx->wViol.as<double>());
+    else
+        smallCycleScanKernel<4><<<gridFor(T, 256), 256, 0, st>>>(T, ctx->scEids[s].as<int32_t>(), ctx->xPtr, ctx->scFlag[s].as<int32_t>(),
+                                                                ctx->scStay[s].as<uint8_t>(), ctx->wViol.as<double>());
+    CU(cudaGetLastError());
+    if (int rc = exclusiveScan(ctx, ctx->scFlag[s].as<int32_t>(), T, ctx->wBase.as<long long>())) return rc;
+    long long U = 0;
+    CU(cudaMemcpyAsync(&U, ctx->wBase.as<long long>() + T, 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    CutListDev &F = ctx->scFin;
+    CU(F.off.ensure((size_t)(U + 1) * 8));
+    CU(F.node.ensure((size_t)std::max<long long>(U * k, 1) * 4));
+    CU(F.eid.ensure((size_t)std::max<long long>(U * k, 1) * 4));
+    CU(F.stay.ensure((size_t)std::max<long long>(U * k, 1)));
+    CU(F.ncross.ensure((size_t)std::max<long long>(U, 1) * 4));
+    CU(F.src.ensure((size_t)std::max<long long>(U, 1) * 4));
+    CU(F.viol.ensure((size_t)std::max<long long>(U, 1) * 8));
+    CU(H.off.ensure((size_t)(U + 1) * 8));
+    CU(H.node.ensure((size_t)std::max<long long>(U * k, 1) * 4));
+    CU(H.eid.ensure((size_t)std::max<long long>(U * k, 1) * 4));
+    CU(H.stay.ensure((size_t)std::max<long long>(U * k, 1)));
+    CU(H.ncross.ensure((size_t)std::max<long long>(U, 1) * 4));
+    CU(H.src.ensure((size_t)std::max<long long>(U, 1) * 4));
+    CU(H.viol.ensure((size_t)std::max<long long>(U, 1) * 8));
+    H.off.as<int64_t>()[0] = 0;
+    if (U > 0) {
+        if (k == 3)
+            smallCycleGatherKernel<3><<<gridFor(T, 256), 256, 0, st>>>(
+                T, ctx->scNodes[s].as<int32_t>(), ctx->scEids[s].as<int32_t>(), ctx->scFlag[s].as<int32_t>(),
+                ctx->scStay[s].as<uint8_t>(), ctx->wViol.as<double>(), ctx->wBase.as<long long>(), F.node.as<int32_t>(),
+                F.eid.as<int32_t>(), F.stay.as<uint8_t>(), F.ncross.as<int32_t>(), F.src.as<int32_t>(), F.viol.as<double>(),
+                F.off.as<long long>());
+        else
+            smallCycleGatherKernel<4><<<gridFor(T, 256), 256, 0, st>>>(
+                T, ctx->scNodes[s].as<int32_t>(), ctx->scEids[s].as<int32_t>(), ctx->scFlag[s].as<int32_t>(),
+                ctx->scStay[s].as<uint8_t>(), ctx->wViol.as<double>(), ctx->wBase.as<long long>(), F.node.as<int32_t>(),
+                F.eid.as<int32_t>(), F.stay.as<uint8_t>(), F.ncross.as<int32_t>(), F.src.as<int32_t>(), F.viol.as<double>(),
+                F.off.as<long long>());
+        CU(cudaGetLastError());
+        CU(cudaMemcpyAsync(H.off.p, F.off.p, (size_t)(U + 1) * 8, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(H.node.p, F.node.p, (size_t)U * k * 4, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(H.eid.p, F.eid.p, (size_t)U * k * 4, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(H.stay.p, F.stay.p, (size_t)U * k, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(H.ncross.p, F.ncross.p, (size_t)U * 4, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(H.src.p, F.src.p, (size_t)U * 4, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(H.viol.p, F.viol.p, (size_t)U * 8, cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+    }
+    H.ncuts = U;
+    H.nnodes = U * k;
+    return SMSGPU_OK;
+}
+
+int smsgpu_get_small_cycle_cuts(smsgpu_ctx *ctx, int k, smsgpu_cuts *out) {
+    if (!ctx || !out) return SMSGPU_ERR_ARG;
+    if (k != 3 && k != 4) return fail(ctx, SMSGPU_ERR_ARG, "k must be 3 or 4");
+    const CutListHost &H = ctx->scHost[k - 3];
+    out->ncuts = H.ncuts;
+    out->nnodes = H.nnodes;
+    out->off = H.off.as<int64_t>();
+    out->node = H.node.as<int32_t>();
+    out->eid = H.eid.as<int32_t>();
+    out->is_stay = H.stay.as<uint8_t>();
+    out->n_cross = H.ncross.as<int32_t>();
+    out->src = H.src.as<int32_t>();
+    out->violation = H.viol.as<double>();
+    return SMSGPU_OK;
+}
+
+} // extern "C"
+
+// =====================================================================================================================
+// multi-GPU: NCCL all-gather of the per-GPU cut lists + global dedup (C1).  NCCL is loaded lazily with dlopen so
+// that the library has no link-time dependency on it (a torch process already carries libnccl.so.2).
+// =====================================================================================================================
+#include <dlfcn.h>
+#include <nccl.h>
+
+namespace {
+
+struct NcclApi {
+    void *handle = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+    const char *(*GetErrorString)(ncclResult_t) = nullptr;
+    bool ok = false;
+};
+NcclApi &nccl() {
+    static NcclApi api;
+    if (api.handle) return api;
+    for (const char *name : {"libnccl.so.2", "libnccl.so"}) {
+        api.handle = dlopen(name, RTLD_NOW | RTLD_GLOBAL);
+        if (api.handle) break;
+    }
+    if (!api.handle) return api;
+    api.GetUniqueId = (decltype(api.GetUniqueId))dlsym(api.handle, "ncclGetUniqueId");
+    api.CommInitRank = (decltype(api.CommInitRank))dlsym(api.handle, "ncclCommInitRank");
+    api.CommDestroy = (decltype(api.CommDestroy))dlsym(api.handle, "ncclCommDestroy");
+    api.AllGather = (decltype(api.AllGather))dlsym(api.handle, "ncclAllGather");
+    api.GroupStart = (decltype(api.GroupStart))dlsym(api.handle, "ncclGroupStart");
+    api.GroupEnd = (decltype(api.GroupEnd))dlsym(api.handle, "ncclGroupEnd");
+    api.GetErrorString = (decltype(api.GetErrorString))dlsym(api.handle, "ncclGetErrorString");
+    api.ok = api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.AllGather && api.GroupStart && api.GroupEnd &&
+             api.GetErrorString;
+    return api;
+}
+
+#define NC(call)                                                                                                  \
+    do {                                                                                                          \
+        ncclResult_t r_ = (call);                                                                                 \
+        if (r_ != ncclSuccess) return fail(ctx, SMSGPU_ERR_NCCL, "%s: %s", #call, nccl().GetErrorString(r_));    \
+    } while (0)
+
+// local final list -> padded send arrays
+__global__ void packCutsKernel(const long long U, const long long N, const long long *off, const int32_t *src,
+                               const int32_t *seq, const int32_t *node, const int32_t *eid, const uint8_t *stay,
+                               int32_t *pLen, int32_t *pSrc, int32_t *pSeq, int32_t *pOff, int32_t *pNode, int32_t *pEid,
+                               uint8_t *pStay) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    const long long t0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    for (long long k = t0; k < U; k += stride) {
+        pLen[k] = (int32_t)(off[k + 1] - off[k]);
+        pOff[k] = (int32_t)off[k];
+        pSrc[k] = src[k];
+        pSeq[k] = seq[k];
+    }
+    for (long long j = t0; j < N; j += stride) {
+        pNode[j] = node[j];
+        pEid[j] = eid[j];
+        pStay[j] = stay[j];
+    }
+}
+__global__ void fixMergedKernel(const long long total, const long long maxU, const long long maxN, const long long *counts,
+                                int32_t *mOff, uint8_t *mValid) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    const long long r = i / maxU, k = i % maxU;
+    const bool v = k < counts[2 * r];
+    mValid[i] = v;
+    mOff[i] = v ? (int32_t)(r * maxN + mOff[i]) : 0;
+}
+
+int mergeAcrossRanks(smsgpu_ctx *ctx, bool dedup) {
+    NcclApi &A = nccl();
+    cudaStream_t st = ctx->stream;
+    const int size = ctx->commSize;
+    if (ctx->nranks != size || ctx->rank != ctx->commRank)
+        return fail(ctx, SMSGPU_ERR_STATE, "source sharding (%d/%d) does not match the communicator (%d/%d)", ctx->rank,
+                    ctx->nranks, ctx->commRank, size);
+    ncclComm_t comm = static_cast<ncclComm_t>(ctx->ncclComm);
+    CutListDev &F = ctx->fin;
+    // 1. counts
+    CU(ctx->gCounts.ensure((size_t)(2 * size + 2) * 8));
+    CU(ctx->hGCounts.ensure((size_t)(2 * size + 2) * 8));
+    long long *hg = ctx->hGCounts.as<long long>();
+    long long *dg = ctx->gCounts.as<long long>();
+    hg[2 * size] = F.ncuts;
+    hg[2 * size + 1] = F.nnodes;
+    CU(cudaMemcpyAsync(dg + 2 * size, hg + 2 * size, 16, cudaMemcpyHostToDevice, st));
+    NC(A.AllGather(dg + 2 * size, dg, 2, ncclInt64, comm, st));
+    CU(cudaMemcpyAsync(hg, dg, (size_t)2 * size * 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    long long maxU = 0, maxN = 0;
+    for (int r = 0; r < size; ++r) {
+        maxU = std::max(maxU, hg[2 * r]);
+        maxN = std::max(maxN, hg[2 * r + 1]);
+    }
+    if (maxU == 0) return 0;
+    maxN = std::max<long long>(maxN, 1);
+    if ((long long)size * maxN > 0x7FFFFFFFll) return fail(ctx, SMSGPU_ERR_INTERNAL, "merged cut list exceeds 2^31 nodes");
+    // 2. pack + gather
+    CU(ctx->pLen.ensure((size_t)maxU * 4));
+    CU(ctx->pSrc.ensure((size_t)maxU * 4));
+    CU(ctx->pSeq.ensure((size_t)maxU * 4));
+    CU(ctx->pOff.ensure((size_t)maxU * 4));
+    CU(ctx->pNode.ensure((size_t)maxN * 4));
+    CU(ctx->pEid.ensure((size_t)maxN * 4));
+    CU(ctx->pStay.ensure((size_t)maxN));
+    const long long tot = (long long)size * maxU, totN = (long long)size * maxN;
+    CU(ctx->mLen.ensure((size_t)tot * 4));
+    CU(ctx->mSrc.ensure((size_t)tot * 4));
+    CU(ctx->mSeq.ensure((size_t)tot * 4));
+    CU(ctx->mOff.ensure((size_t)tot * 4));
+    CU(ctx->mValid.ensure((size_t)tot));
+    CU(ctx->mNode.ensure((size_t)totN * 4));
+    CU(ctx->mEid.ensure((size_t)totN * 4));
+    CU(ctx->mStay.ensure((size_t)totN));
+    packCutsKernel<<<ctx->smCount * 4, 256, 0, st>>>(F.ncuts, F.nnodes, F.off.as<long long>(), F.src.as<int32_t>(),
+                                                     F.seq.as<int32_t>(), F.node.as<int32_t>(), F.eid.as<int32_t>(),
+                                                     F.stay.as<uint8_t>(), ctx->pLen.as<int32_t>(), ctx->pSrc.as<int32_t>(),
+                                                     ctx->pSeq.as<int32_t>(), ctx->pOff.as<int32_t>(), ctx->pNode.as<int32_t>(),
+                                                     ctx->pEid.as<int32_t>(), ctx->pStay.as<uint8_t>());
+    CU(cudaGetLastError());
+    NC(A.GroupStart());
+    NC(A.AllGather(ctx->pLen.p, ctx->mLen.p, (size_t)maxU, ncclInt32, comm, st));
+    NC(A.AllGather(ctx->pSrc.p, ctx->mSrc.p, (size_t)maxU, ncclInt32, comm, st));
+    NC(A.AllGather(ctx->pSeq.p, ctx->mSeq.p, (size_t)maxU, ncclInt32, comm, st));
+    NC(A.AllGather(ctx->pOff.p, ctx->mOff.p, (size_t)maxU, ncclInt32, comm, st));
+    NC(A.AllGather(ctx->pNode.p, ctx->mNode.p, (size_t)maxN, ncclInt32, comm, st));
+    NC(A.AllGather(ctx->pEid.p, ctx->mEid.p, (size_t)maxN, ncclInt32, comm, st));
+    NC(A.AllGather(ctx->pStay.p, ctx->mStay.p, (size_t)maxN, ncclUint8, comm, st));
+    NC(A.GroupEnd());
+    fixMergedKernel<<<gridFor(tot, 256), 256, 0, st>>>(tot, maxU, maxN, dg, ctx->mOff.as<int32_t>(), ctx->mValid.as<uint8_t>());
+    CU(cudaGetLastError());
+    ctx->stats.total_launches += 2;
+    // 3. global dedup: every rank computes the identical full list
+    CutView V{ctx->mNode.as<int32_t>(), ctx->mEid.as<int32_t>(), ctx->mStay.as<uint8_t>(), ctx->mOff.as<int32_t>(),
+              ctx->mLen.as<int32_t>(), ctx->mSrc.as<int32_t>(), ctx->mSeq.as<int32_t>(), ctx->mValid.as<uint8_t>(), tot};
+    return runDedup(ctx, V, totN, false, dedup, 1, 0, ctx->nsrcGlobal);
+}
+
+} // namespace
+
+extern "C" {
+
+int smsgpu_nccl_unique_id(void *id128) {
+    smsgpu_ctx *ctx = nullptr;
+    if (!id128) return fail(ctx, SMSGPU_ERR_ARG, "id128 is null");
+    NcclApi &A = nccl();
+    if (!A.ok) return fail(ctx, SMSGPU_ERR_NCCL, "libnccl.so.2 could not be loaded");
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+    ncclUniqueId id;
+    NC(A.GetUniqueId(&id));
+    std::memcpy(id128, &id, 128);
+    return SMSGPU_OK;
+}
+
+int smsgpu_comm_init(smsgpu_ctx *ctx, const void *id128, int rank, int nranks) {
+    if (!ctx) return SMSGPU_ERR_ARG;
+    if (!id128 || nranks < 1 || rank < 0 || rank >= nranks) return fail(ctx, SMSGPU_ERR_ARG, "bad communicator arguments");
+    NcclApi &A = nccl();
+    if (!A.ok) return fail(ctx, SMSGPU_ERR_NCCL, "libnccl.so.2 could not be loaded");
+    CU(cudaSetDevice(ctx->device));
+    smsgpu_comm_destroy(ctx);
+    ncclUniqueId id;
+    std::memcpy(&id, id128, 128);
+    ncclComm_t comm = nullptr;
+    NC(A.CommInitRank(&comm, nranks, id, rank));
+    ctx->ncclComm = comm;
+    ctx->commRank = rank;
+    ctx->commSize = nranks;
+    return SMSGPU_OK;
+}
+
+int smsgpu_comm_destroy(smsgpu_ctx *ctx) {
+    if (!ctx) return SMSGPU_ERR_ARG;
+    if (ctx->ncclComm) {
+        if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+        nccl().CommDestroy(static_cast<ncclComm_t>(ctx->ncclComm));
+        ctx->ncclComm = nullptr;
+    }
+    ctx->commRank = 0;
+    ctx->commSize = 1;
+    return SMSGPU_OK;
+}
+
+} // extern "C"
