@@ -51,7 +51,7 @@ typedef struct smsgpu_params {
     int32_t export_labels;     /* 1: keep every stored Dijkstra label (node, dist, hops) per source -- parity tests only */
     int32_t export_src_stats;  /* 1: per-source (arcs scanned, settled) counters */
     int32_t start_tier;        /* 0 = auto (shared-memory tier first), 1 = global-memory tier, 2 = dense tier */
-    int32_t tile_width;        /* 0 = auto; 8, 16 or 32 lanes cooperate on one source */
+    int32_t tile_width;        /* 0 = auto; lanes that cooperate on one source: 32 (one warp) is the only width built */
     int32_t reserved[9];
 } smsgpu_params;
 

@@ -12,6 +12,7 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(CSRC, "libsmsgpu.so")
+LIB_DEBUG = os.path.join(CSRC, "libsmsgpu_dbg.so")  # -DSMSGPU_DEBUG_CHECKS: device asserts (SMSGPU_LIB selects it)
 SOURCES = ["smsgpu.cu"]
 HEADERS = ["ocw_types.cuh", "ocw_search.cuh", "ocw_walks.cuh", "ocw_kernels.cuh", "dedup_kernels.cuh",
            "small_cycles.cuh", os.path.join("..", "..", "include", "smsgpu.h")]
@@ -35,8 +36,14 @@ def needs_build() -> bool:
     return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
+def build(force: bool = False, verbose: bool = False, debug: bool = False) -> str:
     """Compile sms_b200/csrc/*.cu for sm_100a into sms_b200/csrc/libsmsgpu.so; returns the path."""
+    if debug:
+        cmd = [_nvcc(), *NVCC_FLAGS, "-DSMSGPU_DEBUG_CHECKS", "-o", LIB_DEBUG, *[os.path.join(CSRC, s) for s in SOURCES], "-ldl"]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError("nvcc failed:\n" + r.stdout + r.stderr)
+        return LIB_DEBUG
     if not force and not needs_build():
         return LIB
     cmd = [_nvcc(), *NVCC_FLAGS, "-o", LIB, *[os.path.join(CSRC, s) for s in SOURCES], "-ldl"]
@@ -52,4 +59,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
 
 if __name__ == "__main__":
-    print(build(force=True, verbose=True))
+    import sys
+    if "--debug" in sys.argv:
+        print(build(debug=True))
+    else:
+        print(build(force=True, verbose=True))

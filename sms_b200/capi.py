@@ -107,7 +107,7 @@ def load_library(path: str | None = None) -> C.CDLL:
     global _lib
     if _lib is not None and path is None:
         return _lib
-    p = path or LIB_PATH
+    p = path or os.environ.get("SMSGPU_LIB") or LIB_PATH  # SMSGPU_LIB: e.g. the device-assert build libsmsgpu_dbg.so
     if not os.path.exists(p):
         raise FileNotFoundError(f"{p} is missing: build it with `python -m sms_b200.build` (there is no CPU fallback)")
     lib = C.CDLL(p)
@@ -214,6 +214,9 @@ class Context:
         p = Params()
         self.lib.smsgpu_default_params(C.byref(p))
         for k, v in kw.items():
+            if k == "debug_flags":  # reserved[0]: debugging aids of the search kernel (ocw_types.cuh SearchParams::debugFlags)
+                p.reserved[0] = int(v)
+                continue
             if not hasattr(p, k):
                 raise TypeError(f"unknown parameter {k}")
             setattr(p, k, v)

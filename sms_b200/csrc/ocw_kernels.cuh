@@ -76,6 +76,7 @@ __global__ void __launch_bounds__(128) ocwSearchKernel(const GraphDev G, const S
         for (uint32_t i = T.lane; i < caps.tabCap; i += TW) storeEntry(&M.tab[i], emptyEntry());
         T.sync();
     }
+    if ((P.debugFlags & 1) && T.shift != 0) return;
     const long long total = P.worklist ? P.nwork : P.nsrc;
     long long accArcs = 0, accSettled = 0, accSources = 0;
     uint32_t sel[16];

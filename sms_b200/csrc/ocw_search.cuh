@@ -27,6 +27,17 @@
 
 namespace smsgpu {
 
+#ifdef SMSGPU_DEBUG_CHECKS
+// value must be identical in all lanes of the tile
+#define SMS_UNI(T, x)                                   \
+    do {                                                \
+        const auto uni_ref_ = (T).shfl((x), 0);         \
+        SMS_CHK(uni_ref_ == (x));                       \
+    } while (0)
+#else
+#define SMS_UNI(T, x) ((void)0)
+#endif
+
 template <int TW>
 struct Tile {
     unsigned mask; // lanes of this tile inside the warp
@@ -133,11 +144,16 @@ __device__ __forceinline__ uint32_t homeSlot(const TileMem &M, uint32_t v) {
 // slot of original vertex v, or -1
 __device__ __forceinline__ int findSlot(const TileMem &M, uint32_t v) {
     uint32_t s = homeSlot(M, v);
+    SMS_CHK(s < M.caps.tabCap);
+#ifdef SMSGPU_DEBUG_CHECKS
+    uint32_t probes = 0;
+#endif
     while (true) {
         const uint32_t k = M.tab[s].key;
         if (k == v) return (int)s;
         if (k == kEmptyKey) return -1;
         s = (s + 1) & M.tabMask;
+        SMS_CHK(++probes <= M.caps.tabCap);
     }
 }
 // find or create; *isNew tells whether this call created it.  Safe against the other lanes of the tile
@@ -145,7 +161,12 @@ __device__ __forceinline__ int findSlot(const TileMem &M, uint32_t v) {
 __device__ __forceinline__ int findOrInsertSlot(const TileMem &M, uint32_t v, bool *isNew) {
     uint32_t s = homeSlot(M, v);
     *isNew = false;
+    SMS_CHK(s < M.caps.tabCap);
+#ifdef SMSGPU_DEBUG_CHECKS
+    uint32_t probes = 0;
+#endif
     while (true) {
+        SMS_CHK(++probes <= M.caps.tabCap);
         uint32_t k = M.tab[s].key;
         if (k == v) return (int)s;
         if (k == kEmptyKey) {
@@ -170,6 +191,9 @@ template <int TW>
 __device__ __forceinline__ void heapPush(const Tile<TW> &T, HeapEnt *heap, uint32_t &heapN, unsigned long long hi,
                                          unsigned long long lo) {
     uint32_t i = heapN++;
+    SMS_UNI(T, i);
+    SMS_UNI(T, hi);
+    SMS_UNI(T, lo);
     while (i > 0) {
         const uint32_t p = (i - 1) / TW;
         const HeapEnt pe = heap[p]; // same address in all lanes: broadcast
@@ -285,6 +309,9 @@ __device__ void searchSource(const Tile<TW> &T, const GraphDev &G, TileMem &M, S
             hc = (uint32_t)(top.lo >> 32);
             dc = __longlong_as_double((long long)top.hi);
             curSlot = findSlot(M, cur >> 1);
+            SMS_CHK(curSlot >= 0);
+            SMS_UNI(T, S.heapN);
+            SMS_UNI(T, cur);
             const uint32_t fl = M.tab[curSlot].flags;
             if (fl & (1u << (cur & 1u))) { // already settled through a fresher entry
                 heapPop<TW>(T, M.heap, S.heapN);
@@ -294,13 +321,21 @@ __device__ void searchSource(const Tile<TW> &T, const GraphDev &G, TileMem &M, S
             break;
         }
         // loop condition of ocw_seperator.cpp:88-90
+        SMS_UNI(T, (int)have);
+        SMS_UNI(T, S.best);
+        SMS_UNI(T, dc);
         if (!have || cur == target || 2 * dc > S.best) break;
         heapPop<TW>(T, M.heap, S.heapN);
+        // every lane has read this entry's flags in the staleness test above; heapPop returns without a barrier
+        // when the queue becomes empty, so order those reads before lane 0 sets the settled bit
+        T.sync();
         if (T.lane == 0) M.tab[curSlot].flags |= (1u << (cur & 1u));
         S.settled++;
         const uint32_t side = cur & 1u;
         const uint32_t u = cur >> 1;
+        SMS_CHK((long long)u < G.n);
         const long long rb = G.rowptr[u], re = G.rowptr[u + 1];
+        SMS_CHK(rb >= 0 && re >= rb && re <= 2 * G.m);
         const uint32_t hNew = hc + 1;
 
         for (long long base = rb; base < re; base += TW) {
@@ -317,6 +352,7 @@ __device__ void searchSource(const Tile<TW> &T, const GraphDev &G, TileMem &M, S
                 const Arc arc = G.arcs[a];
                 nbr = (uint32_t)arc.nbr & 0x7FFFFFFFu;
                 w = arc.w;
+                SMS_CHK((long long)nbr < G.n && w >= 0.0 && w <= 1.0);
                 act = arc.nbr >= 0; // blacklisted neighbours are skipped (:98-99)
             }
             S.arcs += __popc(T.ballot(act));
@@ -337,14 +373,18 @@ __device__ void searchSource(const Tile<TW> &T, const GraphDev &G, TileMem &M, S
             // touched list for the slots created in this chunk
             {
                 const unsigned nm = T.ballot(isNew);
+                SMS_CHK(S.touchedN + __popc(nm) <= M.caps.touchedCap);
                 if (isNew) M.touched[S.touchedN + __popc(nm & ((1u << T.lane) - 1u))] = (uint32_t)slot;
                 S.touchedN += __popc(nm);
+                SMS_UNI(T, S.touchedN);
             }
             bool accS = false, accX = false, evS = false, evX = false;
             double DS = 0, DX = 0;
             uint32_t HS = 0, HX = 0;
             if (slot >= 0) {
+                SMS_CHK((uint32_t)slot < M.caps.tabCap);
                 Entry e = loadEntry(&M.tab[slot]);
+                SMS_CHK(e.key == nbr);
                 // label of the side the stay arc reaches (same side as cur) and of the other side
                 double dA = side ? e.d1 : e.d0, dB = side ? e.d0 : e.d1;
                 uint32_t hA = side ? e.h1 : e.h0, hB = side ? e.h0 : e.h1;
@@ -393,6 +433,7 @@ __device__ void searchSource(const Tile<TW> &T, const GraphDev &G, TileMem &M, S
             T.sync();
             // ---- replay of the record logic in adjacency order (:71-82) -------------------------------------
             unsigned evm = T.ballot(evS || evX);
+            SMS_UNI(T, evm);
             while (evm) {
                 const int l = __ffs(evm) - 1;
                 evm &= evm - 1;
@@ -425,13 +466,26 @@ __device__ void searchSource(const Tile<TW> &T, const GraphDev &G, TileMem &M, S
             }
             // ---- queue admission: only nodes that can still be extracted ------------------------------------
             const bool pushS = accS && 2 * dS <= best0, pushX = accX && 2 * dX <= best0;
+            SMS_UNI(T, S.best);
+            SMS_UNI(T, S.histN);
             unsigned pm = T.ballot(pushS || pushX);
+            SMS_UNI(T, pm);
+            SMS_UNI(T, S.heapN);
             while (pm) {
                 const int l = __ffs(pm) - 1;
                 pm &= pm - 1;
                 const uint32_t nb = T.shfl(nbr, l);
                 const int pS = T.shfl((int)pushS, l), pX = T.shfl((int)pushX, l);
                 const double d0 = T.shfl(dS, l), d1 = T.shfl(dX, l);
+                SMS_UNI(T, l);
+                SMS_UNI(T, nb);
+                SMS_UNI(T, pS);
+                SMS_UNI(T, pX);
+                SMS_UNI(T, d0);
+                SMS_UNI(T, d1);
+                SMS_UNI(T, hNew);
+                SMS_UNI(T, side);
+                SMS_CHK(S.heapN + 2 <= M.caps.heapCap);
                 if (pS)
                     heapPush<TW>(T, M.heap, S.heapN, (unsigned long long)__double_as_longlong(d0),
                                  ((unsigned long long)hNew << 32) | (2 * nb + side));

@@ -4,6 +4,16 @@
 #include <cstdint>
 #include <cuda_runtime.h>
 
+// Debug build (-DSMSGPU_DEBUG_CHECKS, sms_b200/build.py --debug): device-side bounds / invariant checks that stop the
+// kernel with file:line.  compute-sanitizer is not available on the GPU pool, so this is the memory checker.
+#ifdef SMSGPU_DEBUG_CHECKS
+#undef NDEBUG
+#include <cassert>
+#define SMS_CHK(cond) assert(cond)
+#else
+#define SMS_CHK(cond) ((void)0)
+#endif
+
 namespace smsgpu {
 
 // One CSR adjacency entry in HBM, rebuilt every round by K1 (dc_weights): 16 B, one 128-bit load per arc scan.
@@ -113,6 +123,7 @@ struct SearchParams {
     int32_t maxInter;
     int32_t tier;
     int32_t exportLabels;
+    int32_t debugFlags;     // bit 0: only the first tile of every warp works (debugging aid)
 };
 
 } // namespace smsgpu

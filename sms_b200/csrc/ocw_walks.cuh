@@ -47,6 +47,7 @@ __device__ int selectIntermediates(const Tile<TW> &T, TileMem &M, SrcState &S, i
     for (uint32_t i = T.lane; i < H; i += TW) {
         const uint32_t t = M.hist[i];
         const int slot = findSlot(M, t >> 1);
+        SMS_CHK(slot >= 0);
         const Entry e = loadEntry(&M.tab[slot]);
         HeapEnt k;
         k.hi = (unsigned long long)__double_as_longlong((t & 1u) ? e.d1 : e.d0);
@@ -73,6 +74,7 @@ __device__ int selectIntermediates(const Tile<TW> &T, TileMem &M, SrcState &S, i
             }
         }
         const uint32_t idx = (uint32_t)(mlo & 0xFFFFFFFFull);
+        SMS_CHK(idx < H);
         if (T.lane == 0) {
             sel[r] = M.hist[idx];
             HeapEnt k;
@@ -101,6 +103,8 @@ __device__ inline int tracePath(const TileMem &M, uint32_t t, uint32_t src, int3
     while (cur != src) {
         if (len >= (int)M.caps.walkCap) return -1;
         const int slot = findSlot(M, cur >> 1);
+        SMS_CHK(slot >= 0);
+        SMS_CHK(((cur & 1u) ? M.tab[slot].d1 : M.tab[slot].d0) < kUnlabelled);
         cur = M.pred[2 * slot + (cur & 1u)];
         p[++len] = (int32_t)cur;
     }
@@ -121,6 +125,8 @@ __device__ inline void extractCycles(const GraphDev &G, TileMem &M, SrcState &S,
     for (int i = 1; i <= len; ++i) {
         numCross += st[i - 1] ? 0 : 1;
         const long long a = findArc(G, c[i], c[i - 1]);
+        SMS_CHK(a >= 0);
+        SMS_CHK(i <= 2 * (int)M.caps.walkCap + 1);
         warc[i] = (int32_t)a;
         const double w = G.arcs[a].w;
         pathLength += st[i - 1] ? w : 1 - w;
@@ -147,6 +153,7 @@ __device__ inline void extractCycles(const GraphDev &G, TileMem &M, SrcState &S,
             const double outerLen = plen[len] - innerLen;
             // weights_[edgeId(c[i], c[j])]: first arc of c[i] towards c[j]
             const long long ca = findArc(G, cur, nb);
+            SMS_CHK(ca >= 0);
             const double x = G.arcs[ca].w;
             int f0 = -1, l0 = 0, f1 = -1, l1 = 0; // flags: bit0 crossing, bit1 inner
             if ((innerCrossingDif % 2) == 0) {
@@ -291,6 +298,7 @@ __device__ inline int buildWalk(const TileMem &M, uint32_t t, uint32_t src) {
     int W = 0;
     M.wn[0] = pa[0] >> 1;
     auto addEdge = [&](int32_t next, bool stay) {
+        SMS_CHK(W < 2 * (int)M.caps.walkCap + 1);
         M.ws[W] = stay ? 1 : 0;
         M.wn[++W] = next;
     };

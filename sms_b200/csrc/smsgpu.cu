@@ -212,11 +212,9 @@ cudaError_t launchSearchT(smsgpu_ctx *c, const TierCfg &t, const GraphDev &G, co
 cudaError_t launchSearch(smsgpu_ctx *c, int tierIdx, const GraphDev &G, const SearchParams &P, const RawOut &R) {
     const TierCfg &t = c->tier[tierIdx];
     const bool smem = tierIdx == 0;
-    switch (c->tileWidth) {
-    case 8: return smem ? launchSearchT<8, true>(c, t, G, P, R) : launchSearchT<8, false>(c, t, G, P, R);
-    case 16: return smem ? launchSearchT<16, true>(c, t, G, P, R) : launchSearchT<16, false>(c, t, G, P, R);
-    default: return smem ? launchSearchT<32, true>(c, t, G, P, R) : launchSearchT<32, false>(c, t, G, P, R);
-    }
+    // One source per WARP.  Sub-warp tiles (8 / 16 lanes, several sources per warp in independent control
+    // flow) were measured to corrupt each other on sm_100a (DESIGN.md "tile width") and are not instantiated.
+    return smem ? launchSearchT<32, true>(c, t, G, P, R) : launchSearchT<32, false>(c, t, G, P, R);
 }
 template <int TW, bool SMEM>
 int occupancyT(size_t smemBytes) {
@@ -230,11 +228,8 @@ int occupancyT(size_t smemBytes) {
     return std::max(nb, 1);
 }
 int occupancy(int tw, bool smem, size_t smemBytes) {
-    switch (tw) {
-    case 8: return smem ? occupancyT<8, true>(smemBytes) : occupancyT<8, false>(0);
-    case 16: return smem ? occupancyT<16, true>(smemBytes) : occupancyT<16, false>(0);
-    default: return smem ? occupancyT<32, true>(smemBytes) : occupancyT<32, false>(0);
-    }
+    (void)tw;
+    return smem ? occupancyT<32, true>(smemBytes) : occupancyT<32, false>(0);
 }
 
 // Working-memory capacities of the three tiers (DESIGN.md "tiers").
@@ -381,7 +376,8 @@ int smsgpu_create(smsgpu_ctx **out, int64_t n, int64_t m, const int64_t *rowptr,
     CUB(cudaStreamSynchronize(ctx->stream));
     // tile width by average degree: one lane per arc of a typical row
     const double avgDeg = n ? 2.0 * (double)m / (double)n : 0.0;
-    ctx->tileWidth = avgDeg <= 6.5 ? 8 : (avgDeg <= 14.0 ? 16 : 32);
+    (void)avgDeg;
+    ctx->tileWidth = 32;
     configureTiers(ctx);
     ctx->nsrcGlobal = ctx->nsrcLocal = n; // default source list 0..n-1 (conshdlr_oscw.cpp:188-195)
     ctx->rank = 0;
@@ -640,8 +636,7 @@ int smsgpu_separate_async(smsgpu_ctx *ctx, const smsgpu_params *params) {
     else
         smsgpu_default_params(&P);
     if (P.max_intermediates < 0 || P.max_intermediates > 16) return fail(ctx, SMSGPU_ERR_ARG, "max_intermediates must be 0..16");
-    if (P.tile_width != 0 && P.tile_width != 8 && P.tile_width != 16 && P.tile_width != 32)
-        return fail(ctx, SMSGPU_ERR_ARG, "tile_width must be 0, 8, 16 or 32");
+    if (P.tile_width != 0 && P.tile_width != 32) return fail(ctx, SMSGPU_ERR_ARG, "tile_width must be 0 or 32");
     if (P.start_tier < 0 || P.start_tier > 2) return fail(ctx, SMSGPU_ERR_ARG, "start_tier must be 0..2");
     CU(cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->stream;
@@ -732,6 +727,7 @@ int smsgpu_separate_async(smsgpu_ctx *ctx, const smsgpu_params *params) {
         SP.bestInit = P.best_dist_init;
         SP.maxInter = P.max_intermediates;
         SP.exportLabels = P.export_labels;
+        SP.debugFlags = P.reserved[0];
         SP.queueCounter = dc + 8;
         long long nwork = nsrc;
         const int32_t *worklist = nullptr;
