@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define SMSGPU_ABI_VERSION 1
+#define SMSGPU_ABI_VERSION 2
 
 typedef struct smsgpu_ctx smsgpu_ctx;
 
@@ -50,7 +50,7 @@ typedef struct smsgpu_params {
                                   (source index, emission order), exactly what getViolatedOcws returns per source */
     int32_t export_labels;     /* 1: keep every stored Dijkstra label (node, dist, hops) per source -- parity tests only */
     int32_t export_src_stats;  /* 1: per-source (arcs scanned, settled) counters */
-    int32_t start_tier;        /* 0 = auto (shared-memory tier first), 1 = global-memory tier, 2 = dense tier */
+    int32_t start_tier;        /* 0 = auto (shared-memory tier first), 1 / 2 = HBM hashed tiers (medium / large), 3 = dense tier */
     int32_t tile_width;        /* 0 = auto; lanes that cooperate on one source: 32 (one warp) is the only width built */
     int32_t reserved[9];
 } smsgpu_params;
@@ -79,7 +79,7 @@ typedef struct smsgpu_stats {
     int64_t settled;           /* heap extractions summed over sources */
     int64_t raw_walks;         /* walks before dedup */
     int64_t unique_cuts;
-    int64_t tier_sources[3];   /* sources finished in the shared / global / dense tier */
+    int64_t tier_sources[4];   /* sources finished in the shared-memory / HBM medium / HBM large / dense tier */
     double ms_weights;         /* K1 */
     double ms_search;          /* K2-K4 fused: bounded shortest paths + walk extraction + chord repair */
     double ms_dedup;           /* K5 */
@@ -87,7 +87,7 @@ typedef struct smsgpu_stats {
     double ms_h2d, ms_d2h;
     int64_t search_launches;   /* kernel launches of the search kernel this round */
     int64_t total_launches;    /* all kernel launches this round */
-    int64_t reserved[8];
+    int64_t reserved[7];
 } smsgpu_stats;
 
 /* ---- life cycle: replaces OcwSeparator::OcwSeparator (src/graph/ocw_seperator.cpp:9-23) ---------------------- */

@@ -64,7 +64,7 @@ class StatsStruct(C.Structure):
         ("settled", C.c_int64),
         ("raw_walks", C.c_int64),
         ("unique_cuts", C.c_int64),
-        ("tier_sources", C.c_int64 * 3),
+        ("tier_sources", C.c_int64 * 4),
         ("ms_weights", C.c_double),
         ("ms_search", C.c_double),
         ("ms_dedup", C.c_double),
@@ -73,7 +73,7 @@ class StatsStruct(C.Structure):
         ("ms_d2h", C.c_double),
         ("search_launches", C.c_int64),
         ("total_launches", C.c_int64),
-        ("reserved", C.c_int64 * 8),
+        ("reserved", C.c_int64 * 7),
     ]
 
 

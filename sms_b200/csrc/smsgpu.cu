@@ -74,6 +74,7 @@ struct PinBuf {
     }
 };
 
+constexpr int kNumTiers = 4; // 0 shared memory, 1 HBM hashed (medium), 2 HBM hashed (large), 3 HBM dense
 struct TierCfg {
     TileCaps caps{};
     long long ntiles = 0;   // tiles that own HBM working memory (tiers 1, 2)
@@ -118,7 +119,7 @@ struct smsgpu_ctx {
     int rank = 0, nranks = 1;
 
     int tileWidth = 0; // resolved
-    TierCfg tier[3];
+    TierCfg tier[kNumTiers];
 
     // raw arena
     DevBuf rNode, rEid, rStay, rCutOff, rCutLen, rCutSrc, rCutSeq, rCutTier, rValid;
@@ -244,16 +245,28 @@ void configureTiers(smsgpu_ctx *c) {
         t.ctas = c->smCount * occupancy(tw, true, t.smemBytes);
         t.ready = true;
     }
-    // tier 1: per-tile working memory in HBM (L2-resident while hot); hashed table
+    // tiers 1 and 2: per-warp working memory in HBM, hashed table.  Tier 2 has 16x the capacities and catches the
+    // heavy tail of ball sizes at full occupancy.  Capacities are clamped to what the graph can ever need.
     {
-        TierCfg &t = c->tier[1];
-        t.caps = TileCaps{1u << 14, 32 - 14, 0, 1u << 13, 1u << 13, 1u << 12, 256, 1024};
-        t.ctas = c->smCount * occupancy(tw, false, 0);
-        t.ntiles = (long long)t.ctas * tilesPerCta;
+        const uint64_t n = (uint64_t)c->n, m = (uint64_t)c->m;
+        const uint32_t touchedMax = (uint32_t)n + (uint32_t)tw;                                // one entry per vertex
+        const uint32_t pushMax = (uint32_t)std::min<uint64_t>(4 * m + 64 + 2 * tw, 1u << 30); // one push per arc side
+        const uint32_t walkMax = (uint32_t)std::min<uint64_t>(2 * n + 2, 1u << 28);
+        for (int ti = 1; ti <= 2; ++ti) {
+            TierCfg &t = c->tier[ti];
+            const uint32_t lg = ti == 1 ? 13 : 17; // touched-entry capacity 2^lg
+            const uint32_t touched = std::min<uint32_t>(1u << lg, touchedMax);
+            const uint32_t tabLg = std::max<uint32_t>(log2ceil((uint64_t)2 * touched), 5);
+            t.caps = TileCaps{1u << tabLg, 32 - tabLg, 0, touched, std::min<uint32_t>(1u << lg, pushMax),
+                              std::min<uint32_t>(1u << (lg - 1), pushMax), std::min<uint32_t>(ti == 1 ? 256 : 4096, walkMax),
+                              ti == 1 ? 1024u : (1u << 14)};
+            t.ctas = c->smCount * occupancy(tw, false, 0);
+            t.ntiles = (long long)t.ctas * tilesPerCta;
+        }
     }
-    // tier 2: dense table indexed by vertex, capacities that cannot overflow before the graph is exhausted
+    // tier 3: dense table indexed by vertex, capacities that cannot overflow before the graph is exhausted
     {
-        TierCfg &t = c->tier[2];
+        TierCfg &t = c->tier[3];
         const uint64_t n = (uint64_t)c->n, m = (uint64_t)c->m;
         const uint32_t big = (uint32_t)std::min<uint64_t>(4 * m + 64 + 2 * tw, 1u << 30);
         t.caps = TileCaps{(uint32_t)n, 0, 1, (uint32_t)n + (uint32_t)tw, big, big,
@@ -266,12 +279,12 @@ int ensureTierScratch(smsgpu_ctx *ctx, int ti) {
     TierCfg &t = ctx->tier[ti];
     if (t.ready) return 0;
     const size_t tb = tileBytes(t.caps);
-    if (ti == 2) {
+    if (ti >= 2) { // large tiles: as many as fit in a quarter of the free memory, at most the resident warps
         size_t freeB = 0, totalB = 0;
         CU(cudaMemGetInfo(&freeB, &totalB));
         long long nt = (long long)((freeB / 4) / tb);
         const int tilesPerCta = 128 / ctx->tileWidth;
-        nt = std::min<long long>(nt, (long long)ctx->smCount * 2 * tilesPerCta);
+        nt = std::min<long long>(nt, ti == 2 ? t.ntiles : (long long)ctx->smCount * 2 * tilesPerCta);
         if (nt < 1) return fail(ctx, SMSGPU_ERR_NOMEM, "dense tier needs %zu bytes per tile, %zu free", tb, freeB);
         t.ctas = (int)std::max<long long>(1, nt / tilesPerCta);
         t.ntiles = (long long)t.ctas * tilesPerCta;
@@ -393,7 +406,7 @@ void smsgpu_destroy(smsgpu_ctx *ctx) {
     smsgpu_comm_destroy(ctx);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     DevBuf *dev[] = {&ctx->dRowptr, &ctx->dCol, &ctx->dEid, &ctx->dArcs, &ctx->dX, &ctx->dBl, &ctx->dSources,
-                     &ctx->tier[0].scratch, &ctx->tier[1].scratch, &ctx->tier[2].scratch, &ctx->rNode, &ctx->rEid,
+                     &ctx->tier[0].scratch, &ctx->tier[1].scratch, &ctx->tier[2].scratch, &ctx->tier[3].scratch, &ctx->rNode, &ctx->rEid,
                      &ctx->rStay, &ctx->rCutOff, &ctx->rCutLen, &ctx->rCutSrc, &ctx->rCutSeq, &ctx->rCutTier, &ctx->rValid,
                      &ctx->labSrc, &ctx->labNode, &ctx->labHops, &ctx->labDist, &ctx->srcTier, &ctx->srcArcs,
                      &ctx->srcSettled, &ctx->counters, &ctx->ovfA, &ctx->ovfB, &ctx->wCnode, &ctx->wCeid, &ctx->wCstay,
@@ -637,7 +650,7 @@ int smsgpu_separate_async(smsgpu_ctx *ctx, const smsgpu_params *params) {
         smsgpu_default_params(&P);
     if (P.max_intermediates < 0 || P.max_intermediates > 16) return fail(ctx, SMSGPU_ERR_ARG, "max_intermediates must be 0..16");
     if (P.tile_width != 0 && P.tile_width != 32) return fail(ctx, SMSGPU_ERR_ARG, "tile_width must be 0 or 32");
-    if (P.start_tier < 0 || P.start_tier > 2) return fail(ctx, SMSGPU_ERR_ARG, "start_tier must be 0..2");
+    if (P.start_tier < 0 || P.start_tier >= kNumTiers) return fail(ctx, SMSGPU_ERR_ARG, "start_tier must be 0..3");
     CU(cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->stream;
     if (P.tile_width != 0 && P.tile_width != ctx->tileWidth) {
@@ -732,9 +745,9 @@ int smsgpu_separate_async(smsgpu_ctx *ctx, const smsgpu_params *params) {
         long long nwork = nsrc;
         const int32_t *worklist = nullptr;
         int32_t *ovfBufs[2] = {ctx->ovfA.as<int32_t>(), ctx->ovfB.as<int32_t>()};
-        long long done[3] = {0, 0, 0};
+        long long done[kNumTiers] = {0, 0, 0, 0};
         long long prevRun = 0;
-        for (int ti = P.start_tier; ti < 3 && nwork > 0; ++ti) {
+        for (int ti = P.start_tier; ti < kNumTiers && nwork > 0; ++ti) {
             if (int rc = ensureTierScratch(ctx, ti)) return rc;
             const int which = ti & 1;
             SP.tier = ti;
@@ -780,7 +793,7 @@ int smsgpu_separate_async(smsgpu_ctx *ctx, const smsgpu_params *params) {
         ctx->stats.settled = (long long)hc[3];
         ctx->stats.raw_walks = rawCuts;
         ctx->nLabels = nlab;
-        for (int k = 0; k < 3; ++k) ctx->stats.tier_sources[k] = done[k];
+        for (int k = 0; k < kNumTiers; ++k) ctx->stats.tier_sources[k] = done[k];
         break;
     }
     CU(cudaEventRecord(ctx->ev[2], st));

@@ -39,7 +39,7 @@ def test_library_exports_every_declared_symbol(lib):
 
 def test_abi_version_and_default_params(lib):
     from sms_b200 import capi
-    assert lib.smsgpu_abi_version() == 1
+    assert lib.smsgpu_abi_version() == 2
     p = capi.Params()
     lib.smsgpu_default_params(C.byref(p))
     assert p.max_intermediates == 10 and p.best_dist_init == 1.0 - 1e-6 and p.dedup == 1
