@@ -1,0 +1,97 @@
+// Headless driver of the cycleparity handler (sms_b200/host/conshdlr_oscw.cpp) over the recording SCIP fake.
+//   conshdlr_driver <instance.txt> <mode>
+// instance.txt:  n m root nfixed sepacutpool / m lines "u v" in addEdge order / m lines x* by edge id / nfixed vertex ids
+// mode: sepalp | enfolp | sepasol | check | lock
+// Prints one line per row SCIP received: "<pool|lp> <name> <rhs> <len> eid:coef ..." and "result <code>".
+// Exit code 3: the handler could not be constructed (e.g. no CUDA device -- there is no CPU fallback).
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+#include <iostream>
+#include <stdexcept>
+
+#include "sms/conshdlr/conshdlr_oscw.hpp"
+#include "sms/probdata/mc_rooted.hpp"
+
+int main(int argc, char **argv) {
+    if (argc < 3) return 2;
+    std::ifstream in(argv[1]);
+    const std::string mode = argv[2];
+    long n, m, root, nfixed, cutpool;
+    in >> n >> m >> root >> nfixed >> cutpool;
+    NetworKit::Graph g(n);
+    for (long e = 0; e < m; ++e) {
+        long u, v;
+        in >> u >> v;
+        g.addEdge(u, v);
+    }
+    g.indexEdges();
+    Scip scip;
+    ProbDataRootedMc prob(&scip, &g, root);
+    scip.probdata = &prob;
+    scip.lpsol.assign(m + n, 0.);
+    for (long e = 0; e < m; ++e) in >> scip.lpsol[e];
+    for (long k = 0; k < nfixed; ++k) {
+        long u;
+        in >> u;
+        prob.nodeToVar(u)->lbLocal = prob.nodeToVar(u)->ubLocal = 1.;
+    }
+    sms::ConshdlrOscw *h = nullptr;
+    try {
+        h = new sms::ConshdlrOscw(&scip, &g);
+    } catch (const std::exception &e) {
+        std::fprintf(stderr, "handler construction failed: %s\n", e.what());
+        return 3;
+    }
+    if (SCIPincludeObjConshdlr(&scip, h, TRUE) != SCIP_OKAY) return 4;
+    *scip.boolParams.at("constraints/cycleparity/sepacutpool") = cutpool ? TRUE : FALSE;
+    SCIP_CONS *cons = nullptr;
+    if (sms::SCIPcreateConsBasicOddCyclesFast(&scip, &cons, "Odd Cycles", &g) != SCIP_OKAY) return 5;
+    SCIP_CONSHDLR *ch = SCIPfindConshdlr(&scip, "cycleparity");
+    SCIP_RESULT result = SCIP_DIDNOTRUN;
+    SCIP_RETCODE rc = SCIP_OKAY;
+    SCIP_Sol sol{scip.lpsol};
+    if (mode == "sepalp")
+        rc = h->scip_sepalp(&scip, ch, &cons, 1, 1, &result);
+    else if (mode == "enfolp")
+        rc = h->scip_enfolp(&scip, ch, &cons, 1, 1, FALSE, &result);
+    else if (mode == "sepasol")
+        rc = h->scip_sepasol(&scip, ch, &cons, 1, 1, &sol, &result);
+    else if (mode == "check")
+        rc = h->scip_check(&scip, ch, &cons, 1, &sol, TRUE, TRUE, FALSE, FALSE, &result);
+    else if (mode == "lock") {
+        rc = h->scip_lock(&scip, ch, cons, SCIP_LOCKTYPE_MODEL, 1, 0);
+        long locks = 0;
+        for (long e = 0; e < m; ++e) locks += prob.edgeIdToVar(e)->nlocksdown + prob.edgeIdToVar(e)->nlocksup;
+        std::printf("locks %ld\n", locks);
+    } else if (mode == "enfops") {
+        try {
+            h->scip_enfops(&scip, ch, &cons, 1, 1, FALSE, FALSE, &result);
+        } catch (const std::runtime_error &e) {
+            std::printf("threw %s\n", e.what());
+        }
+    } else if (mode == "clone") {
+        SCIP_Bool valid = FALSE;
+        auto *c = h->clone(&scip, &valid);
+        std::printf("clone %s valid %u\n", c ? "ok" : "null", valid);
+        delete c;
+    }
+    if (rc != SCIP_OKAY) {
+        std::printf("retcode %d\n", (int)rc);
+        return 6;
+    }
+    auto dump = [](const char *where, const std::vector<SCIP_ROW> &rows) {
+        for (const auto &r : rows) {
+            std::printf("%s %s %.17g %zu", where, r.name.c_str(), r.rhs, r.terms.size());
+            for (const auto &t : r.terms) std::printf(" %d:%g", t.first->index, t.second);
+            std::printf(" | lhs %g flags %u%u%u\n", r.lhs, r.local, r.modifiable, r.removable);
+        }
+    };
+    dump("pool", scip.poolCuts);
+    dump("lp", scip.lpRows);
+    std::printf("result %d rows_created %ld rows_released %ld addvar %ld cyclelen %llu\n", (int)result, scip.nRowsCreated,
+                scip.nRowsReleased, scip.nAddVar, (unsigned long long)h->totalConstructedCycleLength());
+    SCIPreleaseCons(&scip, &cons);
+    delete h;
+    return 0;
+}
