@@ -3,6 +3,7 @@
 //   ocwSearchKernel  (K2-K4)   persistent tiles pulling sources from an atomic cursor
 //   initTablesKernel           one-time clearing of the HBM label tables of tiers 1 / 2
 #pragma once
+#include "ocw_search_fast.cuh"
 #include "ocw_walks.cuh"
 
 namespace smsgpu {
@@ -60,18 +61,24 @@ __global__ void initTablesKernel(unsigned char *scratch, const size_t tileStride
 }
 
 // ---- K2-K4 ---------------------------------------------------------------------------------------------------
-template <int TW, bool SMEM>
+template <int TW, bool SMEM, bool FAST>
 __global__ void __launch_bounds__(128) ocwSearchKernel(const GraphDev G, const SearchParams P, const RawOut R,
                                                         const TileCaps caps, unsigned char *scratch) {
     extern __shared__ __align__(32) unsigned char smem[];
     const Tile<TW> T;
     const int tilesPerCta = blockDim.x / TW;
     const int tileInCta = threadIdx.x / TW;
-    const size_t tb = tileBytes(caps);
+    const size_t tb = tileBytes(caps), hb = hotBytes(caps);
     TileMem M;
-    carveTileMem(M, SMEM ? smem + (size_t)tileInCta * tb
-                         : scratch + ((size_t)blockIdx.x * tilesPerCta + tileInCta) * tb,
-                 caps);
+    if (FAST) {
+        // working memory in HBM; the hot words (bucket counters, presence bitmap) in shared memory or behind the tile
+        unsigned char *tile = scratch + ((size_t)blockIdx.x * tilesPerCta + tileInCta) * (tb + (P.hotInSmem ? 0 : hb));
+        carveTileMem(M, tile, caps, P.hotInSmem ? smem + (size_t)tileInCta * hb : tile + tb);
+    } else {
+        carveTileMem(M, SMEM ? smem + (size_t)tileInCta * tb
+                             : scratch + ((size_t)blockIdx.x * tilesPerCta + tileInCta) * tb,
+                     caps);
+    }
     if (SMEM) {
         for (uint32_t i = T.lane; i < caps.tabCap; i += TW) storeEntry(&M.tab[i], emptyEntry());
         T.sync();
@@ -94,7 +101,10 @@ __global__ void __launch_bounds__(128) ocwSearchKernel(const GraphDev G, const S
         if ((long long)(src >> 1) >= G.n) continue; // not a node of the double cover
 
         SrcState S;
-        searchSource<TW>(T, G, M, S, src, P.bestInit);
+        if (FAST)
+            searchSourceFast<TW>(T, G, M, S, src, P.bestInit, P.stampBase + (uint32_t)wi + 1u);
+        else
+            searchSource<TW>(T, G, M, S, src, P.bestInit);
         if (!S.overflow && S.histN > 0) {
             const int nsel = selectIntermediates<TW>(T, M, S, maxInter, sel);
             if (!S.overflow && T.lane == 0) {
@@ -117,8 +127,11 @@ __global__ void __launch_bounds__(128) ocwSearchKernel(const GraphDev G, const S
         }
         if (!S.overflow) {
             if (P.exportLabels) {
-                for (uint32_t i = T.lane; i < S.touchedN; i += TW) {
-                    const Entry e = loadEntry(&M.tab[M.touched[i]]);
+                // every label the search kept: the touched list (heap engine) / the occupied slots (fast engine)
+                const uint32_t nscan = FAST ? caps.tabCap : S.touchedN;
+                for (uint32_t i = T.lane; i < nscan; i += TW) {
+                    if (FAST && !((M.bm[i >> 5] >> (i & 31)) & 1u)) continue;
+                    const Entry e = loadEntry(&M.tab[FAST ? i : M.touched[i]]);
 #pragma unroll
                     for (int sd = 0; sd < 2; ++sd) {
                         const double d = sd ? e.d1 : e.d0;
@@ -147,10 +160,12 @@ __global__ void __launch_bounds__(128) ocwSearchKernel(const GraphDev G, const S
             const unsigned long long k = atomicAdd(P.ovfCount, 1ull);
             P.ovfList[k] = srcIdx;
         }
-        // leave the table clean for the next source
+        // leave the table clean for the next source (the fast engine resets its bitmap when a source starts)
         T.sync();
-        for (uint32_t i = T.lane; i < S.touchedN; i += TW) storeEntry(&M.tab[M.touched[i]], emptyEntry());
-        T.sync();
+        if (!FAST) {
+            for (uint32_t i = T.lane; i < S.touchedN; i += TW) storeEntry(&M.tab[M.touched[i]], emptyEntry());
+            T.sync();
+        }
     }
     if (T.lane == 0 && accSources) {
         atomicAdd(&R.counters[2], (unsigned long long)accArcs);

@@ -78,10 +78,21 @@ struct TileMem {
     int32_t *covered;
     TileCaps caps;
     uint32_t tabMask;
+    // fast engine only (null / 0 in the heap engine)
+    uint2 *pq;       // [slot*2 + side] {predecessor doubled id, queue position or kNoQpos}; aliases pred
+    uint32_t *cl;    // bucket counters, two buckets per word: byte 0/2 = appended, byte 1/3 = live
+    uint32_t *bm;    // presence bitmap of the label table, one bit per slot
 };
 
-__device__ inline void carveTileMem(TileMem &M, unsigned char *base, const TileCaps &c) {
+__device__ inline void carveTileMem(TileMem &M, unsigned char *base, const TileCaps &c, unsigned char *hot = nullptr) {
     M.caps = c;
+    M.pq = nullptr;
+    M.cl = nullptr;
+    M.bm = nullptr;
+    if (c.nbuckets) {
+        M.cl = reinterpret_cast<uint32_t *>(hot);
+        M.bm = reinterpret_cast<uint32_t *>(hot + (size_t)c.nbuckets * 2);
+    }
     M.tabMask = c.tabCap - 1;
     unsigned char *p = base;
     M.tab = reinterpret_cast<Entry *>(p);
@@ -91,7 +102,8 @@ __device__ inline void carveTileMem(TileMem &M, unsigned char *base, const TileC
     M.plen = reinterpret_cast<double *>(p);
     p += (size_t)(2 * c.walkCap + 2) * sizeof(double);
     M.pred = reinterpret_cast<uint32_t *>(p);
-    p += (size_t)c.tabCap * 2 * sizeof(uint32_t);
+    if (c.nbuckets) M.pq = reinterpret_cast<uint2 *>(p); // plen above keeps this 8-byte aligned
+    p += (size_t)c.tabCap * 2 * sizeof(uint32_t) * (c.nbuckets ? 2 : 1);
     M.touched = reinterpret_cast<uint32_t *>(p);
     p += (size_t)c.touchedCap * sizeof(uint32_t);
     M.hist = reinterpret_cast<uint32_t *>(p);
@@ -144,6 +156,13 @@ __device__ __forceinline__ uint32_t homeSlot(const TileMem &M, uint32_t v) {
 // slot of original vertex v, or -1
 __device__ __forceinline__ int findSlot(const TileMem &M, uint32_t v) {
     uint32_t s = homeSlot(M, v);
+    if (M.bm) { // fast engine: a slot is occupied iff its bit is set; entries of free slots hold garbage
+        while (true) {
+            if (!((M.bm[s >> 5] >> (s & 31)) & 1u)) return -1;
+            if (M.tab[s].key == v) return (int)s;
+            s = (s + 1) & M.tabMask;
+        }
+    }
     SMS_CHK(s < M.caps.tabCap);
 #ifdef SMSGPU_DEBUG_CHECKS
     uint32_t probes = 0;
@@ -184,6 +203,10 @@ __device__ __forceinline__ int findOrInsertSlot(const TileMem &M, uint32_t v, bo
 __device__ __forceinline__ bool keyLess(unsigned long long ahi, unsigned long long alo, unsigned long long bhi,
                                         unsigned long long blo) {
     return ahi < bhi || (ahi == bhi && alo < blo);
+}
+
+__device__ __forceinline__ uint32_t predOf(const TileMem &M, int slot, uint32_t side) {
+    return M.pq ? M.pq[2 * slot + side].x : M.pred[2 * slot + side];
 }
 
 // ---- TW-ary implicit heap, tile-cooperative ----------------------------------------------------------------

@@ -71,13 +71,17 @@ struct TileCaps {
     uint32_t histCap;    // intermediate-vertex history entries
     uint32_t walkCap;    // max edges of one path / walk
     uint32_t chordCap;   // max good chords of one cycle
+    // "fast" engine (tiers 1 and 2, ocw_search_fast.cuh): monotone bucket queue instead of the heap and a
+    // presence bitmap that arbitrates the label table.  nbuckets == 0 selects the heap engine.
+    uint32_t nbuckets;   // buckets over [0, bestInit / 2]; heapCap == nbuckets * bucketCap
+    uint32_t bucketCap;  // entries per bucket (<= 32: one coalesced load per pop)
 };
 
 // bytes of one tile's working memory
 __host__ __device__ inline size_t tileBytes(const TileCaps &c) {
     size_t b = 0;
     b += (size_t)c.tabCap * sizeof(Entry);         // table
-    b += (size_t)c.tabCap * 2 * sizeof(uint32_t);  // pred per (slot, side)
+    b += (size_t)c.tabCap * 2 * sizeof(uint32_t) * (c.nbuckets ? 2 : 1); // pred (+ queue position) per (slot, side)
     b += (size_t)c.touchedCap * sizeof(uint32_t);  // touched slots
     b += (size_t)c.heapCap * sizeof(HeapEnt);      // queue (re-used as sort scratch after the search)
     b += (size_t)c.histCap * sizeof(uint32_t);     // history of intermediates
@@ -87,6 +91,13 @@ __host__ __device__ inline size_t tileBytes(const TileCaps &c) {
     b += (size_t)c.chordCap * 4 * sizeof(int32_t);     // chords
     b += (size_t)c.chordCap * 0 + (size_t)(4 * c.walkCap + 8) * sizeof(int32_t); // covered list
     return (b + 31) & ~(size_t)31;
+}
+
+// bytes of the fast engine's hot words of one tile: bucket counters (2 bytes per bucket) + table presence bitmap.
+// Shared memory in tier 1, HBM (L2 resident) in tier 2.
+__host__ __device__ inline size_t hotBytes(const TileCaps &c) {
+    if (!c.nbuckets) return 0;
+    return (((size_t)c.nbuckets * 2 + (size_t)c.tabCap / 8) + 31) & ~(size_t)31;
 }
 
 // Raw (pre-dedup) output arena, filled by the search kernel with atomic bump allocation.
@@ -124,6 +135,8 @@ struct SearchParams {
     int32_t tier;
     int32_t exportLabels;
     int32_t debugFlags;     // bit 0: only the first tile of every warp works (debugging aid)
+    uint32_t stampBase;     // fast engine: entry stamp of work item wi is stampBase + wi + 1 (unique per scratch)
+    int32_t hotInSmem;      // fast engine: bucket counters + presence bitmap in shared memory (tier 1) or HBM (tier 2)
 };
 
 } // namespace smsgpu

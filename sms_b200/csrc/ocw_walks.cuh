@@ -105,7 +105,7 @@ __device__ inline int tracePath(const TileMem &M, uint32_t t, uint32_t src, int3
         const int slot = findSlot(M, cur >> 1);
         SMS_CHK(slot >= 0);
         SMS_CHK(((cur & 1u) ? M.tab[slot].d1 : M.tab[slot].d0) < kUnlabelled);
-        cur = M.pred[2 * slot + (cur & 1u)];
+        cur = predOf(M, slot, cur & 1u);
         p[++len] = (int32_t)cur;
     }
     return len;

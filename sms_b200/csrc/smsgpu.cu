@@ -79,7 +79,9 @@ struct TierCfg {
     TileCaps caps{};
     long long ntiles = 0;   // tiles that own HBM working memory (tiers 1, 2)
     int ctas = 0;           // grid size
-    size_t smemBytes = 0;   // tier 0
+    size_t smemBytes = 0;   // dynamic shared memory per CTA (tier 0: whole tiles, tier 1: hot words)
+    bool hotInSmem = false; // fast engine: where the bucket counters and the presence bitmap live
+    uint64_t stampNext = 0; // fast engine: stamps handed out so far for this scratch (ocw_search_fast.cuh)
     DevBuf scratch;
     bool ready = false;
 };
@@ -200,37 +202,37 @@ uint32_t log2ceil(uint64_t v) {
 // =====================================================================================================================
 namespace {
 
-template <int TW, bool SMEM>
+// Three instantiations of the search kernel (one source per WARP; sub-warp tiles were measured to corrupt each
+// other on sm_100a, DESIGN.md "tile width"):
+//   <32, true,  false>  tier 0: heap engine, everything in shared memory
+//   <32, false, true >  tiers 1, 2: fast engine (bucket queue + presence bitmap), working memory in HBM
+//   <32, false, false>  tier 3: heap engine on a dense table in HBM
+template <bool SMEM, bool FAST>
 cudaError_t launchSearchT(smsgpu_ctx *c, const TierCfg &t, const GraphDev &G, const SearchParams &P, const RawOut &R) {
-    auto kern = ocwSearchKernel<TW, SMEM>;
-    if (SMEM) {
+    auto kern = ocwSearchKernel<32, SMEM, FAST>;
+    if (t.smemBytes) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t.smemBytes);
         if (e != cudaSuccess) return e;
     }
-    kern<<<t.ctas, 128, SMEM ? t.smemBytes : 0, c->stream>>>(G, P, R, t.caps, t.scratch.as<unsigned char>());
+    kern<<<t.ctas, 128, t.smemBytes, c->stream>>>(G, P, R, t.caps, t.scratch.as<unsigned char>());
     return cudaGetLastError();
 }
 cudaError_t launchSearch(smsgpu_ctx *c, int tierIdx, const GraphDev &G, const SearchParams &P, const RawOut &R) {
     const TierCfg &t = c->tier[tierIdx];
-    const bool smem = tierIdx == 0;
-    // One source per WARP.  Sub-warp tiles (8 / 16 lanes, several sources per warp in independent control
-    // flow) were measured to corrupt each other on sm_100a (DESIGN.md "tile width") and are not instantiated.
-    return smem ? launchSearchT<32, true>(c, t, G, P, R) : launchSearchT<32, false>(c, t, G, P, R);
+    if (tierIdx == 0) return launchSearchT<true, false>(c, t, G, P, R);
+    if (t.caps.nbuckets) return launchSearchT<false, true>(c, t, G, P, R);
+    return launchSearchT<false, false>(c, t, G, P, R);
 }
-template <int TW, bool SMEM>
+template <bool SMEM, bool FAST>
 int occupancyT(size_t smemBytes) {
     int nb = 0;
-    auto kern = ocwSearchKernel<TW, SMEM>;
-    if (SMEM) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, 128, SMEM ? smemBytes : 0) != cudaSuccess) {
+    auto kern = ocwSearchKernel<32, SMEM, FAST>;
+    if (smemBytes) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, 128, smemBytes) != cudaSuccess) {
         (void)cudaGetLastError();
         nb = 1;
     }
     return std::max(nb, 1);
-}
-int occupancy(int tw, bool smem, size_t smemBytes) {
-    (void)tw;
-    return smem ? occupancyT<32, true>(smemBytes) : occupancyT<32, false>(0);
 }
 
 // Working-memory capacities of the three tiers (DESIGN.md "tiers").
@@ -242,7 +244,7 @@ void configureTiers(smsgpu_ctx *c) {
         TierCfg &t = c->tier[0];
         t.caps = TileCaps{128, 32 - 7, 0, 64 + (uint32_t)tw, 64 + 2 * (uint32_t)tw, 32, 16, 16};
         t.smemBytes = tileBytes(t.caps) * tilesPerCta;
-        t.ctas = c->smCount * occupancy(tw, true, t.smemBytes);
+        t.ctas = c->smCount * occupancyT<true, false>(t.smemBytes);
         t.ready = true;
     }
     // tiers 1 and 2: per-warp working memory in HBM, hashed table.  Tier 2 has 16x the capacities and catches the
@@ -257,10 +259,15 @@ void configureTiers(smsgpu_ctx *c) {
             const uint32_t lg = ti == 1 ? 13 : 17; // touched-entry capacity 2^lg
             const uint32_t touched = std::min<uint32_t>(1u << lg, touchedMax);
             const uint32_t tabLg = std::max<uint32_t>(log2ceil((uint64_t)2 * touched), 5);
-            t.caps = TileCaps{1u << tabLg, 32 - tabLg, 0, touched, std::min<uint32_t>(1u << lg, pushMax),
+            // fast engine: bucket queue of nbuckets x 32 keys; the hot words (2 B per bucket + 1 bit per table slot)
+            // live in shared memory in tier 1 (10 KB per warp) and behind the tile in HBM in tier 2
+            const uint32_t nb = ti == 1 ? 4096u : 16384u, bc = 32u;
+            t.caps = TileCaps{1u << tabLg, 32 - tabLg, 0, touched, nb * bc,
                               std::min<uint32_t>(1u << (lg - 1), pushMax), std::min<uint32_t>(ti == 1 ? 256 : 4096, walkMax),
-                              ti == 1 ? 1024u : (1u << 14)};
-            t.ctas = c->smCount * occupancy(tw, false, 0);
+                              ti == 1 ? 1024u : (1u << 14), nb, bc};
+            t.hotInSmem = ti == 1;
+            t.smemBytes = t.hotInSmem ? hotBytes(t.caps) * tilesPerCta : 0;
+            t.ctas = c->smCount * occupancyT<false, true>(t.smemBytes);
             t.ntiles = (long long)t.ctas * tilesPerCta;
         }
     }
@@ -278,7 +285,7 @@ void configureTiers(smsgpu_ctx *c) {
 int ensureTierScratch(smsgpu_ctx *ctx, int ti) {
     TierCfg &t = ctx->tier[ti];
     if (t.ready) return 0;
-    const size_t tb = tileBytes(t.caps);
+    const size_t tb = tileBytes(t.caps) + (t.hotInSmem ? 0 : hotBytes(t.caps)); // tile stride
     if (ti >= 2) { // large tiles: as many as fit in a quarter of the free memory, at most the resident warps
         size_t freeB = 0, totalB = 0;
         CU(cudaMemGetInfo(&freeB, &totalB));
@@ -292,6 +299,7 @@ int ensureTierScratch(smsgpu_ctx *ctx, int ti) {
     CU(t.scratch.ensure((size_t)t.ntiles * tb));
     initTablesKernel<<<ctx->smCount * 8, 256, 0, ctx->stream>>>(t.scratch.as<unsigned char>(), tb, t.ntiles, t.caps.tabCap);
     CU(cudaGetLastError());
+    t.stampNext = 0;
     t.ready = true;
     return 0;
 }
@@ -757,6 +765,18 @@ int smsgpu_separate_async(smsgpu_ctx *ctx, const smsgpu_params *params) {
             SP.ovfCount = dc + 9 + which;
             CU(cudaMemsetAsync(dc + 8, 0, 8, st));
             CU(cudaMemsetAsync(dc + 9 + which, 0, 8, st));
+            if (ctx->tier[ti].caps.nbuckets) {
+                TierCfg &tc = ctx->tier[ti];
+                if (tc.stampNext + (uint64_t)nwork + 2 >= (1ull << 32)) { // stamps exhausted: forget every old entry
+                    const size_t stride = tileBytes(tc.caps) + (tc.hotInSmem ? 0 : hotBytes(tc.caps));
+                    initTablesKernel<<<ctx->smCount * 8, 256, 0, st>>>(tc.scratch.as<unsigned char>(), stride, tc.ntiles, tc.caps.tabCap);
+                    CU(cudaGetLastError());
+                    tc.stampNext = 0;
+                }
+                SP.stampBase = (uint32_t)tc.stampNext;
+                SP.hotInSmem = tc.hotInSmem ? 1 : 0;
+                tc.stampNext += (uint64_t)nwork;
+            }
             CU(launchSearch(ctx, ti, G, SP, R));
             ctx->stats.search_launches += 1;
             ctx->stats.total_launches += 1;
