@@ -61,8 +61,11 @@ __global__ void initTablesKernel(unsigned char *scratch, const size_t tileStride
 }
 
 // ---- K2-K4 ---------------------------------------------------------------------------------------------------
+#ifndef SMSGPU_FAST_MIN_CTAS
+#define SMSGPU_FAST_MIN_CTAS 5
+#endif
 template <int TW, bool SMEM, bool FAST>
-__global__ void __launch_bounds__(128) ocwSearchKernel(const GraphDev G, const SearchParams P, const RawOut R,
+__global__ void __launch_bounds__(128, FAST ? SMSGPU_FAST_MIN_CTAS : 1) ocwSearchKernel(const GraphDev G, const SearchParams P, const RawOut R,
                                                         const TileCaps caps, unsigned char *scratch) {
     extern __shared__ __align__(32) unsigned char smem[];
     const Tile<TW> T;

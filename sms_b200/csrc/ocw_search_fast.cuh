@@ -27,10 +27,12 @@ constexpr unsigned long long kDeadKey = ~0ull;
 // bucket counters: two buckets per 32-bit word; per bucket one byte "appended" and one byte "live"
 __device__ __forceinline__ uint32_t clShift(uint32_t b) { return (b & 1u) * 16u; }
 
-__device__ __forceinline__ void killKey(const TileMem &M, uint32_t qpos) {
+// returns the bucket the key sat in
+__device__ __forceinline__ uint32_t killKey(const TileMem &M, uint32_t qpos) {
     M.heap[qpos].hi = kDeadKey;
     const uint32_t b = qpos / M.caps.bucketCap;
     atomicSub(&M.cl[b >> 1], 0x0100u << clShift(b));
+    return b;
 }
 
 template <int TW>
@@ -78,34 +80,54 @@ __device__ void searchSourceFast(const Tile<TW> &T, const GraphDev &G, TileMem &
     S.touchedN = 1;
     T.sync();
 
-    uint32_t cb = 0; // first bucket that may hold a live key; extraction keys never decrease
+    // The keys of the current bucket stay in registers (lane i holds position i) together with the row range of
+    // their vertices, so an extraction normally costs four REDUX steps and no memory access; the bucket is
+    // (re)loaded only when it is exhausted or a step appended to / killed a key in it (rare: that needs an arc
+    // lighter than one bucket width).  Loading a bucket also prefetches the arc rows of all its keys into L2.
+    uint32_t cb = 0;       // current bucket; extraction keys never decrease
+    bool needLoad = true;  // registers do not mirror bucket cb
+    uint32_t liveRegs = 0; // live keys among the registers
+    unsigned long long khi = kDeadKey, klo = kDeadKey;
+    long long rowB = 0, rowE = 0;
     while (true) {
-        // ---- first non-empty bucket ------------------------------------------------------------------------------
-        uint32_t b = NB, cnt = 0;
-        for (uint32_t base = cb >> 1; base < nclWords; base += TW) {
-            const uint32_t wi = base + T.lane;
-            const uint32_t word = wi < nclWords ? M.cl[wi] : 0u;
-            uint32_t live = word & 0xFF00FF00u;
-            if (wi == (cb >> 1) && (cb & 1u)) live &= 0xFF000000u;
-            const unsigned bal = T.ballot(live != 0u);
-            if (bal) {
-                const int l = __ffs(bal) - 1;
-                const uint32_t lw = T.shfl(live, l), ww = T.shfl(word, l);
-                const uint32_t odd = (lw & 0x0000FF00u) ? 0u : 1u;
-                b = 2 * (base + l) + odd;
-                cnt = (ww >> (odd * 16u)) & 0xFFu;
-                break;
+        if (needLoad) {
+            // ---- first non-empty bucket at or after cb ------------------------------------------------------------
+            uint32_t b = NB, cnt = 0;
+            for (uint32_t base = cb >> 1; base < nclWords; base += TW) {
+                const uint32_t wi = base + T.lane;
+                const uint32_t word = wi < nclWords ? M.cl[wi] : 0u;
+                uint32_t live = word & 0xFF00FF00u;
+                if (wi == (cb >> 1) && (cb & 1u)) live &= 0xFF000000u;
+                const unsigned bal = T.ballot(live != 0u);
+                if (bal) {
+                    const int l = __ffs(bal) - 1;
+                    const uint32_t lw = T.shfl(live, l), ww = T.shfl(word, l);
+                    const uint32_t odd = (lw & 0x0000FF00u) ? 0u : 1u;
+                    b = 2 * (base + l) + odd;
+                    cnt = (ww >> (odd * 16u)) & 0xFFu;
+                    break;
+                }
             }
+            if (b >= NB) break; // queue empty
+            cb = b;
+            khi = kDeadKey;
+            klo = kDeadKey;
+            if ((uint32_t)T.lane < cnt) {
+                const HeapEnt k = M.heap[b * C + T.lane];
+                khi = k.hi;
+                klo = k.lo;
+            }
+            if (khi != kDeadKey) {
+                const uint32_t v = (uint32_t)klo >> 1;
+                rowB = G.rowptr[v];
+                rowE = G.rowptr[v + 1];
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(G.arcs + rowB));
+            }
+            liveRegs = __popc(T.ballot(khi != kDeadKey));
+            SMS_CHK(liveRegs > 0);
+            needLoad = false;
         }
-        if (b >= NB) break; // queue empty
-        cb = b;
-        // ---- minimum key of the bucket: (dist, hops, id) lexicographic, tombstones = all ones -----------------------
-        unsigned long long khi = kDeadKey, klo = kDeadKey;
-        if ((uint32_t)T.lane < cnt) {
-            const HeapEnt k = M.heap[b * C + T.lane];
-            khi = k.hi;
-            klo = k.lo;
-        }
+        // ---- minimum key of the bucket: (dist, hops, id) lexicographic, tombstones = all ones -------------------------
         const uint32_t k0 = (uint32_t)(khi >> 32), k1 = (uint32_t)khi, k2 = (uint32_t)(klo >> 32), k3 = (uint32_t)klo;
         const uint32_t m0 = __reduce_min_sync(T.mask, k0);
         bool mine = k0 == m0;
@@ -120,14 +142,20 @@ __device__ void searchSourceFast(const Tile<TW> &T, const GraphDev &G, TileMem &
         const double dc = __longlong_as_double((long long)(((unsigned long long)m0 << 32) | m1));
         // loop condition of ocw_seperator.cpp:88-90
         if (cur == target || 2 * dc > S.best) break;
-        if (mine) M.heap[b * C + T.lane].hi = kDeadKey; // extract_top: the key becomes a tombstone
-        if (T.lane == 0) atomicSub(&M.cl[b >> 1], 0x0100u << clShift(b));
+        const int wl = __ffs(T.ballot(mine)) - 1;
+        const long long rb = T.shfl(rowB, wl), re = T.shfl(rowE, wl);
+        if (mine) { // extract_top: the key becomes a tombstone
+            M.heap[cb * C + T.lane].hi = kDeadKey;
+            khi = kDeadKey;
+            atomicSub(&M.cl[cb >> 1], 0x0100u << clShift(cb));
+        }
+        liveRegs--;
+        bool dirty = false; // a key was appended to / killed in bucket cb during this step
         T.sync();
         S.settled++;
         const uint32_t side = cur & 1u;
         const uint32_t u = cur >> 1;
         SMS_CHK((long long)u < G.n);
-        const long long rb = G.rowptr[u], re = G.rowptr[u + 1];
         const uint32_t hNew = hc + 1;
 
         for (long long base = rb; base < re; base += TW) {
@@ -235,17 +263,19 @@ __device__ void searchSourceFast(const Tile<TW> &T, const GraphDev &G, TileMem &
                         // a superseded key leaves the queue now (the heap engine discards it when it surfaces)
                         if (k ? hadB2 : hadA) {
                             const uint32_t oldq = M.pq[2 * slot + sd].y;
-                            if (oldq != kNoQpos) killKey(M, oldq);
+                            if (oldq != kNoQpos) dirty |= killKey(M, oldq) == cb;
                         }
                         uint32_t qpos = kNoQpos;
                         if (2 * d <= best0) { // queue admission: only nodes that can still be extracted
                             const uint32_t bk = min((uint32_t)(d * bscale), NB - 1);
                             const uint32_t sh = clShift(bk);
                             const uint32_t pos = (atomicAdd(&M.cl[bk >> 1], 0x0101u << sh) >> sh) & 0xFFu;
+                            dirty |= bk == cb;
                             if (pos >= C) {
                                 ovf = true;
                             } else {
                                 qpos = bk * C + pos;
+                                asm volatile("prefetch.global.L2 [%0];" ::"l"(G.rowptr + nbr)); // read when its bucket loads
                                 HeapEnt q;
                                 q.hi = (unsigned long long)__double_as_longlong(d);
                                 q.lo = ((unsigned long long)hNew << 32) | (2 * nbr + sd);
@@ -260,6 +290,7 @@ __device__ void searchSourceFast(const Tile<TW> &T, const GraphDev &G, TileMem &
                 S.overflow = 1;
                 return;
             }
+            if (T.ballot(dirty)) needLoad = true;
             // ---- replay of the record logic in adjacency order (:71-82) -------------------------------------------
             unsigned evm = T.ballot(evS || evX);
             while (evm) {
@@ -294,6 +325,7 @@ __device__ void searchSourceFast(const Tile<TW> &T, const GraphDev &G, TileMem &
             }
             T.sync(); // keys, labels and counters of this step are visible to the next extraction
         }
+        if (liveRegs == 0) needLoad = true;
     }
 }
 

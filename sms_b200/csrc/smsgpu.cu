@@ -16,6 +16,10 @@
 #include "ocw_kernels.cuh"
 #include "small_cycles.cuh"
 
+#ifndef SMSGPU_TIER1_BUCKETS
+#define SMSGPU_TIER1_BUCKETS 4096
+#endif
+
 using namespace smsgpu;
 
 namespace {
@@ -261,7 +265,7 @@ void configureTiers(smsgpu_ctx *c) {
             const uint32_t tabLg = std::max<uint32_t>(log2ceil((uint64_t)2 * touched), 5);
             // fast engine: bucket queue of nbuckets x 32 keys; the hot words (2 B per bucket + 1 bit per table slot)
             // live in shared memory in tier 1 (10 KB per warp) and behind the tile in HBM in tier 2
-            const uint32_t nb = ti == 1 ? 4096u : 16384u, bc = 32u;
+            const uint32_t nb = ti == 1 ? (uint32_t)SMSGPU_TIER1_BUCKETS : 16384u, bc = 32u;
             t.caps = TileCaps{1u << tabLg, 32 - tabLg, 0, touched, nb * bc,
                               std::min<uint32_t>(1u << (lg - 1), pushMax), std::min<uint32_t>(ti == 1 ? 256 : 4096, walkMax),
                               ti == 1 ? 1024u : (1u << 14), nb, bc};
