@@ -14,7 +14,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(CSRC, "libsmsgpu.so")
 LIB_DEBUG = os.path.join(CSRC, "libsmsgpu_dbg.so")  # -DSMSGPU_DEBUG_CHECKS: device asserts (SMSGPU_LIB selects it)
 SOURCES = ["smsgpu.cu"]
-HEADERS = ["ocw_types.cuh", "ocw_search.cuh", "ocw_walks.cuh", "ocw_kernels.cuh", "dedup_kernels.cuh",
+HEADERS = ["ocw_types.cuh", "ocw_search.cuh", "ocw_search_fast.cuh", "ocw_search_batch.cuh", "ocw_walks.cuh", "ocw_kernels.cuh", "dedup_kernels.cuh",
            "small_cycles.cuh", os.path.join("..", "..", "include", "smsgpu.h")]
 
 NVCC_FLAGS = ["-std=c++17", "-O3", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-shared",

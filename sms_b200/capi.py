@@ -73,7 +73,10 @@ class StatsStruct(C.Structure):
         ("ms_d2h", C.c_double),
         ("search_launches", C.c_int64),
         ("total_launches", C.c_int64),
-        ("reserved", C.c_int64 * 7),
+        ("fast_steps", C.c_int64),
+        ("fast_bucket_loads", C.c_int64),
+        ("ms_tier", C.c_double * 4),
+        ("reserved", C.c_int64 * 1),
     ]
 
 
@@ -251,8 +254,9 @@ class Context:
     def stats(self) -> dict:
         s = StatsStruct()
         self._check(self.lib.smsgpu_get_stats(self.h, C.byref(s)))
-        d = {k: getattr(s, k) for k, _ in StatsStruct._fields_ if k not in ("reserved", "tier_sources")}
+        d = {k: getattr(s, k) for k, _ in StatsStruct._fields_ if k not in ("reserved", "tier_sources", "ms_tier")}
         d["tier_sources"] = list(s.tier_sources)
+        d["ms_tier"] = [round(v, 4) for v in s.ms_tier]
         return d
 
     def labels(self):

@@ -3,7 +3,7 @@
 //   ocwSearchKernel  (K2-K4)   persistent tiles pulling sources from an atomic cursor
 //   initTablesKernel           one-time clearing of the HBM label tables of tiers 1 / 2
 #pragma once
-#include "ocw_search_fast.cuh"
+#include "ocw_search_batch.cuh"
 #include "ocw_walks.cuh"
 
 namespace smsgpu {
@@ -88,7 +88,7 @@ __global__ void __launch_bounds__(128, FAST ? SMSGPU_FAST_MIN_CTAS : 1) ocwSearc
     }
     if ((P.debugFlags & 1) && T.shift != 0) return;
     const long long total = P.worklist ? P.nwork : P.nsrc;
-    long long accArcs = 0, accSettled = 0, accSources = 0;
+    long long accArcs = 0, accSettled = 0, accSources = 0, accSteps = 0, accLoads = 0;
     uint32_t sel[16];
     const int maxInter = min(P.maxInter, 16);
 
@@ -105,7 +105,11 @@ __global__ void __launch_bounds__(128, FAST ? SMSGPU_FAST_MIN_CTAS : 1) ocwSearc
 
         SrcState S;
         if (FAST)
+#ifdef SMSGPU_BATCH // same-bucket batching: measured slower on the full 1M-source round (profiles/README.md)
+            searchSourceBatch<TW>(T, G, M, S, src, P.bestInit, P.stampBase + (uint32_t)wi + 1u);
+#else
             searchSourceFast<TW>(T, G, M, S, src, P.bestInit, P.stampBase + (uint32_t)wi + 1u);
+#endif
         else
             searchSource<TW>(T, G, M, S, src, P.bestInit);
         if (!S.overflow && S.histN > 0) {
@@ -158,6 +162,10 @@ __global__ void __launch_bounds__(128, FAST ? SMSGPU_FAST_MIN_CTAS : 1) ocwSearc
             }
             accArcs += S.arcs;
             accSettled += S.settled;
+            if (FAST) {
+                accSteps += S.steps;
+                accLoads += S.loads;
+            }
             accSources++;
         } else if (T.lane == 0) {
             const unsigned long long k = atomicAdd(P.ovfCount, 1ull);
@@ -174,6 +182,10 @@ __global__ void __launch_bounds__(128, FAST ? SMSGPU_FAST_MIN_CTAS : 1) ocwSearc
         atomicAdd(&R.counters[2], (unsigned long long)accArcs);
         atomicAdd(&R.counters[3], (unsigned long long)accSettled);
         atomicAdd(&R.counters[4], (unsigned long long)accSources);
+        if (FAST) {
+            atomicAdd(&R.counters[6], (unsigned long long)accSteps);
+            atomicAdd(&R.counters[7], (unsigned long long)accLoads);
+        }
     }
 }
 

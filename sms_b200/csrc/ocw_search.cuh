@@ -283,6 +283,7 @@ struct SrcState {
     double bestHop;    // bestHopDist (a double in the reference, ocw_seperator.cpp:52)
     uint32_t histN, heapN, touchedN;
     long long arcs, settled;
+    long long steps, loads; // extraction steps / bucket loads (fast engines; settled / steps = keys per step)
     int overflow;
 };
 

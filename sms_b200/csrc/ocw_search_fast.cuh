@@ -46,6 +46,8 @@ __device__ void searchSourceFast(const Tile<TW> &T, const GraphDev &G, TileMem &
     S.touchedN = 0;
     S.arcs = 0;
     S.settled = 0;
+    S.steps = 0;
+    S.loads = 0;
     S.overflow = 0;
     const uint32_t target = src ^ 1u;
     const uint32_t NB = M.caps.nbuckets, C = M.caps.bucketCap;

@@ -106,6 +106,7 @@ struct smsgpu_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev[8]{};
+    cudaEvent_t tierEv[2 * 4]{}; // start / end of each tier's search launch
     int smCount = 148;
     long long n = 0, m = 0;
     std::string err;
@@ -383,6 +384,7 @@ int smsgpu_create(smsgpu_ctx **out, int64_t n, int64_t m, const int64_t *rowptr,
     ctx->smCount = prop.multiProcessorCount;
     CUB(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
     for (auto &e : ctx->ev) CUB(cudaEventCreate(&e));
+    for (auto &e : ctx->tierEv) CUB(cudaEventCreate(&e));
     CUB(ctx->dRowptr.ensure((size_t)(n + 1) * sizeof(int64_t)));
     CUB(ctx->dCol.ensure((size_t)std::max<int64_t>(2 * m, 4) * sizeof(int32_t)));
     CUB(ctx->dEid.ensure((size_t)std::max<int64_t>(2 * m, 4) * sizeof(int32_t)));
@@ -442,6 +444,8 @@ void smsgpu_destroy(smsgpu_ctx *ctx) {
         for (auto *b : sc) b->release();
     }
     for (auto &e : ctx->ev)
+        if (e) cudaEventDestroy(e);
+    for (auto &e : ctx->tierEv)
         if (e) cudaEventDestroy(e);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -759,6 +763,7 @@ int smsgpu_separate_async(smsgpu_ctx *ctx, const smsgpu_params *params) {
         int32_t *ovfBufs[2] = {ctx->ovfA.as<int32_t>(), ctx->ovfB.as<int32_t>()};
         long long done[kNumTiers] = {0, 0, 0, 0};
         long long prevRun = 0;
+        bool tierRan[kNumTiers] = {false, false, false, false};
         for (int ti = P.start_tier; ti < kNumTiers && nwork > 0; ++ti) {
             if (int rc = ensureTierScratch(ctx, ti)) return rc;
             const int which = ti & 1;
@@ -781,7 +786,10 @@ int smsgpu_separate_async(smsgpu_ctx *ctx, const smsgpu_params *params) {
                 SP.hotInSmem = tc.hotInSmem ? 1 : 0;
                 tc.stampNext += (uint64_t)nwork;
             }
+            CU(cudaEventRecord(ctx->tierEv[2 * ti], st));
             CU(launchSearch(ctx, ti, G, SP, R));
+            CU(cudaEventRecord(ctx->tierEv[2 * ti + 1], st));
+            tierRan[ti] = true;
             ctx->stats.search_launches += 1;
             ctx->stats.total_launches += 1;
             CU(cudaMemcpyAsync(hc, dc, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
@@ -815,9 +823,16 @@ int smsgpu_separate_async(smsgpu_ctx *ctx, const smsgpu_params *params) {
         ctx->stats.sources_run = (long long)hc[4];
         ctx->stats.arcs_scanned = (long long)hc[2];
         ctx->stats.settled = (long long)hc[3];
+        ctx->stats.fast_steps = (long long)hc[6];
+        ctx->stats.fast_bucket_loads = (long long)hc[7];
         ctx->stats.raw_walks = rawCuts;
         ctx->nLabels = nlab;
-        for (int k = 0; k < kNumTiers; ++k) ctx->stats.tier_sources[k] = done[k];
+        for (int k = 0; k < kNumTiers; ++k) {
+            ctx->stats.tier_sources[k] = done[k];
+            float tms = 0;
+            ctx->stats.ms_tier[k] = 0.0;
+            if (tierRan[k] && cudaEventElapsedTime(&tms, ctx->tierEv[2 * k], ctx->tierEv[2 * k + 1]) == cudaSuccess) ctx->stats.ms_tier[k] = tms;
+        }
         break;
     }
     CU(cudaEventRecord(ctx->ev[2], st));
