@@ -5,6 +5,7 @@
 #pragma once
 #include "ocw_search_batch.cuh"
 #include "ocw_walks.cuh"
+#include "ocw_search_pairs.cuh"
 
 namespace smsgpu {
 

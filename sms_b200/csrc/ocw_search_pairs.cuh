@@ -1,0 +1,557 @@
+// "Pairs" engine of K2 (tier 1): TWO sources per warp, one per half-warp, advanced in LOCK STEP.
+//
+// Same search as searchSourceFast (ocw_search_fast.cuh) -- runDijsktra of the reference
+// (src/graph/ocw_seperator.cpp:37-112) in the canonical order (dist, hops, doubled id), event for event, with the
+// monotone bucket queue + tombstones and the shared-memory presence bitmap -- restructured around what the ncu
+// profiles of the one-source-per-warp engine showed (profiles/r01_fast2_*.md): ~15 of 32 lanes active (a settled
+// node has ~9 arcs), ~450 warp instructions and 3-4 dependent global loads per settled node, 20 sources in flight
+// per SM.  Here
+//   * a settled node's arcs are relaxed by the 16 lanes of a half-warp and the two halves of a warp work on two
+//     different sources with ONE instruction stream: every warp-level primitive is executed by all 32 lanes
+//     (ballot / shfl with the full mask, redux with the half's mask), the per-source control flow is predication
+//     and a small state machine (idle -> running -> finished), so issue slots per settled node halve and twice as
+//     many sources are in flight per resident warp;
+//   * queue entries carry the row (first arc, degree) of their vertex -- read from an 8-byte per-vertex record next
+//     to the arc, off the critical path -- so an extraction goes straight from the key to the arc load, and the
+//     arc row is prefetched into L2 when the key is pushed;
+//   * the bucket index is a monotone piecewise-linear 2^u map of the distance instead of a linear one: balls grow
+//     geometrically with the radius, the map keeps the number of keys per bucket roughly constant, so half the
+//     buckets (and shared memory) hold the same sources and a bucket never needs more than 16 slots;
+//   * one REDUX usually decides the minimum (the high words of the distances differ); the full 128-bit
+//     lexicographic reduction runs only when they tie.
+// When a source ends (target reached, radius exceeded, queue empty, or a capacity hit) the whole warp finishes it
+// with the 32-lane code shared with the other engines (selection of intermediates, walks, label export).
+// Distances, hops, predecessors, the record logic and therefore the walks are bit-identical to the other engines'
+// (tests/test_gpu_parity.py runs every engine against the oracle).
+#pragma once
+#include "ocw_search_fast.cuh"
+#include "ocw_walks.cuh"
+
+namespace smsgpu {
+
+struct PairsParams {
+    const uint2 *rowinfo; // [n] {first arc, degree} of every vertex (32-bit arc indices: 2m < 2^32)
+    float scaleU;         // bucket map: u = (float)dist * scaleU; 0 selects the linear map
+    float scaleB;         // bucket = (2^u - 1) * scaleB   (linear map: dist * scaleB)
+};
+
+// Monotone (non-decreasing in d) bucket index; every operation below is monotone for d >= 0.
+__device__ __forceinline__ uint32_t bucketOf(const double d, const float scaleU, const float scaleB, const uint32_t nbm1) {
+    const float f = __double2float_rn(d);
+    uint32_t b;
+    if (scaleU > 0.f) {
+        // piecewise-linear 2^u through the IEEE exponent field: bits = u * 2^23 + bias
+        const float y = __int_as_float(__float2int_rz(f * scaleU * 8388608.0f) + 0x3F800000);
+        b = __float2uint_rz((y - 1.0f) * scaleB);
+    } else {
+        b = __float2uint_rz(f * scaleB);
+    }
+    return min(b, nbm1);
+}
+
+// Everything after the search of one source, by all 32 lanes (same code path as ocwSearchKernel's tail).
+template <bool DUMMY>
+__device__ __noinline__ void finishSourcePairs(const GraphDev &G, const SearchParams &P, const RawOut &R, const TileCaps &caps,
+                                               unsigned char *tile, unsigned char *hot, SrcState &S, const uint32_t src,
+                                               const int32_t srcIdx, long long *acc) {
+    const Tile<32> T;
+    TileMem M;
+    carveTileMem(M, tile, caps, hot);
+    uint32_t sel[16];
+    const int maxInter = min(P.maxInter, 16);
+    if (!S.overflow && S.histN > 0) {
+        const int nsel = selectIntermediates<32>(T, M, S, maxInter, sel);
+        if (!S.overflow && T.lane == 0) {
+            Emitter E;
+            E.R = &R;
+            E.srcIdx = srcIdx;
+            E.seq = 0;
+            E.tier = P.tier;
+            for (int r = 0; r < nsel; ++r) {
+                const int W = buildWalk(M, sel[r], src);
+                if (W < 0) {
+                    S.overflow = 1;
+                    break;
+                }
+                simpleOddCyclesAndExtract(G, M, S, E, W);
+                if (S.overflow) break;
+            }
+        }
+        S.overflow = T.shfl(S.overflow, 0);
+    }
+    if (!S.overflow) {
+        if (P.exportLabels) {
+            for (uint32_t i = T.lane; i < caps.tabCap; i += 32) {
+                if (!((M.bm[i >> 5] >> (i & 31)) & 1u)) continue;
+                const Entry e = loadEntry(&M.tab[i]);
+#pragma unroll
+                for (int sd = 0; sd < 2; ++sd) {
+                    const double d = sd ? e.d1 : e.d0;
+                    if (d >= kUnlabelled) continue;
+                    const long long li = (long long)atomicAdd(&R.counters[5], 1ull);
+                    if (li < R.labCap) {
+                        R.labSrc[li] = srcIdx;
+                        R.labNode[li] = (int32_t)(2 * e.key + sd);
+                        R.labDist[li] = d;
+                        R.labHops[li] = (int32_t)(sd ? e.h1 : e.h0);
+                    }
+                }
+            }
+        }
+        if (T.lane == 0) {
+            R.srcTier[srcIdx] = (int8_t)P.tier;
+            if (R.srcArcs) {
+                R.srcArcs[srcIdx] = S.arcs;
+                R.srcSettled[srcIdx] = S.settled;
+            }
+        }
+        acc[0] += S.arcs;
+        acc[1] += S.settled;
+        acc[2] += 1;
+    } else if (T.lane == 0) {
+        const unsigned long long k = atomicAdd(P.ovfCount, 1ull);
+        P.ovfList[k] = srcIdx;
+    }
+    T.sync();
+}
+
+#ifndef SMSGPU_PAIRS_MIN_CTAS
+#define SMSGPU_PAIRS_MIN_CTAS 4
+#endif
+
+__global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
+    ocwSearchPairsKernel(const GraphDev G, const PairsParams Q, const SearchParams P, const RawOut R, const TileCaps caps,
+                         unsigned char *scratch) {
+    extern __shared__ __align__(32) unsigned char smem[];
+    constexpr unsigned FULL = 0xFFFFFFFFu;
+    constexpr uint32_t TW = 16;
+    const int lane = threadIdx.x & 31;
+    const int gbase = lane & 16;  // first warp lane of this half
+    const uint32_t tl = lane & 15; // lane within the half
+    const unsigned gmask = 0xFFFFu << gbase;
+    const int warpInCta = threadIdx.x >> 5;
+    const size_t tb = tileBytes(caps), hb = hotBytes(caps);
+    const long long warpTile0 = ((long long)blockIdx.x * (blockDim.x >> 5) + warpInCta) * 2;
+    unsigned char *const warpScratch = scratch + warpTile0 * tb;
+    unsigned char *const warpHot = smem + (size_t)(warpInCta * 2) * hb;
+
+    // hot-loop views of this half's working memory (layout = carveTileMem)
+    Entry *tab;
+    HeapEnt *heap;
+    uint2 *pq, *qrow;
+    uint32_t *hist, *cl, *bm;
+    {
+        TileMem M;
+        carveTileMem(M, warpScratch + (gbase ? tb : 0), caps, warpHot + (gbase ? hb : 0));
+        tab = M.tab;
+        heap = M.heap;
+        pq = M.pq;
+        qrow = M.qrow;
+        hist = M.hist;
+        cl = M.cl;
+        bm = M.bm;
+    }
+    const uint32_t NB = caps.nbuckets, C = caps.bucketCap;
+    const uint32_t nclWords = NB >> 1, nbmWords = caps.tabCap >> 5;
+    const uint32_t tabMask = caps.tabCap - 1, tabShift = caps.tabShift;
+    const uint32_t total = (uint32_t)(P.worklist ? P.nwork : P.nsrc);
+    const double bestInit = P.bestInit;
+
+    // per-source state, identical in the 16 lanes of a half
+    int st = 0; // 0 idle (needs a source), 1 running, 2 ended (to be finished), 3 no work left
+    uint32_t src = 0, stamp = 0;
+    int32_t srcIdx = 0;
+    double best = 0.0, bestHop = 0.0;
+    uint32_t histN = 0, touchedN = 0, arcsN = 0, settledN = 0;
+    int overflow = 0;
+    uint32_t cb = 0, liveRegs = 0;
+    bool needLoad = true;
+    // the current bucket's keys, one per lane, with the row of their vertex
+    unsigned long long khi = kDeadKey, klo = kDeadKey;
+    uint32_t rowB = 0, deg = 0;
+    long long acc[3] = {0, 0, 0}; // arcs, settled, sources (same in all lanes)
+
+    while (true) {
+        // ---- (1) finish ended sources: the whole warp works for one half at a time ---------------------------------
+        const unsigned finb = __ballot_sync(FULL, st == 2);
+        if (finb) {
+#pragma unroll 1
+            for (int gg = 0; gg < 2; ++gg) {
+                if (!(finb & (1u << (gg * 16)))) continue; // warp-uniform
+                const int sl = gg * 16;
+                SrcState S;
+                S.best = __shfl_sync(FULL, best, sl);
+                S.bestHop = __shfl_sync(FULL, bestHop, sl);
+                S.histN = __shfl_sync(FULL, histN, sl);
+                S.touchedN = __shfl_sync(FULL, touchedN, sl);
+                S.heapN = 0;
+                S.arcs = (long long)__shfl_sync(FULL, arcsN, sl);
+                S.settled = (long long)__shfl_sync(FULL, settledN, sl);
+                S.steps = 0;
+                S.loads = 0;
+                S.overflow = __shfl_sync(FULL, overflow, sl);
+                const uint32_t fsrc = __shfl_sync(FULL, src, sl);
+                const int32_t fidx = __shfl_sync(FULL, srcIdx, sl);
+                finishSourcePairs<true>(G, P, R, caps, warpScratch + (gg ? tb : 0), warpHot + (gg ? hb : 0), S, fsrc, fidx, acc);
+            }
+            if (st == 2) st = 0;
+        }
+
+        // ---- (2) idle halves fetch the next source ------------------------------------------------------------------
+        if (__ballot_sync(FULL, st == 0)) {
+            uint32_t wi = 0;
+            if (st == 0 && tl == 0) {
+                const unsigned long long w = atomicAdd(P.queueCounter, 1ull);
+                wi = w >= (unsigned long long)total ? total : (uint32_t)w;
+            }
+            wi = __shfl_sync(FULL, wi, gbase);
+            bool fresh = false;
+            if (st == 0) {
+                if (wi >= total) {
+                    st = 3;
+                } else {
+                    srcIdx = P.worklist ? P.worklist[wi] : (int32_t)wi;
+                    src = P.sources ? (uint32_t)P.sources[srcIdx] : (uint32_t)(P.srcBegin + (long long)srcIdx * P.srcStride);
+                    // `if (blacklist_[currentSource_]) return {}` -- indexed with the DOUBLED id (ocw_seperator.cpp:334)
+                    const bool skip = ((long long)src < G.n && P.blacklist[src]) || (long long)(src >> 1) >= G.n;
+                    if (!skip) {
+                        fresh = true;
+                        stamp = P.stampBase + wi + 1u;
+                        for (uint32_t i = tl; i < nclWords; i += TW) cl[i] = 0;
+                        for (uint32_t i = tl; i < nbmWords; i += TW) bm[i] = 0;
+                    }
+                }
+            }
+            __syncwarp(FULL);
+            if (fresh) {
+                if (tl == 0) { // label and enqueue the source (:54-57)
+                    const uint32_t s = ((src >> 1) * 0x9E3779B1u) >> tabShift;
+                    bm[s >> 5] = 1u << (s & 31);
+                    Entry e = emptyEntry();
+                    e.key = src >> 1;
+                    e.flags = stamp;
+                    if (src & 1u) {
+                        e.d1 = 0.0;
+                        e.h1 = 0;
+                    } else {
+                        e.d0 = 0.0;
+                        e.h0 = 0;
+                    }
+                    storeEntry(&tab[s], e);
+                    pq[2 * s + (src & 1u)] = make_uint2(src, 0u);
+                    HeapEnt k;
+                    k.hi = 0ull;
+                    k.lo = (unsigned long long)src;
+                    heap[0] = k;
+                    qrow[0] = Q.rowinfo[src >> 1];
+                    cl[0] = 0x0101u; // bucket 0: one appended, one live
+                }
+                st = 1;
+                best = bestInit;
+                bestHop = 0.0;
+                histN = 0;
+                touchedN = 1;
+                arcsN = 0;
+                settledN = 0;
+                overflow = 0;
+                cb = 0;
+                liveRegs = 0;
+                needLoad = true;
+                khi = kDeadKey;
+                klo = kDeadKey;
+            }
+            __syncwarp(FULL);
+        }
+        if (__ballot_sync(FULL, st == 1) == 0) {
+            if (__ballot_sync(FULL, st != 3) == 0) break; // both halves are out of work
+            continue;                                     // a skipped source: fetch again
+        }
+
+        // ---- (3) (re)load the current bucket into registers -----------------------------------------------------------
+        const bool needL = (st == 1) && needLoad;
+        if (__ballot_sync(FULL, needL)) {
+            uint32_t b = NB, cnt = 0;
+            bool searching = needL;
+            uint32_t base = cb >> 1;
+            while (__ballot_sync(FULL, searching)) {
+                const uint32_t wi = base + tl;
+                const uint32_t word = (searching && wi < nclWords) ? cl[wi] : 0u;
+                uint32_t live = word & 0xFF00FF00u;
+                if (wi == (cb >> 1) && (cb & 1u)) live &= 0xFF000000u;
+                const unsigned gb = (__ballot_sync(FULL, live != 0u) >> gbase) & 0xFFFFu;
+                const int l = gb ? (__ffs(gb) - 1) : 0;
+                const uint32_t lw = __shfl_sync(FULL, live, gbase + l), ww = __shfl_sync(FULL, word, gbase + l);
+                if (searching) {
+                    if (gb) {
+                        const uint32_t odd = (lw & 0x0000FF00u) ? 0u : 1u;
+                        b = 2 * (base + l) + odd;
+                        cnt = (ww >> (odd * 16u)) & 0xFFu;
+                        searching = false;
+                    } else {
+                        base += TW;
+                        if (base >= nclWords) searching = false; // queue empty
+                    }
+                }
+            }
+            unsigned long long nhi = kDeadKey, nlo = kDeadKey;
+            uint2 nrow = make_uint2(0u, 0u);
+            if (needL && b < NB && tl < cnt) {
+                const HeapEnt k = heap[b * C + tl];
+                nrow = qrow[b * C + tl];
+                nhi = k.hi;
+                nlo = k.lo;
+            }
+            const unsigned lv = (__ballot_sync(FULL, nhi != kDeadKey) >> gbase) & 0xFFFFu;
+            if (needL) {
+                if (b >= NB) {
+                    st = 2; // queue empty (:88)
+                } else {
+                    cb = b;
+                    khi = nhi;
+                    klo = nlo;
+                    rowB = nrow.x;
+                    deg = nrow.y;
+                    liveRegs = __popc(lv);
+                    needLoad = false;
+                    SMS_CHK(liveRegs > 0);
+                }
+            }
+        }
+
+        // ---- (4) extract the minimum key of the bucket: (dist, hops, id) lexicographic -------------------------------
+        bool run = (st == 1);
+        const uint32_t k0 = run ? (uint32_t)(khi >> 32) : 0xFFFFFFFFu;
+        const uint32_t m0 = __reduce_min_sync(gmask, k0);
+        bool mine = run && k0 == m0 && khi != kDeadKey;
+        unsigned gbm = (__ballot_sync(FULL, mine) >> gbase) & 0xFFFFu;
+        if (__ballot_sync(FULL, __popc(gbm) > 1)) { // high words tie somewhere: full 128-bit reduction
+            const uint32_t k1 = (uint32_t)khi, k2 = (uint32_t)(klo >> 32), k3 = (uint32_t)klo;
+            const uint32_t m1 = __reduce_min_sync(gmask, mine ? k1 : 0xFFFFFFFFu);
+            mine = mine && k1 == m1;
+            const uint32_t m2 = __reduce_min_sync(gmask, mine ? k2 : 0xFFFFFFFFu);
+            mine = mine && k2 == m2;
+            const uint32_t m3 = __reduce_min_sync(gmask, mine ? k3 : 0xFFFFFFFFu);
+            mine = mine && k3 == m3;
+            gbm = (__ballot_sync(FULL, mine) >> gbase) & 0xFFFFu;
+        }
+        SMS_CHK(!run || gbm != 0);
+        const int wl = gbase + (gbm ? (__ffs(gbm) - 1) : 0);
+        const unsigned long long chi = __shfl_sync(FULL, khi, wl), clo = __shfl_sync(FULL, klo, wl);
+        const uint32_t rb = __shfl_sync(FULL, rowB, wl), dg = __shfl_sync(FULL, deg, wl);
+        const uint32_t cur = (uint32_t)clo, hc = (uint32_t)(clo >> 32);
+        const double dc = __longlong_as_double((long long)chi);
+        // loop condition of ocw_seperator.cpp:88-90
+        if (run && (cur == (src ^ 1u) || 2 * dc > best)) {
+            st = 2;
+            run = false;
+        }
+        if (run) {
+            if (lane == wl) { // extract_top: the key becomes a tombstone
+                heap[cb * C + tl].hi = kDeadKey;
+                khi = kDeadKey;
+                atomicSub(&cl[cb >> 1], 0x0100u << clShift(cb));
+            }
+            liveRegs--;
+            settledN++;
+        }
+        const uint32_t side = cur & 1u;
+        const uint32_t hNew = hc + 1;
+
+        // ---- (5) relax the arcs of the settled node, 16 per pass ------------------------------------------------------
+        for (uint32_t c0 = 0; __ballot_sync(FULL, run && c0 < dg); c0 += TW) {
+            if (run && touchedN + TW > caps.touchedCap) {
+                overflow = 1;
+                st = 2;
+                run = false;
+            }
+            const double best0 = best; // conservative (>= the running value) for pruning / queue admission
+            bool act = run && (c0 + tl < dg);
+            uint32_t nbr = 0;
+            double w = 0.0;
+            uint2 nrow = make_uint2(0u, 0u);
+            if (act) {
+                const Arc arc = G.arcs[rb + c0 + tl];
+                nbr = (uint32_t)arc.nbr & 0x7FFFFFFFu;
+                w = arc.w;
+                act = arc.nbr >= 0; // blacklisted neighbours are skipped (:98-99)
+                nrow = Q.rowinfo[nbr]; // used only if a key is pushed; in flight while the label is probed
+            }
+            arcsN += __popc((__ballot_sync(FULL, act) >> gbase) & 0xFFFFu);
+            const double dS = dc + w;         // totalStayDist  (:104)
+            const double dX = dc + (1.0 - w); // totalCrossDist (:107-108)
+            const bool creatS = dS + dc <= best0, creatX = dX + dc <= best0; // label pruning, see ocw_search.cuh
+
+            // ---- label table: bitmap-arbitrated open addressing ---------------------------------------------------
+            int slot = -1;
+            bool isNew = false;
+            Entry e = emptyEntry();
+            if (act) {
+                uint32_t s = (nbr * 0x9E3779B1u) >> tabShift;
+                while (true) {
+                    const uint32_t bit = 1u << (s & 31);
+                    if (!(bm[s >> 5] & bit)) {
+                        if (!(creatS || creatX)) break; // no label, and none may be created
+                        if (!(atomicOr(&bm[s >> 5], bit) & bit)) {
+                            isNew = true; // the slot is ours; whatever an earlier source left in it is never read
+                            slot = (int)s;
+                            break;
+                        }
+                        // another lane claimed it for its own (different) neighbour in this very step
+                    } else {
+                        e = loadEntry(&tab[s]);
+                        if (e.key == nbr && e.flags == stamp) {
+                            slot = (int)s;
+                            break;
+                        }
+                    }
+                    s = (s + 1) & tabMask;
+                }
+                if (isNew || slot < 0) e = emptyEntry();
+            }
+            touchedN += __popc((__ballot_sync(FULL, isNew) >> gbase) & 0xFFFFu);
+
+            bool accS = false, accX = false, evS = false, evX = false, ovf = false, dirty = false;
+            double DS = 0, DX = 0;
+            uint32_t HS = 0, HX = 0;
+            if (slot >= 0) {
+                double dA = side ? e.d1 : e.d0, dB = side ? e.d0 : e.d1;
+                uint32_t hA = side ? e.h1 : e.h0, hB = side ? e.h0 : e.h1;
+                const bool hadA = dA < kUnlabelled, hadB = dB < kUnlabelled;
+                // updatePaths(stayNeighbor, ...)   (:59-84)
+                if (!hadA)
+                    accS = dS < kInfDist && (creatS || dS + dB <= best0);
+                else
+                    accS = (dA == dS) ? (hNew < hA) : (dS < dA);
+                if (accS) {
+                    dA = dS;
+                    hA = hNew;
+                    DS = dA + dB;
+                    HS = hA + hB;
+                    evS = DS <= best0;
+                }
+                // updatePaths(crossNeighbor, ...)
+                if (!hadB)
+                    accX = dX < kInfDist && (creatX || dX + dA <= best0);
+                else
+                    accX = (dB == dX) ? (hNew < hB) : (dX < dB);
+                if (accX) {
+                    dB = dX;
+                    hB = hNew;
+                    DX = dB + dA;
+                    HX = hB + hA;
+                    evX = DX <= best0;
+                }
+                if (accS || accX) {
+                    if (side) {
+                        e.d1 = dA;
+                        e.h1 = hA;
+                        e.d0 = dB;
+                        e.h0 = hB;
+                    } else {
+                        e.d0 = dA;
+                        e.h0 = hA;
+                        e.d1 = dB;
+                        e.h1 = hB;
+                    }
+                    e.key = nbr;
+                    e.flags = stamp;
+                    storeEntry(&tab[slot], e);
+#pragma unroll
+                    for (int k = 0; k < 2; ++k) {
+                        if (!(k ? accX : accS)) continue;
+                        const uint32_t sd = k ? (side ^ 1u) : side;
+                        const double d = k ? dX : dS;
+                        // a superseded key leaves the queue now
+                        if (k ? hadB : hadA) {
+                            const uint32_t oldq = pq[2 * slot + sd].y;
+                            if (oldq != kNoQpos) {
+                                heap[oldq].hi = kDeadKey;
+                                const uint32_t ob = oldq / C;
+                                atomicSub(&cl[ob >> 1], 0x0100u << clShift(ob));
+                                dirty |= ob == cb;
+                            }
+                        }
+                        uint32_t qpos = kNoQpos;
+                        if (2 * d <= best0) { // queue admission: only nodes that can still be extracted
+                            const uint32_t bk = bucketOf(d, Q.scaleU, Q.scaleB, NB - 1);
+                            const uint32_t sh = clShift(bk);
+                            const uint32_t pos = (atomicAdd(&cl[bk >> 1], 0x0101u << sh) >> sh) & 0xFFu;
+                            dirty |= bk == cb;
+                            SMS_CHK(bk >= cb);
+                            if (pos >= C) {
+                                ovf = true;
+                            } else {
+                                qpos = bk * C + pos;
+                                HeapEnt q;
+                                q.hi = (unsigned long long)__double_as_longlong(d);
+                                q.lo = ((unsigned long long)hNew << 32) | (2 * nbr + sd);
+                                heap[qpos] = q;
+                                qrow[qpos] = nrow;
+                                // its arcs are read when it is extracted
+                                if (nrow.y) {
+                                    asm volatile("prefetch.global.L2 [%0];" ::"l"(G.arcs + nrow.x));
+                                    asm volatile("prefetch.global.L2 [%0];" ::"l"(G.arcs + nrow.x + nrow.y - 1));
+                                }
+                            }
+                        }
+                        pq[2 * slot + sd] = make_uint2(cur, qpos);
+                    }
+                }
+            }
+            if ((__ballot_sync(FULL, ovf) >> gbase) & 0xFFFFu) {
+                overflow = 1;
+                st = 2;
+                run = false;
+            }
+            if ((__ballot_sync(FULL, dirty) >> gbase) & 0xFFFFu) needLoad = true;
+            // ---- replay of the record logic in adjacency order (:71-82) -------------------------------------------
+            unsigned evm = (__ballot_sync(FULL, evS || evX) >> gbase) & 0xFFFFu;
+            if (!run) evm = 0;
+            while (__ballot_sync(FULL, evm != 0)) {
+                const bool have = evm != 0;
+                const int l = gbase + (have ? (__ffs(evm) - 1) : 0);
+                evm &= evm - 1; // 0 stays 0
+                const uint32_t nb = __shfl_sync(FULL, nbr, l);
+                const int eS = __shfl_sync(FULL, (int)evS, l), eX = __shfl_sync(FULL, (int)evX, l);
+                const double D0 = __shfl_sync(FULL, DS, l), D1 = __shfl_sync(FULL, DX, l);
+                const uint32_t H0 = __shfl_sync(FULL, HS, l), H1 = __shfl_sync(FULL, HX, l);
+                if (have) {
+#pragma unroll
+                    for (int k = 0; k < 2; ++k) {
+                        if (!(k ? eX : eS)) continue;
+                        const double D = k ? D1 : D0;
+                        const double H = (double)(k ? H1 : H0);
+                        bool push = false;
+                        if (D < best || (D == best && H < bestHop)) {
+                            best = D;
+                            bestHop = H;
+                            push = true;
+                        } else if (D == best && H < 2 * bestHop) {
+                            push = true;
+                        }
+                        if (push && !overflow) {
+                            if (histN >= caps.histCap) {
+                                overflow = 1;
+                                st = 2;
+                                run = false;
+                                evm = 0;
+                            } else {
+                                if (tl == 0) hist[histN] = 2 * nb + (k ? (side ^ 1u) : side);
+                                histN++;
+                            }
+                        }
+                    }
+                }
+            }
+            __syncwarp(FULL); // keys, labels and counters of this pass are visible to the next extraction
+        }
+        if (run && liveRegs == 0) needLoad = true;
+    }
+    if (lane == 0 && acc[2]) {
+        atomicAdd(&R.counters[2], (unsigned long long)acc[0]);
+        atomicAdd(&R.counters[3], (unsigned long long)acc[1]);
+        atomicAdd(&R.counters[4], (unsigned long long)acc[2]);
+    }
+}
+
+} // namespace smsgpu

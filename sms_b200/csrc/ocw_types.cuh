@@ -90,6 +90,8 @@ __host__ __device__ inline size_t tileBytes(const TileCaps &c) {
     b += (size_t)(2 * c.walkCap + 2) * sizeof(double); // plen
     b += (size_t)c.chordCap * 4 * sizeof(int32_t);     // chords
     b += (size_t)c.chordCap * 0 + (size_t)(4 * c.walkCap + 8) * sizeof(int32_t); // covered list
+    b = (b + 7) & ~(size_t)7;
+    if (c.nbuckets) b += (size_t)c.heapCap * 2 * sizeof(uint32_t); // pairs engine: {first arc, degree} per queue entry
     return (b + 31) & ~(size_t)31;
 }
 

@@ -6,7 +6,9 @@
 #include "../../include/smsgpu.h"
 
 #include <algorithm>
+#include <cmath>
 #include <cstdarg>
+#include <cstdlib>
 #include <cstdio>
 #include <cstring>
 #include <string>
@@ -16,6 +18,9 @@
 #include "ocw_kernels.cuh"
 #include "small_cycles.cuh"
 
+#ifndef SMSGPU_PAIRS_BUCKETS
+#define SMSGPU_PAIRS_BUCKETS 2048
+#endif
 #ifndef SMSGPU_TIER1_BUCKETS
 #define SMSGPU_TIER1_BUCKETS 4096
 #endif
@@ -85,6 +90,7 @@ struct TierCfg {
     int ctas = 0;           // grid size
     size_t smemBytes = 0;   // dynamic shared memory per CTA (tier 0: whole tiles, tier 1: hot words)
     bool hotInSmem = false; // fast engine: where the bucket counters and the presence bitmap live
+    bool pairs = false;     // pairs engine: two tiles per warp
     uint64_t stampNext = 0; // fast engine: stamps handed out so far for this scratch (ocw_search_fast.cuh)
     DevBuf scratch;
     bool ready = false;
@@ -113,6 +119,10 @@ struct smsgpu_ctx {
 
     // graph (uploaded once)
     DevBuf dRowptr, dCol, dEid, dArcs;
+    DevBuf dRowinfo;          // uint2[n] {first arc, degree}: pairs engine (tier 1)
+    bool pairs = false;       // tier 1 runs the pairs engine (ocw_search_pairs.cuh)
+    float pairsScaleU = 0.f;  // bucket map of the pairs engine (PairsParams)
+    float pairsScaleB = 0.f;
     // round input
     DevBuf dX, dBl;
     const double *xPtr = nullptr;   // device pointer in use (own buffer or caller's)
@@ -225,6 +235,13 @@ cudaError_t launchSearchT(smsgpu_ctx *c, const TierCfg &t, const GraphDev &G, co
 cudaError_t launchSearch(smsgpu_ctx *c, int tierIdx, const GraphDev &G, const SearchParams &P, const RawOut &R) {
     const TierCfg &t = c->tier[tierIdx];
     if (tierIdx == 0) return launchSearchT<true, false>(c, t, G, P, R);
+    if (t.pairs) {
+        cudaError_t e = cudaFuncSetAttribute(ocwSearchPairsKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t.smemBytes);
+        if (e != cudaSuccess) return e;
+        const PairsParams Q{c->dRowinfo.as<uint2>(), c->pairsScaleU, c->pairsScaleB};
+        ocwSearchPairsKernel<<<t.ctas, 128, t.smemBytes, c->stream>>>(G, Q, P, R, t.caps, t.scratch.as<unsigned char>());
+        return cudaGetLastError();
+    }
     if (t.caps.nbuckets) return launchSearchT<false, true>(c, t, G, P, R);
     return launchSearchT<false, false>(c, t, G, P, R);
 }
@@ -271,6 +288,25 @@ void configureTiers(smsgpu_ctx *c) {
                               std::min<uint32_t>(1u << (lg - 1), pushMax), std::min<uint32_t>(ti == 1 ? 256 : 4096, walkMax),
                               ti == 1 ? 1024u : (1u << 14), nb, bc};
             t.hotInSmem = ti == 1;
+            if (ti == 1 && c->pairs) {
+                // pairs engine: two sources per warp, 16-slot buckets under the geometric bucket map
+                const uint32_t pnb = (uint32_t)SMSGPU_PAIRS_BUCKETS, pbc = 16u;
+                t.caps.nbuckets = pnb;
+                t.caps.bucketCap = pbc;
+                t.caps.heapCap = pnb * pbc;
+                t.pairs = true;
+                const int pairTiles = 2 * (128 / 32);
+                t.smemBytes = hotBytes(t.caps) * pairTiles;
+                int nb2 = 0;
+                cudaFuncSetAttribute(ocwSearchPairsKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t.smemBytes);
+                if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb2, ocwSearchPairsKernel, 128, t.smemBytes) != cudaSuccess) {
+                    (void)cudaGetLastError();
+                    nb2 = 1;
+                }
+                t.ctas = c->smCount * std::max(nb2, 1);
+                t.ntiles = (long long)t.ctas * pairTiles;
+                continue;
+            }
             t.smemBytes = t.hotInSmem ? hotBytes(t.caps) * tilesPerCta : 0;
             t.ctas = c->smCount * occupancyT<false, true>(t.smemBytes);
             t.ntiles = (long long)t.ctas * tilesPerCta;
@@ -405,6 +441,31 @@ int smsgpu_create(smsgpu_ctx **out, int64_t n, int64_t m, const int64_t *rowptr,
     const double avgDeg = n ? 2.0 * (double)m / (double)n : 0.0;
     (void)avgDeg;
     ctx->tileWidth = 32;
+    // pairs engine (tier 1): needs 32-bit arc indices; SMSGPU_PAIRS=0 selects the one-source-per-warp engine
+    {
+        const char *ev = std::getenv("SMSGPU_PAIRS");
+        ctx->pairs = (2 * m < (int64_t)0xFFFFFFFFll) && !(ev && ev[0] == '0');
+        if (ctx->pairs) {
+            std::vector<uint2> ri((size_t)std::max<int64_t>(n, 1));
+            for (int64_t u = 0; u < n; ++u) ri[u] = make_uint2((uint32_t)rowptr[u], (uint32_t)(rowptr[u + 1] - rowptr[u]));
+            CUB(ctx->dRowinfo.ensure(ri.size() * sizeof(uint2)));
+            CUB(cudaMemcpy(ctx->dRowinfo.p, ri.data(), (size_t)n * sizeof(uint2), cudaMemcpyHostToDevice));
+            // bucket map: 2^u, u in [0, L] over [0, bestInit/2]; L ~ log2 of the ball growth over the radius,
+            // which is about 1.2 x the average degree (measured on the bench shapes); SMSGPU_PAIRS_L overrides, 0 = linear
+            int L = (int)std::lround(1.2 * avgDeg);
+            if (const char *el = std::getenv("SMSGPU_PAIRS_L")) L = std::atoi(el);
+            L = std::max(0, std::min(L, 20));
+            const double half = 0.5 * (1.0 - 1e-6); // bestInit / 2 of the default parameters; larger radii clamp to the last bucket
+            const double NBd = (double)SMSGPU_PAIRS_BUCKETS;
+            if (L > 0) {
+                ctx->pairsScaleU = (float)((double)L / half);
+                ctx->pairsScaleB = (float)(NBd / (std::ldexp(1.0, L) - 1.0));
+            } else {
+                ctx->pairsScaleU = 0.f;
+                ctx->pairsScaleB = (float)(NBd / half);
+            }
+        }
+    }
     configureTiers(ctx);
     ctx->nsrcGlobal = ctx->nsrcLocal = n; // default source list 0..n-1 (conshdlr_oscw.cpp:188-195)
     ctx->rank = 0;
@@ -419,7 +480,7 @@ void smsgpu_destroy(smsgpu_ctx *ctx) {
     cudaSetDevice(ctx->device);
     smsgpu_comm_destroy(ctx);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-    DevBuf *dev[] = {&ctx->dRowptr, &ctx->dCol, &ctx->dEid, &ctx->dArcs, &ctx->dX, &ctx->dBl, &ctx->dSources,
+    DevBuf *dev[] = {&ctx->dRowinfo, &ctx->dRowptr, &ctx->dCol, &ctx->dEid, &ctx->dArcs, &ctx->dX, &ctx->dBl, &ctx->dSources,
                      &ctx->tier[0].scratch, &ctx->tier[1].scratch, &ctx->tier[2].scratch, &ctx->tier[3].scratch, &ctx->rNode, &ctx->rEid,
                      &ctx->rStay, &ctx->rCutOff, &ctx->rCutLen, &ctx->rCutSrc, &ctx->rCutSeq, &ctx->rCutTier, &ctx->rValid,
                      &ctx->labSrc, &ctx->labNode, &ctx->labHops, &ctx->labDist, &ctx->srcTier, &ctx->srcArcs,

@@ -96,6 +96,18 @@ def test_tiers_and_tile_widths_agree(gpu, orc, tier, tw):
         assert st["tier_sources"][0] == 0 and (tiers[tiers >= 0] >= tier).all()
 
 
+@pytest.mark.parametrize("engine", ["pairs", "one_per_warp"])
+def test_tier1_engines_agree(gpu, orc, engine, monkeypatch):
+    """Tier 1 has two engines: the pairs engine (two sources per warp in lock step, ocw_search_pairs.cuh; the
+    default) and the one-source-per-warp engine (SMSGPU_PAIRS=0).  Both must reproduce the oracle event for event,
+    on tie-free and on tie-heavy x*, on a degree-8 graph (one pass per row) and a degree-40 one (several passes)."""
+    monkeypatch.setenv("SMSGPU_PAIRS", "1" if engine == "pairs" else "0")
+    for inst in (I.random_graph(3000, 12000, seed=11), I.random_graph(200, 4000, seed=12), I.torus3d(7)):
+        for xf in (I.xstar_uniform, I.xstar_lp_like, I.xstar_half_integral):
+            _, _, st, tiers = check_raw(inst, xf(inst.m, seed=6), orc, start_tier=1, sources=np.arange(0, inst.n, 3))
+            assert st["tier_sources"][0] == 0
+
+
 def test_overflow_escalates_to_next_tier(gpu, orc):
     """LP-like x* on a degree-8 graph makes balls that do not fit shared memory: sources must escalate and
     still match."""
