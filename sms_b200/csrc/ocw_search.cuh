@@ -82,7 +82,7 @@ struct TileMem {
     uint2 *pq;       // [slot*2 + side] {predecessor doubled id, queue position or kNoQpos}; aliases pred
     uint32_t *cl;    // bucket counters, two buckets per word: byte 0/2 = appended, byte 1/3 = live
     uint32_t *bm;    // presence bitmap of the label table, one bit per slot
-    uint2 *qrow;     // pairs engine: {first arc, degree} of the vertex of queue entry i (parallel to heap)
+    uint4 *qrow;     // pairs engine: its queue, two uint4 per entry: {dist bits, hops << 32 | id}, {first arc, degree, -, -}
 };
 
 __device__ inline void carveTileMem(TileMem &M, unsigned char *base, const TileCaps &c, unsigned char *hot = nullptr) {
@@ -126,7 +126,7 @@ __device__ inline void carveTileMem(TileMem &M, unsigned char *base, const TileC
     p += (size_t)c.chordCap * 4 * sizeof(int32_t);
     M.covered = reinterpret_cast<int32_t *>(p);
     p += (size_t)(4 * c.walkCap + 8) * sizeof(int32_t);
-    if (c.nbuckets) M.qrow = reinterpret_cast<uint2 *>(base + (((size_t)(p - base) + 7) & ~(size_t)7));
+    if (c.pairs) M.qrow = reinterpret_cast<uint4 *>(base + (((size_t)(p - base) + 31) & ~(size_t)31));
 }
 
 __device__ __forceinline__ Entry emptyEntry() {

@@ -29,11 +29,39 @@
 
 namespace smsgpu {
 
+// The kernel's arguments once more in global memory, for the (cold, not inlined) finishing code: taking the
+// address of by-value kernel parameters would copy all of them to every thread's stack.
+struct PairsKArgs {
+    GraphDev G;
+    SearchParams P;
+    RawOut R;
+    TileCaps caps;
+};
+
 struct PairsParams {
+    const PairsKArgs *kargs;
     const uint2 *rowinfo; // [n] {first arc, degree} of every vertex (32-bit arc indices: 2m < 2^32)
     float scaleU;         // bucket map: u = (float)dist * scaleU; 0 selects the linear map
     float scaleB;         // bucket = (2^u - 1) * scaleB   (linear map: dist * scaleB)
 };
+
+// The per-source working memory (label table, predecessors, queue) is touched once or twice per source and is far
+// larger than L2 in total, while the graph (arcs + rows, ~136 MB at 1M/4M) is shared by every source: working-memory
+// accesses carry the streaming (evict-first) hint so that they do not push the graph out of L2.
+__device__ __forceinline__ Entry loadEntryCS(const Entry *p) {
+    Entry e;
+    const uint4 *q = reinterpret_cast<const uint4 *>(p);
+    uint4 *s = reinterpret_cast<uint4 *>(&e);
+    s[0] = __ldcs(q);
+    s[1] = __ldcs(q + 1);
+    return e;
+}
+__device__ __forceinline__ void storeEntryCS(Entry *p, const Entry &e) {
+    uint4 *q = reinterpret_cast<uint4 *>(p);
+    const uint4 *s = reinterpret_cast<const uint4 *>(&e);
+    __stcs(q, s[0]);
+    __stcs(q + 1, s[1]);
+}
 
 // Monotone (non-decreasing in d) bucket index; every operation below is monotone for d >= 0.
 __device__ __forceinline__ uint32_t bucketOf(const double d, const float scaleU, const float scaleB, const uint32_t nbm1) {
@@ -50,13 +78,29 @@ __device__ __forceinline__ uint32_t bucketOf(const double d, const float scaleU,
 }
 
 // Everything after the search of one source, by all 32 lanes (same code path as ocwSearchKernel's tail).
-template <bool DUMMY>
-__device__ __noinline__ void finishSourcePairs(const GraphDev &G, const SearchParams &P, const RawOut &R, const TileCaps &caps,
-                                               unsigned char *tile, unsigned char *hot, SrcState &S, const uint32_t src,
-                                               const int32_t srcIdx, long long *acc) {
+// Returns 1 when the source completed in this tier (its counters count), 0 when it overflowed.
+__device__ __noinline__ int finishSourcePairs(const PairsKArgs *K, unsigned char *tile, unsigned char *hot, const double best,
+                                              const uint32_t histN, const uint32_t touchedN, const uint32_t arcs,
+                                              const uint32_t settled, const int overflow, const uint32_t src,
+                                              const int32_t srcIdx) {
     const Tile<32> T;
+    const GraphDev G = K->G;
+    const TileCaps caps = K->caps;
+    const RawOut &R = K->R;
+    const SearchParams &P = K->P;
     TileMem M;
     carveTileMem(M, tile, caps, hot);
+    SrcState S;
+    S.best = best;
+    S.bestHop = 0.0;
+    S.histN = histN;
+    S.heapN = 0;
+    S.touchedN = touchedN;
+    S.arcs = arcs;
+    S.settled = settled;
+    S.steps = 0;
+    S.loads = 0;
+    S.overflow = overflow;
     uint32_t sel[16];
     const int maxInter = min(P.maxInter, 16);
     if (!S.overflow && S.histN > 0) {
@@ -79,6 +123,7 @@ __device__ __noinline__ void finishSourcePairs(const GraphDev &G, const SearchPa
         }
         S.overflow = T.shfl(S.overflow, 0);
     }
+    int counted = 0;
     if (!S.overflow) {
         if (P.exportLabels) {
             for (uint32_t i = T.lane; i < caps.tabCap; i += 32) {
@@ -101,75 +146,87 @@ __device__ __noinline__ void finishSourcePairs(const GraphDev &G, const SearchPa
         if (T.lane == 0) {
             R.srcTier[srcIdx] = (int8_t)P.tier;
             if (R.srcArcs) {
-                R.srcArcs[srcIdx] = S.arcs;
-                R.srcSettled[srcIdx] = S.settled;
+                R.srcArcs[srcIdx] = (long long)arcs;
+                R.srcSettled[srcIdx] = (long long)settled;
             }
         }
-        acc[0] += S.arcs;
-        acc[1] += S.settled;
-        acc[2] += 1;
+        counted = 1;
     } else if (T.lane == 0) {
         const unsigned long long k = atomicAdd(P.ovfCount, 1ull);
         P.ovfList[k] = srcIdx;
     }
     T.sync();
+    return counted;
 }
 
 #ifndef SMSGPU_PAIRS_MIN_CTAS
 #define SMSGPU_PAIRS_MIN_CTAS 4
 #endif
 
+#ifdef SMSGPU_PAIRS_CLOCKS // instrumentation build: cycles per phase of the lock-step loop, printed by one warp
+#define PCLK(i_)                                  \
+    do {                                          \
+        const long long now_ = clock64();         \
+        pclk[i_] += now_ - plast;                 \
+        plast = now_;                             \
+    } while (0)
+#else
+#define PCLK(i_) ((void)0)
+#endif
+
 __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
     ocwSearchPairsKernel(const GraphDev G, const PairsParams Q, const SearchParams P, const RawOut R, const TileCaps caps,
                          unsigned char *scratch) {
-    extern __shared__ __align__(32) unsigned char smem[];
+    extern __shared__ __align__(32) uint32_t smemw[];
     constexpr unsigned FULL = 0xFFFFFFFFu;
     constexpr uint32_t TW = 16;
     const int lane = threadIdx.x & 31;
-    const int gbase = lane & 16;  // first warp lane of this half
+    const int gbase = lane & 16;   // first warp lane of this half
     const uint32_t tl = lane & 15; // lane within the half
     const unsigned gmask = 0xFFFFu << gbase;
     const int warpInCta = threadIdx.x >> 5;
-    const size_t tb = tileBytes(caps), hb = hotBytes(caps);
-    const long long warpTile0 = ((long long)blockIdx.x * (blockDim.x >> 5) + warpInCta) * 2;
-    unsigned char *const warpScratch = scratch + warpTile0 * tb;
-    unsigned char *const warpHot = smem + (size_t)(warpInCta * 2) * hb;
+    const size_t tb = tileBytes(caps);
+    const uint32_t hbw = (uint32_t)(hotBytes(caps) >> 2); // hot words of one half
+    unsigned char *const warpScratch = scratch + ((size_t)blockIdx.x * (blockDim.x >> 5) + warpInCta) * 2 * tb;
+    unsigned char *const tileB = warpScratch + (gbase ? tb : 0);
 
-    // hot-loop views of this half's working memory (layout = carveTileMem)
-    Entry *tab;
-    HeapEnt *heap;
-    uint2 *pq, *qrow;
-    uint32_t *hist, *cl, *bm;
+    // this half's working memory: offsets inside the tile as carveTileMem lays it out (uniform: functions of caps)
+    uint32_t offPq, offHist, offQrow;
     {
         TileMem M;
-        carveTileMem(M, warpScratch + (gbase ? tb : 0), caps, warpHot + (gbase ? hb : 0));
-        tab = M.tab;
-        heap = M.heap;
-        pq = M.pq;
-        qrow = M.qrow;
-        hist = M.hist;
-        cl = M.cl;
-        bm = M.bm;
+        carveTileMem(M, tileB, caps, nullptr);
+        offPq = (uint32_t)(reinterpret_cast<unsigned char *>(M.pq) - tileB);
+        offHist = (uint32_t)(reinterpret_cast<unsigned char *>(M.hist) - tileB);
+        offQrow = (uint32_t)(reinterpret_cast<unsigned char *>(M.qrow) - tileB);
     }
+#define TABP(s_) (reinterpret_cast<Entry *>(tileB) + (s_))
+#define PQP(i_) (reinterpret_cast<uint2 *>(tileB + offPq) + (i_))
+#define QP(i_) (reinterpret_cast<uint4 *>(tileB + offQrow) + 2 * (i_)) /* queue entry i: [0] key, [1] row */
+#define HISTP(i_) (reinterpret_cast<uint32_t *>(tileB + offHist) + (i_))
     const uint32_t NB = caps.nbuckets, C = caps.bucketCap;
     const uint32_t nclWords = NB >> 1, nbmWords = caps.tabCap >> 5;
+    uint32_t *const cl = smemw + (uint32_t)(warpInCta * 2 + (gbase >> 4)) * hbw; // bucket counters (shared memory)
+    uint32_t *const bm = cl + nclWords;                                          // presence bitmap (shared memory)
     const uint32_t tabMask = caps.tabCap - 1, tabShift = caps.tabShift;
     const uint32_t total = (uint32_t)(P.worklist ? P.nwork : P.nsrc);
-    const double bestInit = P.bestInit;
 
     // per-source state, identical in the 16 lanes of a half
     int st = 0; // 0 idle (needs a source), 1 running, 2 ended (to be finished), 3 no work left
-    uint32_t src = 0, stamp = 0;
-    int32_t srcIdx = 0;
-    double best = 0.0, bestHop = 0.0;
+    uint32_t src = 0, wi = 0;
+    double best = 0.0;
+    uint32_t bestHop = 0; // bestHopDist: a double in the reference (:52) that only ever holds small integers
     uint32_t histN = 0, touchedN = 0, arcsN = 0, settledN = 0;
     int overflow = 0;
-    uint32_t cb = 0, liveRegs = 0;
+    uint32_t cb = 0, lo = 0, liveRegs = 0; // bucket in registers, bucket of the last extraction, live keys in registers
     bool needLoad = true;
     // the current bucket's keys, one per lane, with the row of their vertex
     unsigned long long khi = kDeadKey, klo = kDeadKey;
     uint32_t rowB = 0, deg = 0;
-    long long acc[3] = {0, 0, 0}; // arcs, settled, sources (same in all lanes)
+    unsigned long long accArcs = 0, accSettled = 0;
+    uint32_t accSources = 0; // same in all lanes
+#ifdef SMSGPU_PAIRS_CLOCKS
+    long long pclk[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, plast = clock64(), piters = 0;
+#endif
 
     while (true) {
         // ---- (1) finish ended sources: the whole warp works for one half at a time ---------------------------------
@@ -179,46 +236,45 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
             for (int gg = 0; gg < 2; ++gg) {
                 if (!(finb & (1u << (gg * 16)))) continue; // warp-uniform
                 const int sl = gg * 16;
-                SrcState S;
-                S.best = __shfl_sync(FULL, best, sl);
-                S.bestHop = __shfl_sync(FULL, bestHop, sl);
-                S.histN = __shfl_sync(FULL, histN, sl);
-                S.touchedN = __shfl_sync(FULL, touchedN, sl);
-                S.heapN = 0;
-                S.arcs = (long long)__shfl_sync(FULL, arcsN, sl);
-                S.settled = (long long)__shfl_sync(FULL, settledN, sl);
-                S.steps = 0;
-                S.loads = 0;
-                S.overflow = __shfl_sync(FULL, overflow, sl);
+                const double fbest = __shfl_sync(FULL, best, sl);
+                const uint32_t fhist = __shfl_sync(FULL, histN, sl), ftouched = __shfl_sync(FULL, touchedN, sl);
+                const uint32_t farcs = __shfl_sync(FULL, arcsN, sl), fsettled = __shfl_sync(FULL, settledN, sl);
+                const int fovf = __shfl_sync(FULL, overflow, sl);
                 const uint32_t fsrc = __shfl_sync(FULL, src, sl);
-                const int32_t fidx = __shfl_sync(FULL, srcIdx, sl);
-                finishSourcePairs<true>(G, P, R, caps, warpScratch + (gg ? tb : 0), warpHot + (gg ? hb : 0), S, fsrc, fidx, acc);
+                const uint32_t fwi = __shfl_sync(FULL, wi, sl);
+                const int32_t fidx = P.worklist ? P.worklist[fwi] : (int32_t)fwi;
+                if (finishSourcePairs(Q.kargs, warpScratch + (gg ? tb : 0),
+                                      reinterpret_cast<unsigned char *>(smemw + (uint32_t)(warpInCta * 2 + gg) * hbw), fbest, fhist,
+                                      ftouched, farcs, fsettled, fovf, fsrc, fidx)) {
+                    accArcs += farcs;
+                    accSettled += fsettled;
+                    accSources += 1;
+                }
             }
             if (st == 2) st = 0;
         }
 
         // ---- (2) idle halves fetch the next source ------------------------------------------------------------------
         if (__ballot_sync(FULL, st == 0)) {
-            uint32_t wi = 0;
+            uint32_t w32 = 0;
             if (st == 0 && tl == 0) {
                 const unsigned long long w = atomicAdd(P.queueCounter, 1ull);
-                wi = w >= (unsigned long long)total ? total : (uint32_t)w;
+                w32 = w >= (unsigned long long)total ? total : (uint32_t)w;
             }
-            wi = __shfl_sync(FULL, wi, gbase);
+            w32 = __shfl_sync(FULL, w32, gbase);
             bool fresh = false;
             if (st == 0) {
-                if (wi >= total) {
+                if (w32 >= total) {
                     st = 3;
                 } else {
-                    srcIdx = P.worklist ? P.worklist[wi] : (int32_t)wi;
+                    wi = w32;
+                    const int32_t srcIdx = P.worklist ? P.worklist[wi] : (int32_t)wi;
                     src = P.sources ? (uint32_t)P.sources[srcIdx] : (uint32_t)(P.srcBegin + (long long)srcIdx * P.srcStride);
                     // `if (blacklist_[currentSource_]) return {}` -- indexed with the DOUBLED id (ocw_seperator.cpp:334)
                     const bool skip = ((long long)src < G.n && P.blacklist[src]) || (long long)(src >> 1) >= G.n;
                     if (!skip) {
                         fresh = true;
-                        stamp = P.stampBase + wi + 1u;
-                        for (uint32_t i = tl; i < nclWords; i += TW) cl[i] = 0;
-                        for (uint32_t i = tl; i < nbmWords; i += TW) bm[i] = 0;
+                        for (uint32_t i = tl; i < nclWords + nbmWords; i += TW) cl[i] = 0; // counters, then the bitmap
                     }
                 }
             }
@@ -229,7 +285,7 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
                     bm[s >> 5] = 1u << (s & 31);
                     Entry e = emptyEntry();
                     e.key = src >> 1;
-                    e.flags = stamp;
+                    e.flags = P.stampBase + wi + 1u;
                     if (src & 1u) {
                         e.d1 = 0.0;
                         e.h1 = 0;
@@ -237,24 +293,23 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
                         e.d0 = 0.0;
                         e.h0 = 0;
                     }
-                    storeEntry(&tab[s], e);
-                    pq[2 * s + (src & 1u)] = make_uint2(src, 0u);
-                    HeapEnt k;
-                    k.hi = 0ull;
-                    k.lo = (unsigned long long)src;
-                    heap[0] = k;
-                    qrow[0] = Q.rowinfo[src >> 1];
+                    storeEntryCS(TABP(s), e);
+                    __stcs(PQP(2 * s + (src & 1u)), make_uint2(src, 0u));
+                    const uint2 srow = Q.rowinfo[src >> 1];
+                    __stcs(QP(0), make_uint4(0u, 0u, src, 0u)); // dist 0, id src, 0 hops
+                    __stcs(QP(0) + 1, make_uint4(srow.x, srow.y, 0u, 0u));
                     cl[0] = 0x0101u; // bucket 0: one appended, one live
                 }
                 st = 1;
-                best = bestInit;
-                bestHop = 0.0;
+                best = P.bestInit;
+                bestHop = 0;
                 histN = 0;
                 touchedN = 1;
                 arcsN = 0;
                 settledN = 0;
                 overflow = 0;
                 cb = 0;
+                lo = 0;
                 liveRegs = 0;
                 needLoad = true;
                 khi = kDeadKey;
@@ -267,22 +322,26 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
             continue;                                     // a skipped source: fetch again
         }
 
+        PCLK(0);
         // ---- (3) (re)load the current bucket into registers -----------------------------------------------------------
         const bool needL = (st == 1) && needLoad;
+        if (needL) cb = lo; // registers are stale or empty: rescan from the bucket of the last extraction
         if (__ballot_sync(FULL, needL)) {
             uint32_t b = NB, cnt = 0;
             bool searching = needL;
             uint32_t base = cb >> 1;
             while (__ballot_sync(FULL, searching)) {
-                const uint32_t wi = base + tl;
-                const uint32_t word = (searching && wi < nclWords) ? cl[wi] : 0u;
+                const uint32_t wd = base + tl;
+                const uint32_t word = (searching && wd < nclWords) ? cl[wd] : 0u;
                 uint32_t live = word & 0xFF00FF00u;
-                if (wi == (cb >> 1) && (cb & 1u)) live &= 0xFF000000u;
+                if (wd == (cb >> 1) && (cb & 1u)) live &= 0xFF000000u;
                 const unsigned gb = (__ballot_sync(FULL, live != 0u) >> gbase) & 0xFFFFu;
                 const int l = gb ? (__ffs(gb) - 1) : 0;
-                const uint32_t lw = __shfl_sync(FULL, live, gbase + l), ww = __shfl_sync(FULL, word, gbase + l);
+                const uint32_t ww = __shfl_sync(FULL, word, gbase + l);
                 if (searching) {
                     if (gb) {
+                        uint32_t lw = ww & 0xFF00FF00u;
+                        if ((base + l) == (cb >> 1) && (cb & 1u)) lw &= 0xFF000000u;
                         const uint32_t odd = (lw & 0x0000FF00u) ? 0u : 1u;
                         b = 2 * (base + l) + odd;
                         cnt = (ww >> (odd * 16u)) & 0xFFu;
@@ -296,10 +355,10 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
             unsigned long long nhi = kDeadKey, nlo = kDeadKey;
             uint2 nrow = make_uint2(0u, 0u);
             if (needL && b < NB && tl < cnt) {
-                const HeapEnt k = heap[b * C + tl];
-                nrow = qrow[b * C + tl];
-                nhi = k.hi;
-                nlo = k.lo;
+                const uint4 k = __ldcs(QP(b * C + tl)), r = __ldcs(QP(b * C + tl) + 1);
+                nrow = make_uint2(r.x, r.y);
+                nhi = ((unsigned long long)k.y << 32) | k.x;
+                nlo = ((unsigned long long)k.w << 32) | k.z;
             }
             const unsigned lv = (__ballot_sync(FULL, nhi != kDeadKey) >> gbase) & 0xFFFFu;
             if (needL) {
@@ -318,13 +377,14 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
             }
         }
 
+        PCLK(1);
         // ---- (4) extract the minimum key of the bucket: (dist, hops, id) lexicographic -------------------------------
         bool run = (st == 1);
-        const uint32_t k0 = run ? (uint32_t)(khi >> 32) : 0xFFFFFFFFu;
+        const uint32_t k0 = (run && khi != kDeadKey) ? (uint32_t)(khi >> 32) : 0xFFFFFFFFu;
         const uint32_t m0 = __reduce_min_sync(gmask, k0);
         bool mine = run && k0 == m0 && khi != kDeadKey;
         unsigned gbm = (__ballot_sync(FULL, mine) >> gbase) & 0xFFFFu;
-        if (__ballot_sync(FULL, __popc(gbm) > 1)) { // high words tie somewhere: full 128-bit reduction
+        if (__ballot_sync(FULL, (gbm & (gbm - 1)) != 0)) { // high words tie somewhere: full 128-bit reduction
             const uint32_t k1 = (uint32_t)khi, k2 = (uint32_t)(klo >> 32), k3 = (uint32_t)klo;
             const uint32_t m1 = __reduce_min_sync(gmask, mine ? k1 : 0xFFFFFFFFu);
             mine = mine && k1 == m1;
@@ -338,7 +398,7 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
         const int wl = gbase + (gbm ? (__ffs(gbm) - 1) : 0);
         const unsigned long long chi = __shfl_sync(FULL, khi, wl), clo = __shfl_sync(FULL, klo, wl);
         const uint32_t rb = __shfl_sync(FULL, rowB, wl), dg = __shfl_sync(FULL, deg, wl);
-        const uint32_t cur = (uint32_t)clo, hc = (uint32_t)(clo >> 32);
+        const uint32_t cur = (uint32_t)clo;
         const double dc = __longlong_as_double((long long)chi);
         // loop condition of ocw_seperator.cpp:88-90
         if (run && (cur == (src ^ 1u) || 2 * dc > best)) {
@@ -347,16 +407,73 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
         }
         if (run) {
             if (lane == wl) { // extract_top: the key becomes a tombstone
-                heap[cb * C + tl].hi = kDeadKey;
+                __stcs(reinterpret_cast<unsigned long long *>(QP(cb * C + tl)), kDeadKey);
                 khi = kDeadKey;
                 atomicSub(&cl[cb >> 1], 0x0100u << clShift(cb));
             }
             liveRegs--;
             settledN++;
         }
+        __syncwarp(FULL); // the tombstone and the counter update are visible to the scan below
         const uint32_t side = cur & 1u;
-        const uint32_t hNew = hc + 1;
+        const uint32_t hNew = (uint32_t)(clo >> 32) + 1;
+        const uint32_t stamp = P.stampBase + wi + 1u;
 
+        PCLK(2);
+        // ---- (4b) bucket exhausted by this extraction: find the next one and issue its loads NOW, so that they are in
+        // flight during the relax phase below instead of in front of the next extraction.  Nothing here waits for the
+        // loaded keys (the number of live keys comes from the counters).  A push of the relax phase that lands at or
+        // before the bucket loaded here makes the registers stale: `dirty` below, and the slow path (3) rescans from
+        // `lo`, the bucket of the node being settled.
+        lo = cb;
+        const bool early = run && liveRegs == 0;
+        if (__ballot_sync(FULL, early)) {
+            uint32_t b = NB, cnt = 0, nlive = 0;
+            bool searching = early;
+            uint32_t base = cb >> 1;
+            while (__ballot_sync(FULL, searching)) {
+                const uint32_t wd = base + tl;
+                const uint32_t word = (searching && wd < nclWords) ? cl[wd] : 0u;
+                uint32_t live = word & 0xFF00FF00u;
+                if (wd == (cb >> 1) && (cb & 1u)) live &= 0xFF000000u;
+                const unsigned gb = (__ballot_sync(FULL, live != 0u) >> gbase) & 0xFFFFu;
+                const int l = gb ? (__ffs(gb) - 1) : 0;
+                const uint32_t ww = __shfl_sync(FULL, word, gbase + l);
+                if (searching) {
+                    if (gb) {
+                        uint32_t lw = ww & 0xFF00FF00u;
+                        if ((base + l) == (cb >> 1) && (cb & 1u)) lw &= 0xFF000000u;
+                        const uint32_t odd = (lw & 0x0000FF00u) ? 0u : 1u;
+                        b = 2 * (base + l) + odd;
+                        cnt = (ww >> (odd * 16u)) & 0xFFu;
+                        nlive = (ww >> (odd * 16u + 8u)) & 0xFFu;
+                        searching = false;
+                    } else {
+                        base += TW;
+                        if (base >= nclWords) searching = false; // nothing queued right now
+                    }
+                }
+            }
+            if (early) {
+                if (b >= NB) {
+                    needLoad = true; // empty unless this step pushes something: (3) decides after the relax phase
+                } else {
+                    khi = kDeadKey;
+                    klo = kDeadKey;
+                    if (tl < cnt) {
+                        const uint4 k = __ldcs(QP(b * C + tl)), r = __ldcs(QP(b * C + tl) + 1);
+                        khi = ((unsigned long long)k.y << 32) | k.x;
+                        klo = ((unsigned long long)k.w << 32) | k.z;
+                        rowB = r.x;
+                        deg = r.y;
+                    }
+                    cb = b;
+                    liveRegs = nlive;
+                }
+            }
+        }
+
+        PCLK(3);
         // ---- (5) relax the arcs of the settled node, 16 per pass ------------------------------------------------------
         for (uint32_t c0 = 0; __ballot_sync(FULL, run && c0 < dg); c0 += TW) {
             if (run && touchedN + TW > caps.touchedCap) {
@@ -373,10 +490,10 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
                 const Arc arc = G.arcs[rb + c0 + tl];
                 nbr = (uint32_t)arc.nbr & 0x7FFFFFFFu;
                 w = arc.w;
-                act = arc.nbr >= 0; // blacklisted neighbours are skipped (:98-99)
-                nrow = Q.rowinfo[nbr]; // used only if a key is pushed; in flight while the label is probed
+                act = arc.nbr >= 0;    // blacklisted neighbours are skipped (:98-99)
             }
             arcsN += __popc((__ballot_sync(FULL, act) >> gbase) & 0xFFFFu);
+            PCLK(4);
             const double dS = dc + w;         // totalStayDist  (:104)
             const double dX = dc + (1.0 - w); // totalCrossDist (:107-108)
             const bool creatS = dS + dc <= best0, creatX = dX + dc <= best0; // label pruning, see ocw_search.cuh
@@ -384,7 +501,8 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
             // ---- label table: bitmap-arbitrated open addressing ---------------------------------------------------
             int slot = -1;
             bool isNew = false;
-            Entry e = emptyEntry();
+            double dA = kUnlabelled, dB = kUnlabelled; // label of the side the stay arc reaches / of the other side
+            uint32_t hA = kUnlabelledHops, hB = kUnlabelledHops;
             if (act) {
                 uint32_t s = (nbr * 0x9E3779B1u) >> tabShift;
                 while (true) {
@@ -398,25 +516,27 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
                         }
                         // another lane claimed it for its own (different) neighbour in this very step
                     } else {
-                        e = loadEntry(&tab[s]);
+                        const Entry e = loadEntryCS(TABP(s));
                         if (e.key == nbr && e.flags == stamp) {
                             slot = (int)s;
+                            dA = side ? e.d1 : e.d0;
+                            dB = side ? e.d0 : e.d1;
+                            hA = side ? e.h1 : e.h0;
+                            hB = side ? e.h0 : e.h1;
                             break;
                         }
                     }
                     s = (s + 1) & tabMask;
                 }
-                if (isNew || slot < 0) e = emptyEntry();
             }
             touchedN += __popc((__ballot_sync(FULL, isNew) >> gbase) & 0xFFFFu);
+            PCLK(5);
 
-            bool accS = false, accX = false, evS = false, evX = false, ovf = false, dirty = false;
+            bool accS = false, accX = false, evS = false, evX = false;
+            const bool hadA = dA < kUnlabelled, hadB = dB < kUnlabelled;
             double DS = 0, DX = 0;
             uint32_t HS = 0, HX = 0;
             if (slot >= 0) {
-                double dA = side ? e.d1 : e.d0, dB = side ? e.d0 : e.d1;
-                uint32_t hA = side ? e.h1 : e.h0, hB = side ? e.h0 : e.h1;
-                const bool hadA = dA < kUnlabelled, hadB = dB < kUnlabelled;
                 // updatePaths(stayNeighbor, ...)   (:59-84)
                 if (!hadA)
                     accS = dS < kInfDist && (creatS || dS + dB <= best0);
@@ -441,70 +561,8 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
                     HX = hB + hA;
                     evX = DX <= best0;
                 }
-                if (accS || accX) {
-                    if (side) {
-                        e.d1 = dA;
-                        e.h1 = hA;
-                        e.d0 = dB;
-                        e.h0 = hB;
-                    } else {
-                        e.d0 = dA;
-                        e.h0 = hA;
-                        e.d1 = dB;
-                        e.h1 = hB;
-                    }
-                    e.key = nbr;
-                    e.flags = stamp;
-                    storeEntry(&tab[slot], e);
-#pragma unroll
-                    for (int k = 0; k < 2; ++k) {
-                        if (!(k ? accX : accS)) continue;
-                        const uint32_t sd = k ? (side ^ 1u) : side;
-                        const double d = k ? dX : dS;
-                        // a superseded key leaves the queue now
-                        if (k ? hadB : hadA) {
-                            const uint32_t oldq = pq[2 * slot + sd].y;
-                            if (oldq != kNoQpos) {
-                                heap[oldq].hi = kDeadKey;
-                                const uint32_t ob = oldq / C;
-                                atomicSub(&cl[ob >> 1], 0x0100u << clShift(ob));
-                                dirty |= ob == cb;
-                            }
-                        }
-                        uint32_t qpos = kNoQpos;
-                        if (2 * d <= best0) { // queue admission: only nodes that can still be extracted
-                            const uint32_t bk = bucketOf(d, Q.scaleU, Q.scaleB, NB - 1);
-                            const uint32_t sh = clShift(bk);
-                            const uint32_t pos = (atomicAdd(&cl[bk >> 1], 0x0101u << sh) >> sh) & 0xFFu;
-                            dirty |= bk == cb;
-                            SMS_CHK(bk >= cb);
-                            if (pos >= C) {
-                                ovf = true;
-                            } else {
-                                qpos = bk * C + pos;
-                                HeapEnt q;
-                                q.hi = (unsigned long long)__double_as_longlong(d);
-                                q.lo = ((unsigned long long)hNew << 32) | (2 * nbr + sd);
-                                heap[qpos] = q;
-                                qrow[qpos] = nrow;
-                                // its arcs are read when it is extracted
-                                if (nrow.y) {
-                                    asm volatile("prefetch.global.L2 [%0];" ::"l"(G.arcs + nrow.x));
-                                    asm volatile("prefetch.global.L2 [%0];" ::"l"(G.arcs + nrow.x + nrow.y - 1));
-                                }
-                            }
-                        }
-                        pq[2 * slot + sd] = make_uint2(cur, qpos);
-                    }
-                }
             }
-            if ((__ballot_sync(FULL, ovf) >> gbase) & 0xFFFFu) {
-                overflow = 1;
-                st = 2;
-                run = false;
-            }
-            if ((__ballot_sync(FULL, dirty) >> gbase) & 0xFFFFu) needLoad = true;
-            // ---- replay of the record logic in adjacency order (:71-82) -------------------------------------------
+            // ---- replay of the record logic in adjacency order (:71-82), before the stores so that its operands die ----
             unsigned evm = (__ballot_sync(FULL, evS || evX) >> gbase) & 0xFFFFu;
             if (!run) evm = 0;
             while (__ballot_sync(FULL, evm != 0)) {
@@ -520,7 +578,7 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
                     for (int k = 0; k < 2; ++k) {
                         if (!(k ? eX : eS)) continue;
                         const double D = k ? D1 : D0;
-                        const double H = (double)(k ? H1 : H0);
+                        const uint32_t H = k ? H1 : H0;
                         bool push = false;
                         if (D < best || (D == best && H < bestHop)) {
                             best = D;
@@ -536,22 +594,93 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
                                 run = false;
                                 evm = 0;
                             } else {
-                                if (tl == 0) hist[histN] = 2 * nb + (k ? (side ^ 1u) : side);
+                                if (tl == 0) *HISTP(histN) = 2 * nb + (k ? (side ^ 1u) : side);
                                 histN++;
                             }
                         }
                     }
                 }
             }
+            PCLK(6);
+            // ---- store the label, retire superseded keys, push the new ones ---------------------------------------
+            bool ovf = false, dirty = false;
+            // the row of the neighbour travels with its key: one 8-byte read per PUSHING lane (about one per settled node)
+            if ((accS && 2 * dS <= best0) || (accX && 2 * dX <= best0)) nrow = Q.rowinfo[nbr];
+            if (accS || accX) {
+                Entry e;
+                e.d0 = side ? dB : dA;
+                e.d1 = side ? dA : dB;
+                e.h0 = side ? hB : hA;
+                e.h1 = side ? hA : hB;
+                e.key = nbr;
+                e.flags = stamp;
+                storeEntryCS(TABP(slot), e);
+#pragma unroll
+                for (int k = 0; k < 2; ++k) {
+                    if (!(k ? accX : accS)) continue;
+                    const uint32_t sd = k ? (side ^ 1u) : side;
+                    const double d = k ? dX : dS;
+                    // a superseded key leaves the queue now
+                    if (k ? hadB : hadA) {
+                        const uint32_t oldq = __ldcs(PQP(2 * slot + sd)).y;
+                        if (oldq != kNoQpos) {
+                            __stcs(reinterpret_cast<unsigned long long *>(QP(oldq)), kDeadKey);
+                            const uint32_t ob = oldq / C;
+                            atomicSub(&cl[ob >> 1], 0x0100u << clShift(ob));
+                            dirty |= ob == cb;
+                        }
+                    }
+                    uint32_t qpos = kNoQpos;
+                    if (2 * d <= best0) { // queue admission: only nodes that can still be extracted
+                        const uint32_t bk = bucketOf(d, Q.scaleU, Q.scaleB, NB - 1);
+                        const uint32_t sh = clShift(bk);
+                        const uint32_t pos = (atomicAdd(&cl[bk >> 1], 0x0101u << sh) >> sh) & 0xFFu;
+                        dirty |= bk <= cb; // at or before the bucket held in registers (which may be ahead of this node's)
+                        SMS_CHK(bk >= lo);
+                        if (pos >= C) {
+                            ovf = true;
+                        } else {
+                            qpos = bk * C + pos;
+                            const unsigned long long dbits = (unsigned long long)__double_as_longlong(d);
+                            __stcs(QP(qpos), make_uint4((uint32_t)dbits, (uint32_t)(dbits >> 32), 2 * nbr + sd, hNew));
+                            __stcs(QP(qpos) + 1, make_uint4(nrow.x, nrow.y, 0u, 0u));
+                            if (nrow.y) { // its arcs are read when it is extracted
+                                asm volatile("prefetch.global.L2 [%0];" ::"l"(G.arcs + nrow.x));
+                                asm volatile("prefetch.global.L2 [%0];" ::"l"(G.arcs + nrow.x + nrow.y - 1));
+                            }
+                        }
+                    }
+                    __stcs(PQP(2 * slot + sd), make_uint2(cur, qpos));
+                }
+            }
+            if ((__ballot_sync(FULL, ovf) >> gbase) & 0xFFFFu) {
+                overflow = 1;
+                st = 2;
+                run = false;
+            }
+            if ((__ballot_sync(FULL, dirty) >> gbase) & 0xFFFFu) needLoad = true;
             __syncwarp(FULL); // keys, labels and counters of this pass are visible to the next extraction
+            PCLK(7);
         }
+#ifdef SMSGPU_PAIRS_CLOCKS
+        piters++;
+#endif
         if (run && liveRegs == 0) needLoad = true;
     }
-    if (lane == 0 && acc[2]) {
-        atomicAdd(&R.counters[2], (unsigned long long)acc[0]);
-        atomicAdd(&R.counters[3], (unsigned long long)acc[1]);
-        atomicAdd(&R.counters[4], (unsigned long long)acc[2]);
+#ifdef SMSGPU_PAIRS_CLOCKS
+    if (lane == 0 && (blockIdx.x % 97) == 0 && warpInCta == 0)
+        printf("PCLK blk %d iters %lld fin+fetch %lld slowload %lld extract %lld early %lld arc %lld probe %lld relax+replay %lld store+push %lld\n",
+               (int)blockIdx.x, piters, pclk[0], pclk[1], pclk[2], pclk[3], pclk[4], pclk[5], pclk[6], pclk[7]);
+#endif
+    if (lane == 0 && accSources) {
+        atomicAdd(&R.counters[2], accArcs);
+        atomicAdd(&R.counters[3], accSettled);
+        atomicAdd(&R.counters[4], (unsigned long long)accSources);
     }
+#undef TABP
+#undef PQP
+#undef QP
+#undef HISTP
 }
 
 } // namespace smsgpu

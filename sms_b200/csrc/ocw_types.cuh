@@ -75,6 +75,7 @@ struct TileCaps {
     // presence bitmap that arbitrates the label table.  nbuckets == 0 selects the heap engine.
     uint32_t nbuckets;   // buckets over [0, bestInit / 2]; heapCap == nbuckets * bucketCap
     uint32_t bucketCap;  // entries per bucket (<= 32: one coalesced load per pop)
+    uint32_t pairs;      // pairs engine (ocw_search_pairs.cuh): the queue is an array of 32-byte entries {key, row}
 };
 
 // bytes of one tile's working memory
@@ -90,8 +91,8 @@ __host__ __device__ inline size_t tileBytes(const TileCaps &c) {
     b += (size_t)(2 * c.walkCap + 2) * sizeof(double); // plen
     b += (size_t)c.chordCap * 4 * sizeof(int32_t);     // chords
     b += (size_t)c.chordCap * 0 + (size_t)(4 * c.walkCap + 8) * sizeof(int32_t); // covered list
-    b = (b + 7) & ~(size_t)7;
-    if (c.nbuckets) b += (size_t)c.heapCap * 2 * sizeof(uint32_t); // pairs engine: {first arc, degree} per queue entry
+    b = (b + 31) & ~(size_t)31;
+    if (c.pairs) b += (size_t)c.heapCap * 32; // pairs engine: queue entries {dist, hops|id, first arc, degree}, one sector each
     return (b + 31) & ~(size_t)31;
 }
 

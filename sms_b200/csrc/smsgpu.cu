@@ -119,6 +119,7 @@ struct smsgpu_ctx {
 
     // graph (uploaded once)
     DevBuf dRowptr, dCol, dEid, dArcs;
+    DevBuf dPairsArgs;        // PairsKArgs of the launch in flight
     DevBuf dRowinfo;          // uint2[n] {first arc, degree}: pairs engine (tier 1)
     bool pairs = false;       // tier 1 runs the pairs engine (ocw_search_pairs.cuh)
     float pairsScaleU = 0.f;  // bucket map of the pairs engine (PairsParams)
@@ -238,7 +239,12 @@ cudaError_t launchSearch(smsgpu_ctx *c, int tierIdx, const GraphDev &G, const Se
     if (t.pairs) {
         cudaError_t e = cudaFuncSetAttribute(ocwSearchPairsKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t.smemBytes);
         if (e != cudaSuccess) return e;
-        const PairsParams Q{c->dRowinfo.as<uint2>(), c->pairsScaleU, c->pairsScaleB};
+        PairsKArgs K{G, P, R, t.caps};
+        e = c->dPairsArgs.ensure(sizeof K);
+        if (e != cudaSuccess) return e;
+        e = cudaMemcpyAsync(c->dPairsArgs.p, &K, sizeof K, cudaMemcpyHostToDevice, c->stream); // pageable source: staged before return
+        if (e != cudaSuccess) return e;
+        const PairsParams Q{c->dPairsArgs.as<PairsKArgs>(), c->dRowinfo.as<uint2>(), c->pairsScaleU, c->pairsScaleB};
         ocwSearchPairsKernel<<<t.ctas, 128, t.smemBytes, c->stream>>>(G, Q, P, R, t.caps, t.scratch.as<unsigned char>());
         return cudaGetLastError();
     }
@@ -294,6 +300,7 @@ void configureTiers(smsgpu_ctx *c) {
                 t.caps.nbuckets = pnb;
                 t.caps.bucketCap = pbc;
                 t.caps.heapCap = pnb * pbc;
+                t.caps.pairs = 1;
                 t.pairs = true;
                 const int pairTiles = 2 * (128 / 32);
                 t.smemBytes = hotBytes(t.caps) * pairTiles;
@@ -480,7 +487,7 @@ void smsgpu_destroy(smsgpu_ctx *ctx) {
     cudaSetDevice(ctx->device);
     smsgpu_comm_destroy(ctx);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-    DevBuf *dev[] = {&ctx->dRowinfo, &ctx->dRowptr, &ctx->dCol, &ctx->dEid, &ctx->dArcs, &ctx->dX, &ctx->dBl, &ctx->dSources,
+    DevBuf *dev[] = {&ctx->dPairsArgs, &ctx->dRowinfo, &ctx->dRowptr, &ctx->dCol, &ctx->dEid, &ctx->dArcs, &ctx->dX, &ctx->dBl, &ctx->dSources,
                      &ctx->tier[0].scratch, &ctx->tier[1].scratch, &ctx->tier[2].scratch, &ctx->tier[3].scratch, &ctx->rNode, &ctx->rEid,
                      &ctx->rStay, &ctx->rCutOff, &ctx->rCutLen, &ctx->rCutSrc, &ctx->rCutSeq, &ctx->rCutTier, &ctx->rValid,
                      &ctx->labSrc, &ctx->labNode, &ctx->labHops, &ctx->labDist, &ctx->srcTier, &ctx->srcArcs,
