@@ -38,6 +38,8 @@ struct PairsKArgs {
     TileCaps caps;
 };
 
+constexpr uint32_t kPairsSaveWords = 32 + 6 * 32; // shared-memory save area of one warp (state of its two searches)
+
 struct PairsParams {
     const PairsKArgs *kargs;
     const uint2 *rowinfo; // [n] {first arc, degree} of every vertex (32-bit arc indices: 2m < 2^32)
@@ -151,6 +153,11 @@ __device__ __noinline__ int finishSourcePairs(const PairsKArgs *K, unsigned char
             }
         }
         counted = 1;
+        if (T.lane == 0) { // round totals
+            atomicAdd(&R.counters[2], (unsigned long long)arcs);
+            atomicAdd(&R.counters[3], (unsigned long long)settled);
+            atomicAdd(&R.counters[4], 1ull);
+        }
     } else if (T.lane == 0) {
         const unsigned long long k = atomicAdd(P.ovfCount, 1ull);
         P.ovfList[k] = srcIdx;
@@ -187,8 +194,7 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
     const int warpInCta = threadIdx.x >> 5;
     const size_t tb = tileBytes(caps);
     const uint32_t hbw = (uint32_t)(hotBytes(caps) >> 2); // hot words of one half
-    unsigned char *const warpScratch = scratch + ((size_t)blockIdx.x * (blockDim.x >> 5) + warpInCta) * 2 * tb;
-    unsigned char *const tileB = warpScratch + (gbase ? tb : 0);
+    unsigned char *const tileB = scratch + (((size_t)blockIdx.x * (blockDim.x >> 5) + warpInCta) * 2 + (gbase >> 4)) * tb;
 
     // this half's working memory: offsets inside the tile as carveTileMem lays it out (uniform: functions of caps)
     uint32_t offPq, offHist, offQrow;
@@ -210,49 +216,43 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
     const uint32_t tabMask = caps.tabCap - 1, tabShift = caps.tabShift;
     const uint32_t total = (uint32_t)(P.worklist ? P.nwork : P.nsrc);
 
-    // per-source state, identical in the 16 lanes of a half
-    int st = 0; // 0 idle (needs a source), 1 running, 2 ended (to be finished), 3 no work left
-    uint32_t src = 0, wi = 0;
-    double best = 0.0;
-    uint32_t bestHop = 0; // bestHopDist: a double in the reference (:52) that only ever holds small integers
-    uint32_t histN = 0, touchedN = 0, arcsN = 0, settledN = 0;
-    int overflow = 0;
-    uint32_t cb = 0, lo = 0, liveRegs = 0; // bucket in registers, bucket of the last extraction, live keys in registers
-    bool needLoad = true;
-    // the current bucket's keys, one per lane, with the row of their vertex
-    unsigned long long khi = kDeadKey, klo = kDeadKey;
-    uint32_t rowB = 0, deg = 0;
-    unsigned long long accArcs = 0, accSettled = 0;
-    uint32_t accSources = 0; // same in all lanes
+    // State of the two searches of this warp.  Registers inside the stepping loop; saved to shared memory around the
+    // (cold, register-hungry, not inlined) finishing call so that nothing of it is live across that call -- otherwise
+    // the register allocator spills it at its definitions and uses, i.e. inside the hot loop (measured: half of the
+    // L1->L2 traffic of the first version of this kernel was spill traffic).
+    //   per half (16 words, written by its lane 0): st src wi best(2) bestHop histN touchedN arcsN settledN overflow
+    //                                               cb lo liveRegs needLoad
+    //   per lane (6 words): the current bucket's key and the row of its vertex
+    uint32_t *const svU = smemw + (uint32_t)(blockDim.x >> 5) * 2 * hbw + (uint32_t)warpInCta * kPairsSaveWords + (gbase >> 4) * 16;
+    uint32_t *const svK = smemw + (uint32_t)(blockDim.x >> 5) * 2 * hbw + (uint32_t)warpInCta * kPairsSaveWords + 32 + lane;
+    if (tl == 0) {
+        svU[0] = 0; // st: idle
+        svU[14] = 1;
+    }
+    __syncwarp(FULL);
 #ifdef SMSGPU_PAIRS_CLOCKS
     long long pclk[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, plast = clock64(), piters = 0;
 #endif
 
     while (true) {
-        // ---- (1) finish ended sources: the whole warp works for one half at a time ---------------------------------
-        const unsigned finb = __ballot_sync(FULL, st == 2);
-        if (finb) {
-#pragma unroll 1
-            for (int gg = 0; gg < 2; ++gg) {
-                if (!(finb & (1u << (gg * 16)))) continue; // warp-uniform
-                const int sl = gg * 16;
-                const double fbest = __shfl_sync(FULL, best, sl);
-                const uint32_t fhist = __shfl_sync(FULL, histN, sl), ftouched = __shfl_sync(FULL, touchedN, sl);
-                const uint32_t farcs = __shfl_sync(FULL, arcsN, sl), fsettled = __shfl_sync(FULL, settledN, sl);
-                const int fovf = __shfl_sync(FULL, overflow, sl);
-                const uint32_t fsrc = __shfl_sync(FULL, src, sl);
-                const uint32_t fwi = __shfl_sync(FULL, wi, sl);
-                const int32_t fidx = P.worklist ? P.worklist[fwi] : (int32_t)fwi;
-                if (finishSourcePairs(Q.kargs, warpScratch + (gg ? tb : 0),
-                                      reinterpret_cast<unsigned char *>(smemw + (uint32_t)(warpInCta * 2 + gg) * hbw), fbest, fhist,
-                                      ftouched, farcs, fsettled, fovf, fsrc, fidx)) {
-                    accArcs += farcs;
-                    accSettled += fsettled;
-                    accSources += 1;
-                }
-            }
-            if (st == 2) st = 0;
-        }
+        // per-source state, identical in the 16 lanes of a half
+        int st = (int)svU[0]; // 0 idle (needs a source), 1 running, 2 ended (to be finished), 3 no work left
+        uint32_t src = svU[1], wi = svU[2];
+        double best = __hiloint2double((int)svU[4], (int)svU[3]);
+        uint32_t bestHop = svU[5]; // bestHopDist: a double in the reference (:52) that only ever holds small integers
+        uint32_t histN = svU[6], touchedN = svU[7], arcsN = svU[8], settledN = svU[9];
+        int overflow = (int)svU[10];
+        uint32_t cb = svU[11], lo = svU[12], liveRegs = svU[13]; // bucket in registers, bucket of the last extraction, live keys
+        bool needLoad = svU[14] != 0;
+        // the current bucket's keys, one per lane, with the row of their vertex
+        unsigned long long khi = ((unsigned long long)svK[32] << 32) | svK[0], klo = ((unsigned long long)svK[96] << 32) | svK[64];
+        uint32_t rowB = svK[128], deg = svK[160];
+        bool done = false;
+        unsigned finb = 0;
+
+      while (true) { // the stepping loop: leaves when a half has ended its source (or no work is left)
+        finb = __ballot_sync(FULL, st == 2);
+        if (finb) break;
 
         // ---- (2) idle halves fetch the next source ------------------------------------------------------------------
         if (__ballot_sync(FULL, st == 0)) {
@@ -318,8 +318,11 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
             __syncwarp(FULL);
         }
         if (__ballot_sync(FULL, st == 1) == 0) {
-            if (__ballot_sync(FULL, st != 3) == 0) break; // both halves are out of work
-            continue;                                     // a skipped source: fetch again
+            if (__ballot_sync(FULL, st != 3) == 0) { // both halves are out of work
+                done = true;
+                break;
+            }
+            continue; // a skipped source: fetch again
         }
 
         PCLK(0);
@@ -666,16 +669,45 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
         piters++;
 #endif
         if (run && liveRegs == 0) needLoad = true;
-    }
-#ifdef SMSGPU_PAIRS_CLOCKS
-    if (lane == 0 && (blockIdx.x % 97) == 0 && warpInCta == 0)
-        printf("PCLK blk %d iters %lld fin+fetch %lld slowload %lld extract %lld early %lld arc %lld probe %lld relax+replay %lld store+push %lld\n",
-               (int)blockIdx.x, piters, pclk[0], pclk[1], pclk[2], pclk[3], pclk[4], pclk[5], pclk[6], pclk[7]);
-#endif
-    if (lane == 0 && accSources) {
-        atomicAdd(&R.counters[2], accArcs);
-        atomicAdd(&R.counters[3], accSettled);
-        atomicAdd(&R.counters[4], (unsigned long long)accSources);
+      } // stepping loop
+        if (done) break;
+
+        // ---- (1) finish ended sources: state to shared memory, then the whole warp works for one half at a time ---------
+        if (tl == 0) {
+            svU[0] = st == 2 ? 0u : (uint32_t)st; // an ended half is idle afterwards
+            svU[1] = src;
+            svU[2] = wi;
+            svU[3] = (uint32_t)__double2loint(best);
+            svU[4] = (uint32_t)__double2hiint(best);
+            svU[5] = bestHop;
+            svU[6] = histN;
+            svU[7] = touchedN;
+            svU[8] = arcsN;
+            svU[9] = settledN;
+            svU[10] = (uint32_t)overflow;
+            svU[11] = cb;
+            svU[12] = lo;
+            svU[13] = liveRegs;
+            svU[14] = needLoad ? 1u : 0u;
+        }
+        svK[0] = (uint32_t)khi;
+        svK[32] = (uint32_t)(khi >> 32);
+        svK[64] = (uint32_t)klo;
+        svK[96] = (uint32_t)(klo >> 32);
+        svK[128] = rowB;
+        svK[160] = deg;
+        __syncwarp(FULL);
+#pragma unroll 1
+        for (int gg = 0; gg < 2; ++gg) {
+            if (!(finb & (1u << (gg * 16)))) continue; // warp-uniform
+            const uint32_t *u = smemw + (uint32_t)(blockDim.x >> 5) * 2 * hbw + (uint32_t)warpInCta * kPairsSaveWords + gg * 16;
+            const uint32_t fwi = u[2];
+            const int32_t fidx = P.worklist ? P.worklist[fwi] : (int32_t)fwi;
+            finishSourcePairs(Q.kargs, scratch + (((size_t)blockIdx.x * (blockDim.x >> 5) + warpInCta) * 2 + gg) * tileBytes(caps),
+                              reinterpret_cast<unsigned char *>(smemw + (uint32_t)(warpInCta * 2 + gg) * hbw),
+                              __hiloint2double((int)u[4], (int)u[3]), u[6], u[7], u[8], u[9], (int)u[10], u[1], fidx);
+        }
+        __syncwarp(FULL);
     }
 #undef TABP
 #undef PQP

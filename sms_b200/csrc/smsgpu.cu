@@ -303,7 +303,7 @@ void configureTiers(smsgpu_ctx *c) {
                 t.caps.pairs = 1;
                 t.pairs = true;
                 const int pairTiles = 2 * (128 / 32);
-                t.smemBytes = hotBytes(t.caps) * pairTiles;
+                t.smemBytes = hotBytes(t.caps) * pairTiles + (128 / 32) * kPairsSaveWords * sizeof(uint32_t);
                 int nb2 = 0;
                 cudaFuncSetAttribute(ocwSearchPairsKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t.smemBytes);
                 if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb2, ocwSearchPairsKernel, 128, t.smemBytes) != cudaSuccess) {
