@@ -508,6 +508,41 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
             uint32_t hA = kUnlabelledHops, hB = kUnlabelledHops;
             if (act) {
                 uint32_t s = (nbr * 0x9E3779B1u) >> tabShift;
+#ifndef SMSGPU_PAIRS_PROBE1 // default: two slots per round trip (-11 % on the 1M/4M round); PROBE1 = one slot
+                // two slots per round trip: the 32 lanes wait for the slowest probe sequence of the pass
+                while (true) {
+                    const uint32_t bit = 1u << (s & 31);
+                    if (!(bm[s >> 5] & bit)) {
+                        if (!(creatS || creatX)) break;
+                        if (!(atomicOr(&bm[s >> 5], bit) & bit)) {
+                            isNew = true;
+                            slot = (int)s;
+                            break;
+                        }
+                        s = (s + 1) & tabMask;
+                        continue;
+                    }
+                    const uint32_t s1 = (s + 1) & tabMask;
+                    const bool occ1 = (bm[s1 >> 5] >> (s1 & 31)) & 1u;
+                    Entry e = loadEntryCS(TABP(s));
+                    if (occ1) {
+                        const Entry e1 = loadEntryCS(TABP(s1));
+                        if (!(e.key == nbr && e.flags == stamp) && e1.key == nbr && e1.flags == stamp) {
+                            e = e1;
+                            s = s1;
+                        }
+                    }
+                    if (e.key == nbr && e.flags == stamp) {
+                        slot = (int)s;
+                        dA = side ? e.d1 : e.d0;
+                        dB = side ? e.d0 : e.d1;
+                        hA = side ? e.h1 : e.h0;
+                        hB = side ? e.h0 : e.h1;
+                        break;
+                    }
+                    s = occ1 ? ((s1 + 1) & tabMask) : s1;
+                }
+#else
                 while (true) {
                     const uint32_t bit = 1u << (s & 31);
                     if (!(bm[s >> 5] & bit)) {
@@ -531,6 +566,7 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
                     }
                     s = (s + 1) & tabMask;
                 }
+#endif
             }
             touchedN += __popc((__ballot_sync(FULL, isNew) >> gbase) & 0xFFFFu);
             PCLK(5);
@@ -647,10 +683,12 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
                             const unsigned long long dbits = (unsigned long long)__double_as_longlong(d);
                             __stcs(QP(qpos), make_uint4((uint32_t)dbits, (uint32_t)(dbits >> 32), 2 * nbr + sd, hNew));
                             __stcs(QP(qpos) + 1, make_uint4(nrow.x, nrow.y, 0u, 0u));
-                            if (nrow.y) { // its arcs are read when it is extracted
+#ifdef SMSGPU_PAIRS_PREFETCH // measured useless: L2 turns over ~50x between the push of a key and its extraction
+                            if (nrow.y) {
                                 asm volatile("prefetch.global.L2 [%0];" ::"l"(G.arcs + nrow.x));
                                 asm volatile("prefetch.global.L2 [%0];" ::"l"(G.arcs + nrow.x + nrow.y - 1));
                             }
+#endif
                         }
                     }
                     __stcs(PQP(2 * slot + sd), make_uint2(cur, qpos));
