@@ -93,7 +93,7 @@ __device__ inline void carveTileMem(TileMem &M, unsigned char *base, const TileC
     M.qrow = nullptr;
     if (c.nbuckets) {
         M.cl = reinterpret_cast<uint32_t *>(hot);
-        M.bm = reinterpret_cast<uint32_t *>(hot + (size_t)c.nbuckets * 2);
+        M.bm = reinterpret_cast<uint32_t *>(hot + (size_t)c.nbuckets * (c.pairs ? 1 : 2));
     }
     M.tabMask = c.tabCap - 1;
     unsigned char *p = base;

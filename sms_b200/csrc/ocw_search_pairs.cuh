@@ -167,7 +167,7 @@ __device__ __noinline__ int finishSourcePairs(const PairsKArgs *K, unsigned char
 }
 
 #ifndef SMSGPU_PAIRS_MIN_CTAS
-#define SMSGPU_PAIRS_MIN_CTAS 4
+#define SMSGPU_PAIRS_MIN_CTAS 6
 #endif
 
 #ifdef SMSGPU_PAIRS_CLOCKS // instrumentation build: cycles per phase of the lock-step loop, printed by one warp
@@ -209,8 +209,9 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
 #define PQP(i_) (reinterpret_cast<uint2 *>(tileB + offPq) + (i_))
 #define QP(i_) (reinterpret_cast<uint4 *>(tileB + offQrow) + 2 * (i_)) /* queue entry i: [0] key, [1] row */
 #define HISTP(i_) (reinterpret_cast<uint32_t *>(tileB + offHist) + (i_))
-    const uint32_t NB = caps.nbuckets, C = caps.bucketCap;
-    const uint32_t nclWords = NB >> 1, nbmWords = caps.tabCap >> 5;
+    const uint32_t NB = caps.nbuckets;
+    constexpr uint32_t C = 16, CAP = 15; // queue positions per bucket (stride) / usable ones (the counter is a nibble)
+    const uint32_t nclWords = NB >> 2, nbmWords = caps.tabCap >> 5;
     uint32_t *const cl = smemw + (uint32_t)(warpInCta * 2 + (gbase >> 4)) * hbw; // bucket counters (shared memory)
     uint32_t *const bm = cl + nclWords;                                          // presence bitmap (shared memory)
     const uint32_t tabMask = caps.tabCap - 1, tabShift = caps.tabShift;
@@ -298,7 +299,7 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
                     const uint2 srow = Q.rowinfo[src >> 1];
                     __stcs(QP(0), make_uint4(0u, 0u, src, 0u)); // dist 0, id src, 0 hops
                     __stcs(QP(0) + 1, make_uint4(srow.x, srow.y, 0u, 0u));
-                    cl[0] = 0x0101u; // bucket 0: one appended, one live
+                    cl[0] = 0x11u; // bucket 0: one appended, one live
                 }
                 st = 1;
                 best = P.bestInit;
@@ -332,22 +333,22 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
         if (__ballot_sync(FULL, needL)) {
             uint32_t b = NB, cnt = 0;
             bool searching = needL;
-            uint32_t base = cb >> 1;
+            uint32_t base = cb >> 2;
             while (__ballot_sync(FULL, searching)) {
                 const uint32_t wd = base + tl;
                 const uint32_t word = (searching && wd < nclWords) ? cl[wd] : 0u;
-                uint32_t live = word & 0xFF00FF00u;
-                if (wd == (cb >> 1) && (cb & 1u)) live &= 0xFF000000u;
+                uint32_t live = word & 0xF0F0F0F0u; // four buckets per word: low nibble appended, high nibble live
+                if (wd == (cb >> 2)) live &= 0xFFFFFFFFu << ((cb & 3u) * 8u);
                 const unsigned gb = (__ballot_sync(FULL, live != 0u) >> gbase) & 0xFFFFu;
                 const int l = gb ? (__ffs(gb) - 1) : 0;
                 const uint32_t ww = __shfl_sync(FULL, word, gbase + l);
                 if (searching) {
                     if (gb) {
-                        uint32_t lw = ww & 0xFF00FF00u;
-                        if ((base + l) == (cb >> 1) && (cb & 1u)) lw &= 0xFF000000u;
-                        const uint32_t odd = (lw & 0x0000FF00u) ? 0u : 1u;
-                        b = 2 * (base + l) + odd;
-                        cnt = (ww >> (odd * 16u)) & 0xFFu;
+                        uint32_t lw = ww & 0xF0F0F0F0u;
+                        if ((base + l) == (cb >> 2)) lw &= 0xFFFFFFFFu << ((cb & 3u) * 8u);
+                        const uint32_t byte = (uint32_t)(__ffs(lw) - 1) >> 3;
+                        b = 4 * (base + l) + byte;
+                        cnt = (ww >> (byte * 8u)) & 0xFu;
                         searching = false;
                     } else {
                         base += TW;
@@ -412,7 +413,7 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
             if (lane == wl) { // extract_top: the key becomes a tombstone
                 __stcs(reinterpret_cast<unsigned long long *>(QP(cb * C + tl)), kDeadKey);
                 khi = kDeadKey;
-                atomicSub(&cl[cb >> 1], 0x0100u << clShift(cb));
+                atomicSub(&cl[cb >> 2], 0x10u << ((cb & 3u) * 8u));
             }
             liveRegs--;
             settledN++;
@@ -433,23 +434,23 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
         if (__ballot_sync(FULL, early)) {
             uint32_t b = NB, cnt = 0, nlive = 0;
             bool searching = early;
-            uint32_t base = cb >> 1;
+            uint32_t base = cb >> 2;
             while (__ballot_sync(FULL, searching)) {
                 const uint32_t wd = base + tl;
                 const uint32_t word = (searching && wd < nclWords) ? cl[wd] : 0u;
-                uint32_t live = word & 0xFF00FF00u;
-                if (wd == (cb >> 1) && (cb & 1u)) live &= 0xFF000000u;
+                uint32_t live = word & 0xF0F0F0F0u; // four buckets per word: low nibble appended, high nibble live
+                if (wd == (cb >> 2)) live &= 0xFFFFFFFFu << ((cb & 3u) * 8u);
                 const unsigned gb = (__ballot_sync(FULL, live != 0u) >> gbase) & 0xFFFFu;
                 const int l = gb ? (__ffs(gb) - 1) : 0;
                 const uint32_t ww = __shfl_sync(FULL, word, gbase + l);
                 if (searching) {
                     if (gb) {
-                        uint32_t lw = ww & 0xFF00FF00u;
-                        if ((base + l) == (cb >> 1) && (cb & 1u)) lw &= 0xFF000000u;
-                        const uint32_t odd = (lw & 0x0000FF00u) ? 0u : 1u;
-                        b = 2 * (base + l) + odd;
-                        cnt = (ww >> (odd * 16u)) & 0xFFu;
-                        nlive = (ww >> (odd * 16u + 8u)) & 0xFFu;
+                        uint32_t lw = ww & 0xF0F0F0F0u;
+                        if ((base + l) == (cb >> 2)) lw &= 0xFFFFFFFFu << ((cb & 3u) * 8u);
+                        const uint32_t byte = (uint32_t)(__ffs(lw) - 1) >> 3;
+                        b = 4 * (base + l) + byte;
+                        cnt = (ww >> (byte * 8u)) & 0xFu;
+                        nlive = (ww >> (byte * 8u + 4u)) & 0xFu;
                         searching = false;
                     } else {
                         base += TW;
@@ -480,6 +481,7 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
         // ---- (5) relax the arcs of the settled node, 16 per pass ------------------------------------------------------
         for (uint32_t c0 = 0; __ballot_sync(FULL, run && c0 < dg); c0 += TW) {
             if (run && touchedN + TW > caps.touchedCap) {
+                if (tl == 0) atomicAdd(&R.counters[12], 1ull); // overflow reasons (diagnostics): label table
                 overflow = 1;
                 st = 2;
                 run = false;
@@ -628,6 +630,7 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
                         }
                         if (push && !overflow) {
                             if (histN >= caps.histCap) {
+                                if (tl == 0) atomicAdd(&R.counters[14], 1ull); // history of intermediates
                                 overflow = 1;
                                 st = 2;
                                 run = false;
@@ -665,18 +668,18 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
                         if (oldq != kNoQpos) {
                             __stcs(reinterpret_cast<unsigned long long *>(QP(oldq)), kDeadKey);
                             const uint32_t ob = oldq / C;
-                            atomicSub(&cl[ob >> 1], 0x0100u << clShift(ob));
+                            atomicSub(&cl[ob >> 2], 0x10u << ((ob & 3u) * 8u));
                             dirty |= ob == cb;
                         }
                     }
                     uint32_t qpos = kNoQpos;
                     if (2 * d <= best0) { // queue admission: only nodes that can still be extracted
                         const uint32_t bk = bucketOf(d, Q.scaleU, Q.scaleB, NB - 1);
-                        const uint32_t sh = clShift(bk);
-                        const uint32_t pos = (atomicAdd(&cl[bk >> 1], 0x0101u << sh) >> sh) & 0xFFu;
+                        const uint32_t sh = (bk & 3u) * 8u;
+                        const uint32_t pos = (atomicAdd(&cl[bk >> 2], 0x11u << sh) >> sh) & 0xFu;
                         dirty |= bk <= cb; // at or before the bucket held in registers (which may be ahead of this node's)
                         SMS_CHK(bk >= lo);
-                        if (pos >= C) {
+                        if (pos >= CAP) { // the carry of a full nibble corrupts the counters of a source that is given up anyway
                             ovf = true;
                         } else {
                             qpos = bk * C + pos;
@@ -695,6 +698,7 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
                 }
             }
             if ((__ballot_sync(FULL, ovf) >> gbase) & 0xFFFFu) {
+                if (tl == 0) atomicAdd(&R.counters[13], 1ull); // a bucket is full
                 overflow = 1;
                 st = 2;
                 run = false;

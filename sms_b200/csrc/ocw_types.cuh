@@ -100,7 +100,7 @@ __host__ __device__ inline size_t tileBytes(const TileCaps &c) {
 // Shared memory in tier 1, HBM (L2 resident) in tier 2.
 __host__ __device__ inline size_t hotBytes(const TileCaps &c) {
     if (!c.nbuckets) return 0;
-    return (((size_t)c.nbuckets * 2 + (size_t)c.tabCap / 8) + 31) & ~(size_t)31;
+    return (((size_t)c.nbuckets * (c.pairs ? 1 : 2) + (size_t)c.tabCap / 8) + 31) & ~(size_t)31;
 }
 
 // Raw (pre-dedup) output arena, filled by the search kernel with atomic bump allocation.
