@@ -301,6 +301,9 @@ void configureTiers(smsgpu_ctx *c) {
                 t.caps.bucketCap = pbc;
                 t.caps.heapCap = pnb * pbc;
                 t.caps.pairs = 1;
+                // the table may fill to 3/4 (the other engines stop at 1/2): only the heaviest sources get there, and a longer
+                // probe sequence in tier 1 is far cheaper than a second run in tier 2 (measured: 2/3 of tier 1's overflows)
+                t.caps.touchedCap = std::min<uint32_t>(t.caps.tabCap / 4 * 3, touchedMax);
                 t.pairs = true;
                 const int pairTiles = 2 * (128 / 32);
                 t.smemBytes = hotBytes(t.caps) * pairTiles + (128 / 32) * kPairsSaveWords * sizeof(uint32_t);
