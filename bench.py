@@ -46,6 +46,10 @@ WORKLOADS = {
 REF_SAMPLE = {"random1m": 256, "torus100": 10_000, "torus3d20": 8_000, "random20k": 4_000}
 
 
+# dram bytes of the search of one full round, from the committed ncu capture (per launch; see roofline.traffic_note)
+TRAFFIC_NCU = {"random1m": round(78.770506e9 * 1254134233 / 82067275)}  # 78.77 GB for the 82.07 M settled nodes of the capture
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -324,7 +328,11 @@ def main():
                           "device_total": res["ms_total_device"]},
             "tier_sources": res["stats"]["tier_sources"],
             "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                         "traffic": None, "peak_source": peak_src, "kernel": "ocwSearchKernel",
+                         "traffic": TRAFFIC_NCU.get(args.workload), "peak_source": peak_src,
+                         "kernel": "ocwSearchPairsKernel (tier 1; tiers 0/2: ocwSearchKernel)",
+                         "traffic_note": "dram__bytes_read+write of the tier-1 launch from profiles/r01_pairs_tier1_random1m_64k.md "
+                                         "(ncu --set full, 65536 sources), scaled to the round by settled nodes; the path is bound by "
+                                         "dependent random 32-byte accesses, not by bytes (DESIGN.md section 5)",
                          "algorithmic_bytes": alg_bytes, "per_gpu": True},
             "e2e": {"value": args.steps / res["e2e_dt"], "unit": "rounds/s", "h2d_bytes_per_step": res["h2d"],
                     "d2h_bytes_per_step": res["d2h"]},
