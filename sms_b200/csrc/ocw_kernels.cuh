@@ -61,6 +61,53 @@ __global__ void initTablesKernel(unsigned char *scratch, const size_t tileStride
     }
 }
 
+// ---- longest-first order of the next round's sources -------------------------------------------------------------------
+// A source is ~1250 DEPENDENT steps on one (half-)warp; a 10 000-step source started near the end of the launch keeps
+// the kernel alive for tens of milliseconds with the GPU almost idle.  Ball sizes change slowly from one LP solve to
+// the next, so the sources of a round are issued in descending order of the work they did in the previous round.
+// The unit of the order is a PAIR of consecutive local source indices (2k, 2k+1): in the handler's source list these
+// are the two sides (v,0), (v,1) of one vertex, whose searches are mirror images of each other -- issued together they
+// run on the two halves of one warp and read the same arc rows at the same time (measured: 70 ms of a 920 ms round
+// between pairs kept together and pairs scattered).  1024 bins of 16 settled nodes; the order inside a bin is
+// arbitrary (results do not depend on the issue order).
+constexpr int kOrderBins = 1024;
+constexpr int kOrderShift = 4; // 16 settled nodes per bin
+__device__ __forceinline__ int orderBinOfPair(const uint32_t *__restrict__ work, const long long k, const long long nsrc) {
+    uint32_t w = work[2 * k];
+    if (2 * k + 1 < nsrc) w = max(w, work[2 * k + 1]);
+    return kOrderBins - 1 - (int)min(w >> kOrderShift, (uint32_t)(kOrderBins - 1)); // bin 0 = heaviest
+}
+__global__ void orderHistKernel(const long long nsrc, const uint32_t *__restrict__ work, unsigned int *__restrict__ bins) {
+    __shared__ unsigned int h[kOrderBins];
+    for (int b = threadIdx.x; b < kOrderBins; b += blockDim.x) h[b] = 0;
+    __syncthreads();
+    const long long npairs = nsrc >> 1; // an odd last source goes last (orderScatterKernel)
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < npairs; k += (long long)gridDim.x * blockDim.x)
+        atomicAdd(&h[orderBinOfPair(work, k, nsrc)], 1u);
+    __syncthreads();
+    for (int b = threadIdx.x; b < kOrderBins; b += blockDim.x)
+        if (h[b]) atomicAdd(&bins[b], h[b]);
+}
+__global__ void orderScanKernel(unsigned int *bins) { // bins[0..kOrderBins) counts -> bins[kOrderBins..) running cursors
+    if (threadIdx.x == 0) {
+        unsigned int acc = 0;
+        for (int b = 0; b < kOrderBins; ++b) {
+            bins[kOrderBins + b] = acc;
+            acc += bins[b];
+        }
+    }
+}
+__global__ void orderScatterKernel(const long long nsrc, const uint32_t *__restrict__ work, unsigned int *__restrict__ bins,
+                                   int32_t *__restrict__ order) {
+    const long long npairs = nsrc >> 1;
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < npairs; k += (long long)gridDim.x * blockDim.x) {
+        const unsigned int pos = atomicAdd(&bins[kOrderBins + orderBinOfPair(work, k, nsrc)], 1u);
+        order[2 * (long long)pos] = (int32_t)(2 * k);
+        order[2 * (long long)pos + 1] = (int32_t)(2 * k + 1);
+    }
+    if ((nsrc & 1) && blockIdx.x == 0 && threadIdx.x == 0) order[nsrc - 1] = (int32_t)(nsrc - 1);
+}
+
 // ---- K2-K4 ---------------------------------------------------------------------------------------------------
 #ifndef SMSGPU_FAST_MIN_CTAS
 #define SMSGPU_FAST_MIN_CTAS 5
@@ -156,6 +203,7 @@ __global__ void __launch_bounds__(128, FAST ? SMSGPU_FAST_MIN_CTAS : 1) ocwSearc
             }
             if (T.lane == 0) {
                 R.srcTier[srcIdx] = (int8_t)P.tier;
+                if (R.srcWork) R.srcWork[srcIdx] = (uint32_t)min(S.settled, 0xFFFFFFFFll);
                 if (R.srcArcs) {
                     R.srcArcs[srcIdx] = S.arcs;
                     R.srcSettled[srcIdx] = S.settled;

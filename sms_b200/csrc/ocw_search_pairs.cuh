@@ -38,6 +38,7 @@ struct PairsKArgs {
     TileCaps caps;
 };
 
+constexpr uint32_t kNoItem = 0xFFFFFFFFu;
 constexpr uint32_t kPairsSaveWords = 32 + 6 * 32; // shared-memory save area of one warp (state of its two searches)
 
 struct PairsParams {
@@ -147,6 +148,7 @@ __device__ __noinline__ int finishSourcePairs(const PairsKArgs *K, unsigned char
         }
         if (T.lane == 0) {
             R.srcTier[srcIdx] = (int8_t)P.tier;
+            if (R.srcWork) R.srcWork[srcIdx] = settled;
             if (R.srcArcs) {
                 R.srcArcs[srcIdx] = (long long)arcs;
                 R.srcSettled[srcIdx] = (long long)settled;
@@ -226,10 +228,12 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
     //   per lane (6 words): the current bucket's key and the row of its vertex
     uint32_t *const svU = smemw + (uint32_t)(blockDim.x >> 5) * 2 * hbw + (uint32_t)warpInCta * kPairsSaveWords + (gbase >> 4) * 16;
     uint32_t *const svK = smemw + (uint32_t)(blockDim.x >> 5) * 2 * hbw + (uint32_t)warpInCta * kPairsSaveWords + 32 + lane;
+    uint32_t *const svW = smemw + (uint32_t)(blockDim.x >> 5) * 2 * hbw + (uint32_t)warpInCta * kPairsSaveWords;
     if (tl == 0) {
         svU[0] = 0; // st: idle
         svU[14] = 1;
     }
+    if (lane == 0) svW[15] = kNoItem;
     __syncwarp(FULL);
 #ifdef SMSGPU_PAIRS_CLOCKS
     long long pclk[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, plast = clock64(), piters = 0;
@@ -248,6 +252,7 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
         // the current bucket's keys, one per lane, with the row of their vertex
         unsigned long long khi = ((unsigned long long)svK[32] << 32) | svK[0], klo = ((unsigned long long)svK[96] << 32) | svK[64];
         uint32_t rowB = svK[128], deg = svK[160];
+        uint32_t stash = svW[15]; // second item of a pair this warp owns (warp-uniform), kNoItem if none
         bool done = false;
         unsigned finb = 0;
 
@@ -257,12 +262,39 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
 
         // ---- (2) idle halves fetch the next source ------------------------------------------------------------------
         if (__ballot_sync(FULL, st == 0)) {
-            uint32_t w32 = 0;
-            if (st == 0 && tl == 0) {
-                const unsigned long long w = atomicAdd(P.queueCounter, 1ull);
-                w32 = w >= (unsigned long long)total ? total : (uint32_t)w;
+            // Work items are handed out in PAIRS (2p, 2p+1) -- in the handler's source list the two sides of one vertex,
+            // mirror-image searches that read the same arc rows -- and both items of a pair stay in this warp: two idle
+            // halves start them together; a half that is idle alone starts the first and the second waits in `stash`
+            // for whichever half of this warp is idle next.
+            const unsigned idleb = __ballot_sync(FULL, st == 0);
+            const bool idle0 = idleb & 1u, idle1 = (idleb >> 16) & 1u;
+            uint32_t take0 = kNoItem, take1 = kNoItem;
+            if (idle0 && stash != kNoItem) {
+                take0 = stash;
+                stash = kNoItem;
             }
-            w32 = __shfl_sync(FULL, w32, gbase);
+            if (idle1 && stash != kNoItem) {
+                take1 = stash;
+                stash = kNoItem;
+            }
+            if ((idle0 && take0 == kNoItem) || (idle1 && take1 == kNoItem)) { // warp-uniform
+                unsigned long long pr = 0;
+                if (lane == 0) pr = atomicAdd(P.queueCounter, 1ull);
+                pr = __shfl_sync(FULL, pr, 0);
+                const uint32_t a = 2 * pr < (unsigned long long)total ? (uint32_t)(2 * pr) : total;
+                const uint32_t b = 2 * pr + 1 < (unsigned long long)total ? (uint32_t)(2 * pr + 1) : kNoItem;
+                if (idle0 && take0 == kNoItem) {
+                    take0 = a;
+                    if (idle1 && take1 == kNoItem)
+                        take1 = b == kNoItem ? total : b;
+                    else
+                        stash = b;
+                } else {
+                    take1 = a;
+                    stash = b;
+                }
+            }
+            const uint32_t w32 = gbase ? take1 : take0;
             bool fresh = false;
             if (st == 0) {
                 if (w32 >= total) {
@@ -732,6 +764,7 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
             svU[13] = liveRegs;
             svU[14] = needLoad ? 1u : 0u;
         }
+        if (lane == 0) svW[15] = stash;
         svK[0] = (uint32_t)khi;
         svK[32] = (uint32_t)(khi >> 32);
         svK[64] = (uint32_t)klo;

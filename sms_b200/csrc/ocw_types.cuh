@@ -121,6 +121,7 @@ struct RawOut {
     // per-source
     int8_t *srcTier;       // [nsrc] tier the source finished in, -1 = not finished / skipped
     long long *srcArcs, *srcSettled; // nullable
+    uint32_t *srcWork;     // [nsrc] settled nodes of the source (always written): next round's longest-first order
 };
 
 struct SearchParams {

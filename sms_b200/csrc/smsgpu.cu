@@ -143,6 +143,11 @@ struct smsgpu_ctx {
     DevBuf rNode, rEid, rStay, rCutOff, rCutLen, rCutSrc, rCutSeq, rCutTier, rValid;
     DevBuf labSrc, labNode, labHops, labDist;
     DevBuf srcTier, srcArcs, srcSettled;
+    // history used by the next round (DESIGN.md "issue order"): per-source work, the longest-first order built from it,
+    // and whether the shared-memory tier is worth running
+    DevBuf srcWork, srcOrder, orderBins;
+    bool haveOrder = false, useHistory = true;
+    int skipTier0 = 0; // > 0: rounds for which tier 0 is still skipped (it completed < 1/4 of its sources last time)
     long long cutCap = 0, nodeCap = 0, labCap = 0;
     DevBuf counters; // 16 x u64: see RawOut::counters; [8] queue cursor, [9] ovf count A, [10] ovf count B, [11] collisions
     PinBuf hCounters;
@@ -476,6 +481,7 @@ int smsgpu_create(smsgpu_ctx **out, int64_t n, int64_t m, const int64_t *rowptr,
             }
         }
     }
+    if (const char *eh = std::getenv("SMSGPU_NO_HISTORY")) ctx->useHistory = !(eh[0] == '1');
     configureTiers(ctx);
     ctx->nsrcGlobal = ctx->nsrcLocal = n; // default source list 0..n-1 (conshdlr_oscw.cpp:188-195)
     ctx->rank = 0;
@@ -494,7 +500,7 @@ void smsgpu_destroy(smsgpu_ctx *ctx) {
                      &ctx->tier[0].scratch, &ctx->tier[1].scratch, &ctx->tier[2].scratch, &ctx->tier[3].scratch, &ctx->rNode, &ctx->rEid,
                      &ctx->rStay, &ctx->rCutOff, &ctx->rCutLen, &ctx->rCutSrc, &ctx->rCutSeq, &ctx->rCutTier, &ctx->rValid,
                      &ctx->labSrc, &ctx->labNode, &ctx->labHops, &ctx->labDist, &ctx->srcTier, &ctx->srcArcs,
-                     &ctx->srcSettled, &ctx->counters, &ctx->ovfA, &ctx->ovfB, &ctx->wCnode, &ctx->wCeid, &ctx->wCstay,
+                     &ctx->srcSettled, &ctx->srcWork, &ctx->srcOrder, &ctx->orderBins, &ctx->counters, &ctx->ovfA, &ctx->ovfB, &ctx->wCnode, &ctx->wCeid, &ctx->wCstay,
                      &ctx->wHash, &ctx->wRank, &ctx->wSlot, &ctx->wKeep, &ctx->wNcross, &ctx->wViol, &ctx->wTabKey,
                      &ctx->wTabRank, &ctx->wTabIdx, &ctx->wCnt, &ctx->wCursor, &ctx->wBase, &ctx->wOrder, &ctx->wOutLen,
                      &ctx->wBlockSums, &ctx->fin.off, &ctx->fin.node, &ctx->fin.eid, &ctx->fin.stay, &ctx->fin.ncross,
@@ -565,6 +571,8 @@ int smsgpu_set_sources(smsgpu_ctx *ctx, const int32_t *sources, int64_t nsrc, in
     // block-cyclic deal: local index j <-> global index j * nranks + rank
     ctx->nsrcLocal = ctx->nsrcGlobal > rank ? (ctx->nsrcGlobal - rank + nranks - 1) / nranks : 0;
     ctx->explicitSources = sources != nullptr;
+    ctx->haveOrder = false; // the local index space changed
+    ctx->skipTier0 = 0;
     if (sources) {
         std::vector<int32_t> mine((size_t)ctx->nsrcLocal);
         for (int64_t j = 0; j < ctx->nsrcLocal; ++j) {
@@ -774,6 +782,9 @@ int smsgpu_separate_async(smsgpu_ctx *ctx, const smsgpu_params *params) {
     CU(ctx->srcTier.ensure((size_t)std::max<long long>(nsrc, 1)));
     CU(ctx->ovfA.ensure((size_t)std::max<long long>(nsrc, 1) * 4));
     CU(ctx->ovfB.ensure((size_t)std::max<long long>(nsrc, 1) * 4));
+    CU(ctx->srcWork.ensure((size_t)std::max<long long>(nsrc, 1) * 4));
+    CU(ctx->srcOrder.ensure((size_t)std::max<long long>(nsrc, 1) * 4));
+    CU(ctx->orderBins.ensure(2 * kOrderBins * sizeof(unsigned int)));
     if (P.export_src_stats) {
         CU(ctx->srcArcs.ensure((size_t)std::max<long long>(nsrc, 1) * 8));
         CU(ctx->srcSettled.ensure((size_t)std::max<long long>(nsrc, 1) * 8));
@@ -797,6 +808,7 @@ int smsgpu_separate_async(smsgpu_ctx *ctx, const smsgpu_params *params) {
         if (attempt > 4) return fail(ctx, SMSGPU_ERR_INTERNAL, "raw arena kept overflowing");
         CU(cudaMemsetAsync(dc, 0, 16 * sizeof(unsigned long long), st));
         CU(cudaMemsetAsync(ctx->srcTier.p, 0xFF, (size_t)std::max<long long>(nsrc, 1), st));
+        CU(cudaMemsetAsync(ctx->srcWork.p, 0, (size_t)std::max<long long>(nsrc, 1) * 4, st)); // skipped sources: no work
         RawOut R{};
         R.node = ctx->rNode.as<int32_t>();
         R.eid = ctx->rEid.as<int32_t>();
@@ -817,6 +829,7 @@ int smsgpu_separate_async(smsgpu_ctx *ctx, const smsgpu_params *params) {
         R.srcTier = ctx->srcTier.as<int8_t>();
         R.srcArcs = P.export_src_stats ? ctx->srcArcs.as<long long>() : nullptr;
         R.srcSettled = P.export_src_stats ? ctx->srcSettled.as<long long>() : nullptr;
+        R.srcWork = ctx->srcWork.as<uint32_t>();
 
         SearchParams SP{};
         SP.sources = ctx->explicitSources ? ctx->dSources.as<int32_t>() : nullptr;
@@ -831,11 +844,14 @@ int smsgpu_separate_async(smsgpu_ctx *ctx, const smsgpu_params *params) {
         SP.queueCounter = dc + 8;
         long long nwork = nsrc;
         const int32_t *worklist = nullptr;
+        if (ctx->useHistory && ctx->haveOrder) worklist = ctx->srcOrder.as<int32_t>(); // longest first (previous round)
+        int firstTier = P.start_tier;
+        if (ctx->useHistory && ctx->skipTier0 > 0 && firstTier == 0) firstTier = 1;
         int32_t *ovfBufs[2] = {ctx->ovfA.as<int32_t>(), ctx->ovfB.as<int32_t>()};
         long long done[kNumTiers] = {0, 0, 0, 0};
         long long prevRun = 0;
         bool tierRan[kNumTiers] = {false, false, false, false};
-        for (int ti = P.start_tier; ti < kNumTiers && nwork > 0; ++ti) {
+        for (int ti = firstTier; ti < kNumTiers && nwork > 0; ++ti) {
             if (int rc = ensureTierScratch(ctx, ti)) return rc;
             const int which = ti & 1;
             SP.tier = ti;
@@ -894,6 +910,22 @@ int smsgpu_separate_async(smsgpu_ctx *ctx, const smsgpu_params *params) {
             redo = true;
         }
         if (redo) continue;
+        if (ctx->useHistory && nsrc > 0) {
+            // tier 0 (shared memory) is skipped for the next 15 rounds when it completed fewer than 1/4 of its sources
+            if (tierRan[0])
+                ctx->skipTier0 = (done[0] * 4 < nsrc) ? 15 : 0;
+            else if (ctx->skipTier0 > 0)
+                ctx->skipTier0--;
+            unsigned int *bins = ctx->orderBins.as<unsigned int>();
+            CU(cudaMemsetAsync(bins, 0, 2 * kOrderBins * sizeof(unsigned int), st));
+            const unsigned g = std::min<unsigned>(gridFor(nsrc, 256), (unsigned)ctx->smCount * 8);
+            orderHistKernel<<<g, 256, 0, st>>>(nsrc, ctx->srcWork.as<uint32_t>(), bins);
+            orderScanKernel<<<1, 32, 0, st>>>(bins);
+            orderScatterKernel<<<g, 256, 0, st>>>(nsrc, ctx->srcWork.as<uint32_t>(), bins, ctx->srcOrder.as<int32_t>());
+            CU(cudaGetLastError());
+            ctx->stats.total_launches += 3;
+            ctx->haveOrder = true;
+        }
         ctx->stats.sources_run = (long long)hc[4];
         ctx->stats.arcs_scanned = (long long)hc[2];
         ctx->stats.settled = (long long)hc[3];
