@@ -5,7 +5,7 @@
 
 A "step" is one root-node separation round: the round's x* and blacklist -> K1 arc records -> K2-K4 bounded
 shortest paths + walk extraction + chord repair for every source 0..n-1 -> K5 canonical dedup
-(-> NCCL all-gather + global dedup when N > 1).  N > 1 shards the SOURCES of the same round block-cyclically over
+(-> NCCL all-gather + global dedup when N > 1).  N > 1 shards the SOURCES of the same round cyclically, in pairs, over
 the ranks (each GPU holds a graph replica), so total work is fixed: "scaling": "strong".
 
   value    rounds/s with x*/blacklist already resident in HBM, result left on the device
@@ -320,7 +320,7 @@ def main():
             "config": {"workload": WORKLOADS[args.workload][1], "name": args.workload, "n": res["n"], "m": res["m"],
                        "sources": res["n"], "mode": "I (independent sources), canonical ties, dedup on",
                        "l2": "256 MiB buffer rewritten between timed iterations; arc array alone is 16 B x 2m",
-                       "parallelism": f"sources block-cyclic over {world} GPU(s), graph replicated"},
+                       "parallelism": f"source pairs cyclic over {world} GPU(s), graph replicated"},
             "gteps": res["arcs"] / sec / 1e9,
             "arcs_scanned_per_round": res["arcs"], "settled_per_round": res["settled"], "raw_walks": res["raw_walks"],
             "unique_cuts": res["ncuts"],

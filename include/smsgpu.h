@@ -111,7 +111,7 @@ int smsgpu_set_round_input(smsgpu_ctx *ctx, const double *x_by_eid, const uint8_
 int smsgpu_set_round_input_device(smsgpu_ctx *ctx, const double *d_x_by_eid, const uint8_t *d_blacklist);
 
 /* Source list: doubled ids, in the order ConshdlrOscw issues them (conshdlr_oscw.cpp:188-195 passes
- * 0..n-1).  sources == NULL selects 0..n-1.  With (rank, nranks) the list is dealt block-cyclically and this
+ * 0..n-1).  sources == NULL selects 0..n-1.  With (rank, nranks) the list is dealt cyclically in pairs (2p, 2p+1) and this
  * context runs only its share (source sharding across GPUs). */
 int smsgpu_set_sources(smsgpu_ctx *ctx, const int32_t *sources, int64_t nsrc, int rank, int nranks);
 

@@ -210,7 +210,8 @@ class Context:
             s = np.ascontiguousarray(sources, dtype=np.int32)
             self._check(self.lib.smsgpu_set_sources(self.h, s.ctypes.data, s.shape[0], rank, nranks))
             g = int(s.shape[0])
-        self.local_source_count = max(0, (g - rank + nranks - 1) // nranks) if g > rank else 0
+        from .sharding import local_count
+        self.local_source_count = local_count(g, rank, nranks)
 
     # ---- a round ----
     def params(self, **kw) -> Params:

@@ -110,7 +110,8 @@ __global__ void __launch_bounds__(128) canonKernel(const CutView V, const DedupW
     D.hash[i] = h | 1ull; // 0 = empty slot
     D.ncross[i] = nc;
     D.viol[i] = 1.0 - length;
-    const unsigned long long gsrc = (unsigned long long)V.src[i] * srcMul + srcAdd;
+    // local -> global source index under the pair-cyclic deal of smsgpu_set_sources (identity for srcMul 1, srcAdd 0)
+    const unsigned long long gsrc = ((((unsigned long long)V.src[i] >> 1) * srcMul + srcAdd) << 1) | ((unsigned)V.src[i] & 1u);
     D.rank[i] = (gsrc << 20) | (unsigned)V.seq[i];
     D.keep[i] = 1;
 }

@@ -146,7 +146,7 @@ __global__ void __launch_bounds__(128, FAST ? SMSGPU_FAST_MIN_CTAS : 1) ocwSearc
         wi = T.shfl(wi, 0);
         if (wi >= total) break;
         const int32_t srcIdx = P.worklist ? P.worklist[wi] : (int32_t)wi;
-        const uint32_t src = P.sources ? (uint32_t)P.sources[srcIdx] : (uint32_t)(P.srcBegin + srcIdx * P.srcStride);
+        const uint32_t src = P.sources ? (uint32_t)P.sources[srcIdx] : (uint32_t)(((((long long)(srcIdx >> 1)) * P.srcStride + P.srcBegin) << 1) | (srcIdx & 1));
         // `if (blacklist_[currentSource_]) return {}` -- indexed with the DOUBLED id (ocw_seperator.cpp:334, quirk A.7.1)
         if ((long long)src < G.n && P.blacklist[src]) continue;
         if ((long long)(src >> 1) >= G.n) continue; // not a node of the double cover

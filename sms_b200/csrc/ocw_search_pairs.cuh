@@ -302,7 +302,7 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
                 } else {
                     wi = w32;
                     const int32_t srcIdx = P.worklist ? P.worklist[wi] : (int32_t)wi;
-                    src = P.sources ? (uint32_t)P.sources[srcIdx] : (uint32_t)(P.srcBegin + (long long)srcIdx * P.srcStride);
+                    src = P.sources ? (uint32_t)P.sources[srcIdx] : (uint32_t)(((((long long)(srcIdx >> 1)) * P.srcStride + P.srcBegin) << 1) | (srcIdx & 1));
                     // `if (blacklist_[currentSource_]) return {}` -- indexed with the DOUBLED id (ocw_seperator.cpp:334)
                     const bool skip = ((long long)src < G.n && P.blacklist[src]) || (long long)(src >> 1) >= G.n;
                     if (!skip) {

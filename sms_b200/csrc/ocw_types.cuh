@@ -125,7 +125,7 @@ struct RawOut {
 };
 
 struct SearchParams {
-    const int32_t *sources; // doubled ids; nullptr -> srcBegin + i*srcStride
+    const int32_t *sources; // doubled ids; nullptr -> ((i >> 1) * srcStride + srcBegin) * 2 + (i & 1)  (pairs dealt cyclically)
     long long nsrc;         // local number of sources
     long long srcBegin, srcStride;
     const int32_t *worklist; // nullptr in the first tier, else local source indices that overflowed

@@ -568,15 +568,22 @@ int smsgpu_set_sources(smsgpu_ctx *ctx, const int32_t *sources, int64_t nsrc, in
     ctx->rank = rank;
     ctx->nranks = nranks;
     ctx->nsrcGlobal = sources ? nsrc : ctx->n;
-    // block-cyclic deal: local index j <-> global index j * nranks + rank
-    ctx->nsrcLocal = ctx->nsrcGlobal > rank ? (ctx->nsrcGlobal - rank + nranks - 1) / nranks : 0;
+    // PAIRS of consecutive sources are dealt cyclically (the two sides of a vertex stay on one GPU, where their mirror-image
+    // searches share a warp): local index j <-> global index ((j >> 1) * nranks + rank) * 2 + (j & 1)
+    {
+        const long long N = ctx->nsrcGlobal, pairsAll = (N + 1) / 2;
+        const long long pairsMine = pairsAll > rank ? (pairsAll - rank + nranks - 1) / nranks : 0;
+        long long cnt = 2 * pairsMine;
+        if (pairsMine > 0 && (N & 1) && ((pairsMine - 1) * nranks + rank) == pairsAll - 1) cnt--; // the odd last source
+        ctx->nsrcLocal = cnt;
+    }
     ctx->explicitSources = sources != nullptr;
     ctx->haveOrder = false; // the local index space changed
     ctx->skipTier0 = 0;
     if (sources) {
         std::vector<int32_t> mine((size_t)ctx->nsrcLocal);
         for (int64_t j = 0; j < ctx->nsrcLocal; ++j) {
-            mine[j] = sources[j * nranks + rank];
+            mine[j] = sources[((j >> 1) * nranks + rank) * 2 + (j & 1)];
             if (mine[j] < 0) return fail(ctx, SMSGPU_ERR_ARG, "negative source id");
         }
         CU(ctx->dSources.ensure(std::max<size_t>(mine.size(), 1) * sizeof(int32_t)));

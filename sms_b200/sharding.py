@@ -11,16 +11,30 @@ from __future__ import annotations
 import numpy as np
 
 
-def local_sources(sources: np.ndarray, rank: int, nranks: int) -> np.ndarray:
-    """Cyclic deal: local index j <-> global index j * nranks + rank (smsgpu_set_sources)."""
-    if nranks < 1 or not 0 <= rank < nranks:
-        raise ValueError(f"bad rank {rank} / {nranks}")
-    return np.ascontiguousarray(np.asarray(sources)[rank::nranks])
+def local_count(nsrc: int, rank: int, nranks: int) -> int:
+    """Number of sources rank owns: PAIRS (2p, 2p+1) of consecutive sources are dealt cyclically, so that the two sides
+    of a vertex -- mirror-image searches -- stay on one GPU and share a warp there (smsgpu_set_sources)."""
+    pairs_all = (nsrc + 1) // 2
+    pairs_mine = (pairs_all - rank + nranks - 1) // nranks if pairs_all > rank else 0
+    cnt = 2 * pairs_mine
+    if pairs_mine > 0 and nsrc % 2 == 1 and (pairs_mine - 1) * nranks + rank == pairs_all - 1:
+        cnt -= 1
+    return cnt
 
 
 def global_index(local_index, rank: int, nranks: int):
-    """Position in the round's source list of a rank's local source index."""
-    return np.asarray(local_index) * nranks + rank
+    """Position in the round's source list of a rank's local source index j: ((j >> 1) * nranks + rank) * 2 + (j & 1)."""
+    j = np.asarray(local_index)
+    return ((j >> 1) * nranks + rank) * 2 + (j & 1)
+
+
+def local_sources(sources: np.ndarray, rank: int, nranks: int) -> np.ndarray:
+    """The sources rank owns, in local index order (smsgpu_set_sources)."""
+    if nranks < 1 or not 0 <= rank < nranks:
+        raise ValueError(f"bad rank {rank} / {nranks}")
+    src = np.asarray(sources)
+    j = np.arange(local_count(len(src), rank, nranks))
+    return np.ascontiguousarray(src[global_index(j, rank, nranks)])
 
 
 def canonical_walk(nodes, stay):

@@ -53,7 +53,7 @@ def _worker(rank, world, port, q):
         dist.destroy_process_group()
 
 
-def test_cyclic_deal_partitions_the_sources():
+def test_pair_cyclic_deal_partitions_the_sources():
     sys.path.insert(0, ROOT)
     from sms_b200 import sharding
     src = np.arange(1001, dtype=np.int32) * 3
@@ -64,7 +64,7 @@ def test_cyclic_deal_partitions_the_sources():
         for r, p in enumerate(parts):
             back[sharding.global_index(np.arange(len(p)), r, world)] = p
         assert np.array_equal(back, src)
-        assert max(len(p) for p in parts) - min(len(p) for p in parts) <= 1
+        assert max(len(p) for p in parts) - min(len(p) for p in parts) <= 2  # pairs are the unit of the deal
     with pytest.raises(ValueError):
         sharding.local_sources(src, 2, 2)
 
