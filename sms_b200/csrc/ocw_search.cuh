@@ -82,6 +82,7 @@ struct TileMem {
     uint2 *pq;       // [slot*2 + side] {predecessor doubled id, queue position or kNoQpos}; aliases pred
     uint32_t *cl;    // bucket counters, two buckets per word: byte 0/2 = appended, byte 1/3 = live
     uint32_t *bm;    // presence bitmap of the label table, one bit per slot
+    uint32_t hopMask; // hop words: all 32 bits, except in the pairs engine (hops | queue position << 16)
     uint4 *qrow;     // pairs engine: its queue, two uint4 per entry: {dist bits, hops << 32 | id}, {first arc, degree, -, -}
 };
 
@@ -91,6 +92,7 @@ __device__ inline void carveTileMem(TileMem &M, unsigned char *base, const TileC
     M.cl = nullptr;
     M.bm = nullptr;
     M.qrow = nullptr;
+    M.hopMask = c.pairs ? 0xFFFFu : 0xFFFFFFFFu;
     if (c.nbuckets) {
         M.cl = reinterpret_cast<uint32_t *>(hot);
         M.bm = reinterpret_cast<uint32_t *>(hot + (size_t)c.nbuckets * (c.pairs ? 1 : 2));

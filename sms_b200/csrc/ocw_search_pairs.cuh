@@ -39,6 +39,7 @@ struct PairsKArgs {
 };
 
 constexpr uint32_t kNoItem = 0xFFFFFFFFu;
+constexpr uint32_t kPackedNone = 0xFFFFFFFFu; // label hop word of the pairs engine: no hops, no queue position
 constexpr uint32_t kPairsSaveWords = 32 + 6 * 32; // shared-memory save area of one warp (state of its two searches)
 
 struct PairsParams {
@@ -141,7 +142,7 @@ __device__ __noinline__ int finishSourcePairs(const PairsKArgs *K, unsigned char
                         R.labSrc[li] = srcIdx;
                         R.labNode[li] = (int32_t)(2 * e.key + sd);
                         R.labDist[li] = d;
-                        R.labHops[li] = (int32_t)(sd ? e.h1 : e.h0);
+                        R.labHops[li] = (int32_t)((sd ? e.h1 : e.h0) & M.hopMask);
                     }
                 }
             }
@@ -253,6 +254,7 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
         unsigned long long khi = ((unsigned long long)svK[32] << 32) | svK[0], klo = ((unsigned long long)svK[96] << 32) | svK[64];
         uint32_t rowB = svK[128], deg = svK[160];
         uint32_t stash = svW[15]; // second item of a pair this warp owns (warp-uniform), kNoItem if none
+        bool freshB = false; // the keys in registers were loaded since the last extraction
         bool done = false;
         unsigned finb = 0;
 
@@ -319,15 +321,16 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
                     Entry e = emptyEntry();
                     e.key = src >> 1;
                     e.flags = P.stampBase + wi + 1u;
+                    e.h0 = e.h1 = kPackedNone; // hop words of this engine: hops | queue position << 16
                     if (src & 1u) {
                         e.d1 = 0.0;
-                        e.h1 = 0;
+                        e.h1 = 0; // 0 hops, queue position 0
                     } else {
                         e.d0 = 0.0;
                         e.h0 = 0;
                     }
                     storeEntryCS(TABP(s), e);
-                    __stcs(PQP(2 * s + (src & 1u)), make_uint2(src, 0u));
+                    __stcs(&PQP(2 * s + (src & 1u))->x, src);
                     const uint2 srow = Q.rowinfo[src >> 1];
                     __stcs(QP(0), make_uint4(0u, 0u, src, 0u)); // dist 0, id src, 0 hops
                     __stcs(QP(0) + 1, make_uint4(srow.x, srow.y, 0u, 0u));
@@ -408,6 +411,7 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
                     deg = nrow.y;
                     liveRegs = __popc(lv);
                     needLoad = false;
+                    freshB = true;
                     SMS_CHK(liveRegs > 0);
                 }
             }
@@ -451,6 +455,15 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
             settledN++;
         }
         __syncwarp(FULL); // the tombstone and the counter update are visible to the scan below
+        // first extraction from a bucket: the rows of its other keys are needed within the next few steps -- start
+        // them towards L2 now (the row of the key just extracted is being loaded anyway)
+        if (freshB) {
+            if (run && khi != kDeadKey && deg) {
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(G.arcs + rowB));
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(G.arcs + rowB + deg - 1));
+            }
+            freshB = false;
+        }
         const uint32_t side = cur & 1u;
         const uint32_t hNew = (uint32_t)(clo >> 32) + 1;
         const uint32_t stamp = P.stampBase + wi + 1u;
@@ -505,6 +518,7 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
                     }
                     cb = b;
                     liveRegs = nlive;
+                    freshB = true;
                 }
             }
         }
@@ -539,7 +553,7 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
             int slot = -1;
             bool isNew = false;
             double dA = kUnlabelled, dB = kUnlabelled; // label of the side the stay arc reaches / of the other side
-            uint32_t hA = kUnlabelledHops, hB = kUnlabelledHops;
+            uint32_t pA = kPackedNone, pB = kPackedNone; // hops | queue position << 16 of the two sides
             if (act) {
                 uint32_t s = (nbr * 0x9E3779B1u) >> tabShift;
 #ifndef SMSGPU_PAIRS_PROBE1 // default: two slots per round trip (-11 % on the 1M/4M round); PROBE1 = one slot
@@ -570,8 +584,8 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
                         slot = (int)s;
                         dA = side ? e.d1 : e.d0;
                         dB = side ? e.d0 : e.d1;
-                        hA = side ? e.h1 : e.h0;
-                        hB = side ? e.h0 : e.h1;
+                        pA = side ? e.h1 : e.h0;
+                        pB = side ? e.h0 : e.h1;
                         break;
                     }
                     s = occ1 ? ((s1 + 1) & tabMask) : s1;
@@ -593,8 +607,8 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
                             slot = (int)s;
                             dA = side ? e.d1 : e.d0;
                             dB = side ? e.d0 : e.d1;
-                            hA = side ? e.h1 : e.h0;
-                            hB = side ? e.h0 : e.h1;
+                            pA = side ? e.h1 : e.h0;
+                            pB = side ? e.h0 : e.h1;
                             break;
                         }
                     }
@@ -607,6 +621,7 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
 
             bool accS = false, accX = false, evS = false, evX = false;
             const bool hadA = dA < kUnlabelled, hadB = dB < kUnlabelled;
+            uint32_t hA = pA & 0xFFFFu, hB = pB & 0xFFFFu;
             double DS = 0, DX = 0;
             uint32_t HS = 0, HX = 0;
             if (slot >= 0) {
@@ -681,30 +696,21 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
             // the row of the neighbour travels with its key: one 8-byte read per PUSHING lane (about one per settled node)
             if ((accS && 2 * dS <= best0) || (accX && 2 * dX <= best0)) nrow = Q.rowinfo[nbr];
             if (accS || accX) {
-                Entry e;
-                e.d0 = side ? dB : dA;
-                e.d1 = side ? dA : dB;
-                e.h0 = side ? hB : hA;
-                e.h1 = side ? hA : hB;
-                e.key = nbr;
-                e.flags = stamp;
-                storeEntryCS(TABP(slot), e);
+                if (hNew >= 0xFFFFu) ovf = true; // hops share a word with the queue position in this engine
 #pragma unroll
                 for (int k = 0; k < 2; ++k) {
                     if (!(k ? accX : accS)) continue;
                     const uint32_t sd = k ? (side ^ 1u) : side;
                     const double d = k ? dX : dS;
-                    // a superseded key leaves the queue now
-                    if (k ? hadB : hadA) {
-                        const uint32_t oldq = __ldcs(PQP(2 * slot + sd)).y;
-                        if (oldq != kNoQpos) {
-                            __stcs(reinterpret_cast<unsigned long long *>(QP(oldq)), kDeadKey);
-                            const uint32_t ob = oldq / C;
-                            atomicSub(&cl[ob >> 2], 0x10u << ((ob & 3u) * 8u));
-                            dirty |= ob == cb;
-                        }
+                    // a superseded key leaves the queue now (its position sits in the label's hop word: no extra load)
+                    const uint32_t oldq = (k ? pB : pA) >> 16;
+                    if ((k ? hadB : hadA) && oldq != 0xFFFFu) {
+                        __stcs(reinterpret_cast<unsigned long long *>(QP(oldq)), kDeadKey);
+                        const uint32_t ob = oldq / C;
+                        atomicSub(&cl[ob >> 2], 0x10u << ((ob & 3u) * 8u));
+                        dirty |= ob == cb;
                     }
-                    uint32_t qpos = kNoQpos;
+                    uint32_t qpos = 0xFFFFu;
                     if (2 * d <= best0) { // queue admission: only nodes that can still be extracted
                         const uint32_t bk = bucketOf(d, Q.scaleU, Q.scaleB, NB - 1);
                         const uint32_t sh = (bk & 3u) * 8u;
@@ -718,16 +724,22 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
                             const unsigned long long dbits = (unsigned long long)__double_as_longlong(d);
                             __stcs(QP(qpos), make_uint4((uint32_t)dbits, (uint32_t)(dbits >> 32), 2 * nbr + sd, hNew));
                             __stcs(QP(qpos) + 1, make_uint4(nrow.x, nrow.y, 0u, 0u));
-#ifdef SMSGPU_PAIRS_PREFETCH // measured useless: L2 turns over ~50x between the push of a key and its extraction
-                            if (nrow.y) {
-                                asm volatile("prefetch.global.L2 [%0];" ::"l"(G.arcs + nrow.x));
-                                asm volatile("prefetch.global.L2 [%0];" ::"l"(G.arcs + nrow.x + nrow.y - 1));
-                            }
-#endif
                         }
                     }
-                    __stcs(PQP(2 * slot + sd), make_uint2(cur, qpos));
+                    if (k)
+                        pB = (hNew & 0xFFFFu) | (qpos << 16);
+                    else
+                        pA = (hNew & 0xFFFFu) | (qpos << 16);
+                    __stcs(&PQP(2 * slot + sd)->x, cur); // predecessor
                 }
+                Entry e;
+                e.d0 = side ? dB : dA;
+                e.d1 = side ? dA : dB;
+                e.h0 = side ? pB : pA;
+                e.h1 = side ? pA : pB;
+                e.key = nbr;
+                e.flags = stamp;
+                storeEntryCS(TABP(slot), e);
             }
             if ((__ballot_sync(FULL, ovf) >> gbase) & 0xFFFFu) {
                 if (tl == 0) atomicAdd(&R.counters[13], 1ull); // a bucket is full

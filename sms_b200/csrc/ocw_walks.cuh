@@ -51,7 +51,7 @@ __device__ int selectIntermediates(const Tile<TW> &T, TileMem &M, SrcState &S, i
         const Entry e = loadEntry(&M.tab[slot]);
         HeapEnt k;
         k.hi = (unsigned long long)__double_as_longlong((t & 1u) ? e.d1 : e.d0);
-        k.lo = ((unsigned long long)((t & 1u) ? e.h1 : e.h0) << 32) | i; // history index: stable order
+        k.lo = ((unsigned long long)(((t & 1u) ? e.h1 : e.h0) & M.hopMask) << 32) | i; // history index: stable order
         M.heap[i] = k;
     }
     T.sync();
