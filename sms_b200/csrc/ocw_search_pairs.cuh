@@ -47,6 +47,7 @@ struct PairsParams {
     const uint2 *rowinfo; // [n] {first arc, degree} of every vertex (32-bit arc indices: 2m < 2^32)
     float scaleU;         // bucket map: u = (float)dist * scaleU; 0 selects the linear map
     float scaleB;         // bucket = (2^u - 1) * scaleB   (linear map: dist * scaleB)
+    int mirror;           // 1: twin sources (v,0)/(v,1) are searched once when no id tie-break occurred
 };
 
 // The per-source working memory (label table, predecessors, queue) is touched once or twice per source and is far
@@ -86,7 +87,7 @@ __device__ __forceinline__ uint32_t bucketOf(const double d, const float scaleU,
 __device__ __noinline__ int finishSourcePairs(const PairsKArgs *K, unsigned char *tile, unsigned char *hot, const double best,
                                               const uint32_t histN, const uint32_t touchedN, const uint32_t arcs,
                                               const uint32_t settled, const int overflow, const uint32_t src,
-                                              const int32_t srcIdx) {
+                                              const int32_t srcIdx, const int32_t srcIdx2) {
     const Tile<32> T;
     const GraphDev G = K->G;
     const TileCaps caps = K->caps;
@@ -110,19 +111,23 @@ __device__ __noinline__ int finishSourcePairs(const PairsKArgs *K, unsigned char
     if (!S.overflow && S.histN > 0) {
         const int nsel = selectIntermediates<32>(T, M, S, maxInter, sel);
         if (!S.overflow && T.lane == 0) {
-            Emitter E;
-            E.R = &R;
-            E.srcIdx = srcIdx;
-            E.seq = 0;
-            E.tier = P.tier;
-            for (int r = 0; r < nsel; ++r) {
-                const int W = buildWalk(M, sel[r], src);
-                if (W < 0) {
-                    S.overflow = 1;
-                    break;
+            // srcIdx2 >= 0: the twin source (other side of the same vertex) gets the same walks -- its search is the mirror
+            // image of this one, and a walk is a sequence of ORIGINAL vertices and stay/cross flags
+            for (int pass = 0; pass < (srcIdx2 >= 0 ? 2 : 1) && !S.overflow; ++pass) {
+                Emitter E;
+                E.R = &R;
+                E.srcIdx = pass ? srcIdx2 : srcIdx;
+                E.seq = 0;
+                E.tier = P.tier;
+                for (int r = 0; r < nsel; ++r) {
+                    const int W = buildWalk(M, sel[r], src);
+                    if (W < 0) {
+                        S.overflow = 1;
+                        break;
+                    }
+                    simpleOddCyclesAndExtract(G, M, S, E, W);
+                    if (S.overflow) break;
                 }
-                simpleOddCyclesAndExtract(G, M, S, E, W);
-                if (S.overflow) break;
             }
         }
         S.overflow = T.shfl(S.overflow, 0);
@@ -137,29 +142,39 @@ __device__ __noinline__ int finishSourcePairs(const PairsKArgs *K, unsigned char
                 for (int sd = 0; sd < 2; ++sd) {
                     const double d = sd ? e.d1 : e.d0;
                     if (d >= kUnlabelled) continue;
-                    const long long li = (long long)atomicAdd(&R.counters[5], 1ull);
-                    if (li < R.labCap) {
-                        R.labSrc[li] = srcIdx;
-                        R.labNode[li] = (int32_t)(2 * e.key + sd);
-                        R.labDist[li] = d;
-                        R.labHops[li] = (int32_t)((sd ? e.h1 : e.h0) & M.hopMask);
+                    for (int pass = 0; pass < (srcIdx2 >= 0 ? 2 : 1); ++pass) { // the twin's labels: sides swapped
+                        const long long li = (long long)atomicAdd(&R.counters[5], 1ull);
+                        if (li < R.labCap) {
+                            R.labSrc[li] = pass ? srcIdx2 : srcIdx;
+                            R.labNode[li] = (int32_t)(2 * e.key + (sd ^ pass));
+                            R.labDist[li] = d;
+                            R.labHops[li] = (int32_t)((sd ? e.h1 : e.h0) & M.hopMask);
+                        }
                     }
                 }
             }
         }
         if (T.lane == 0) {
-            R.srcTier[srcIdx] = (int8_t)P.tier;
-            if (R.srcWork) R.srcWork[srcIdx] = settled;
-            if (R.srcArcs) {
-                R.srcArcs[srcIdx] = (long long)arcs;
-                R.srcSettled[srcIdx] = (long long)settled;
+            for (int pass = 0; pass < (srcIdx2 >= 0 ? 2 : 1); ++pass) {
+                const int32_t si = pass ? srcIdx2 : srcIdx;
+                R.srcTier[si] = (int8_t)P.tier;
+                if (R.srcWork) R.srcWork[si] = settled;
+                if (R.srcArcs) {
+                    R.srcArcs[si] = (long long)arcs;
+                    R.srcSettled[si] = (long long)settled;
+                }
             }
         }
         counted = 1;
         if (T.lane == 0) { // round totals
-            atomicAdd(&R.counters[2], (unsigned long long)arcs);
-            atomicAdd(&R.counters[3], (unsigned long long)settled);
-            atomicAdd(&R.counters[4], 1ull);
+            const unsigned long long mult = srcIdx2 >= 0 ? 2ull : 1ull; // what the reference would have scanned / settled
+            atomicAdd(&R.counters[2], mult * arcs);
+            atomicAdd(&R.counters[3], mult * settled);
+            atomicAdd(&R.counters[4], mult);
+            if (srcIdx2 >= 0) { // ... of which obtained by symmetry, not scanned
+                atomicAdd(&R.counters[6], 1ull);
+                atomicAdd(&R.counters[7], (unsigned long long)arcs);
+            }
         }
     } else if (T.lane == 0) {
         const unsigned long long k = atomicAdd(P.ovfCount, 1ull);
@@ -229,12 +244,11 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
     //   per lane (6 words): the current bucket's key and the row of its vertex
     uint32_t *const svU = smemw + (uint32_t)(blockDim.x >> 5) * 2 * hbw + (uint32_t)warpInCta * kPairsSaveWords + (gbase >> 4) * 16;
     uint32_t *const svK = smemw + (uint32_t)(blockDim.x >> 5) * 2 * hbw + (uint32_t)warpInCta * kPairsSaveWords + 32 + lane;
-    uint32_t *const svW = smemw + (uint32_t)(blockDim.x >> 5) * 2 * hbw + (uint32_t)warpInCta * kPairsSaveWords;
     if (tl == 0) {
         svU[0] = 0; // st: idle
         svU[14] = 1;
+        svU[15] = 0;
     }
-    if (lane == 0) svW[15] = kNoItem;
     __syncwarp(FULL);
 #ifdef SMSGPU_PAIRS_CLOCKS
     long long pclk[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, plast = clock64(), piters = 0;
@@ -253,7 +267,8 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
         // the current bucket's keys, one per lane, with the row of their vertex
         unsigned long long khi = ((unsigned long long)svK[32] << 32) | svK[0], klo = ((unsigned long long)svK[96] << 32) | svK[64];
         uint32_t rowB = svK[128], deg = svK[160];
-        uint32_t stash = svW[15]; // second item of a pair this warp owns (warp-uniform), kNoItem if none
+        uint32_t pend = svU[15] & 3u; // second source of the item: 0 none / done, 1 to be searched next, 2 mirror candidate
+        bool tie = (svU[15] >> 2) != 0; // an extraction of the current search had to break a (dist, hops) tie by id
         bool freshB = false; // the keys in registers were loaded since the last extraction
         bool done = false;
         unsigned finb = 0;
@@ -264,51 +279,57 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
 
         // ---- (2) idle halves fetch the next source ------------------------------------------------------------------
         if (__ballot_sync(FULL, st == 0)) {
-            // Work items are handed out in PAIRS (2p, 2p+1) -- in the handler's source list the two sides of one vertex,
-            // mirror-image searches that read the same arc rows -- and both items of a pair stay in this warp: two idle
-            // halves start them together; a half that is idle alone starts the first and the second waits in `stash`
-            // for whichever half of this warp is idle next.
-            const unsigned idleb = __ballot_sync(FULL, st == 0);
-            const bool idle0 = idleb & 1u, idle1 = (idleb >> 16) & 1u;
-            uint32_t take0 = kNoItem, take1 = kNoItem;
-            if (idle0 && stash != kNoItem) {
-                take0 = stash;
-                stash = kNoItem;
+            // A work item is a PAIR (2p, 2p+1) of consecutive entries of the source list -- in the handler's list the
+            // two sides (v,0), (v,1) of one vertex.  Their searches are mirror images of each other under the side swap
+            // (u,s) -> (u,1-s): same distances, hops, events and therefore walks, as long as no decision depends on the
+            // doubled ids, i.e. as long as no extraction has to break a (dist, hops) tie by id.  So a half searches the
+            // first source of its item; if that search saw no tie and the second source is the first one's twin, the
+            // finishing code emits the second's results from the same labels (pend == 2 -> mirrored); otherwise the
+            // second source is searched right afterwards on the same half (pend == 1).
+            const bool second = st == 0 && pend == 1; // the second source of the item is due: no fetch
+            uint32_t w32 = 0;
+            if (st == 0 && !second && tl == 0) {
+                const unsigned long long pr = atomicAdd(P.queueCounter, 1ull);
+                w32 = 2 * pr < (unsigned long long)total ? (uint32_t)(2 * pr) : total;
             }
-            if (idle1 && stash != kNoItem) {
-                take1 = stash;
-                stash = kNoItem;
-            }
-            if ((idle0 && take0 == kNoItem) || (idle1 && take1 == kNoItem)) { // warp-uniform
-                unsigned long long pr = 0;
-                if (lane == 0) pr = atomicAdd(P.queueCounter, 1ull);
-                pr = __shfl_sync(FULL, pr, 0);
-                const uint32_t a = 2 * pr < (unsigned long long)total ? (uint32_t)(2 * pr) : total;
-                const uint32_t b = 2 * pr + 1 < (unsigned long long)total ? (uint32_t)(2 * pr + 1) : kNoItem;
-                if (idle0 && take0 == kNoItem) {
-                    take0 = a;
-                    if (idle1 && take1 == kNoItem)
-                        take1 = b == kNoItem ? total : b;
-                    else
-                        stash = b;
-                } else {
-                    take1 = a;
-                    stash = b;
-                }
-            }
-            const uint32_t w32 = gbase ? take1 : take0;
+            w32 = __shfl_sync(FULL, w32, gbase);
             bool fresh = false;
             if (st == 0) {
+                if (second) w32 = wi + 1;
                 if (w32 >= total) {
                     st = 3;
                 } else {
-                    wi = w32;
-                    const int32_t srcIdx = P.worklist ? P.worklist[wi] : (int32_t)wi;
-                    src = P.sources ? (uint32_t)P.sources[srcIdx] : (uint32_t)(((((long long)(srcIdx >> 1)) * P.srcStride + P.srcBegin) << 1) | (srcIdx & 1));
+                    const int32_t i0 = P.worklist ? P.worklist[w32] : (int32_t)w32;
+                    const uint32_t s0 = P.sources ? (uint32_t)P.sources[i0] : (uint32_t)(((((long long)(i0 >> 1)) * P.srcStride + P.srcBegin) << 1) | (i0 & 1));
                     // `if (blacklist_[currentSource_]) return {}` -- indexed with the DOUBLED id (ocw_seperator.cpp:334)
-                    const bool skip = ((long long)src < G.n && P.blacklist[src]) || (long long)(src >> 1) >= G.n;
-                    if (!skip) {
+                    const bool skip0 = ((long long)s0 < G.n && P.blacklist[s0]) || (long long)(s0 >> 1) >= G.n;
+                    if (second) { // skip test already passed when the item was fetched
+                        wi = w32;
+                        src = s0;
+                        pend = 0;
                         fresh = true;
+                    } else {
+                        bool have1 = w32 + 1 < total;
+                        uint32_t s1 = 0;
+                        if (have1) {
+                            const int32_t i1 = P.worklist ? P.worklist[w32 + 1] : (int32_t)(w32 + 1);
+                            s1 = P.sources ? (uint32_t)P.sources[i1] : (uint32_t)(((((long long)(i1 >> 1)) * P.srcStride + P.srcBegin) << 1) | (i1 & 1));
+                            have1 = !(((long long)s1 < G.n && P.blacklist[s1]) || (long long)(s1 >> 1) >= G.n);
+                        }
+                        if (!skip0) {
+                            wi = w32;
+                            src = s0;
+                            pend = have1 ? ((s1 == (s0 ^ 1u) && Q.mirror) ? 2u : 1u) : 0u;
+                            fresh = true;
+                        } else if (have1) {
+                            wi = w32 + 1;
+                            src = s1;
+                            pend = 0;
+                            fresh = true;
+                        } // else: both skipped, fetch again
+                    }
+                    if (fresh) {
+                        tie = false;
                         for (uint32_t i = tl; i < nclWords + nbmWords; i += TW) cl[i] = 0; // counters, then the bitmap
                     }
                 }
@@ -430,6 +451,8 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
             mine = mine && k1 == m1;
             const uint32_t m2 = __reduce_min_sync(gmask, mine ? k2 : 0xFFFFFFFFu);
             mine = mine && k2 == m2;
+            const unsigned g2 = (__ballot_sync(FULL, mine) >> gbase) & 0xFFFFu;
+            if (run && (g2 & (g2 - 1)) != 0) tie = true; // equal (dist, hops): the doubled id decides -> not mirror invariant
             const uint32_t m3 = __reduce_min_sync(gmask, mine ? k3 : 0xFFFFFFFFu);
             mine = mine && k3 == m3;
             gbm = (__ballot_sync(FULL, mine) >> gbase) & 0xFFFFu;
@@ -775,8 +798,8 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
             svU[12] = lo;
             svU[13] = liveRegs;
             svU[14] = needLoad ? 1u : 0u;
+            svU[15] = pend | (tie ? 4u : 0u);
         }
-        if (lane == 0) svW[15] = stash;
         svK[0] = (uint32_t)khi;
         svK[32] = (uint32_t)(khi >> 32);
         svK[64] = (uint32_t)klo;
@@ -787,12 +810,18 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
 #pragma unroll 1
         for (int gg = 0; gg < 2; ++gg) {
             if (!(finb & (1u << (gg * 16)))) continue; // warp-uniform
-            const uint32_t *u = smemw + (uint32_t)(blockDim.x >> 5) * 2 * hbw + (uint32_t)warpInCta * kPairsSaveWords + gg * 16;
+            uint32_t *u = smemw + (uint32_t)(blockDim.x >> 5) * 2 * hbw + (uint32_t)warpInCta * kPairsSaveWords + gg * 16;
             const uint32_t fwi = u[2];
             const int32_t fidx = P.worklist ? P.worklist[fwi] : (int32_t)fwi;
-            finishSourcePairs(Q.kargs, scratch + (((size_t)blockIdx.x * (blockDim.x >> 5) + warpInCta) * 2 + gg) * tileBytes(caps),
-                              reinterpret_cast<unsigned char *>(smemw + (uint32_t)(warpInCta * 2 + gg) * hbw),
-                              __hiloint2double((int)u[4], (int)u[3]), u[6], u[7], u[8], u[9], (int)u[10], u[1], fidx);
+            const uint32_t fpend = u[15] & 3u;
+            // the twin's results come from the same labels iff this search never broke a tie by id and did not overflow
+            const bool mirror = fpend == 2u && (u[15] >> 2) == 0u && u[10] == 0u;
+            const int32_t fidx2 = mirror ? (P.worklist ? P.worklist[fwi + 1] : (int32_t)(fwi + 1)) : -1;
+            const int ok = finishSourcePairs(Q.kargs, scratch + (((size_t)blockIdx.x * (blockDim.x >> 5) + warpInCta) * 2 + gg) * tileBytes(caps),
+                                             reinterpret_cast<unsigned char *>(smemw + (uint32_t)(warpInCta * 2 + gg) * hbw),
+                                             __hiloint2double((int)u[4], (int)u[3]), u[6], u[7], u[8], u[9], (int)u[10], u[1], fidx, fidx2);
+            __syncwarp(FULL);
+            if (lane == 0) u[15] = (fpend != 0u && !(mirror && ok)) ? 1u : 0u; // 1: the second source is searched next
         }
         __syncwarp(FULL);
     }

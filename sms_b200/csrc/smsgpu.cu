@@ -124,6 +124,7 @@ struct smsgpu_ctx {
     bool pairs = false;       // tier 1 runs the pairs engine (ocw_search_pairs.cuh)
     float pairsScaleU = 0.f;  // bucket map of the pairs engine (PairsParams)
     float pairsScaleB = 0.f;
+    bool pairsMirror = true;  // twin sources searched once (SMSGPU_MIRROR=0 turns it off)
     // round input
     DevBuf dX, dBl;
     const double *xPtr = nullptr;   // device pointer in use (own buffer or caller's)
@@ -249,7 +250,7 @@ cudaError_t launchSearch(smsgpu_ctx *c, int tierIdx, const GraphDev &G, const Se
         if (e != cudaSuccess) return e;
         e = cudaMemcpyAsync(c->dPairsArgs.p, &K, sizeof K, cudaMemcpyHostToDevice, c->stream); // pageable source: staged before return
         if (e != cudaSuccess) return e;
-        const PairsParams Q{c->dPairsArgs.as<PairsKArgs>(), c->dRowinfo.as<uint2>(), c->pairsScaleU, c->pairsScaleB};
+        const PairsParams Q{c->dPairsArgs.as<PairsKArgs>(), c->dRowinfo.as<uint2>(), c->pairsScaleU, c->pairsScaleB, c->pairsMirror ? 1 : 0};
         ocwSearchPairsKernel<<<t.ctas, 128, t.smemBytes, c->stream>>>(G, Q, P, R, t.caps, t.scratch.as<unsigned char>());
         return cudaGetLastError();
     }
@@ -460,6 +461,7 @@ int smsgpu_create(smsgpu_ctx **out, int64_t n, int64_t m, const int64_t *rowptr,
     {
         const char *ev = std::getenv("SMSGPU_PAIRS");
         ctx->pairs = (2 * m < (int64_t)0xFFFFFFFFll) && !(ev && ev[0] == '0');
+        if (const char *em = std::getenv("SMSGPU_MIRROR")) ctx->pairsMirror = !(em[0] == '0');
         if (ctx->pairs) {
             std::vector<uint2> ri((size_t)std::max<int64_t>(n, 1));
             for (int64_t u = 0; u < n; ++u) ri[u] = make_uint2((uint32_t)rowptr[u], (uint32_t)(rowptr[u + 1] - rowptr[u]));
