@@ -47,7 +47,7 @@ REF_SAMPLE = {"random1m": 256, "torus100": 10_000, "torus3d20": 8_000, "random20
 
 
 # dram bytes of the search of one full round, from the committed ncu capture (per launch; see roofline.traffic_note)
-TRAFFIC_NCU = {"random1m": round(78.770506e9 * 1254134233 / 82067275)}  # 78.77 GB for the 82.07 M settled nodes of the capture
+TRAFFIC_NCU = {"random1m": round(41.649689e9 * 1254134233 / 82067275)}  # 41.65 GB for the capture's 82.07 M (reference-equivalent) settled nodes
 
 
 def peaks():
@@ -190,7 +190,15 @@ def time_rounds(ctx, torch, dist, world, steps, warmup, step_fn, flush):
     per = []
     for _ in range(steps):
         flush()
-        per.append(step_fn())
+        t1 = time.perf_counter()
+        step_fn()
+        if os.environ.get("BENCH_DEBUG"):
+            torch.cuda.synchronize()
+            ctx.fetch()
+            st = ctx.stats()
+            print(f"[bench] step wall {1e3 * (time.perf_counter() - t1):.1f} ms, device search {st['ms_search']:.1f} ms, tiers {st['tier_sources']}, "
+                  f"ms_tier {[round(v, 1) for v in st['ms_tier']]}", file=sys.stderr, flush=True)
+        per.append(None)
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
@@ -236,11 +244,11 @@ def measure_workload(name, args, torch, dist, rank, world, device, full=True):
         return None
 
     sampler = ClockSampler(device)
-    # warm-up (allocations, tier scratch) happens inside time_rounds
+    sampler.start()  # before the warm-up: starting nvidia-smi (NVML init) inside the timed region once cost a step 400 ms
+    # warm-up: allocations, tier scratch, and the history the engine keeps between rounds (issue order, tier-0 decision)
     for _ in range(max(args.warmup, 3)):
         step_dev()
     torch.cuda.synchronize()
-    sampler.start()
     dt, _ = time_rounds(ctx, torch, dist, world, args.steps, 0, step_dev, flush)
     clocks = sampler.stop()
     # per-round device stats of the last round (events on the library's own stream)
@@ -249,12 +257,13 @@ def measure_workload(name, args, torch, dist, rank, world, device, full=True):
     ncuts, nnodes = ctx.cut_counts()
     res = {"dt": dt, "stats": st, "ncuts": ncuts, "nnodes": nnodes, "clocks": clocks, "n": inst.n, "m": inst.m}
     # aggregate algorithmic work over ranks (each rank searched its share of the sources)
-    work = torch.tensor([st["arcs_scanned"], st["settled"], st["sources_run"], st["raw_walks"]], dtype=torch.float64, device="cuda")
+    work = torch.tensor([st["arcs_scanned"], st["settled"], st["sources_run"], st["raw_walks"], st["mirrored_arcs"], st["mirrored_sources"]],
+                        dtype=torch.float64, device="cuda")
     ms = torch.tensor([st["ms_search"], st["ms_weights"], st["ms_dedup"], st["ms_total_device"]], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(work, op=dist.ReduceOp.SUM)
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    res["arcs"], res["settled"], res["sources_run"], res["raw_walks"] = (int(v) for v in work.tolist())
+    res["arcs"], res["settled"], res["sources_run"], res["raw_walks"], res["mirrored_arcs"], res["mirrored_sources"] = (int(v) for v in work.tolist())
     res["ms_search"], res["ms_weights"], res["ms_dedup"], res["ms_total_device"] = ms.tolist()
 
     # ---- e2e leg: host buffers through the C ABI, H2D and D2H inside the timed region ----
@@ -310,7 +319,10 @@ def main():
     if rank == 0:
         peak, peak_src = peaks()
         sec = res["dt"] / args.steps
-        alg_bytes = 12.0 * res["arcs"] + 8.0 * res["settled"]
+        # roofline on the work actually done: the scans / settled nodes of mirrored twin sources are results obtained by
+        # symmetry, not traffic (settled nodes of mirrored sources are not counted separately: same share as their arcs)
+        done_share = 1.0 - res["mirrored_arcs"] / max(res["arcs"], 1)
+        alg_bytes = (12.0 * res["arcs"] + 8.0 * res["settled"]) * done_share
         # the search kernels of all ranks run concurrently: aggregate bytes / slowest rank's kernel time / N GPUs
         ach = alg_bytes / (res["ms_search"] * 1e-3) / 1e9 / world if res["ms_search"] > 0 else 0.0
         line = {
@@ -318,10 +330,12 @@ def main():
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": WORKLOADS[args.workload][1], "name": args.workload, "n": res["n"], "m": res["m"],
-                       "sources": res["n"], "mode": "I (independent sources), canonical ties, dedup on",
+                       "sources": res["n"], "mode": "I (independent sources), canonical ties, dedup on; twin sources (v,0)/(v,1) searched once when tie-free; issue order from the previous (warm-up) round",
                        "l2": "256 MiB buffer rewritten between timed iterations; arc array alone is 16 B x 2m",
                        "parallelism": f"source pairs cyclic over {world} GPU(s), graph replicated"},
-            "gteps": res["arcs"] / sec / 1e9,
+            "gteps": res["arcs"] / sec / 1e9,  # arc scans of the reference's sweep (its numberOfEdgesSeen) per second
+            "gteps_scanned": (res["arcs"] - res["mirrored_arcs"]) / sec / 1e9,  # ... of which actually scanned by the GPU
+            "mirrored_sources": res["mirrored_sources"], "mirrored_arcs": res["mirrored_arcs"],
             "arcs_scanned_per_round": res["arcs"], "settled_per_round": res["settled"], "raw_walks": res["raw_walks"],
             "unique_cuts": res["ncuts"],
             "kernel_ms": {"weights": res["ms_weights"], "search": res["ms_search"], "dedup_and_merge": res["ms_dedup"],

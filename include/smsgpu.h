@@ -87,8 +87,8 @@ typedef struct smsgpu_stats {
     double ms_h2d, ms_d2h;
     int64_t search_launches;   /* kernel launches of the search kernel this round */
     int64_t total_launches;    /* all kernel launches this round */
-    int64_t fast_steps;        /* fast engine: extraction steps (settled / fast_steps = keys extracted per step) */
-    int64_t fast_bucket_loads; /* fast engine: bucket (re)loads */
+    int64_t mirrored_sources;  /* sources whose results were derived from their twin's search (same vertex, other side) */
+    int64_t mirrored_arcs;     /* part of arcs_scanned that was NOT scanned: the twin's scans stand for them */
     double ms_tier[4];         /* search kernel time per tier (shared / HBM medium / HBM large / dense) */
     int64_t reserved[1];
 } smsgpu_stats;

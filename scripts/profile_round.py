@@ -29,5 +29,5 @@ for r in range(a.rounds):
     ctx.fetch()
     st = ctx.stats()
     print({k: st[k] for k in ("sources_run", "arcs_scanned", "settled", "raw_walks", "unique_cuts", "tier_sources", "ms_weights",
-                              "ms_search", "ms_tier", "ms_dedup", "ms_total_device", "total_launches", "fast_steps", "fast_bucket_loads")})
+                              "ms_search", "ms_tier", "ms_dedup", "ms_total_device", "total_launches", "mirrored_sources", "mirrored_arcs")})
 ctx.close()

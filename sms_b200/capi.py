@@ -73,8 +73,8 @@ class StatsStruct(C.Structure):
         ("ms_d2h", C.c_double),
         ("search_launches", C.c_int64),
         ("total_launches", C.c_int64),
-        ("fast_steps", C.c_int64),
-        ("fast_bucket_loads", C.c_int64),
+        ("mirrored_sources", C.c_int64),
+        ("mirrored_arcs", C.c_int64),
         ("ms_tier", C.c_double * 4),
         ("reserved", C.c_int64 * 1),
     ]

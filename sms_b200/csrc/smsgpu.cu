@@ -938,8 +938,8 @@ int smsgpu_separate_async(smsgpu_ctx *ctx, const smsgpu_params *params) {
         ctx->stats.sources_run = (long long)hc[4];
         ctx->stats.arcs_scanned = (long long)hc[2];
         ctx->stats.settled = (long long)hc[3];
-        ctx->stats.fast_steps = (long long)hc[6];
-        ctx->stats.fast_bucket_loads = (long long)hc[7];
+        ctx->stats.mirrored_sources = (long long)hc[6];
+        ctx->stats.mirrored_arcs = (long long)hc[7];
         ctx->stats.raw_walks = rawCuts;
         ctx->nLabels = nlab;
         for (int k = 0; k < kNumTiers; ++k) {
