@@ -112,13 +112,37 @@ __device__ __noinline__ int finishSourcePairs(const PairsKArgs *K, unsigned char
         const int nsel = selectIntermediates<32>(T, M, S, maxInter, sel);
         if (!S.overflow && T.lane == 0) {
             // srcIdx2 >= 0: the twin source (other side of the same vertex) gets the same walks -- its search is the mirror
-            // image of this one, and a walk is a sequence of ORIGINAL vertices and stay/cross flags
+            // image of this one, and a walk is a sequence of ORIGINAL vertices and stay/cross flags.  The cuts of the first
+            // pass are logged and copied; only if there are more than the log holds, the walks are built a second time.
+            constexpr int kLog = 64;
+            long long logCut[kLog];
+            int32_t logLen[kLog];
+            int nlogged = 0;
             for (int pass = 0; pass < (srcIdx2 >= 0 ? 2 : 1) && !S.overflow; ++pass) {
                 Emitter E;
                 E.R = &R;
                 E.srcIdx = pass ? srcIdx2 : srcIdx;
                 E.seq = 0;
                 E.tier = P.tier;
+                if (pass == 0 && srcIdx2 >= 0) {
+                    E.logCut = logCut;
+                    E.logLen = logLen;
+                    E.logCap = kLog;
+                }
+                if (pass == 1 && nlogged <= kLog) { // copy
+                    for (int i = 0; i < nlogged; ++i) {
+                        long long cut, off;
+                        if (emitReserve(E, logLen[i], cut, off) && logCut[i] >= 0) {
+                            const long long so = R.cutOff[logCut[i]];
+                            for (int k = 0; k < logLen[i]; ++k) {
+                                R.node[off + k] = R.node[so + k];
+                                R.eid[off + k] = R.eid[so + k];
+                                R.stay[off + k] = R.stay[so + k];
+                            }
+                        }
+                    }
+                    break;
+                }
                 for (int r = 0; r < nsel; ++r) {
                     const int W = buildWalk(M, sel[r], src);
                     if (W < 0) {
@@ -128,6 +152,7 @@ __device__ __noinline__ int finishSourcePairs(const PairsKArgs *K, unsigned char
                     simpleOddCyclesAndExtract(G, M, S, E, W);
                     if (S.overflow) break;
                 }
+                nlogged = E.nlog;
             }
         }
         S.overflow = T.shfl(S.overflow, 0);

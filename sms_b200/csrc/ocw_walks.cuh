@@ -17,6 +17,10 @@ struct Emitter {
     int32_t srcIdx;
     int32_t seq;
     int32_t tier;
+    // optional log of the cuts emitted (pairs engine: the twin source gets copies of them)
+    long long *logCut = nullptr; // arena index of cut i, -1 if the arena was full
+    int32_t *logLen = nullptr;
+    int32_t nlog = 0, logCap = 0;
 };
 
 // reserve room for one cut; returns false (and still counts) when the arena is full
@@ -30,6 +34,13 @@ __device__ __forceinline__ bool emitReserve(Emitter &E, int len, long long &cut,
         E.R->cutSrc[cut] = E.srcIdx;
         E.R->cutSeq[cut] = E.seq;
         E.R->cutTier[cut] = (int8_t)E.tier;
+    }
+    if (E.logCut) {
+        if (E.nlog < E.logCap) {
+            E.logCut[E.nlog] = ok ? cut : -1;
+            E.logLen[E.nlog] = len;
+        }
+        E.nlog++;
     }
     E.seq++;
     return ok;
