@@ -87,7 +87,11 @@ __device__ __forceinline__ uint32_t bucketOf(const double d, const float scaleU,
 __device__ __noinline__ int finishSourcePairs(const PairsKArgs *K, unsigned char *tile, unsigned char *hot, const double best,
                                               const uint32_t histN, const uint32_t touchedN, const uint32_t arcs,
                                               const uint32_t settled, const int overflow, const uint32_t src,
-                                              const int32_t srcIdx, const int32_t srcIdx2) {
+                                              const int32_t srcIdx, const int32_t twinIdx, const int mirrorOk) {
+    // twinIdx >= 0: the next entry of the source list is this source's twin (other side of the same vertex).  Its results
+    // are emitted from this search when mirrorOk; if this source overflows, the twin goes to the next tier with it (its
+    // search is the mirror image and would hit the same capacity).  Returns 0 / 1 / 2 = sources disposed of... see below.
+    const int32_t srcIdx2 = (twinIdx >= 0 && mirrorOk && !overflow) ? twinIdx : -1;
     const Tile<32> T;
     const GraphDev G = K->G;
     const TileCaps caps = K->caps;
@@ -201,12 +205,17 @@ __device__ __noinline__ int finishSourcePairs(const PairsKArgs *K, unsigned char
                 atomicAdd(&R.counters[7], (unsigned long long)arcs);
             }
         }
-    } else if (T.lane == 0) {
-        const unsigned long long k = atomicAdd(P.ovfCount, 1ull);
-        P.ovfList[k] = srcIdx;
+        if (srcIdx2 >= 0) counted = 2;
+    } else {
+        if (T.lane == 0) {
+            const unsigned long long k = atomicAdd(P.ovfCount, twinIdx >= 0 ? 2ull : 1ull);
+            P.ovfList[k] = srcIdx;
+            if (twinIdx >= 0) P.ovfList[k + 1] = twinIdx; // adjacent: the next tier can pair them again
+        }
+        if (twinIdx >= 0) counted = 2;
     }
     T.sync();
-    return counted;
+    return counted; // 2: the twin is disposed of as well (mirrored, or sent to the next tier with this source)
 }
 
 #ifndef SMSGPU_PAIRS_MIN_CTAS
@@ -839,14 +848,14 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
             const uint32_t fwi = u[2];
             const int32_t fidx = P.worklist ? P.worklist[fwi] : (int32_t)fwi;
             const uint32_t fpend = u[15] & 3u;
-            // the twin's results come from the same labels iff this search never broke a tie by id and did not overflow
-            const bool mirror = fpend == 2u && (u[15] >> 2) == 0u && u[10] == 0u;
-            const int32_t fidx2 = mirror ? (P.worklist ? P.worklist[fwi + 1] : (int32_t)(fwi + 1)) : -1;
+            // the twin's results come from the same labels iff this search never broke a tie by id (and did not overflow)
+            const int32_t fidx2 = fpend == 2u ? (P.worklist ? P.worklist[fwi + 1] : (int32_t)(fwi + 1)) : -1;
+            const int mirrorOk = (u[15] >> 2) == 0u;
             const int ok = finishSourcePairs(Q.kargs, scratch + (((size_t)blockIdx.x * (blockDim.x >> 5) + warpInCta) * 2 + gg) * tileBytes(caps),
                                              reinterpret_cast<unsigned char *>(smemw + (uint32_t)(warpInCta * 2 + gg) * hbw),
-                                             __hiloint2double((int)u[4], (int)u[3]), u[6], u[7], u[8], u[9], (int)u[10], u[1], fidx, fidx2);
+                                             __hiloint2double((int)u[4], (int)u[3]), u[6], u[7], u[8], u[9], (int)u[10], u[1], fidx, fidx2, mirrorOk);
             __syncwarp(FULL);
-            if (lane == 0) u[15] = (fpend != 0u && !(mirror && ok)) ? 1u : 0u; // 1: the second source is searched next
+            if (lane == 0) u[15] = (fpend != 0u && ok != 2) ? 1u : 0u; // 1: the second source is searched next
         }
         __syncwarp(FULL);
     }
