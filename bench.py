@@ -47,7 +47,7 @@ REF_SAMPLE = {"random1m": 256, "torus100": 10_000, "torus3d20": 8_000, "random20
 
 
 # dram bytes of the search of one full round, from the committed ncu capture (per launch; see roofline.traffic_note)
-TRAFFIC_NCU = {"random1m": round(41.649689e9 * 1254134233 / 82067275)}  # 41.65 GB for the capture's 82.07 M (reference-equivalent) settled nodes
+TRAFFIC_NCU = {"random1m": round(165.474537e9 * 1254134233 / 329005693)}  # 165.47 GB for the capture's 329.0 M (reference-equivalent) settled nodes
 
 
 def peaks():
@@ -344,8 +344,8 @@ def main():
             "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                          "traffic": TRAFFIC_NCU.get(args.workload), "peak_source": peak_src,
                          "kernel": "ocwSearchPairsKernel (tier 1; tiers 0/2: ocwSearchKernel)",
-                         "traffic_note": "dram__bytes_read+write of the tier-1 launch from profiles/r01_pairs_tier1_random1m_64k.md "
-                                         "(ncu --set full, 65536 sources), scaled to the round by settled nodes; the path is bound by "
+                         "traffic_note": "dram__bytes_read+write of the tier-1 launch from profiles/r01_pairs_tier1_random1m_256k.md "
+                                         "(ncu --set full, 262144 sources), scaled to the round by settled nodes; the path is bound by "
                                          "dependent random 32-byte accesses, not by bytes (DESIGN.md section 5)",
                          "algorithmic_bytes": alg_bytes, "per_gpu": True},
             "e2e": {"value": args.steps / res["e2e_dt"], "unit": "rounds/s", "h2d_bytes_per_step": res["h2d"],
