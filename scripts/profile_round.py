@@ -16,13 +16,15 @@ ap.add_argument("--workload", default="random1m")
 ap.add_argument("--sources", type=int, default=0)
 ap.add_argument("--rounds", type=int, default=2)
 ap.add_argument("--start-tier", type=int, default=0)
+ap.add_argument("--rank", type=int, default=0, help="with --nranks: run this rank's shard of the sources only (no communicator)")
+ap.add_argument("--nranks", type=int, default=1)
 ap.add_argument("--xstar", default="uniform", choices=["uniform", "lp_like"])
 a = ap.parse_args()
 inst = WORKLOADS[a.workload][0]()
 x = I.xstar_uniform(inst.m, seed=1) if a.xstar == "uniform" else I.xstar_lp_like(inst.m, seed=1)
 ctx = capi.Context(inst.n, inst.rowptr, inst.col, inst.eid, device=0)
-if a.sources:
-    ctx.set_sources(np.arange(a.sources, dtype=np.int32))
+if a.sources or a.nranks > 1:
+    ctx.set_sources(np.arange(a.sources or inst.n, dtype=np.int32), rank=a.rank, nranks=a.nranks)
 for r in range(a.rounds):
     ctx.set_round_input(x, inst.root_blacklist())
     ctx.separate_async(dedup=1, start_tier=a.start_tier)

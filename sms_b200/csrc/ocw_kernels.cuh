@@ -72,36 +72,48 @@ __global__ void initTablesKernel(unsigned char *scratch, const size_t tileStride
 // arbitrary (results do not depend on the issue order).
 constexpr int kOrderBins = 1024;
 constexpr int kOrderShift = 4; // 16 settled nodes per bin
-__device__ __forceinline__ int orderBinOfPair(const uint32_t *__restrict__ work, const long long k, const long long nsrc) {
+// Pairs with a member that needed tier 2 or 3 this round ("heavy") sort in front of all others, in bins
+// [0, kOrderBins); the rest in [kOrderBins, 2 kOrderBins).  The next round starts the heavy prefix in tier 2 at once, on
+// a second stream beside tier 1, instead of letting it overflow out of tier 1 first and run as a tail.
+__device__ __forceinline__ int orderBinOfPair(const uint32_t *__restrict__ work, const int8_t *__restrict__ tier, const long long k,
+                                              const long long nsrc) {
     uint32_t w = work[2 * k];
-    if (2 * k + 1 < nsrc) w = max(w, work[2 * k + 1]);
-    return kOrderBins - 1 - (int)min(w >> kOrderShift, (uint32_t)(kOrderBins - 1)); // bin 0 = heaviest
+    int t = tier[2 * k];
+    if (2 * k + 1 < nsrc) {
+        w = max(w, work[2 * k + 1]);
+        t = max(t, (int)tier[2 * k + 1]);
+    }
+    const int b = kOrderBins - 1 - (int)min(w >> kOrderShift, (uint32_t)(kOrderBins - 1)); // bin 0 = heaviest
+    return t >= 2 ? b : kOrderBins + b;
 }
-__global__ void orderHistKernel(const long long nsrc, const uint32_t *__restrict__ work, unsigned int *__restrict__ bins) {
-    __shared__ unsigned int h[kOrderBins];
-    for (int b = threadIdx.x; b < kOrderBins; b += blockDim.x) h[b] = 0;
+__global__ void orderHistKernel(const long long nsrc, const uint32_t *__restrict__ work, const int8_t *__restrict__ tier,
+                                unsigned int *__restrict__ bins) {
+    __shared__ unsigned int h[2 * kOrderBins];
+    for (int b = threadIdx.x; b < 2 * kOrderBins; b += blockDim.x) h[b] = 0;
     __syncthreads();
     const long long npairs = nsrc >> 1; // an odd last source goes last (orderScatterKernel)
     for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < npairs; k += (long long)gridDim.x * blockDim.x)
-        atomicAdd(&h[orderBinOfPair(work, k, nsrc)], 1u);
+        atomicAdd(&h[orderBinOfPair(work, tier, k, nsrc)], 1u);
     __syncthreads();
-    for (int b = threadIdx.x; b < kOrderBins; b += blockDim.x)
+    for (int b = threadIdx.x; b < 2 * kOrderBins; b += blockDim.x)
         if (h[b]) atomicAdd(&bins[b], h[b]);
 }
-__global__ void orderScanKernel(unsigned int *bins) { // bins[0..kOrderBins) counts -> bins[kOrderBins..) running cursors
+// bins[0 .. 2 kOrderBins) counts -> bins[2 kOrderBins .. 4 kOrderBins) running cursors; bins[4 kOrderBins] = heavy pairs
+__global__ void orderScanKernel(unsigned int *bins) {
     if (threadIdx.x == 0) {
         unsigned int acc = 0;
-        for (int b = 0; b < kOrderBins; ++b) {
-            bins[kOrderBins + b] = acc;
+        for (int b = 0; b < 2 * kOrderBins; ++b) {
+            if (b == kOrderBins) bins[4 * kOrderBins] = acc;
+            bins[2 * kOrderBins + b] = acc;
             acc += bins[b];
         }
     }
 }
-__global__ void orderScatterKernel(const long long nsrc, const uint32_t *__restrict__ work, unsigned int *__restrict__ bins,
-                                   int32_t *__restrict__ order) {
+__global__ void orderScatterKernel(const long long nsrc, const uint32_t *__restrict__ work, const int8_t *__restrict__ tier,
+                                   unsigned int *__restrict__ bins, int32_t *__restrict__ order) {
     const long long npairs = nsrc >> 1;
     for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < npairs; k += (long long)gridDim.x * blockDim.x) {
-        const unsigned int pos = atomicAdd(&bins[kOrderBins + orderBinOfPair(work, k, nsrc)], 1u);
+        const unsigned int pos = atomicAdd(&bins[2 * kOrderBins + orderBinOfPair(work, tier, k, nsrc)], 1u);
         order[2 * (long long)pos] = (int32_t)(2 * k);
         order[2 * (long long)pos + 1] = (int32_t)(2 * k + 1);
     }
@@ -230,7 +242,7 @@ __global__ void __launch_bounds__(128, FAST ? SMSGPU_FAST_MIN_CTAS : 1) ocwSearc
     if (T.lane == 0 && accSources) {
         atomicAdd(&R.counters[2], (unsigned long long)accArcs);
         atomicAdd(&R.counters[3], (unsigned long long)accSettled);
-        atomicAdd(&R.counters[4], (unsigned long long)accSources);
+        atomicAdd(&R.counters[P.runSlot], (unsigned long long)accSources);
         if (FAST) {
             atomicAdd(&R.counters[6], (unsigned long long)accSteps);
             atomicAdd(&R.counters[7], (unsigned long long)accLoads);

@@ -141,6 +141,7 @@ struct SearchParams {
     int32_t debugFlags;     // bit 0: only the first tile of every warp works (debugging aid)
     uint32_t stampBase;     // fast engine: entry stamp of work item wi is stampBase + wi + 1 (unique per scratch)
     int32_t hotInSmem;      // fast engine: bucket counters + presence bitmap in shared memory (tier 1) or HBM (tier 2)
+    int32_t runSlot;        // RawOut::counters slot that counts the sources run (4; another one for an overlapped launch)
 };
 
 } // namespace smsgpu

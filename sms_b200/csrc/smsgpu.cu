@@ -111,8 +111,10 @@ struct CutListHost {
 struct smsgpu_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t stream2 = nullptr; // the overlapped tier-2 launch of the sources known to be heavy
     cudaEvent_t ev[8]{};
-    cudaEvent_t tierEv[2 * 4]{}; // start / end of each tier's search launch
+    cudaEvent_t tierEv[2 * 5]{}; // start / end of each tier's search launch; [8], [9]: the overlapped tier-2 launch
+    cudaEvent_t joinEv = nullptr;
     int smCount = 148;
     long long n = 0, m = 0;
     std::string err;
@@ -147,12 +149,16 @@ struct smsgpu_ctx {
     // history used by the next round (DESIGN.md "issue order"): per-source work, the longest-first order built from it,
     // and whether the shared-memory tier is worth running
     DevBuf srcWork, srcOrder, orderBins;
-    bool haveOrder = false, useHistory = true;
+    bool haveOrder = false, useHistory = true, overlapHeavy = true;
+    long long heavyPairs = 0; // srcOrder[0 .. 2 heavyPairs): pairs with a member that finished in tier >= 2 last round
     int skipTier0 = 0; // > 0: rounds for which tier 0 is still skipped (it completed < 1/4 of its sources last time)
     long long cutCap = 0, nodeCap = 0, labCap = 0;
-    DevBuf counters; // 16 x u64: see RawOut::counters; [8] queue cursor, [9] ovf count A, [10] ovf count B, [11] collisions
+    // 24 x u64: see RawOut::counters; [8] queue cursor, [9] ovf count A, [10] ovf count B, [11] collisions;
+    // [16] queue cursor, [17] ovf count, [18] sources run of the overlapped tier-2 launch
+    DevBuf counters;
     PinBuf hCounters;
-    DevBuf ovfA, ovfB;
+    DevBuf ovfA, ovfB, ovfC;
+    std::vector<int32_t> hSources; // the local explicit source list as uploaded (smsgpu_set_sources)
 
     // dedup work
     DevBuf wCnode, wCeid, wCstay, wHash, wRank, wSlot, wKeep, wNcross, wViol, wTabKey, wTabRank, wTabIdx;
@@ -230,32 +236,36 @@ namespace {
 //   <32, false, true >  tiers 1, 2: fast engine (bucket queue + presence bitmap), working memory in HBM
 //   <32, false, false>  tier 3: heap engine on a dense table in HBM
 template <bool SMEM, bool FAST>
-cudaError_t launchSearchT(smsgpu_ctx *c, const TierCfg &t, const GraphDev &G, const SearchParams &P, const RawOut &R) {
+cudaError_t launchSearchT(smsgpu_ctx *c, const TierCfg &t, const GraphDev &G, const SearchParams &P, const RawOut &R, cudaStream_t st,
+                          int ctas) {
     auto kern = ocwSearchKernel<32, SMEM, FAST>;
     if (t.smemBytes) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t.smemBytes);
         if (e != cudaSuccess) return e;
     }
-    kern<<<t.ctas, 128, t.smemBytes, c->stream>>>(G, P, R, t.caps, t.scratch.as<unsigned char>());
+    kern<<<ctas, 128, t.smemBytes, st>>>(G, P, R, t.caps, t.scratch.as<unsigned char>());
     return cudaGetLastError();
 }
-cudaError_t launchSearch(smsgpu_ctx *c, int tierIdx, const GraphDev &G, const SearchParams &P, const RawOut &R) {
+// `ctasCap` > 0 launches fewer CTAs than the tier has tiles for (a short work list beside another launch)
+cudaError_t launchSearch(smsgpu_ctx *c, int tierIdx, const GraphDev &G, const SearchParams &P, const RawOut &R, cudaStream_t st,
+                         int ctasCap = 0) {
     const TierCfg &t = c->tier[tierIdx];
-    if (tierIdx == 0) return launchSearchT<true, false>(c, t, G, P, R);
+    const int ctas = ctasCap > 0 ? std::min(ctasCap, t.ctas) : t.ctas;
+    if (tierIdx == 0) return launchSearchT<true, false>(c, t, G, P, R, st, ctas);
     if (t.pairs) {
         cudaError_t e = cudaFuncSetAttribute(ocwSearchPairsKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t.smemBytes);
         if (e != cudaSuccess) return e;
         PairsKArgs K{G, P, R, t.caps};
         e = c->dPairsArgs.ensure(sizeof K);
         if (e != cudaSuccess) return e;
-        e = cudaMemcpyAsync(c->dPairsArgs.p, &K, sizeof K, cudaMemcpyHostToDevice, c->stream); // pageable source: staged before return
+        e = cudaMemcpyAsync(c->dPairsArgs.p, &K, sizeof K, cudaMemcpyHostToDevice, st); // pageable source: staged before return
         if (e != cudaSuccess) return e;
         const PairsParams Q{c->dPairsArgs.as<PairsKArgs>(), c->dRowinfo.as<uint2>(), c->pairsScaleU, c->pairsScaleB, c->pairsMirror ? 1 : 0};
-        ocwSearchPairsKernel<<<t.ctas, 128, t.smemBytes, c->stream>>>(G, Q, P, R, t.caps, t.scratch.as<unsigned char>());
+        ocwSearchPairsKernel<<<ctas, 128, t.smemBytes, st>>>(G, Q, P, R, t.caps, t.scratch.as<unsigned char>());
         return cudaGetLastError();
     }
-    if (t.caps.nbuckets) return launchSearchT<false, true>(c, t, G, P, R);
-    return launchSearchT<false, false>(c, t, G, P, R);
+    if (t.caps.nbuckets) return launchSearchT<false, true>(c, t, G, P, R, st, ctas);
+    return launchSearchT<false, false>(c, t, G, P, R, st, ctas);
 }
 template <bool SMEM, bool FAST>
 int occupancyT(size_t smemBytes) {
@@ -437,6 +447,12 @@ int smsgpu_create(smsgpu_ctx **out, int64_t n, int64_t m, const int64_t *rowptr,
     CUB(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
     for (auto &e : ctx->ev) CUB(cudaEventCreate(&e));
     for (auto &e : ctx->tierEv) CUB(cudaEventCreate(&e));
+    {
+        int prLow = 0, prHigh = 0; // its CTAs take free SM slots before tier 1's
+        CUB(cudaDeviceGetStreamPriorityRange(&prLow, &prHigh));
+        CUB(cudaStreamCreateWithPriority(&ctx->stream2, cudaStreamNonBlocking, prHigh));
+    }
+    CUB(cudaEventCreateWithFlags(&ctx->joinEv, cudaEventDisableTiming));
     CUB(ctx->dRowptr.ensure((size_t)(n + 1) * sizeof(int64_t)));
     CUB(ctx->dCol.ensure((size_t)std::max<int64_t>(2 * m, 4) * sizeof(int32_t)));
     CUB(ctx->dEid.ensure((size_t)std::max<int64_t>(2 * m, 4) * sizeof(int32_t)));
@@ -450,8 +466,8 @@ int smsgpu_create(smsgpu_ctx **out, int64_t n, int64_t m, const int64_t *rowptr,
     CUB(ctx->dBl.ensure((size_t)n));
     CUB(ctx->hX.ensure((size_t)std::max<int64_t>(m, 1) * sizeof(double)));
     CUB(ctx->hBl.ensure((size_t)n));
-    CUB(ctx->counters.ensure(16 * sizeof(unsigned long long)));
-    CUB(ctx->hCounters.ensure(16 * sizeof(unsigned long long)));
+    CUB(ctx->counters.ensure(24 * sizeof(unsigned long long)));
+    CUB(ctx->hCounters.ensure(24 * sizeof(unsigned long long)));
     CUB(cudaStreamSynchronize(ctx->stream));
     // tile width by average degree: one lane per arc of a typical row
     const double avgDeg = n ? 2.0 * (double)m / (double)n : 0.0;
@@ -484,6 +500,7 @@ int smsgpu_create(smsgpu_ctx **out, int64_t n, int64_t m, const int64_t *rowptr,
         }
     }
     if (const char *eh = std::getenv("SMSGPU_NO_HISTORY")) ctx->useHistory = !(eh[0] == '1');
+    if (const char *eo = std::getenv("SMSGPU_NO_OVERLAP")) ctx->overlapHeavy = !(eo[0] == '1');
     configureTiers(ctx);
     ctx->nsrcGlobal = ctx->nsrcLocal = n; // default source list 0..n-1 (conshdlr_oscw.cpp:188-195)
     ctx->rank = 0;
@@ -498,11 +515,12 @@ void smsgpu_destroy(smsgpu_ctx *ctx) {
     cudaSetDevice(ctx->device);
     smsgpu_comm_destroy(ctx);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    if (ctx->stream2) cudaStreamSynchronize(ctx->stream2);
     DevBuf *dev[] = {&ctx->dPairsArgs, &ctx->dRowinfo, &ctx->dRowptr, &ctx->dCol, &ctx->dEid, &ctx->dArcs, &ctx->dX, &ctx->dBl, &ctx->dSources,
                      &ctx->tier[0].scratch, &ctx->tier[1].scratch, &ctx->tier[2].scratch, &ctx->tier[3].scratch, &ctx->rNode, &ctx->rEid,
                      &ctx->rStay, &ctx->rCutOff, &ctx->rCutLen, &ctx->rCutSrc, &ctx->rCutSeq, &ctx->rCutTier, &ctx->rValid,
                      &ctx->labSrc, &ctx->labNode, &ctx->labHops, &ctx->labDist, &ctx->srcTier, &ctx->srcArcs,
-                     &ctx->srcSettled, &ctx->srcWork, &ctx->srcOrder, &ctx->orderBins, &ctx->counters, &ctx->ovfA, &ctx->ovfB, &ctx->wCnode, &ctx->wCeid, &ctx->wCstay,
+                     &ctx->srcSettled, &ctx->srcWork, &ctx->srcOrder, &ctx->orderBins, &ctx->counters, &ctx->ovfA, &ctx->ovfB, &ctx->ovfC, &ctx->wCnode, &ctx->wCeid, &ctx->wCstay,
                      &ctx->wHash, &ctx->wRank, &ctx->wSlot, &ctx->wKeep, &ctx->wNcross, &ctx->wViol, &ctx->wTabKey,
                      &ctx->wTabRank, &ctx->wTabIdx, &ctx->wCnt, &ctx->wCursor, &ctx->wBase, &ctx->wOrder, &ctx->wOutLen,
                      &ctx->wBlockSums, &ctx->fin.off, &ctx->fin.node, &ctx->fin.eid, &ctx->fin.stay, &ctx->fin.ncross,
@@ -526,6 +544,8 @@ void smsgpu_destroy(smsgpu_ctx *ctx) {
         if (e) cudaEventDestroy(e);
     for (auto &e : ctx->tierEv)
         if (e) cudaEventDestroy(e);
+    if (ctx->joinEv) cudaEventDestroy(ctx->joinEv);
+    if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -567,6 +587,9 @@ int smsgpu_set_sources(smsgpu_ctx *ctx, const int32_t *sources, int64_t nsrc, in
     if (nranks < 1 || rank < 0 || rank >= nranks) return fail(ctx, SMSGPU_ERR_ARG, "bad rank %d / %d", rank, nranks);
     if (sources && nsrc < 0) return fail(ctx, SMSGPU_ERR_ARG, "negative source count");
     CU(cudaSetDevice(ctx->device));
+    // the same list again (a handler that sets its sources before every round): the history of the previous round stays
+    bool same = ctx->rank == rank && ctx->nranks == nranks && ctx->nsrcGlobal == (sources ? nsrc : ctx->n) &&
+                ctx->explicitSources == (sources != nullptr);
     ctx->rank = rank;
     ctx->nranks = nranks;
     ctx->nsrcGlobal = sources ? nsrc : ctx->n;
@@ -580,17 +603,26 @@ int smsgpu_set_sources(smsgpu_ctx *ctx, const int32_t *sources, int64_t nsrc, in
         ctx->nsrcLocal = cnt;
     }
     ctx->explicitSources = sources != nullptr;
-    ctx->haveOrder = false; // the local index space changed
-    ctx->skipTier0 = 0;
     if (sources) {
         std::vector<int32_t> mine((size_t)ctx->nsrcLocal);
         for (int64_t j = 0; j < ctx->nsrcLocal; ++j) {
             mine[j] = sources[((j >> 1) * nranks + rank) * 2 + (j & 1)];
             if (mine[j] < 0) return fail(ctx, SMSGPU_ERR_ARG, "negative source id");
         }
-        CU(ctx->dSources.ensure(std::max<size_t>(mine.size(), 1) * sizeof(int32_t)));
-        CU(cudaMemcpyAsync(ctx->dSources.p, mine.data(), mine.size() * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
-        CU(cudaStreamSynchronize(ctx->stream));
+        same = same && mine == ctx->hSources;
+        if (!same) {
+            CU(ctx->dSources.ensure(std::max<size_t>(mine.size(), 1) * sizeof(int32_t)));
+            CU(cudaMemcpyAsync(ctx->dSources.p, mine.data(), mine.size() * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
+            CU(cudaStreamSynchronize(ctx->stream));
+            ctx->hSources.swap(mine);
+        }
+    } else {
+        ctx->hSources.clear();
+    }
+    if (!same) { // the local index space changed
+        ctx->haveOrder = false;
+        ctx->skipTier0 = 0;
+        ctx->heavyPairs = 0;
     }
     return SMSGPU_OK;
 }
@@ -793,7 +825,7 @@ int smsgpu_separate_async(smsgpu_ctx *ctx, const smsgpu_params *params) {
     CU(ctx->ovfB.ensure((size_t)std::max<long long>(nsrc, 1) * 4));
     CU(ctx->srcWork.ensure((size_t)std::max<long long>(nsrc, 1) * 4));
     CU(ctx->srcOrder.ensure((size_t)std::max<long long>(nsrc, 1) * 4));
-    CU(ctx->orderBins.ensure(2 * kOrderBins * sizeof(unsigned int)));
+    CU(ctx->orderBins.ensure((4 * kOrderBins + 1) * sizeof(unsigned int)));
     if (P.export_src_stats) {
         CU(ctx->srcArcs.ensure((size_t)std::max<long long>(nsrc, 1) * 8));
         CU(ctx->srcSettled.ensure((size_t)std::max<long long>(nsrc, 1) * 8));
@@ -815,7 +847,7 @@ int smsgpu_separate_async(smsgpu_ctx *ctx, const smsgpu_params *params) {
     long long rawCuts = 0, rawNodes = 0;
     for (int attempt = 0;; ++attempt) {
         if (attempt > 4) return fail(ctx, SMSGPU_ERR_INTERNAL, "raw arena kept overflowing");
-        CU(cudaMemsetAsync(dc, 0, 16 * sizeof(unsigned long long), st));
+        CU(cudaMemsetAsync(dc, 0, 24 * sizeof(unsigned long long), st));
         CU(cudaMemsetAsync(ctx->srcTier.p, 0xFF, (size_t)std::max<long long>(nsrc, 1), st));
         CU(cudaMemsetAsync(ctx->srcWork.p, 0, (size_t)std::max<long long>(nsrc, 1) * 4, st)); // skipped sources: no work
         RawOut R{};
@@ -851,6 +883,7 @@ int smsgpu_separate_async(smsgpu_ctx *ctx, const smsgpu_params *params) {
         SP.exportLabels = P.export_labels;
         SP.debugFlags = P.reserved[0];
         SP.queueCounter = dc + 8;
+        SP.runSlot = 4;
         long long nwork = nsrc;
         const int32_t *worklist = nullptr;
         if (ctx->useHistory && ctx->haveOrder) worklist = ctx->srcOrder.as<int32_t>(); // longest first (previous round)
@@ -860,43 +893,98 @@ int smsgpu_separate_async(smsgpu_ctx *ctx, const smsgpu_params *params) {
         long long done[kNumTiers] = {0, 0, 0, 0};
         long long prevRun = 0;
         bool tierRan[kNumTiers] = {false, false, false, false};
-        for (int ti = firstTier; ti < kNumTiers && nwork > 0; ++ti) {
-            if (int rc = ensureTierScratch(ctx, ti)) return rc;
-            const int which = ti & 1;
-            SP.tier = ti;
-            SP.worklist = worklist;
-            SP.nwork = nwork;
-            SP.ovfList = ovfBufs[which];
-            SP.ovfCount = dc + 9 + which;
-            CU(cudaMemsetAsync(dc + 8, 0, 8, st));
-            CU(cudaMemsetAsync(dc + 9 + which, 0, 8, st));
+        // one search launch (no synchronisation): tier `ti` over `wl[0 .. nw)`, overflows appended to `ovf`
+        auto launchTier = [&](int ti, const int32_t *wl, long long nw, int32_t *ovf, int ovfSlot, int queueSlot, int runSlot,
+                              cudaStream_t s, int evIdx, int ctasCap) -> int {
+            SearchParams Q = SP;
+            Q.tier = ti;
+            Q.worklist = wl;
+            Q.nwork = nw;
+            Q.ovfList = ovf;
+            Q.ovfCount = dc + ovfSlot;
+            Q.queueCounter = dc + queueSlot;
+            Q.runSlot = runSlot;
+            CU(cudaMemsetAsync(dc + queueSlot, 0, 8, s));
+            CU(cudaMemsetAsync(dc + ovfSlot, 0, 8, s));
             if (ctx->tier[ti].caps.nbuckets) {
                 TierCfg &tc = ctx->tier[ti];
-                if (tc.stampNext + (uint64_t)nwork + 2 >= (1ull << 32)) { // stamps exhausted: forget every old entry
+                if (tc.stampNext + (uint64_t)nw + 2 >= (1ull << 32)) { // stamps exhausted: forget every old entry
                     const size_t stride = tileBytes(tc.caps) + (tc.hotInSmem ? 0 : hotBytes(tc.caps));
-                    initTablesKernel<<<ctx->smCount * 8, 256, 0, st>>>(tc.scratch.as<unsigned char>(), stride, tc.ntiles, tc.caps.tabCap);
+                    initTablesKernel<<<ctx->smCount * 8, 256, 0, s>>>(tc.scratch.as<unsigned char>(), stride, tc.ntiles, tc.caps.tabCap);
                     CU(cudaGetLastError());
                     tc.stampNext = 0;
                 }
-                SP.stampBase = (uint32_t)tc.stampNext;
-                SP.hotInSmem = tc.hotInSmem ? 1 : 0;
-                tc.stampNext += (uint64_t)nwork;
+                Q.stampBase = (uint32_t)tc.stampNext;
+                Q.hotInSmem = tc.hotInSmem ? 1 : 0;
+                tc.stampNext += (uint64_t)nw;
             }
-            CU(cudaEventRecord(ctx->tierEv[2 * ti], st));
-            CU(launchSearch(ctx, ti, G, SP, R));
-            CU(cudaEventRecord(ctx->tierEv[2 * ti + 1], st));
-            tierRan[ti] = true;
+            CU(cudaEventRecord(ctx->tierEv[evIdx], s));
+            CU(launchSearch(ctx, ti, G, Q, R, s, ctasCap));
+            CU(cudaEventRecord(ctx->tierEv[evIdx + 1], s));
             ctx->stats.search_launches += 1;
             ctx->stats.total_launches += 1;
+            return 0;
+        };
+        // The pairs that needed tier 2 last round (the prefix of the order) start in tier 2 at once, on a second stream,
+        // with as many CTAs as they have sources for; tier 1 fills the rest of the GPU with everything else.  Run one
+        // after the other, tier 2 is a tail of a few thousand long searches on an otherwise idle GPU.
+        long long heavy = 0;
+        if (worklist && ctx->overlapHeavy && firstTier == 1 && ctx->heavyPairs > 0 && kNumTiers > 2 && ctx->tier[2].caps.nbuckets) {
+            heavy = std::min<long long>(2 * ctx->heavyPairs, nsrc & ~1ll);
+            if (int rc = ensureTierScratch(ctx, 1)) return rc;
+            if (int rc = ensureTierScratch(ctx, 2)) return rc;
+            CU(ctx->ovfC.ensure((size_t)heavy * 4));
+            // Tier 1's CTAs are persistent and fill every SM: tier 2 has to be resident BEFORE them.  A cross-stream event
+            // wait would let the tier-1 launch overtake it (measured: tier 2 then runs after tier 1), hence the host wait.
+            CU(cudaStreamSynchronize(st));
+            const int tilesPerCta = 128 / ctx->tileWidth;
+            if (int rc = launchTier(2, worklist, heavy, ctx->ovfC.as<int32_t>(), 17, 16, 18, ctx->stream2, 8,
+                                    (int)std::min<long long>((heavy + tilesPerCta - 1) / tilesPerCta, 1 << 20)))
+                return rc;
+            CU(cudaEventRecord(ctx->joinEv, ctx->stream2));
+            worklist += heavy;
+            nwork -= heavy;
+        }
+        for (int ti = firstTier; ti < kNumTiers && nwork > 0; ++ti) {
+            if (int rc = ensureTierScratch(ctx, ti)) return rc;
+            const int which = ti & 1;
+            if (heavy > 0 && ti >= 2) CU(cudaStreamWaitEvent(st, ctx->joinEv, 0)); // tier 2's tiles are in use until then
+            if (int rc = launchTier(ti, worklist, nwork, ovfBufs[which], 9 + which, 8, 4, st, 2 * ti, 0)) return rc;
+            tierRan[ti] = true;
             CU(cudaMemcpyAsync(hc, dc, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
             CU(cudaStreamSynchronize(st));
             if (std::getenv("SMSGPU_DEBUG_OVF"))
                 std::fprintf(stderr, "[smsgpu] tier %d: %lld sources in, %llu overflowed (table %llu, bucket %llu, history %llu)\n", ti,
                              nwork, hc[9 + which], hc[12], hc[13], hc[14]);
-            done[ti] = (long long)hc[4] - prevRun;
+            done[ti] += (long long)hc[4] - prevRun;
             prevRun = (long long)hc[4];
             nwork = (long long)hc[9 + which];
             worklist = ovfBufs[which];
+        }
+        long long heavyRun = 0;
+        bool heavyRan = false;
+        if (heavy > 0 && nwork == 0) {
+            CU(cudaStreamWaitEvent(st, ctx->joinEv, 0));
+            CU(cudaMemcpyAsync(hc, dc, 24 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+            CU(cudaStreamSynchronize(st));
+            heavyRan = true;
+            heavyRun = (long long)hc[18];
+            done[2] += heavyRun;
+            nwork = (long long)hc[17];
+            if (std::getenv("SMSGPU_DEBUG_OVF"))
+                std::fprintf(stderr, "[smsgpu] tier 2 beside tier 1: %lld sources in, %lld overflowed\n", heavy, nwork);
+            if (nwork > 0) { // they exceeded tier 2 as well: the dense tier
+                if (int rc = ensureTierScratch(ctx, 3)) return rc;
+                if (int rc = launchTier(3, ctx->ovfC.as<int32_t>(), nwork, ovfBufs[0], 9, 8, 4, st, 6, 0)) return rc;
+                tierRan[3] = true;
+                CU(cudaMemcpyAsync(hc, dc, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+                CU(cudaStreamSynchronize(st));
+                done[3] += (long long)hc[4] - prevRun;
+                prevRun = (long long)hc[4];
+                nwork = (long long)hc[9];
+            }
+        } else if (heavy > 0) {
+            CU(cudaStreamSynchronize(ctx->stream2)); // failing below: leave no launch behind
         }
         if (nwork > 0)
             return fail(ctx, SMSGPU_ERR_INTERNAL, "%lld sources exceeded the capacities of the dense tier", nwork);
@@ -926,16 +1014,21 @@ int smsgpu_separate_async(smsgpu_ctx *ctx, const smsgpu_params *params) {
             else if (ctx->skipTier0 > 0)
                 ctx->skipTier0--;
             unsigned int *bins = ctx->orderBins.as<unsigned int>();
-            CU(cudaMemsetAsync(bins, 0, 2 * kOrderBins * sizeof(unsigned int), st));
+            CU(cudaMemsetAsync(bins, 0, (4 * kOrderBins + 1) * sizeof(unsigned int), st));
             const unsigned g = std::min<unsigned>(gridFor(nsrc, 256), (unsigned)ctx->smCount * 8);
-            orderHistKernel<<<g, 256, 0, st>>>(nsrc, ctx->srcWork.as<uint32_t>(), bins);
+            orderHistKernel<<<g, 256, 0, st>>>(nsrc, ctx->srcWork.as<uint32_t>(), ctx->srcTier.as<int8_t>(), bins);
             orderScanKernel<<<1, 32, 0, st>>>(bins);
-            orderScatterKernel<<<g, 256, 0, st>>>(nsrc, ctx->srcWork.as<uint32_t>(), bins, ctx->srcOrder.as<int32_t>());
+            orderScatterKernel<<<g, 256, 0, st>>>(nsrc, ctx->srcWork.as<uint32_t>(), ctx->srcTier.as<int8_t>(), bins,
+                                                 ctx->srcOrder.as<int32_t>());
             CU(cudaGetLastError());
             ctx->stats.total_launches += 3;
+            unsigned int *hHeavy = reinterpret_cast<unsigned int *>(hc + 23);
+            CU(cudaMemcpyAsync(hHeavy, bins + 4 * kOrderBins, sizeof(unsigned int), cudaMemcpyDeviceToHost, st));
+            CU(cudaStreamSynchronize(st));
+            ctx->heavyPairs = (long long)*hHeavy;
             ctx->haveOrder = true;
         }
-        ctx->stats.sources_run = (long long)hc[4];
+        ctx->stats.sources_run = (long long)hc[4] + heavyRun;
         ctx->stats.arcs_scanned = (long long)hc[2];
         ctx->stats.settled = (long long)hc[3];
         ctx->stats.mirrored_sources = (long long)hc[6];
@@ -948,6 +1041,8 @@ int smsgpu_separate_async(smsgpu_ctx *ctx, const smsgpu_params *params) {
             ctx->stats.ms_tier[k] = 0.0;
             if (tierRan[k] && cudaEventElapsedTime(&tms, ctx->tierEv[2 * k], ctx->tierEv[2 * k + 1]) == cudaSuccess) ctx->stats.ms_tier[k] = tms;
         }
+        float hms = 0; // the overlapped launch ran beside tier 1: the tier times no longer add up to the search time
+        if (heavyRan && cudaEventElapsedTime(&hms, ctx->tierEv[8], ctx->tierEv[9]) == cudaSuccess) ctx->stats.ms_tier[2] += hms;
         break;
     }
     CU(cudaEventRecord(ctx->ev[2], st));

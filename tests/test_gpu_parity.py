@@ -108,6 +108,38 @@ def test_tier1_engines_agree(gpu, orc, engine, monkeypatch):
             assert st["tier_sources"][0] == 0
 
 
+def test_rounds_with_history_equal_the_oracle(gpu, orc):
+    """From the second round on a context issues its sources in the order of the previous round's work, skips the
+    shared-memory tier when it was useless, and starts the pairs that needed tier 2 there at once, on a second
+    stream beside tier 1 (smsgpu.cu "heavy").  None of it may change a result: three rounds with alternating x* on
+    one context, each equal to the oracle walk for walk, with the overlapped tier-2 launch actually exercised."""
+    from sms_b200.separator import GpuOcwSeparator
+    inst = I.random_graph(3000, 12000, seed=11)
+    xs = [I.xstar_lp_like(inst.m, seed=6), I.xstar_uniform(inst.m, seed=7), I.xstar_lp_like(inst.m, seed=6),
+          I.xstar_lp_like(inst.m, seed=8)]
+    bl = inst.root_blacklist()
+    src = inst.handler_sources()
+    sep = GpuOcwSeparator(inst.n, inst.rowptr, inst.col, inst.eid)
+    heavy_rounds = 0
+    try:
+        for r, x in enumerate(xs):
+            exp = orc.sweep(inst, x, blacklist=bl, sources=src, mode="I", canonical=True)
+            sep.setRoundInput(x, bl)
+            got = sep.separateRound(sources=src, dedup=False, start_tier=1, export_src_stats=1)
+            assert got.walks() == exp.walks(), f"round {r}: walks differ"
+            arcs, settled, tier = sep.ctx.src_stats()
+            assert np.array_equal(arcs, exp.stats[:, 0]) and np.array_equal(settled, exp.stats[:, 1])
+            st = sep.ctx.stats()
+            assert st["sources_run"] == int((tier >= 0).sum()) == sum(st["tier_sources"])
+            assert [int((tier == t).sum()) for t in range(4)] == st["tier_sources"]
+            if r > 0 and prev_heavy > 0:
+                heavy_rounds += 1
+            prev_heavy = int((tier >= 2).sum())
+    finally:
+        sep.close()
+    assert heavy_rounds >= 2, "no round started with sources known to need tier 2: the test instance is too easy"
+
+
 def test_overflow_escalates_to_next_tier(gpu, orc):
     """LP-like x* on a degree-8 graph makes balls that do not fit shared memory: sources must escalate and
     still match."""
