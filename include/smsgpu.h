@@ -89,7 +89,8 @@ typedef struct smsgpu_stats {
     int64_t total_launches;    /* all kernel launches this round */
     int64_t mirrored_sources;  /* sources whose results were derived from their twin's search (same vertex, other side) */
     int64_t mirrored_arcs;     /* part of arcs_scanned that was NOT scanned: the twin's scans stand for them */
-    double ms_tier[4];         /* search kernel time per tier (shared / HBM medium / HBM large / dense) */
+    double ms_tier[4];         /* search kernel time per tier (shared / HBM medium / HBM large / dense); the HBM large
+                                * tier may run beside the medium one, so the four need not add up to ms_search */
     int64_t reserved[1];
 } smsgpu_stats;
 
@@ -112,7 +113,9 @@ int smsgpu_set_round_input_device(smsgpu_ctx *ctx, const double *d_x_by_eid, con
 
 /* Source list: doubled ids, in the order ConshdlrOscw issues them (conshdlr_oscw.cpp:188-195 passes
  * 0..n-1).  sources == NULL selects 0..n-1.  With (rank, nranks) the list is dealt cyclically in pairs (2p, 2p+1) and this
- * context runs only its share (source sharding across GPUs). */
+ * context runs only its share (source sharding across GPUs).  A context remembers, per source,
+ * how much work the previous round was and issues the next round accordingly (results never depend on it); setting
+ * the SAME list again keeps that memory, a different list drops it. */
 int smsgpu_set_sources(smsgpu_ctx *ctx, const int32_t *sources, int64_t nsrc, int rank, int nranks);
 
 /* ---- one separation round: replaces the loop over OcwSeparator::getViolatedOcws(source)

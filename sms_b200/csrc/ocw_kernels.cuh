@@ -120,6 +120,26 @@ __global__ void orderScatterKernel(const long long nsrc, const uint32_t *__restr
     if ((nsrc & 1) && blockIdx.x == 0 && threadIdx.x == 0) order[nsrc - 1] = (int32_t)(nsrc - 1);
 }
 
+// The overflow list of a one-source-per-warp tier is in completion order: the two sides of a vertex end up far apart
+// and the pairs engine behind it could not mirror them.  This rebuilds the list from srcTier (< 0: not finished yet,
+// or skipped -- the next tier skips those again): pairs with both members unfinished first, adjacent and aligned,
+// then the single members (`singles`, appended by the host once the counts are known).
+__global__ void pairCompactKernel(const long long nsrc, const int8_t *__restrict__ tier, int32_t *__restrict__ pairsOut,
+                                  int32_t *__restrict__ singles, unsigned long long *__restrict__ counts) {
+    const long long npairs = (nsrc + 1) >> 1;
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < npairs; k += (long long)gridDim.x * blockDim.x) {
+        const bool u0 = tier[2 * k] < 0;
+        const bool u1 = 2 * k + 1 < nsrc && tier[2 * k + 1] < 0;
+        if (u0 && u1) {
+            const unsigned long long pos = atomicAdd(&counts[0], 1ull);
+            pairsOut[2 * pos] = (int32_t)(2 * k);
+            pairsOut[2 * pos + 1] = (int32_t)(2 * k + 1);
+        } else if (u0 || u1) {
+            singles[atomicAdd(&counts[1], 1ull)] = (int32_t)(2 * k + (u1 ? 1 : 0));
+        }
+    }
+}
+
 // ---- K2-K4 ---------------------------------------------------------------------------------------------------
 #ifndef SMSGPU_FAST_MIN_CTAS
 #define SMSGPU_FAST_MIN_CTAS 5

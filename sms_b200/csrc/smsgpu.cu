@@ -960,6 +960,22 @@ int smsgpu_separate_async(smsgpu_ctx *ctx, const smsgpu_params *params) {
             prevRun = (long long)hc[4];
             nwork = (long long)hc[9 + which];
             worklist = ovfBufs[which];
+            if (ti == 0 && nwork > 1 && kNumTiers > 1 && ctx->tier[1].pairs && ctx->pairsMirror) {
+                // tier 0's overflow list is in completion order; the pairs engine wants the two sides of a vertex adjacent
+                CU(ctx->ovfC.ensure((size_t)(nsrc + 1) * 4));
+                CU(cudaMemsetAsync(dc + 19, 0, 16, st));
+                pairCompactKernel<<<std::min<unsigned>(gridFor((nsrc + 1) / 2, 256), (unsigned)ctx->smCount * 8), 256, 0, st>>>(
+                    nsrc, ctx->srcTier.as<int8_t>(), ctx->ovfC.as<int32_t>(), ovfBufs[which], dc + 19);
+                CU(cudaGetLastError());
+                ctx->stats.total_launches += 1;
+                CU(cudaMemcpyAsync(hc + 19, dc + 19, 16, cudaMemcpyDeviceToHost, st));
+                CU(cudaStreamSynchronize(st));
+                const long long both = (long long)hc[19], singles = (long long)hc[20];
+                if (singles > 0)
+                    CU(cudaMemcpyAsync(ctx->ovfC.as<int32_t>() + 2 * both, ovfBufs[which], (size_t)singles * 4, cudaMemcpyDeviceToDevice, st));
+                nwork = 2 * both + singles; // the overflowed sources plus the skipped ones (skipped again by the next tier)
+                worklist = ctx->ovfC.as<int32_t>();
+            }
         }
         long long heavyRun = 0;
         bool heavyRan = false;
