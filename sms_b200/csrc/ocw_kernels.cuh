@@ -98,16 +98,34 @@ __global__ void orderHistKernel(const long long nsrc, const uint32_t *__restrict
     for (int b = threadIdx.x; b < 2 * kOrderBins; b += blockDim.x)
         if (h[b]) atomicAdd(&bins[b], h[b]);
 }
-// bins[0 .. 2 kOrderBins) counts -> bins[2 kOrderBins .. 4 kOrderBins) running cursors; bins[4 kOrderBins] = heavy pairs
-__global__ void orderScanKernel(unsigned int *bins) {
-    if (threadIdx.x == 0) {
-        unsigned int acc = 0;
-        for (int b = 0; b < 2 * kOrderBins; ++b) {
-            if (b == kOrderBins) bins[4 * kOrderBins] = acc;
-            bins[2 * kOrderBins + b] = acc;
-            acc += bins[b];
-        }
+// bins[0 .. 2 kOrderBins) counts -> bins[2 kOrderBins .. 4 kOrderBins) running cursors; bins[4 kOrderBins] = heavy pairs.
+// One block of kOrderBins threads, two bins per thread.
+__global__ void __launch_bounds__(kOrderBins) orderScanKernel(unsigned int *bins) {
+    static_assert(kOrderBins == 1024, "one block of 1024 threads scans two bins per thread");
+    __shared__ unsigned int warpSums[32];
+    const int t = threadIdx.x;
+    const unsigned int a = bins[2 * t], b = bins[2 * t + 1];
+    unsigned int incl = a + b;
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+        if ((t & 31) >= o) incl += v;
     }
+    if ((t & 31) == 31) warpSums[t >> 5] = incl;
+    __syncthreads();
+    if (t < 32) {
+        const unsigned int w = warpSums[t];
+        unsigned int wi = w;
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned int v = __shfl_up_sync(0xFFFFFFFFu, wi, o);
+            if (t >= o) wi += v;
+        }
+        warpSums[t] = wi - w;
+    }
+    __syncthreads();
+    const unsigned int excl = incl - (a + b) + warpSums[t >> 5];
+    bins[2 * kOrderBins + 2 * t] = excl;
+    bins[2 * kOrderBins + 2 * t + 1] = excl + a;
+    if (2 * t == kOrderBins) bins[4 * kOrderBins] = excl;
 }
 __global__ void orderScatterKernel(const long long nsrc, const uint32_t *__restrict__ work, const int8_t *__restrict__ tier,
                                    unsigned int *__restrict__ bins, int32_t *__restrict__ order) {

@@ -114,7 +114,7 @@ struct smsgpu_ctx {
     cudaStream_t stream2 = nullptr; // the overlapped tier-2 launch of the sources known to be heavy
     cudaEvent_t ev[8]{};
     cudaEvent_t tierEv[2 * 5]{}; // start / end of each tier's search launch; [8], [9]: the overlapped tier-2 launch
-    cudaEvent_t joinEv = nullptr;
+    cudaEvent_t joinEv = nullptr, heavyEv = nullptr;
     int smCount = 148;
     long long n = 0, m = 0;
     std::string err;
@@ -156,7 +156,8 @@ struct smsgpu_ctx {
     // 24 x u64: see RawOut::counters; [8] queue cursor, [9] ovf count A, [10] ovf count B, [11] collisions;
     // [16] queue cursor, [17] ovf count, [18] sources run of the overlapped tier-2 launch
     DevBuf counters;
-    PinBuf hCounters;
+    PinBuf hCounters, hHeavy;
+    bool heavyPending = false; // hHeavy is being written behind heavyEv
     DevBuf ovfA, ovfB, ovfC;
     std::vector<int32_t> hSources; // the local explicit source list as uploaded (smsgpu_set_sources)
 
@@ -453,6 +454,8 @@ int smsgpu_create(smsgpu_ctx **out, int64_t n, int64_t m, const int64_t *rowptr,
         CUB(cudaStreamCreateWithPriority(&ctx->stream2, cudaStreamNonBlocking, prHigh));
     }
     CUB(cudaEventCreateWithFlags(&ctx->joinEv, cudaEventDisableTiming));
+    CUB(cudaEventCreateWithFlags(&ctx->heavyEv, cudaEventDisableTiming));
+    CUB(ctx->hHeavy.ensure(16));
     CUB(ctx->dRowptr.ensure((size_t)(n + 1) * sizeof(int64_t)));
     CUB(ctx->dCol.ensure((size_t)std::max<int64_t>(2 * m, 4) * sizeof(int32_t)));
     CUB(ctx->dEid.ensure((size_t)std::max<int64_t>(2 * m, 4) * sizeof(int32_t)));
@@ -530,7 +533,7 @@ void smsgpu_destroy(smsgpu_ctx *ctx) {
                      &ctx->pLen, &ctx->pSrc, &ctx->pSeq, &ctx->pOff, &ctx->pNode, &ctx->pEid, &ctx->pStay, &ctx->mNode, &ctx->mEid, &ctx->mStay, &ctx->mOff, &ctx->mLen, &ctx->mSrc,
                      &ctx->mSeq, &ctx->mValid};
     for (auto *b : dev) b->release();
-    PinBuf *pin[] = {&ctx->hX, &ctx->hBl, &ctx->hCounters, &ctx->host.off, &ctx->host.node, &ctx->host.eid,
+    PinBuf *pin[] = {&ctx->hX, &ctx->hBl, &ctx->hCounters, &ctx->hHeavy, &ctx->host.off, &ctx->host.node, &ctx->host.eid,
                      &ctx->host.stay, &ctx->host.ncross, &ctx->host.src, &ctx->host.viol, &ctx->hLabOff, &ctx->hLabNode,
                      &ctx->hLabDist, &ctx->hLabHops, &ctx->hSrcArcs, &ctx->hSrcSettled, &ctx->hSrcTier, &ctx->scTmp,
                      &ctx->hGCounts};
@@ -545,6 +548,7 @@ void smsgpu_destroy(smsgpu_ctx *ctx) {
     for (auto &e : ctx->tierEv)
         if (e) cudaEventDestroy(e);
     if (ctx->joinEv) cudaEventDestroy(ctx->joinEv);
+    if (ctx->heavyEv) cudaEventDestroy(ctx->heavyEv);
     if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -623,6 +627,7 @@ int smsgpu_set_sources(smsgpu_ctx *ctx, const int32_t *sources, int64_t nsrc, in
         ctx->haveOrder = false;
         ctx->skipTier0 = 0;
         ctx->heavyPairs = 0;
+        ctx->heavyPending = false;
     }
     return SMSGPU_OK;
 }
@@ -929,6 +934,11 @@ int smsgpu_separate_async(smsgpu_ctx *ctx, const smsgpu_params *params) {
         // with as many CTAs as they have sources for; tier 1 fills the rest of the GPU with everything else.  Run one
         // after the other, tier 2 is a tail of a few thousand long searches on an otherwise idle GPU.
         long long heavy = 0;
+        if (worklist && ctx->heavyPending) {
+            CU(cudaEventSynchronize(ctx->heavyEv));
+            ctx->heavyPairs = (long long)*ctx->hHeavy.as<unsigned int>();
+            ctx->heavyPending = false;
+        }
         if (worklist && ctx->overlapHeavy && firstTier == 1 && ctx->heavyPairs > 0 && kNumTiers > 2 && ctx->tier[2].caps.nbuckets) {
             heavy = std::min<long long>(2 * ctx->heavyPairs, nsrc & ~1ll);
             if (int rc = ensureTierScratch(ctx, 1)) return rc;
@@ -1033,15 +1043,15 @@ int smsgpu_separate_async(smsgpu_ctx *ctx, const smsgpu_params *params) {
             CU(cudaMemsetAsync(bins, 0, (4 * kOrderBins + 1) * sizeof(unsigned int), st));
             const unsigned g = std::min<unsigned>(gridFor(nsrc, 256), (unsigned)ctx->smCount * 8);
             orderHistKernel<<<g, 256, 0, st>>>(nsrc, ctx->srcWork.as<uint32_t>(), ctx->srcTier.as<int8_t>(), bins);
-            orderScanKernel<<<1, 32, 0, st>>>(bins);
+            orderScanKernel<<<1, kOrderBins, 0, st>>>(bins);
             orderScatterKernel<<<g, 256, 0, st>>>(nsrc, ctx->srcWork.as<uint32_t>(), ctx->srcTier.as<int8_t>(), bins,
                                                  ctx->srcOrder.as<int32_t>());
             CU(cudaGetLastError());
             ctx->stats.total_launches += 3;
-            unsigned int *hHeavy = reinterpret_cast<unsigned int *>(hc + 23);
-            CU(cudaMemcpyAsync(hHeavy, bins + 4 * kOrderBins, sizeof(unsigned int), cudaMemcpyDeviceToHost, st));
-            CU(cudaStreamSynchronize(st));
-            ctx->heavyPairs = (long long)*hHeavy;
+            // read when the next round needs it (heavyEv): no host wait here
+            CU(cudaMemcpyAsync(ctx->hHeavy.p, bins + 4 * kOrderBins, sizeof(unsigned int), cudaMemcpyDeviceToHost, st));
+            CU(cudaEventRecord(ctx->heavyEv, st));
+            ctx->heavyPending = true;
             ctx->haveOrder = true;
         }
         ctx->stats.sources_run = (long long)hc[4] + heavyRun;
