@@ -131,6 +131,23 @@ def read_mc(path: str) -> Instance:
     return _finish(path.split("/")[-1], n, e[:, 0], e[:, 1])
 
 
+def write_mc(inst: Instance, path: str, weights=None, seed: int = 1) -> None:
+    """Writes `inst` in the '.mc' format the reference's `sms` binary reads (src/io/io.cpp: header 'n m', then
+    1-based 'u v w' lines; mcFileToGraph adds the edges in file order, so NetworKit's adjacency order and edge ids
+    equal this instance's).  `weights` by edge-list position; default: +-1 couplings from mt19937_64(seed)."""
+    if weights is None:
+        rng = np.random.Generator(np.random.MT19937(seed))
+        weights = np.where(rng.integers(0, 2, size=inst.m) == 1, 1, -1)
+    weights = np.asarray(weights)
+    if weights.shape[0] != inst.m:
+        raise ValueError("one weight per edge")
+    integral = np.all(weights == np.round(weights))
+    with open(path, "w") as f:
+        f.write(f"{inst.n} {inst.m}\n")
+        for u, v, w in zip(inst.eu.tolist(), inst.ev.tolist(), weights.tolist()):
+            f.write(f"{u + 1} {v + 1} {int(w) if integral else repr(float(w))}\n")
+
+
 # ----------------------------------------------------------------------------------------------------
 # LP points x* (indexed by edge id)
 # ----------------------------------------------------------------------------------------------------

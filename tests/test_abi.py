@@ -90,3 +90,20 @@ def test_product_never_imports_oracle():
                 if re.search(r"^\s*(from|import)\s+oracle|#include\s+[\"<].*oracle|liborc|libsmsref", txt, flags=re.M):
                     bad.append(f)
     assert not bad, bad
+
+
+def test_mc_files_round_trip(tmp_path):
+    """'.mc' writer / reader (harness I/O; format of the reference's src/io/io.cpp): the written file
+    reads back to the same numbering -- adjacency order and edge ids are functions of the edge order in the file."""
+    import numpy as np
+    from sms_b200 import instances as I
+    for inst in (I.torus2d(7), I.torus3d(4), I.random_graph(300, 1200, seed=4)):
+        path = tmp_path / (inst.name + ".mc")
+        I.write_mc(inst, str(path), seed=3)
+        lines = path.read_text().splitlines()
+        assert lines[0].split() == [str(inst.n), str(inst.m)] and len(lines) == inst.m + 1
+        assert all(ln.split()[2] in ("1", "-1") for ln in lines[1:])
+        back = I.read_mc(str(path))
+        assert back.n == inst.n and back.m == inst.m
+        for a in ("rowptr", "col", "eid", "eu", "ev"):
+            assert np.array_equal(getattr(back, a), getattr(inst, a)), a
