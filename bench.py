@@ -72,12 +72,19 @@ class ClockSampler:
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", os.environ.get("BENCH_SMI_MS", "250"),
                                           "-i", str(self.idx)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
         except Exception:
             self.proc = None
+
+    def wait_first(self, timeout: float = 30.0):
+        """Blocks until nvidia-smi has delivered its first sample: on a fresh box its start-up (NVML initialisation) takes
+        seconds and, falling into the timed region, cost single steps tens to hundreds of ms."""
+        t0 = time.perf_counter()
+        while self.proc and not self.lines and self.proc.poll() is None and time.perf_counter() - t0 < timeout:
+            time.sleep(0.05)
 
     def _read(self):
         for ln in self.proc.stdout:
@@ -249,6 +256,7 @@ def measure_workload(name, args, torch, dist, rank, world, device, full=True):
     for _ in range(max(args.warmup, 3)):
         step_dev()
     torch.cuda.synchronize()
+    sampler.wait_first()
     dt, _ = time_rounds(ctx, torch, dist, world, args.steps, 0, step_dev, flush)
     clocks = sampler.stop()
     # per-round device stats of the last round (events on the library's own stream)

@@ -486,9 +486,10 @@ int smsgpu_create(smsgpu_ctx **out, int64_t n, int64_t m, const int64_t *rowptr,
             for (int64_t u = 0; u < n; ++u) ri[u] = make_uint2((uint32_t)rowptr[u], (uint32_t)(rowptr[u + 1] - rowptr[u]));
             CUB(ctx->dRowinfo.ensure(ri.size() * sizeof(uint2)));
             CUB(cudaMemcpy(ctx->dRowinfo.p, ri.data(), (size_t)n * sizeof(uint2), cudaMemcpyHostToDevice));
-            // bucket map: 2^u, u in [0, L] over [0, bestInit/2]; L ~ log2 of the ball growth over the radius,
-            // which is about 1.2 x the average degree (measured on the bench shapes); SMSGPU_PAIRS_L overrides, 0 = linear
-            int L = (int)std::lround(1.2 * avgDeg);
+            // bucket map: 2^u, u in [0, L] over [0, bestInit/2]; L ~ log2 of the ball growth over the radius.  Measured on
+            // config 5 (degree 8): L = 6..8 leaves 0.2 % of the sources with a full bucket, L = 10 0.6 %, L = 14 9 %, L <= 4
+            // more again (and slower extraction); the round is 4 % faster at 7 than at 10.  SMSGPU_PAIRS_L overrides, 0 = linear
+            int L = (int)std::lround(0.85 * avgDeg);
             if (const char *el = std::getenv("SMSGPU_PAIRS_L")) L = std::atoi(el);
             L = std::max(0, std::min(L, 20));
             const double half = 0.5 * (1.0 - 1e-6); // bestInit / 2 of the default parameters; larger radii clamp to the last bucket
