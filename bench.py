@@ -71,6 +71,8 @@ class ClockSampler:
         self.lines = []
 
     def start(self):
+        if os.environ.get("BENCH_NO_SMI"):  # experiment only: what the sampling itself costs
+            return
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", os.environ.get("BENCH_SMI_MS", "250"),
                                           "-i", str(self.idx)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
@@ -254,6 +256,7 @@ def measure_workload(name, args, torch, dist, rank, world, device, full=True):
     sampler.start()  # before the warm-up: starting nvidia-smi (NVML init) inside the timed region once cost a step 400 ms
     # warm-up: allocations, tier scratch, and the history the engine keeps between rounds (issue order, tier-0 decision)
     for _ in range(max(args.warmup, 3)):
+        flush()  # also warms the flush itself: its first call loads torch's fill kernel (measured: +7..75 ms on one step)
         step_dev()
     torch.cuda.synchronize()
     sampler.wait_first()
