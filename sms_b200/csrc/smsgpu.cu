@@ -359,7 +359,9 @@ int ensureTierScratch(smsgpu_ctx *ctx, int ti) {
         CU(cudaMemGetInfo(&freeB, &totalB));
         long long nt = (long long)((freeB / 4) / tb);
         const int tilesPerCta = 128 / ctx->tileWidth;
-        nt = std::min<long long>(nt, ti == 2 ? t.ntiles : (long long)ctx->smCount * 2 * tilesPerCta);
+        // dense tier: as many tiles as warps can be resident (LP-like x* with its exact distance ties sends whole rounds
+        // here: no bucket holds a zero-weight component; measured 2 -> 4 CTAs per SM: see profiles/README.md)
+        nt = std::min<long long>(nt, ti == 2 ? t.ntiles : (long long)ctx->smCount * std::max(1, occupancyT<false, false>(0)) * tilesPerCta);
         if (nt < 1) return fail(ctx, SMSGPU_ERR_NOMEM, "dense tier needs %zu bytes per tile, %zu free", tb, freeB);
         t.ctas = (int)std::max<long long>(1, nt / tilesPerCta);
         t.ntiles = (long long)t.ctas * tilesPerCta;
