@@ -47,7 +47,7 @@ REF_SAMPLE = {"random1m": 256, "torus100": 10_000, "torus3d20": 8_000, "random20
 
 
 # dram bytes of the search of one full round, from the committed ncu capture (per launch; see roofline.traffic_note)
-TRAFFIC_NCU = {"random1m": round(165.474537e9 * 1254134233 / 329005693)}  # 165.47 GB for the capture's 329.0 M (reference-equivalent) settled nodes
+TRAFFIC_NCU = {"random1m": round(165.588185e9 * 1254134233 / 329005693)}  # 165.59 GB for the capture's 329.0 M (reference-equivalent) settled nodes
 
 
 def peaks():
