@@ -799,7 +799,10 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
                 storeEntryCS(TABP(slot), e);
             }
             if ((__ballot_sync(FULL, ovf) >> gbase) & 0xFFFFu) {
-                if (tl == 0) atomicAdd(&R.counters[13], 1ull); // a bucket is full
+                if (tl == 0) {
+                    atomicAdd(&R.counters[13], 1ull); // a bucket is full
+                    atomicAdd(&R.counters[15], (unsigned long long)lo); // diagnostics: where in the queue (bucket being settled)
+                }
                 overflow = 1;
                 st = 2;
                 run = false;

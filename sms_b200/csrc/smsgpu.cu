@@ -967,8 +967,8 @@ int smsgpu_separate_async(smsgpu_ctx *ctx, const smsgpu_params *params) {
             CU(cudaMemcpyAsync(hc, dc, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
             CU(cudaStreamSynchronize(st));
             if (std::getenv("SMSGPU_DEBUG_OVF"))
-                std::fprintf(stderr, "[smsgpu] tier %d: %lld sources in, %llu overflowed (table %llu, bucket %llu, history %llu)\n", ti,
-                             nwork, hc[9 + which], hc[12], hc[13], hc[14]);
+                std::fprintf(stderr, "[smsgpu] tier %d: %lld sources in, %llu overflowed (table %llu, bucket %llu at mean bucket %.0f, history %llu)\n", ti,
+                             nwork, hc[9 + which], hc[12], hc[13], hc[13] ? (double)hc[15] / (double)hc[13] : 0.0, hc[14]);
             done[ti] += (long long)hc[4] - prevRun;
             prevRun = (long long)hc[4];
             nwork = (long long)hc[9 + which];
