@@ -244,6 +244,13 @@ cudaError_t launchSearchT(smsgpu_ctx *c, const TierCfg &t, const GraphDev &G, co
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t.smemBytes);
         if (e != cudaSuccess) return e;
     }
+    if (FAST) {
+        // This kernel may run beside the pairs kernel (heavy sources, second stream), whose CTAs need 36 KB of shared memory
+        // each: an SM configured for a large L1 by a resident CTA of this kernel takes none of them until it drains
+        // (measured: one such CTA on every SM cost the pairs kernel 32 ms).  Ask for the shared-memory-heavy split.
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
+        if (e != cudaSuccess) return e;
+    }
     kern<<<ctas, 128, t.smemBytes, st>>>(G, P, R, t.caps, t.scratch.as<unsigned char>());
     return cudaGetLastError();
 }
