@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define SMSGPU_ABI_VERSION 2
+#define SMSGPU_ABI_VERSION 3
 
 typedef struct smsgpu_ctx smsgpu_ctx;
 
@@ -51,9 +51,29 @@ typedef struct smsgpu_params {
     int32_t export_labels;     /* 1: keep every stored Dijkstra label (node, dist, hops) per source -- parity tests only */
     int32_t export_src_stats;  /* 1: per-source (arcs scanned, settled) counters */
     int32_t start_tier;        /* 0 = auto (shared-memory tier first), 1 / 2 = HBM hashed tiers (medium / large), 3 = dense tier */
-    int32_t tile_width;        /* 0 = auto; lanes that cooperate on one source: 32 (one warp) is the only width built */
-    int32_t reserved[9];
+    int32_t mode;              /* SMSGPU_MODE_INDEPENDENT (default) or SMSGPU_MODE_VERBATIM, see below */
+    int32_t debug_flags;       /* 0; debugging aids of the search kernels (tests only) */
+    double min_efficacy;       /* 0.0 = keep everything.  Cuts with violation / sqrt(len) <= min_efficacy are dropped on the
+                                  device before dedup: the SCIPisCutEfficacious test of conshdlr_oscw.cpp:221,232 (efficacy =
+                                  (activity - rhs) / ||a||_2 = (1 - length) / sqrt(len); separating/minefficacyroot = 1e-6,
+                                  src/solver/basic_ocw.cpp:244) as a PRE-filter with a relative slack of 1e-9; the handler
+                                  still asks SCIP for the survivors */
+    int32_t reserved[6];
 } smsgpu_params;
+
+/* The reference's sweep over the sources is ORDER DEPENDENT: a source that finds nothing blacklists its vertex and
+ * everything reachable over integral edges (blacklistIntReachable, ocw_seperator.cpp:113-114,363-382), and building a
+ * walk blacklists the stem it cuts off (:162-169); later sources skip blacklisted neighbours (:98-99) and blacklisted
+ * sources (:334-335).
+ *   SMSGPU_MODE_INDEPENDENT  every source sees the round's INITIAL blacklist (what sharding sources over GPUs means);
+ *                            the cut set is a superset-like variant of the reference's (DESIGN.md section 2 has the
+ *                            measured differences).
+ *   SMSGPU_MODE_VERBATIM     the cut list of the reference's own sequential sweep, reproduced exactly: the blacklist is
+ *                            kept as a per-vertex TIME STAMP (index of the first source that blacklists the vertex), every
+ *                            source reads "blacklisted before me", and the round is iterated to the fixed point of the
+ *                            stamps (smsgpu_stats.verbatim_iterations sweeps).  Single GPU. */
+#define SMSGPU_MODE_INDEPENDENT 0
+#define SMSGPU_MODE_VERBATIM 1
 
 /* Host-visible result of one round; all pointers are owned by the context and stay valid until the next
  * smsgpu_separate / smsgpu_destroy.  Cut k is the closed walk
@@ -108,6 +128,10 @@ void smsgpu_default_params(smsgpu_params *p);
  * x_by_eid[m] is the LP point indexed by edge id (clamped to [0,1] on the device); blacklist[n] is 1 for the
  * root and locally fixed vertices.  Host buffers; copied through pinned staging, asynchronously. */
 int smsgpu_set_round_input(smsgpu_ctx *ctx, const double *x_by_eid, const uint8_t *blacklist);
+/* The context's own pinned staging buffers (x[m], blacklist[n]).  A handler that gathers x* edge by edge
+ * (SCIPgetSolVal per edge, conshdlr_oscw.cpp:175-180) writes straight into them and passes the same pointers to
+ * smsgpu_set_round_input, which then skips the pageable -> pinned copy.  Valid until smsgpu_destroy. */
+int smsgpu_input_buffers(smsgpu_ctx *ctx, double **x_by_eid, uint8_t **blacklist);
 /* Same, with buffers already resident on ctx's device (bench "value" leg; a GPU LP solver would use this). */
 int smsgpu_set_round_input_device(smsgpu_ctx *ctx, const double *d_x_by_eid, const uint8_t *d_blacklist);
 

@@ -46,6 +46,7 @@ class Sweep:
     seconds: float
     n_walks: int
     total_len: int
+    timing: tuple = ()  # (set-up s, sum of per-source s, sum of squares, max per-source s, sources timed)
 
     @property
     def ncuts(self) -> int:
@@ -74,6 +75,7 @@ class _Lib:
         f("sizes").argtypes = [C.c_void_p, _i64p]
         f("seconds").argtypes = [C.c_void_p]
         f("seconds").restype = C.c_double
+        f("timing").argtypes = [C.c_void_p, _f64p]
         f("copy_cuts").argtypes = [C.c_void_p, _i64p, _i32p, _i32p, _u8p]
         f("copy_labels").argtypes = [C.c_void_p, _i64p, _i32p, _f64p, _i32p]
         f("copy_stats").argtypes = [C.c_void_p, _i64p]
@@ -121,8 +123,11 @@ class _Lib:
         if nstat:
             self._f("copy_stats")(h, stats)
         secs = float(self._f("seconds")(h))
+        tm = np.zeros(5, np.float64)
+        self._f("timing")(h, tm)
         self._f("free")(h)
-        return Sweep(cut_off, cut_src, node, stay, lo, ln, ld, lh, stats.reshape(-1, 6), secs, int(sz[4]), int(sz[5]))
+        return Sweep(cut_off, cut_src, node, stay, lo, ln, ld, lh, stats.reshape(-1, 6), secs, int(sz[4]), int(sz[5]),
+                     tuple(float(v) for v in tm))
 
     def sweep(self, inst, x, blacklist=None, sources=None, mode="I", want_labels=False, want_cuts=True,
               canonical=False) -> Sweep:

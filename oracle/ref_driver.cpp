@@ -109,6 +109,7 @@ void *ref_sweep(int64_t n, int64_t m, const int32_t *eu, const int32_t *ev, cons
 }
 void ref_sizes(void *h, int64_t *out) { sweep::sizes(static_cast<sweep::Result *>(h), out); }
 double ref_seconds(void *h) { return static_cast<sweep::Result *>(h)->seconds; }
+void ref_timing(void *h, double *out) { sweep::timing(static_cast<sweep::Result *>(h), out); }
 void ref_copy_cuts(void *h, int64_t *cutOff, int32_t *cutSrc, int32_t *node, uint8_t *stay) {
     sweep::copyCuts(static_cast<sweep::Result *>(h), cutOff, cutSrc, node, stay);
 }

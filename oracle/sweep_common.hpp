@@ -31,6 +31,10 @@ struct Result {
     // per-source stats: arcs, settled, labelled, heapMax, intermediates, maxWalkLen (zeros for the reference engine)
     std::vector<int64_t> srcStats;
     double seconds = 0;
+    // the same time split up (bench.py's CPU baseline): once-per-round set-up (m x updateEdgeWeight + blacklist, the
+    // part of conshdlr_oscw.cpp:174-185 that does not scale with the number of sources) and the sources themselves
+    double secondsSetup = 0, secondsSources = 0, sumSqSource = 0, maxSource = 0;
+    int64_t sourcesTimed = 0;
     int64_t nWalks = 0, totalLen = 0; // counted even when cuts are not stored (timing runs)
 };
 
@@ -41,12 +45,19 @@ Result *run(Engine &eng, int64_t n, const double *x, int64_t m, const uint8_t *b
     auto t0 = std::chrono::steady_clock::now();
     for (int64_t e = 0; e < m; ++e) eng.updateEdgeWeight(e, x[e]);
     eng.resetBlacklist(bl0);
+    r->secondsSetup = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     for (int64_t k = 0; k < nsrc; ++k) {
         const int64_t s = sources[k];
         bool skip = (s < n) ? bl0[s] != 0 : false; // handler-level skip (conshdlr_oscw.cpp:191-193)
         if (!skip) {
             if (mode == 0) eng.resetBlacklist(bl0);
+            const auto ts = std::chrono::steady_clock::now();
             auto walks = eng.getViolatedOcws(s);
+            const double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - ts).count();
+            r->secondsSources += dt;
+            r->sumSqSource += dt * dt;
+            r->maxSource = dt > r->maxSource ? dt : r->maxSource;
+            r->sourcesTimed += 1;
             if (wantCuts) {
                 for (auto &w : walks) {
                     for (uint64_t i = 0; i < w.size(); ++i) {
@@ -79,6 +90,13 @@ inline void sizes(const Result *r, int64_t *out) {
     out[3] = static_cast<int64_t>(r->srcStats.size() / 6);
     out[4] = r->nWalks;
     out[5] = r->totalLen;
+}
+inline void timing(const Result *r, double *out) {
+    out[0] = r->secondsSetup;
+    out[1] = r->secondsSources;
+    out[2] = r->sumSqSource;
+    out[3] = r->maxSource;
+    out[4] = static_cast<double>(r->sourcesTimed);
 }
 inline void copyCuts(const Result *r, int64_t *cutOff, int32_t *cutSrc, int32_t *node, uint8_t *stay) {
     std::memcpy(cutOff, r->cutOff.data(), r->cutOff.size() * sizeof(int64_t));

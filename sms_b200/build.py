@@ -5,6 +5,8 @@ travels to the GPU box with the gpurun snapshot.
 """
 from __future__ import annotations
 
+import glob
+import hashlib
 import os
 import shutil
 import subprocess
@@ -14,8 +16,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(CSRC, "libsmsgpu.so")
 LIB_DEBUG = os.path.join(CSRC, "libsmsgpu_dbg.so")  # -DSMSGPU_DEBUG_CHECKS: device asserts (SMSGPU_LIB selects it)
 SOURCES = ["smsgpu.cu"]
-HEADERS = ["ocw_types.cuh", "ocw_search.cuh", "ocw_search_fast.cuh", "ocw_search_batch.cuh", "ocw_walks.cuh", "ocw_kernels.cuh", "dedup_kernels.cuh",
-           "small_cycles.cuh", os.path.join("..", "..", "include", "smsgpu.h")]
+STAMP = LIB + ".srchash"  # sha256 of every source the library was built from (bench.py prints it)
 
 NVCC_FLAGS = ["-std=c++17", "-O3", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-shared",
               "-Xcompiler", "-fPIC", "-cudart", "static"]
@@ -28,12 +29,36 @@ def _nvcc() -> str:
     raise RuntimeError("nvcc not found")
 
 
+def dependencies() -> list[str]:
+    """Every file the library is compiled from: all of csrc/*.cu, csrc/*.cuh and the C-ABI header."""
+    deps = sorted(glob.glob(os.path.join(CSRC, "*.cu")) + glob.glob(os.path.join(CSRC, "*.cuh")))
+    deps.append(os.path.normpath(os.path.join(HERE, "..", "include", "smsgpu.h")))
+    return deps
+
+
+def source_hash() -> str:
+    h = hashlib.sha256()
+    for d in dependencies():
+        h.update(os.path.basename(d).encode())
+        with open(d, "rb") as f:
+            h.update(f.read())
+    h.update(" ".join(NVCC_FLAGS).encode())
+    return h.hexdigest()[:16]
+
+
+def built_hash() -> str | None:
+    """Source hash recorded when libsmsgpu.so was built (None: no library / no stamp)."""
+    try:
+        with open(STAMP) as f:
+            return f.read().strip()
+    except OSError:
+        return None
+
+
 def needs_build() -> bool:
-    if not os.path.exists(LIB):
-        return True
-    t = os.path.getmtime(LIB)
-    deps = [os.path.join(CSRC, f) for f in SOURCES + HEADERS]
-    return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
+    """The library is stale when its recorded source hash differs from the sources' (content, not mtime: the
+    snapshot that travels to the GPU box does not keep mtimes in order)."""
+    return not os.path.exists(LIB) or built_hash() != source_hash()
 
 
 def build(force: bool = False, verbose: bool = False, debug: bool = False) -> str:
@@ -55,6 +80,8 @@ def build(force: bool = False, verbose: bool = False, debug: bool = False) -> st
         raise RuntimeError("nvcc failed:\n" + r.stdout + r.stderr)
     if verbose:
         print(r.stderr)
+    with open(STAMP, "w") as f:
+        f.write(source_hash() + "\n")
     return LIB
 
 

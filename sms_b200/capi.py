@@ -17,7 +17,7 @@ LIB_PATH = os.path.join(_HERE, "csrc", "libsmsgpu.so")
 # every symbol include/smsgpu.h declares (tests/test_abi.py checks the header against this list and the .so)
 SYMBOLS = [
     "smsgpu_create", "smsgpu_destroy", "smsgpu_last_error", "smsgpu_abi_version", "smsgpu_default_params",
-    "smsgpu_set_round_input", "smsgpu_set_round_input_device", "smsgpu_set_sources", "smsgpu_separate",
+    "smsgpu_set_round_input", "smsgpu_input_buffers", "smsgpu_set_round_input_device", "smsgpu_set_sources", "smsgpu_separate",
     "smsgpu_separate_async", "smsgpu_fetch_cuts", "smsgpu_get_cuts", "smsgpu_get_stats", "smsgpu_get_labels",
     "smsgpu_get_src_stats", "smsgpu_small_cycles_set", "smsgpu_small_cycles_scan", "smsgpu_get_small_cycle_cuts",
     "smsgpu_nccl_unique_id", "smsgpu_comm_init", "smsgpu_comm_destroy",
@@ -38,8 +38,10 @@ class Params(C.Structure):
         ("export_labels", C.c_int32),
         ("export_src_stats", C.c_int32),
         ("start_tier", C.c_int32),
-        ("tile_width", C.c_int32),
-        ("reserved", C.c_int32 * 9),
+        ("mode", C.c_int32),
+        ("debug_flags", C.c_int32),
+        ("min_efficacy", C.c_double),
+        ("reserved", C.c_int32 * 6),
     ]
 
 
@@ -124,6 +126,7 @@ def load_library(path: str | None = None) -> C.CDLL:
     lib.smsgpu_default_params.restype = None
     lib.smsgpu_set_round_input.argtypes = [vp, vp, vp]
     lib.smsgpu_set_round_input_device.argtypes = [vp, vp, vp]
+    lib.smsgpu_input_buffers.argtypes = [vp, C.POINTER(vp), C.POINTER(vp)]
     lib.smsgpu_set_sources.argtypes = [vp, vp, i64, i32, i32]
     lib.smsgpu_separate.argtypes = [vp, C.POINTER(Params)]
     lib.smsgpu_separate_async.argtypes = [vp, C.POINTER(Params)]
@@ -199,6 +202,15 @@ class Context:
             raise ValueError("x_by_eid must have m entries and blacklist n")
         self._check(self.lib.smsgpu_set_round_input(self.h, x.ctypes.data, bl.ctypes.data))
 
+    def input_buffers(self):
+        """(x[m] float64, blacklist[n] uint8) numpy views of the context's pinned staging buffers: fill them in place and
+        pass them to set_round_input (no pageable -> pinned copy)."""
+        px, pb = C.c_void_p(), C.c_void_p()
+        self._check(self.lib.smsgpu_input_buffers(self.h, C.byref(px), C.byref(pb)))
+        x = np.ctypeslib.as_array(C.cast(px, C.POINTER(C.c_double)), shape=(max(self.m, 1),))[:self.m]
+        bl = np.ctypeslib.as_array(C.cast(pb, C.POINTER(C.c_uint8)), shape=(self.n,))
+        return x, bl
+
     def set_round_input_device(self, x_ptr: int, bl_ptr: int):
         self._check(self.lib.smsgpu_set_round_input_device(self.h, C.c_void_p(x_ptr), C.c_void_p(bl_ptr)))
 
@@ -218,9 +230,6 @@ class Context:
         p = Params()
         self.lib.smsgpu_default_params(C.byref(p))
         for k, v in kw.items():
-            if k == "debug_flags":  # reserved[0]: debugging aids of the search kernel (ocw_types.cuh SearchParams::debugFlags)
-                p.reserved[0] = int(v)
-                continue
             if not hasattr(p, k):
                 raise TypeError(f"unknown parameter {k}")
             setattr(p, k, v)

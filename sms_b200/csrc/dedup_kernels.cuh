@@ -46,8 +46,9 @@ __device__ __forceinline__ unsigned long long mix64(unsigned long long h, unsign
 
 // One thread per cut: canonical rotation / direction, canonical copy, hash, #cross, violation.
 // xByEid is the round's raw LP point; it is clamped here exactly as K1 clamps it.
+// Cuts below the efficacy threshold are dropped here (keep = 0), before dedup and ordering.
 __global__ void __launch_bounds__(128) canonKernel(const CutView V, const DedupWork D, const double *__restrict__ xByEid,
-                                                   const int canonicalise, const int srcMul, const int srcAdd) {
+                                                   const int canonicalise, const int srcMul, const int srcAdd, const double minEfficacy) {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= V.n) return;
     if (!V.valid[i]) {
@@ -113,7 +114,9 @@ __global__ void __launch_bounds__(128) canonKernel(const CutView V, const DedupW
     // local -> global source index under the pair-cyclic deal of smsgpu_set_sources (identity for srcMul 1, srcAdd 0)
     const unsigned long long gsrc = ((((unsigned long long)V.src[i] >> 1) * srcMul + srcAdd) << 1) | ((unsigned)V.src[i] & 1u);
     D.rank[i] = (gsrc << 20) | (unsigned)V.seq[i];
-    D.keep[i] = 1;
+    // efficacy pre-filter (smsgpu_params::min_efficacy): SCIP's efficacy of the row is (activity - rhs) / ||a||_2 =
+    // (1 - length) / sqrt(len) (conshdlr_oscw.cpp:221,232 -> SCIPisCutEfficacious); relative slack 1e-9, SCIP decides the rest
+    D.keep[i] = !(minEfficacy > 0.0) || (1.0 - length) > minEfficacy * (1.0 - 1e-9) * sqrt((double)L);
 }
 
 __global__ void __launch_bounds__(256) dedupInsertKernel(const long long n, const DedupWork D) {

@@ -3,7 +3,6 @@
 //   ocwSearchKernel  (K2-K4)   persistent tiles pulling sources from an atomic cursor
 //   initTablesKernel           one-time clearing of the HBM label tables of tiers 1 / 2
 #pragma once
-#include "ocw_search_batch.cuh"
 #include "ocw_walks.cuh"
 #include "ocw_search_pairs.cuh"
 
@@ -203,11 +202,7 @@ __global__ void __launch_bounds__(128, FAST ? SMSGPU_FAST_MIN_CTAS : 1) ocwSearc
 
         SrcState S;
         if (FAST)
-#ifdef SMSGPU_BATCH // same-bucket batching: measured slower on the full 1M-source round (profiles/README.md)
-            searchSourceBatch<TW>(T, G, M, S, src, P.bestInit, P.stampBase + (uint32_t)wi + 1u);
-#else
             searchSourceFast<TW>(T, G, M, S, src, P.bestInit, P.stampBase + (uint32_t)wi + 1u);
-#endif
         else
             searchSource<TW>(T, G, M, S, src, P.bestInit);
         if (!S.overflow && S.histN > 0) {

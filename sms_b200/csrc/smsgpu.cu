@@ -186,7 +186,7 @@ struct smsgpu_ctx {
     // multi-GPU
     void *ncclComm = nullptr;
     int commRank = 0, commSize = 1;
-    DevBuf gCounts, pLen, pSrc, pSeq, pOff, pNode, pEid, pStay;
+    DevBuf gCounts, pBlock, mBlocks;
     PinBuf hGCounts;
     DevBuf mNode, mEid, mStay, mOff, mLen, mSrc, mSeq, mValid;
 };
@@ -410,7 +410,7 @@ int smsgpu_create(smsgpu_ctx **out, int64_t n, int64_t m, const int64_t *rowptr,
         std::vector<int32_t> seen(n, -1);
         std::vector<uint8_t> eidCount(m, 0);
         for (int64_t u = 0; u < n; ++u) {
-            if (rowptr[u + 1] < rowptr[u]) return fail(ctx, SMSGPU_ERR_ARG, "rowptr not monotone at %lld", (long long)u);
+            if (rowptr[u + 1] < rowptr[u] || rowptr[u + 1] > 2 * m) return fail(ctx, SMSGPU_ERR_ARG, "rowptr not monotone or beyond 2m at %lld", (long long)u);
             for (int64_t a = rowptr[u]; a < rowptr[u + 1]; ++a) {
                 const int32_t v = col[a];
                 if (v < 0 || v >= n) return fail(ctx, SMSGPU_ERR_ARG, "neighbour out of range at arc %lld", (long long)a);
@@ -540,7 +540,7 @@ void smsgpu_destroy(smsgpu_ctx *ctx) {
                      &ctx->fin.src, &ctx->fin.seq, &ctx->fin.viol, &ctx->scFin.off, &ctx->scFin.node, &ctx->scFin.eid,
                      &ctx->scFin.stay, &ctx->scFin.ncross, &ctx->scFin.src, &ctx->scFin.viol, &ctx->scNodes[0], &ctx->scNodes[1], &ctx->scEids[0],
                      &ctx->scEids[1], &ctx->scFlag[0], &ctx->scFlag[1], &ctx->scStay[0], &ctx->scStay[1], &ctx->gCounts,
-                     &ctx->pLen, &ctx->pSrc, &ctx->pSeq, &ctx->pOff, &ctx->pNode, &ctx->pEid, &ctx->pStay, &ctx->mNode, &ctx->mEid, &ctx->mStay, &ctx->mOff, &ctx->mLen, &ctx->mSrc,
+                     &ctx->pBlock, &ctx->mBlocks, &ctx->mNode, &ctx->mEid, &ctx->mStay, &ctx->mOff, &ctx->mLen, &ctx->mSrc,
                      &ctx->mSeq, &ctx->mValid};
     for (auto *b : dev) b->release();
     PinBuf *pin[] = {&ctx->hX, &ctx->hBl, &ctx->hCounters, &ctx->hHeavy, &ctx->host.off, &ctx->host.node, &ctx->host.eid,
@@ -570,8 +570,8 @@ int smsgpu_set_round_input(smsgpu_ctx *ctx, const double *x, const uint8_t *bl) 
     if (!x || !bl) return fail(ctx, SMSGPU_ERR_ARG, "x_by_eid or blacklist is null");
     CU(cudaSetDevice(ctx->device));
     // pageable -> pinned staging -> device, all on the context's stream
-    std::memcpy(ctx->hX.p, x, (size_t)ctx->m * sizeof(double));
-    std::memcpy(ctx->hBl.p, bl, (size_t)ctx->n);
+    if (x != ctx->hX.p) std::memcpy(ctx->hX.p, x, (size_t)ctx->m * sizeof(double)); // smsgpu_input_buffers: already there
+    if (bl != ctx->hBl.p) std::memcpy(ctx->hBl.p, bl, (size_t)ctx->n);
     CU(cudaEventRecord(ctx->ev[6], ctx->stream));
     if (ctx->m) CU(cudaMemcpyAsync(ctx->dX.p, ctx->hX.p, (size_t)ctx->m * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
     CU(cudaMemcpyAsync(ctx->dBl.p, ctx->hBl.p, (size_t)ctx->n, cudaMemcpyHostToDevice, ctx->stream));
@@ -580,6 +580,13 @@ int smsgpu_set_round_input(smsgpu_ctx *ctx, const double *x, const uint8_t *bl) 
     ctx->blPtr = ctx->dBl.as<uint8_t>();
     ctx->haveInput = true;
     ctx->arcsDirty = true;
+    return SMSGPU_OK;
+}
+
+int smsgpu_input_buffers(smsgpu_ctx *ctx, double **x, uint8_t **bl) {
+    if (!ctx || !x || !bl) return SMSGPU_ERR_ARG;
+    *x = ctx->hX.as<double>();
+    *bl = ctx->hBl.as<uint8_t>();
     return SMSGPU_OK;
 }
 
@@ -691,7 +698,7 @@ int ensureRawArena(smsgpu_ctx *ctx, long long cutCap, long long nodeCap) {
 
 // K5 on an arbitrary cut view; result in ctx->fin.  srcMul/srcAdd map the view's source index to the global one.
 int runDedup(smsgpu_ctx *ctx, const CutView &V, long long totalNodes, bool canonicalise, bool dedup, int srcMul,
-             int srcAdd, long long nsrcGlobal) {
+             int srcAdd, long long nsrcGlobal, double minEfficacy = 0.0) {
     const long long R = V.n;
     cudaStream_t st = ctx->stream;
     CutListDev &F = ctx->fin;
@@ -721,7 +728,7 @@ int runDedup(smsgpu_ctx *ctx, const CutView &V, long long totalNodes, bool canon
     D.ncross = ctx->wNcross.as<int32_t>();
     D.viol = ctx->wViol.as<double>();
     D.collisions = ctx->counters.as<unsigned long long>() + 11;
-    canonKernel<<<gridFor(R, 128), 128, 0, st>>>(V, D, ctx->xPtr, canonicalise ? 1 : 0, srcMul, srcAdd);
+    canonKernel<<<gridFor(R, 128), 128, 0, st>>>(V, D, ctx->xPtr, canonicalise ? 1 : 0, srcMul, srcAdd, minEfficacy);
     ctx->stats.total_launches += 1;
     if (dedup) {
         const uint64_t tabCap = 1ull << log2ceil((uint64_t)2 * R + 16);
@@ -785,7 +792,8 @@ int runDedup(smsgpu_ctx *ctx, const CutView &V, long long totalNodes, bool canon
     return 0;
 }
 
-int mergeAcrossRanks(smsgpu_ctx *ctx, bool dedup); // multi-GPU part below
+int mergeAcrossRanks(smsgpu_ctx *ctx, bool dedup, int localRc); // multi-GPU part below
+int separateLocal(smsgpu_ctx *ctx, const smsgpu_params &P);
 
 } // namespace
 
@@ -800,25 +808,38 @@ int smsgpu_separate_async(smsgpu_ctx *ctx, const smsgpu_params *params) {
     else
         smsgpu_default_params(&P);
     if (P.max_intermediates < 0 || P.max_intermediates > 16) return fail(ctx, SMSGPU_ERR_ARG, "max_intermediates must be 0..16");
-    if (P.tile_width != 0 && P.tile_width != 32) return fail(ctx, SMSGPU_ERR_ARG, "tile_width must be 0 or 32");
+    if (P.mode != SMSGPU_MODE_INDEPENDENT && P.mode != SMSGPU_MODE_VERBATIM) return fail(ctx, SMSGPU_ERR_ARG, "mode must be 0 (independent) or 1 (verbatim)");
+    if (!(P.min_efficacy >= 0.0)) return fail(ctx, SMSGPU_ERR_ARG, "min_efficacy must be >= 0");
+    // the bucket maps assume radii up to bestInit / 2 <= 0.5; a cycle of length >= kInfDist is never labelled anyway
+    if (!(P.best_dist_init > 0.0) || !(P.best_dist_init <= 1.0 + 1e-3))
+        return fail(ctx, SMSGPU_ERR_ARG, "best_dist_init must lie in (0, 1.001]");
     if (P.start_tier < 0 || P.start_tier >= kNumTiers) return fail(ctx, SMSGPU_ERR_ARG, "start_tier must be 0..3");
     CU(cudaSetDevice(ctx->device));
-    cudaStream_t st = ctx->stream;
-    if (P.tile_width != 0 && P.tile_width != ctx->tileWidth) {
-        CU(cudaStreamSynchronize(st));
-        for (auto &t : ctx->tier) {
-            t.scratch.release();
-            t.ready = false;
-        }
-        ctx->tileWidth = P.tile_width;
-        configureTiers(ctx);
-    }
     ctx->lastParams = P;
     ctx->fetched = false;
     ctx->haveLabels = ctx->haveSrcStats = false;
-    const long long keepH2dStats = 0;
-    (void)keepH2dStats;
     std::memset(&ctx->stats, 0, sizeof ctx->stats);
+    // A rank whose local round fails still joins the exchange (with its error flag): its peers must not wait forever.
+    const int rcLocal = separateLocal(ctx, P);
+    if (ctx->ncclComm && ctx->commSize > 1) {
+        const int rcMerge = mergeAcrossRanks(ctx, P.dedup != 0, rcLocal);
+        if (rcLocal) return rcLocal;
+        if (rcMerge) return rcMerge;
+    } else if (rcLocal) {
+        return rcLocal;
+    }
+    ctx->stats.unique_cuts = ctx->fin.ncuts;
+    CU(cudaEventRecord(ctx->ev[3], ctx->stream));
+    return SMSGPU_OK;
+}
+
+} // extern "C"
+
+namespace {
+
+// the local part of a round: K1 -> K2-K4 (tiers) -> K5 over this context's share of the sources; result in ctx->fin
+int separateLocal(smsgpu_ctx *ctx, const smsgpu_params &P) {
+    cudaStream_t st = ctx->stream;
     const long long nsrc = ctx->nsrcLocal;
     unsigned long long *dc = ctx->counters.as<unsigned long long>();
     unsigned long long *hc = ctx->hCounters.as<unsigned long long>();
@@ -896,7 +917,7 @@ int smsgpu_separate_async(smsgpu_ctx *ctx, const smsgpu_params *params) {
         SP.bestInit = P.best_dist_init;
         SP.maxInter = P.max_intermediates;
         SP.exportLabels = P.export_labels;
-        SP.debugFlags = P.reserved[0];
+        SP.debugFlags = P.debug_flags;
         SP.queueCounter = dc + 8;
         SP.runSlot = 4;
         long long nwork = nsrc;
@@ -1092,13 +1113,12 @@ int smsgpu_separate_async(smsgpu_ctx *ctx, const smsgpu_params *params) {
     CutView V{ctx->rNode.as<int32_t>(), ctx->rEid.as<int32_t>(), ctx->rStay.as<uint8_t>(), ctx->rCutOff.as<int32_t>(),
               ctx->rCutLen.as<int32_t>(), ctx->rCutSrc.as<int32_t>(), ctx->rCutSeq.as<int32_t>(), ctx->rValid.as<uint8_t>(),
               rawCuts};
-    if (int rc = runDedup(ctx, V, rawNodes, P.dedup != 0, P.dedup != 0, ctx->nranks, ctx->rank, ctx->nsrcGlobal)) return rc;
-    if (ctx->ncclComm && ctx->commSize > 1)
-        if (int rc = mergeAcrossRanks(ctx, P.dedup != 0)) return rc;
-    ctx->stats.unique_cuts = ctx->fin.ncuts;
-    CU(cudaEventRecord(ctx->ev[3], st));
-    return SMSGPU_OK;
+    return runDedup(ctx, V, rawNodes, P.dedup != 0, P.dedup != 0, ctx->nranks, ctx->rank, ctx->nsrcGlobal, P.min_efficacy);
 }
+
+} // namespace
+
+extern "C" {
 
 int smsgpu_fetch_cuts(smsgpu_ctx *ctx) {
     if (!ctx) return SMSGPU_ERR_ARG;
@@ -1392,28 +1412,28 @@ struct NcclApi {
     ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
     ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
-    ncclResult_t (*GroupStart)() = nullptr;
-    ncclResult_t (*GroupEnd)() = nullptr;
     const char *(*GetErrorString)(ncclResult_t) = nullptr;
     bool ok = false;
 };
-NcclApi &nccl() {
-    static NcclApi api;
-    if (api.handle) return api;
+NcclApi loadNccl() {
+    NcclApi api;
+    void *h = nullptr;
     for (const char *name : {"libnccl.so.2", "libnccl.so"}) {
-        api.handle = dlopen(name, RTLD_NOW | RTLD_GLOBAL);
-        if (api.handle) break;
+        h = dlopen(name, RTLD_NOW | RTLD_GLOBAL);
+        if (h) break;
     }
-    if (!api.handle) return api;
-    api.GetUniqueId = (decltype(api.GetUniqueId))dlsym(api.handle, "ncclGetUniqueId");
-    api.CommInitRank = (decltype(api.CommInitRank))dlsym(api.handle, "ncclCommInitRank");
-    api.CommDestroy = (decltype(api.CommDestroy))dlsym(api.handle, "ncclCommDestroy");
-    api.AllGather = (decltype(api.AllGather))dlsym(api.handle, "ncclAllGather");
-    api.GroupStart = (decltype(api.GroupStart))dlsym(api.handle, "ncclGroupStart");
-    api.GroupEnd = (decltype(api.GroupEnd))dlsym(api.handle, "ncclGroupEnd");
-    api.GetErrorString = (decltype(api.GetErrorString))dlsym(api.handle, "ncclGetErrorString");
-    api.ok = api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.AllGather && api.GroupStart && api.GroupEnd &&
-             api.GetErrorString;
+    if (!h) return api;
+    api.GetUniqueId = (decltype(api.GetUniqueId))dlsym(h, "ncclGetUniqueId");
+    api.CommInitRank = (decltype(api.CommInitRank))dlsym(h, "ncclCommInitRank");
+    api.CommDestroy = (decltype(api.CommDestroy))dlsym(h, "ncclCommDestroy");
+    api.AllGather = (decltype(api.AllGather))dlsym(h, "ncclAllGather");
+    api.GetErrorString = (decltype(api.GetErrorString))dlsym(h, "ncclGetErrorString");
+    api.ok = api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.AllGather && api.GetErrorString;
+    api.handle = h; // published last, with every symbol resolved
+    return api;
+}
+NcclApi &nccl() {
+    static NcclApi api = loadNccl(); // function-local static: initialised once, thread-safe (one thread per GPU may race here)
     return api;
 }
 
@@ -1423,13 +1443,38 @@ NcclApi &nccl() {
         if (r_ != ncclSuccess) return fail(ctx, SMSGPU_ERR_NCCL, "%s: %s", #call, nccl().GetErrorString(r_));    \
     } while (0)
 
-// local final list -> padded send arrays
+// The exchange is TWO collectives per round: an all-gather of a 4-word header per rank
+// {cuts, nodes, error flag, -} and ONE all-gather of a packed byte block per rank
+//   [len | src | seq | off : int32 x maxU each][node | eid : int32 x maxN each][stay : uint8 x maxN, padded to 16]
+// with maxU / maxN the largest counts of the header.  A rank whose local round failed still joins the header
+// exchange with its error flag set, so that every rank returns an error together instead of waiting for it forever.
+struct PackLayout {
+    long long maxU, maxN, oLen, oSrc, oSeq, oOff, oNode, oEid, oStay, bytes;
+};
+__host__ __device__ inline PackLayout packLayout(long long maxU, long long maxN) {
+    PackLayout L;
+    L.maxU = maxU;
+    L.maxN = maxN;
+    L.oLen = 0;
+    L.oSrc = 4 * maxU;
+    L.oSeq = 8 * maxU;
+    L.oOff = 12 * maxU;
+    L.oNode = 16 * maxU;
+    L.oEid = L.oNode + 4 * maxN;
+    L.oStay = L.oEid + 4 * maxN;
+    L.bytes = (L.oStay + maxN + 15) & ~15ll;
+    return L;
+}
+// local final list -> this rank's block
 __global__ void packCutsKernel(const long long U, const long long N, const long long *off, const int32_t *src,
                                const int32_t *seq, const int32_t *node, const int32_t *eid, const uint8_t *stay,
-                               int32_t *pLen, int32_t *pSrc, int32_t *pSeq, int32_t *pOff, int32_t *pNode, int32_t *pEid,
-                               uint8_t *pStay) {
+                               const PackLayout L, unsigned char *blk) {
     const long long stride = (long long)gridDim.x * blockDim.x;
     const long long t0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    int32_t *pLen = reinterpret_cast<int32_t *>(blk + L.oLen), *pSrc = reinterpret_cast<int32_t *>(blk + L.oSrc);
+    int32_t *pSeq = reinterpret_cast<int32_t *>(blk + L.oSeq), *pOff = reinterpret_cast<int32_t *>(blk + L.oOff);
+    int32_t *pNode = reinterpret_cast<int32_t *>(blk + L.oNode), *pEid = reinterpret_cast<int32_t *>(blk + L.oEid);
+    uint8_t *pStay = blk + L.oStay;
     for (long long k = t0; k < U; k += stride) {
         pLen[k] = (int32_t)(off[k + 1] - off[k]);
         pOff[k] = (int32_t)off[k];
@@ -1442,17 +1487,33 @@ __global__ void packCutsKernel(const long long U, const long long N, const long 
         pStay[j] = stay[j];
     }
 }
-__global__ void fixMergedKernel(const long long total, const long long maxU, const long long maxN, const long long *counts,
-                                int32_t *mOff, uint8_t *mValid) {
-    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= total) return;
-    const long long r = i / maxU, k = i % maxU;
-    const bool v = k < counts[2 * r];
-    mValid[i] = v;
-    mOff[i] = v ? (int32_t)(r * maxN + mOff[i]) : 0;
+// gathered blocks -> one cut view over all ranks (cut r * maxU + k = cut k of rank r; padding cuts are invalid)
+__global__ void unpackMergedKernel(const int size, const PackLayout L, const long long *hdr, const unsigned char *all,
+                                   int32_t *mLen, int32_t *mSrc, int32_t *mSeq, int32_t *mOff, uint8_t *mValid,
+                                   int32_t *mNode, int32_t *mEid, uint8_t *mStay) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    const long long t0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    for (long long i = t0; i < (long long)size * L.maxU; i += stride) {
+        const long long r = i / L.maxU, k = i % L.maxU;
+        const unsigned char *blk = all + r * L.bytes;
+        const bool v = k < hdr[4 * r];
+        mValid[i] = v;
+        mLen[i] = v ? reinterpret_cast<const int32_t *>(blk + L.oLen)[k] : 0;
+        mSrc[i] = v ? reinterpret_cast<const int32_t *>(blk + L.oSrc)[k] : 0;
+        mSeq[i] = v ? reinterpret_cast<const int32_t *>(blk + L.oSeq)[k] : 0;
+        mOff[i] = v ? (int32_t)(r * L.maxN + reinterpret_cast<const int32_t *>(blk + L.oOff)[k]) : 0;
+    }
+    for (long long i = t0; i < (long long)size * L.maxN; i += stride) {
+        const long long r = i / L.maxN, j = i % L.maxN;
+        const unsigned char *blk = all + r * L.bytes;
+        const bool v = j < hdr[4 * r + 1];
+        mNode[i] = v ? reinterpret_cast<const int32_t *>(blk + L.oNode)[j] : 0;
+        mEid[i] = v ? reinterpret_cast<const int32_t *>(blk + L.oEid)[j] : 0;
+        mStay[i] = v ? (blk + L.oStay)[j] : 0;
+    }
 }
 
-int mergeAcrossRanks(smsgpu_ctx *ctx, bool dedup) {
+int mergeAcrossRanks(smsgpu_ctx *ctx, bool dedup, int localRc) {
     NcclApi &A = nccl();
     cudaStream_t st = ctx->stream;
     const int size = ctx->commSize;
@@ -1461,33 +1522,35 @@ int mergeAcrossRanks(smsgpu_ctx *ctx, bool dedup) {
                     ctx->nranks, ctx->commRank, size);
     ncclComm_t comm = static_cast<ncclComm_t>(ctx->ncclComm);
     CutListDev &F = ctx->fin;
-    // 1. counts
-    CU(ctx->gCounts.ensure((size_t)(2 * size + 2) * 8));
-    CU(ctx->hGCounts.ensure((size_t)(2 * size + 2) * 8));
+    // 1. header
+    CU(ctx->gCounts.ensure((size_t)(4 * size + 4) * 8));
+    CU(ctx->hGCounts.ensure((size_t)(4 * size + 4) * 8));
     long long *hg = ctx->hGCounts.as<long long>();
     long long *dg = ctx->gCounts.as<long long>();
-    hg[2 * size] = F.ncuts;
-    hg[2 * size + 1] = F.nnodes;
-    CU(cudaMemcpyAsync(dg + 2 * size, hg + 2 * size, 16, cudaMemcpyHostToDevice, st));
-    NC(A.AllGather(dg + 2 * size, dg, 2, ncclInt64, comm, st));
-    CU(cudaMemcpyAsync(hg, dg, (size_t)2 * size * 8, cudaMemcpyDeviceToHost, st));
+    hg[4 * size] = localRc ? 0 : F.ncuts;
+    hg[4 * size + 1] = localRc ? 0 : F.nnodes;
+    hg[4 * size + 2] = localRc;
+    hg[4 * size + 3] = 0;
+    CU(cudaMemcpyAsync(dg + 4 * size, hg + 4 * size, 32, cudaMemcpyHostToDevice, st));
+    NC(A.AllGather(dg + 4 * size, dg, 4, ncclInt64, comm, st));
+    CU(cudaMemcpyAsync(hg, dg, (size_t)4 * size * 8, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     long long maxU = 0, maxN = 0;
     for (int r = 0; r < size; ++r) {
-        maxU = std::max(maxU, hg[2 * r]);
-        maxN = std::max(maxN, hg[2 * r + 1]);
+        if (hg[4 * r + 2] != 0) {
+            if (localRc) return localRc; // this rank's own error text stays
+            return fail(ctx, SMSGPU_ERR_INTERNAL, "rank %d failed its local round (status %lld); no rank returns cuts", r, hg[4 * r + 2]);
+        }
+        maxU = std::max(maxU, hg[4 * r]);
+        maxN = std::max(maxN, hg[4 * r + 1]);
     }
     if (maxU == 0) return 0;
     maxN = std::max<long long>(maxN, 1);
     if ((long long)size * maxN > 0x7FFFFFFFll) return fail(ctx, SMSGPU_ERR_INTERNAL, "merged cut list exceeds 2^31 nodes");
     // 2. pack + gather
-    CU(ctx->pLen.ensure((size_t)maxU * 4));
-    CU(ctx->pSrc.ensure((size_t)maxU * 4));
-    CU(ctx->pSeq.ensure((size_t)maxU * 4));
-    CU(ctx->pOff.ensure((size_t)maxU * 4));
-    CU(ctx->pNode.ensure((size_t)maxN * 4));
-    CU(ctx->pEid.ensure((size_t)maxN * 4));
-    CU(ctx->pStay.ensure((size_t)maxN));
+    const PackLayout L = packLayout(maxU, maxN);
+    CU(ctx->pBlock.ensure((size_t)L.bytes));
+    CU(ctx->mBlocks.ensure((size_t)L.bytes * size));
     const long long tot = (long long)size * maxU, totN = (long long)size * maxN;
     CU(ctx->mLen.ensure((size_t)tot * 4));
     CU(ctx->mSrc.ensure((size_t)tot * 4));
@@ -1499,20 +1562,13 @@ int mergeAcrossRanks(smsgpu_ctx *ctx, bool dedup) {
     CU(ctx->mStay.ensure((size_t)totN));
     packCutsKernel<<<ctx->smCount * 4, 256, 0, st>>>(F.ncuts, F.nnodes, F.off.as<long long>(), F.src.as<int32_t>(),
                                                      F.seq.as<int32_t>(), F.node.as<int32_t>(), F.eid.as<int32_t>(),
-                                                     F.stay.as<uint8_t>(), ctx->pLen.as<int32_t>(), ctx->pSrc.as<int32_t>(),
-                                                     ctx->pSeq.as<int32_t>(), ctx->pOff.as<int32_t>(), ctx->pNode.as<int32_t>(),
-                                                     ctx->pEid.as<int32_t>(), ctx->pStay.as<uint8_t>());
+                                                     F.stay.as<uint8_t>(), L, ctx->pBlock.as<unsigned char>());
     CU(cudaGetLastError());
-    NC(A.GroupStart());
-    NC(A.AllGather(ctx->pLen.p, ctx->mLen.p, (size_t)maxU, ncclInt32, comm, st));
-    NC(A.AllGather(ctx->pSrc.p, ctx->mSrc.p, (size_t)maxU, ncclInt32, comm, st));
-    NC(A.AllGather(ctx->pSeq.p, ctx->mSeq.p, (size_t)maxU, ncclInt32, comm, st));
-    NC(A.AllGather(ctx->pOff.p, ctx->mOff.p, (size_t)maxU, ncclInt32, comm, st));
-    NC(A.AllGather(ctx->pNode.p, ctx->mNode.p, (size_t)maxN, ncclInt32, comm, st));
-    NC(A.AllGather(ctx->pEid.p, ctx->mEid.p, (size_t)maxN, ncclInt32, comm, st));
-    NC(A.AllGather(ctx->pStay.p, ctx->mStay.p, (size_t)maxN, ncclUint8, comm, st));
-    NC(A.GroupEnd());
-    fixMergedKernel<<<gridFor(tot, 256), 256, 0, st>>>(tot, maxU, maxN, dg, ctx->mOff.as<int32_t>(), ctx->mValid.as<uint8_t>());
+    NC(A.AllGather(ctx->pBlock.p, ctx->mBlocks.p, (size_t)L.bytes, ncclUint8, comm, st));
+    unpackMergedKernel<<<ctx->smCount * 4, 256, 0, st>>>(size, L, dg, ctx->mBlocks.as<unsigned char>(), ctx->mLen.as<int32_t>(),
+                                                         ctx->mSrc.as<int32_t>(), ctx->mSeq.as<int32_t>(), ctx->mOff.as<int32_t>(),
+                                                         ctx->mValid.as<uint8_t>(), ctx->mNode.as<int32_t>(), ctx->mEid.as<int32_t>(),
+                                                         ctx->mStay.as<uint8_t>());
     CU(cudaGetLastError());
     ctx->stats.total_launches += 2;
     // 3. global dedup: every rank computes the identical full list

@@ -39,10 +39,10 @@ def test_library_exports_every_declared_symbol(lib):
 
 def test_abi_version_and_default_params(lib):
     from sms_b200 import capi
-    assert lib.smsgpu_abi_version() == 2
+    assert lib.smsgpu_abi_version() == 3
     p = capi.Params()
     lib.smsgpu_default_params(C.byref(p))
-    assert p.max_intermediates == 10 and p.best_dist_init == 1.0 - 1e-6 and p.dedup == 1
+    assert p.max_intermediates == 10 and p.best_dist_init == 1.0 - 1e-6 and p.dedup == 1 and p.mode == 0 and p.min_efficacy == 0.0
 
 
 def test_struct_sizes_match_header():
@@ -68,6 +68,9 @@ def test_create_rejects_bad_graphs_and_fails_loudly_without_gpu(lib):
     h = C.c_void_p()
     rp = inst.rowptr.copy()
     rp[-1] += 1
+    assert lib.smsgpu_create(C.byref(h), inst.n, inst.m, rp.ctypes.data, inst.col.ctypes.data, inst.eid.ctypes.data, 0) == -1
+    rp = inst.rowptr.copy()
+    rp[1] = 2 * inst.m + 5  # an inner row pointer beyond the arc arrays: rejected before any arc is read
     assert lib.smsgpu_create(C.byref(h), inst.n, inst.m, rp.ctypes.data, inst.col.ctypes.data, inst.eid.ctypes.data, 0) == -1
     col = inst.col.copy()
     col[0] = 0  # self loop at vertex 0

@@ -1,6 +1,6 @@
 """The C++ host side above the C ABI: sms::GpuOcwSeparator (sms_b200/host/gpu_ocw_separator.hpp) and the drop-in
 SCIP handler `cycleparity` (sms_b200/host/conshdlr_oscw.cpp), compiled against the recording SCIP fake and the
-NetworKit stand-in (sms_b200/host/shim) because neither SCIP nor a built NetworKit exists on the test boxes.
+NetworKit stand-in (tests/cpp/shim) because neither SCIP nor a built NetworKit exists on the test boxes.
 
 CPU: the sources compile, link against libsmsgpu.so, and construction fails loudly without a device.
 GPU (-m gpu): one CONSSEPALP / CONSENFOLP / CONSSEPASOL round through the handler delivers to (fake) SCIP exactly
@@ -27,9 +27,9 @@ def driver():
     lib = build.build()
     os.makedirs(OUT, exist_ok=True)
     srcs = [os.path.join(ROOT, "tests", "cpp", "conshdlr_driver.cpp"), os.path.join(ROOT, "sms_b200", "host", "conshdlr_oscw.cpp")]
-    hdrs = [os.path.join(ROOT, "sms_b200", "host", "gpu_ocw_separator.hpp"), os.path.join(ROOT, "sms_b200", "host", "shim", "scip", "scip.h")]
+    hdrs = [os.path.join(ROOT, "sms_b200", "host", "gpu_ocw_separator.hpp"), os.path.join(ROOT, "tests", "cpp", "shim", "scip", "scip.h")]
     if not os.path.exists(DRIVER) or any(os.path.getmtime(s) > os.path.getmtime(DRIVER) for s in srcs + hdrs + [lib]):
-        cmd = ["g++", "-std=c++17", "-O2", "-Wall", "-Wextra", "-Werror", f"-I{ROOT}/sms_b200/host", f"-I{ROOT}/sms_b200/host/shim",
+        cmd = ["g++", "-std=c++17", "-O2", "-Wall", "-Wextra", "-Werror", f"-I{ROOT}/sms_b200/host", f"-I{ROOT}/tests/cpp/shim",
                f"-I{ROOT}/include", *srcs, "-o", DRIVER, f"-L{os.path.dirname(lib)}", "-lsmsgpu", f"-Wl,-rpath,{os.path.dirname(lib)}"]
         r = subprocess.run(cmd, capture_output=True, text=True)
         assert r.returncode == 0, r.stderr
