@@ -324,7 +324,7 @@ public:
         currentSource_ = source;
         last_ = SourceStats{};
         std::vector<Walk> violated;
-        if (blacklist_[currentSource_]) return violated; // indexed with the DOUBLED id (quirk A.7.1)
+        if (isBl(currentSource_)) return violated; // indexed with the DOUBLED id (quirk A.7.1)
         runDijkstra();
         if (intermediateVertices_.empty()) return violated;
         std::vector<Walk> startOcws;
@@ -541,7 +541,7 @@ private:
             last_.settled++;
             for (int64_t a = g_.rowptr[cur]; a < g_.rowptr[cur + 1]; ++a) { // :96-111
                 int64_t nb = g_.col[a];
-                if (blacklist_[nb]) continue;
+                if (isBl(nb)) continue;
                 last_.arcsScanned++;
                 const double newHopDist = hopDistances_[current] + 1;
                 const double stayW = weights_[g_.eid[a]];
@@ -594,7 +594,7 @@ private:
         while ((path[endPath].v == twinPath[endTwin].v) && (endPath > 0) && (endTwin > 0)) { // :164-169
             endPath--;
             endTwin--;
-            blacklist_[path[endPath].v] = true; // stem blacklisting side effect
+            setBl(path[endPath].v); // stem blacklisting side effect
         }
         if (path[endPath].v != twinPath[endTwin].v) {
             endPath++;
@@ -607,20 +607,63 @@ private:
     }
 
     void blacklistIntReachable(int64_t source) { // :363-382
-        blacklist_[source] = true;
+        setBl(source);
         std::vector<int64_t> stack{source};
         while (!stack.empty()) {
             auto next = stack.back();
             stack.pop_back();
             for (int64_t a = g_.rowptr[next]; a < g_.rowptr[next + 1]; ++a) {
                 auto w = weights_[g_.eid[a]];
-                if ((w == 0.0 || w == 1.0) && !blacklist_[g_.col[a]]) {
-                    blacklist_[g_.col[a]] = true;
+                // stamp mode: a vertex stamped <= now in THIS sweep is blacklisted as well (by an earlier source, or by
+                // this very flood: the reference's DFS reads its own writes)
+                if ((w == 0.0 || w == 1.0) && !isBl(g_.col[a]) && !(stampMode_ && stampNext_[g_.col[a]] <= now_)) {
+                    setBl(g_.col[a]);
                     stack.push_back(g_.col[a]);
                 }
             }
         }
     }
+
+    // ---- time-stamped blacklist (the device's SMSGPU_MODE_VERBATIM, restated on the CPU) -------------------------------
+    // The sequential sweep's blacklist is a function of time: vertex v is blacklisted for the source at position t of
+    // the sweep iff some source at a position < t blacklisted it (or it was blacklisted initially).  With
+    // stamp[v] = position of the FIRST source that blacklists v (-1: initially, kNever: never) the sweep becomes a
+    // fixed-point problem: every source t reads "stamp[v] < t" and writes min(stamp[v], t).  Sources are then independent
+    // GIVEN the stamps, and iterating whole sweeps (each reading the stamps of the previous sweep) converges to the
+    // sequential result: after k sweeps the first k sources are exact, in practice after a handful.
+    bool isBl(int64_t v) const { return stampMode_ ? stampCur_[v] < now_ : blacklist_[v] != 0; }
+    void setBl(int64_t v) {
+        if (stampMode_) {
+            if (now_ < stampNext_[v]) stampNext_[v] = now_;
+        } else {
+            blacklist_[v] = true;
+        }
+    }
+
+public:
+    static constexpr int64_t kNever = INT64_MAX;
+    void stampBegin(const uint8_t *bl0) { // before the first sweep
+        stampMode_ = true;
+        stampCur_.assign(n_, kNever);
+        for (int64_t v = 0; v < n_; ++v)
+            if (bl0[v]) stampCur_[v] = -1;
+        stampNext_ = stampCur_;
+    }
+    void stampSweepBegin(const uint8_t *bl0) { // every sweep writes a fresh stamp array
+        for (int64_t v = 0; v < n_; ++v) stampNext_[v] = bl0[v] ? -1 : kNever;
+    }
+    bool stampSweepEnd() { // true: the sweep reproduced the stamps it read -> fixed point
+        const bool same = stampNext_ == stampCur_;
+        stampCur_ = stampNext_;
+        return same;
+    }
+    void stampNow(int64_t t) { now_ = t; }
+    const std::vector<int64_t> &stamps() const { return stampCur_; }
+
+private:
+    bool stampMode_ = false;
+    int64_t now_ = 0;
+    std::vector<int64_t> stampCur_, stampNext_;
 
     const int64_t n_;
     const Csr &g_;

@@ -84,6 +84,65 @@ void *orc_sweep(int64_t n, int64_t m, const int32_t *eu, const int32_t *ev, cons
     OrcEngineFast eng(n, m, eu, ev, (mode & 2) != 0);
     return sweep::run(eng, n, x, m, bl0, sources, nsrc, mode & 1, wantLabels, wantCuts);
 }
+// The sequential sweep (mode V) computed as the fixed point of independent sweeps over a time-stamped blacklist
+// (ocw_oracle.hpp "time-stamped blacklist"): the CPU statement of the device's SMSGPU_MODE_VERBATIM.  info[0] = sweeps
+// run, info[1] = sources whose walk list changed after the first sweep (summed over sweeps), info[2] = sources run in
+// the last sweep, info[3] = vertices blacklisted at the end.  The result must equal orc_sweep(mode V) -- tests check it.
+void *orc_sweep_fixpoint(int64_t n, int64_t m, const int32_t *eu, const int32_t *ev, const double *x, const uint8_t *bl0,
+                         const int32_t *sources, int64_t nsrc, int canonical, int maxSweeps, int64_t *info) {
+    OrcEngine eng(n, m, eu, ev, canonical != 0);
+    for (int64_t e = 0; e < m; ++e) eng.updateEdgeWeight(e, x[e]);
+    eng.sep.stampBegin(bl0);
+    sweep::Result *r = nullptr;
+    std::vector<uint64_t> prevSig(nsrc, 0), sig(nsrc, 0);
+    int64_t sweeps = 0, changed = 0;
+    auto t0 = std::chrono::steady_clock::now();
+    for (;;) {
+        delete r;
+        r = new sweep::Result();
+        eng.sep.stampSweepBegin(bl0);
+        int64_t ran = 0;
+        for (int64_t k = 0; k < nsrc; ++k) {
+            const int64_t s = sources[k];
+            sig[k] = 0;
+            const bool skip = (s < n) ? bl0[s] != 0 : false;
+            if (!skip) {
+                eng.sep.stampNow(k);
+                auto walks = eng.getViolatedOcws(s);
+                ran += eng.sep.lastStats().settled > 0;
+                for (auto &w : walks) {
+                    uint64_t h = 1469598103934665603ull;
+                    for (uint64_t i = 0; i < w.size(); ++i) {
+                        r->node.push_back(static_cast<int32_t>(w.getIthNode(i)));
+                        r->stay.push_back(w.ithEdgeIsStay(i) ? 1 : 0);
+                        h = (h ^ (uint64_t)(2 * w.getIthNode(i) + w.ithEdgeIsStay(i))) * 1099511628211ull;
+                    }
+                    sig[k] = sig[k] * 31 + h;
+                    r->cutOff.push_back(static_cast<int64_t>(r->node.size()));
+                    r->cutSrc.push_back(static_cast<int32_t>(k));
+                    r->nWalks += 1;
+                    r->totalLen += static_cast<int64_t>(w.size());
+                }
+                eng.appendStats(*r);
+            } else {
+                for (int i = 0; i < 6; ++i) r->srcStats.push_back(0);
+            }
+        }
+        ++sweeps;
+        if (sweeps > 1)
+            for (int64_t k = 0; k < nsrc; ++k) changed += sig[k] != prevSig[k];
+        prevSig = sig;
+        info[2] = ran;
+        if (eng.sep.stampSweepEnd() || sweeps >= maxSweeps) break;
+    }
+    r->seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    info[0] = sweeps;
+    info[1] = changed;
+    int64_t nbl = 0;
+    for (auto v : eng.sep.stamps()) nbl += v != orc::OcwOracle::kNever;
+    info[3] = nbl;
+    return r;
+}
 void orc_sizes(void *h, int64_t *out) { sweep::sizes(static_cast<sweep::Result *>(h), out); }
 double orc_seconds(void *h) { return static_cast<sweep::Result *>(h)->seconds; }
 void orc_timing(void *h, double *out) { sweep::timing(static_cast<sweep::Result *>(h), out); }

@@ -80,6 +80,9 @@ class _Lib:
         f("copy_labels").argtypes = [C.c_void_p, _i64p, _i32p, _f64p, _i32p]
         f("copy_stats").argtypes = [C.c_void_p, _i64p]
         f("free").argtypes = [C.c_void_p]
+        if prefix == "orc":
+            f("sweep_fixpoint").argtypes = [C.c_int64, C.c_int64, _i32p, _i32p, _f64p, _u8p, _i32p, C.c_int64, C.c_int, C.c_int, _i64p]
+            f("sweep_fixpoint").restype = C.c_void_p
         for name in ("simple_odd_cycles", "extract_cycles"):
             f(name).argtypes = [C.c_int64, C.c_int64, _i32p, _i32p, _f64p, _i32p, _u8p, C.c_int64]
             f(name).restype = C.c_void_p
@@ -140,6 +143,17 @@ class _Lib:
         h = self._f("sweep")(inst.n, inst.m, inst.eu, inst.ev, _c(x, np.float64), bl, src, len(src),
                              {"I": 0, "V": 1}[mode] | (2 if canonical else 0), int(want_labels), int(want_cuts))
         return self._unpack(h, len(src), want_labels)
+
+    def sweep_fixpoint(self, inst, x, blacklist=None, sources=None, canonical=True, max_sweeps=10000):
+        """Mode V as the fixed point of independent sweeps over a time-stamped blacklist (restatement only): the CPU
+        statement of SMSGPU_MODE_VERBATIM.  Returns (Sweep, info) with info = dict(sweeps, changed, ran_last, blacklisted)."""
+        bl = inst.root_blacklist() if blacklist is None else _c(blacklist, np.uint8)
+        src = inst.handler_sources() if sources is None else _c(sources, np.int32)
+        info = np.zeros(4, np.int64)
+        h = self._f("sweep_fixpoint")(inst.n, inst.m, inst.eu, inst.ev, _c(x, np.float64), bl, src, len(src),
+                                      int(canonical), int(max_sweeps), info)
+        return self._unpack(h, len(src), False), dict(sweeps=int(info[0]), changed=int(info[1]), ran_last=int(info[2]),
+                                                       blacklisted=int(info[3]))
 
     def _walk_call(self, name, inst, x, nodes, stay):
         h = self._f(name)(inst.n, inst.m, inst.eu, inst.ev, _c(x, np.float64), _c(nodes, np.int32),

@@ -131,6 +131,16 @@ def read_mc(path: str) -> Instance:
     return _finish(path.split("/")[-1], n, e[:, 0], e[:, 1])
 
 
+def read_mc_weighted(path: str):
+    """like read_mc, plus the weights by edge-list position: (Instance, float64[m])"""
+    with open(path) as f:
+        rows = [ln.split() for ln in f if ln.strip() and not ln.startswith("#")]
+    n, m = int(rows[0][0]), int(rows[0][1])
+    e = np.array([[int(r[0]) - 1, int(r[1]) - 1] for r in rows[1 : 1 + m]], dtype=np.int64)
+    w = np.array([float(r[2]) for r in rows[1 : 1 + m]], dtype=np.float64)
+    return _finish(path.split("/")[-1], n, e[:, 0], e[:, 1]), w
+
+
 def write_mc(inst: Instance, path: str, weights=None, seed: int = 1) -> None:
     """Writes `inst` in the '.mc' format the reference's `sms` binary reads (src/io/io.cpp: header 'n m', then
     1-based 'u v w' lines; mcFileToGraph adds the edges in file order, so NetworKit's adjacency order and edge ids
