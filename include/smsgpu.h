@@ -111,7 +111,8 @@ typedef struct smsgpu_stats {
     int64_t mirrored_arcs;     /* part of arcs_scanned that was NOT scanned: the twin's scans stand for them */
     double ms_tier[4];         /* search kernel time per tier (shared / HBM medium / HBM large / dense); the HBM large
                                 * tier may run beside the medium one, so the four need not add up to ms_search */
-    int64_t reserved[1];
+    int64_t verbatim_sweeps;   /* SMSGPU_MODE_VERBATIM: sweeps over the sources until the stamps reached their fixed point
+                                * (arcs_scanned / settled are summed over them); 0 in independent-source mode */
 } smsgpu_stats;
 
 /* ---- life cycle: replaces OcwSeparator::OcwSeparator (src/graph/ocw_seperator.cpp:9-23) ---------------------- */

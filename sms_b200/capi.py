@@ -78,7 +78,7 @@ class StatsStruct(C.Structure):
         ("mirrored_sources", C.c_int64),
         ("mirrored_arcs", C.c_int64),
         ("ms_tier", C.c_double * 4),
-        ("reserved", C.c_int64 * 1),
+        ("verbatim_sweeps", C.c_int64),
     ]
 
 
@@ -264,7 +264,7 @@ class Context:
     def stats(self) -> dict:
         s = StatsStruct()
         self._check(self.lib.smsgpu_get_stats(self.h, C.byref(s)))
-        d = {k: getattr(s, k) for k, _ in StatsStruct._fields_ if k not in ("reserved", "tier_sources", "ms_tier")}
+        d = {k: getattr(s, k) for k, _ in StatsStruct._fields_ if k not in ("tier_sources", "ms_tier")}
         d["tier_sources"] = list(s.tier_sources)
         d["ms_tier"] = [round(v, 4) for v in s.ms_tier]
         return d

@@ -157,6 +157,64 @@ __global__ void pairCompactKernel(const long long nsrc, const int8_t *__restrict
     }
 }
 
+// ---- SMSGPU_MODE_VERBATIM: the time-stamped blacklist (GraphDev::blStamp) -------------------------------------------
+// stamps of a fresh sweep: -1 where the round's initial blacklist is set, never elsewhere
+__global__ void initStampsKernel(const long long n, const uint8_t *__restrict__ bl, int32_t *stamp) {
+    for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < n; v += (long long)gridDim.x * blockDim.x)
+        stamp[v] = bl[v] ? -1 : kNeverStamp;
+}
+// The rest of blacklistIntReachable (ocw_seperator.cpp:363-382) for every empty source of the sweep at once: the stamp t
+// of a source that found nothing floods from the vertices that carry it over integral edges (weight exactly 0.0 / 1.0)
+// to vertices that are not blacklisted before t (previous sweep's stamps) and do not carry a smaller stamp yet.  One
+// relaxation pass per launch; the host repeats it until nothing changes (min-label propagation).
+__global__ void floodStampsKernel(const GraphDev G, unsigned int *changed) {
+    bool any = false;
+    for (long long u = (long long)blockIdx.x * blockDim.x + threadIdx.x; u < G.n; u += (long long)gridDim.x * blockDim.x) {
+        const int32_t t = G.blStampNext[u];
+        if (t < 0 || t == kNeverStamp || !G.srcEmpty[t]) continue; // only the stamps of empty sources flood
+        for (long long a = G.rowptr[u]; a < G.rowptr[u + 1]; ++a) {
+            const Arc arc = G.arcs[a];
+            const uint32_t v = (uint32_t)arc.nbr & 0x7FFFFFFFu;
+            if (!(arc.w == 0.0 || arc.w == 1.0) || stampedBefore(G, v, t)) continue;
+            if (atomicMin(&G.blStampNext[v], t) > t) any = true;
+        }
+    }
+    if (any) *changed = 1u;
+}
+// Sources known to find nothing whatever the blacklist (they found nothing against the round's INITIAL blacklist, and a
+// larger blacklist only removes walks) are not searched again in later sweeps; their writes are repeated here: nothing
+// when the source is blacklisted at its time (ocw_seperator.cpp:334), else the seed of blacklistIntReachable.
+__global__ void reseedEmptySourcesKernel(const GraphDev G, const long long nsrc, const int32_t *__restrict__ sources,
+                                         const uint8_t *__restrict__ emptyB0) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nsrc; i += (long long)gridDim.x * blockDim.x) {
+        if (!emptyB0[i]) continue;
+        const int32_t now = (int32_t)i;
+        const uint32_t src = sources ? (uint32_t)sources[i] : (uint32_t)i;
+        if ((long long)src < G.n && stampedBefore(G, src, now)) { // skipped at its time: no search, no writes
+            G.srcEmpty[i] = 0;
+            continue;
+        }
+        G.srcEmpty[i] = 1;
+        const uint32_t u = src >> 1;
+        atomicMin(&G.blStampNext[u], now);
+        for (long long a = G.rowptr[u]; a < G.rowptr[u + 1]; ++a) {
+            const Arc arc = G.arcs[a];
+            const uint32_t v = (uint32_t)arc.nbr & 0x7FFFFFFFu;
+            if ((arc.w == 0.0 || arc.w == 1.0) && !stampedBefore(G, v, now)) atomicMin(&G.blStampNext[v], now);
+        }
+    }
+}
+// work list of the later sweeps: every source that is not known to be empty
+__global__ void activeSourcesKernel(const long long nsrc, const uint8_t *__restrict__ emptyB0, int32_t *list, unsigned int *count) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nsrc; i += (long long)gridDim.x * blockDim.x)
+        if (!emptyB0[i]) list[atomicAdd(count, 1u)] = (int32_t)i;
+}
+__global__ void compareStampsKernel(const long long n, const int32_t *__restrict__ a, const int32_t *__restrict__ b, unsigned int *differ) {
+    bool d = false;
+    for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < n; v += (long long)gridDim.x * blockDim.x) d |= a[v] != b[v];
+    if (d) *differ = 1u;
+}
+
 // ---- K2-K4 ---------------------------------------------------------------------------------------------------
 #ifndef SMSGPU_FAST_MIN_CTAS
 #define SMSGPU_FAST_MIN_CTAS 5
@@ -197,14 +255,14 @@ __global__ void __launch_bounds__(128, FAST ? SMSGPU_FAST_MIN_CTAS : 1) ocwSearc
         const int32_t srcIdx = P.worklist ? P.worklist[wi] : (int32_t)wi;
         const uint32_t src = P.sources ? (uint32_t)P.sources[srcIdx] : (uint32_t)(((((long long)(srcIdx >> 1)) * P.srcStride + P.srcBegin) << 1) | (srcIdx & 1));
         // `if (blacklist_[currentSource_]) return {}` -- indexed with the DOUBLED id (ocw_seperator.cpp:334, quirk A.7.1)
-        if ((long long)src < G.n && P.blacklist[src]) continue;
+        if ((long long)src < G.n && (G.blStamp ? stampedBefore(G, src, srcIdx) : P.blacklist[src] != 0)) continue;
         if ((long long)(src >> 1) >= G.n) continue; // not a node of the double cover
 
         SrcState S;
         if (FAST)
-            searchSourceFast<TW>(T, G, M, S, src, P.bestInit, P.stampBase + (uint32_t)wi + 1u);
+            searchSourceFast<TW>(T, G, M, S, src, P.bestInit, P.stampBase + (uint32_t)wi + 1u, srcIdx);
         else
-            searchSource<TW>(T, G, M, S, src, P.bestInit);
+            searchSource<TW>(T, G, M, S, src, P.bestInit, srcIdx);
         if (!S.overflow && S.histN > 0) {
             const int nsel = selectIntermediates<TW>(T, M, S, maxInter, sel);
             if (!S.overflow && T.lane == 0) {
@@ -214,7 +272,7 @@ __global__ void __launch_bounds__(128, FAST ? SMSGPU_FAST_MIN_CTAS : 1) ocwSearc
                 E.seq = 0;
                 E.tier = P.tier;
                 for (int r = 0; r < nsel; ++r) {
-                    const int W = buildWalk(M, sel[r], src);
+                    const int W = buildWalk(G, M, sel[r], src, srcIdx);
                     if (W < 0) {
                         S.overflow = 1;
                         break;
@@ -225,6 +283,7 @@ __global__ void __launch_bounds__(128, FAST ? SMSGPU_FAST_MIN_CTAS : 1) ocwSearc
             }
             S.overflow = T.shfl(S.overflow, 0);
         }
+        if (!S.overflow && G.blStampNext) verbatimSourceDone<TW>(T, G, src, srcIdx, S.histN == 0);
         if (!S.overflow) {
             if (P.exportLabels) {
                 // every label the search kept: the touched list (heap engine) / the occupied slots (fast engine)

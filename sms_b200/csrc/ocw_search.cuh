@@ -296,7 +296,7 @@ struct SrcState {
 // runDijsktra (ocw_seperator.cpp:37-112), canonical order.  Returns with S.overflow != 0 if a capacity was hit.
 template <int TW>
 __device__ void searchSource(const Tile<TW> &T, const GraphDev &G, TileMem &M, SrcState &S, const uint32_t src,
-                             const double bestInit) {
+                             const double bestInit, const int32_t now) {
     S.best = bestInit;
     S.bestHop = 0.0;
     S.histN = 0;
@@ -384,6 +384,7 @@ __device__ void searchSource(const Tile<TW> &T, const GraphDev &G, TileMem &M, S
                 w = arc.w;
                 SMS_CHK((long long)nbr < G.n && w >= 0.0 && w <= 1.0);
                 act = arc.nbr >= 0; // blacklisted neighbours are skipped (:98-99)
+                if (G.blStamp && act) act = !stampedBefore(G, nbr, now); // mode V: blacklisted by an earlier source
             }
             S.arcs += __popc(T.ballot(act));
             const double dS = dc + w;         // totalStayDist  (:104)

@@ -37,7 +37,7 @@ __device__ __forceinline__ uint32_t killKey(const TileMem &M, uint32_t qpos) {
 
 template <int TW>
 __device__ void searchSourceFast(const Tile<TW> &T, const GraphDev &G, TileMem &M, SrcState &S, const uint32_t src,
-                                 const double bestInit, const uint32_t stamp) {
+                                 const double bestInit, const uint32_t stamp, const int32_t now) {
     static_assert(TW == 32, "the fast engine uses full-warp REDUX");
     S.best = bestInit;
     S.bestHop = 0.0;
@@ -175,6 +175,7 @@ __device__ void searchSourceFast(const Tile<TW> &T, const GraphDev &G, TileMem &
                 nbr = (uint32_t)arc.nbr & 0x7FFFFFFFu;
                 w = arc.w;
                 act = arc.nbr >= 0; // blacklisted neighbours are skipped (:98-99)
+                if (G.blStamp && act) act = !stampedBefore(G, nbr, now); // mode V: blacklisted by an earlier source
             }
             S.arcs += __popc(T.ballot(act));
             const double dS = dc + w;         // totalStayDist  (:104)

@@ -148,7 +148,7 @@ __device__ __noinline__ int finishSourcePairs(const PairsKArgs *K, unsigned char
                     break;
                 }
                 for (int r = 0; r < nsel; ++r) {
-                    const int W = buildWalk(M, sel[r], src);
+                    const int W = buildWalk(G, M, sel[r], src, srcIdx);
                     if (W < 0) {
                         S.overflow = 1;
                         break;
@@ -162,6 +162,7 @@ __device__ __noinline__ int finishSourcePairs(const PairsKArgs *K, unsigned char
         S.overflow = T.shfl(S.overflow, 0);
     }
     int counted = 0;
+    if (!S.overflow && G.blStampNext) verbatimSourceDone<32>(T, G, src, srcIdx, histN == 0); // mode V (never mirrored)
     if (!S.overflow) {
         if (P.exportLabels) {
             for (uint32_t i = T.lane; i < caps.tabCap; i += 32) {
@@ -336,7 +337,7 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
                     const int32_t i0 = P.worklist ? P.worklist[w32] : (int32_t)w32;
                     const uint32_t s0 = P.sources ? (uint32_t)P.sources[i0] : (uint32_t)(((((long long)(i0 >> 1)) * P.srcStride + P.srcBegin) << 1) | (i0 & 1));
                     // `if (blacklist_[currentSource_]) return {}` -- indexed with the DOUBLED id (ocw_seperator.cpp:334)
-                    const bool skip0 = ((long long)s0 < G.n && P.blacklist[s0]) || (long long)(s0 >> 1) >= G.n;
+                    const bool skip0 = ((long long)s0 < G.n && (G.blStamp ? stampedBefore(G, s0, i0) : P.blacklist[s0] != 0)) || (long long)(s0 >> 1) >= G.n;
                     if (second) { // skip test already passed when the item was fetched
                         wi = w32;
                         src = s0;
@@ -348,7 +349,7 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
                         if (have1) {
                             const int32_t i1 = P.worklist ? P.worklist[w32 + 1] : (int32_t)(w32 + 1);
                             s1 = P.sources ? (uint32_t)P.sources[i1] : (uint32_t)(((((long long)(i1 >> 1)) * P.srcStride + P.srcBegin) << 1) | (i1 & 1));
-                            have1 = !(((long long)s1 < G.n && P.blacklist[s1]) || (long long)(s1 >> 1) >= G.n);
+                            have1 = !(((long long)s1 < G.n && (G.blStamp ? stampedBefore(G, s1, i1) : P.blacklist[s1] != 0)) || (long long)(s1 >> 1) >= G.n);
                         }
                         if (!skip0) {
                             wi = w32;
@@ -524,6 +525,8 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
         const uint32_t side = cur & 1u;
         const uint32_t hNew = (uint32_t)(clo >> 32) + 1;
         const uint32_t stamp = P.stampBase + wi + 1u;
+        int32_t nowIdx = 0; // mode V: position of this half's source in the source list (its time stamp)
+        if (G.blStamp && run) nowIdx = P.worklist ? P.worklist[wi] : (int32_t)wi;
 
         PCLK(2);
         // ---- (4b) bucket exhausted by this extraction: find the next one and issue its loads NOW, so that they are in
@@ -599,6 +602,7 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
                 nbr = (uint32_t)arc.nbr & 0x7FFFFFFFu;
                 w = arc.w;
                 act = arc.nbr >= 0;    // blacklisted neighbours are skipped (:98-99)
+                if (G.blStamp && act) act = !stampedBefore(G, nbr, nowIdx); // mode V: blacklisted by an earlier source
             }
             arcsN += __popc((__ballot_sync(FULL, act) >> gbase) & 0xFFFFu);
             PCLK(4);

@@ -59,7 +59,18 @@ struct GraphDev {
     int64_t n, m;
     const int64_t *rowptr; // n+1
     const Arc *arcs;       // 2m, adjacency order of the reference graph
+    // SMSGPU_MODE_VERBATIM only (all three null in independent-source mode): the reference's blacklist as a function of
+    // time.  stamp[v] = position in the source list of the FIRST source that blacklists v (-1: blacklisted from the
+    // start, kNeverStamp: never); the source at position `now` sees v blacklisted iff stamp[v] < now.
+    const int32_t *blStamp; // [n] stamps of the previous sweep (read)
+    int32_t *blStampNext;   // [n] stamps this sweep produces (atomicMin)
+    uint8_t *srcEmpty;      // [nsrc] 1: the source ran and found no intermediate (its stamp floods integral edges)
 };
+constexpr int32_t kNeverStamp = 0x7FFFFFFF;
+// `if (blacklist_[neighbor]) continue` (ocw_seperator.cpp:98-99) / `if (blacklist_[currentSource_])` (:334) in mode V
+__device__ __forceinline__ bool stampedBefore(const GraphDev &G, const uint32_t v, const int32_t now) {
+    return G.blStamp[v] < now;
+}
 
 // Capacities of one tile's private working memory (shared memory in tier 0, HBM in tiers 1 and 2).
 struct TileCaps {

@@ -298,8 +298,9 @@ __device__ inline void simpleOddCyclesAndExtract(const GraphDev &G, TileMem &M, 
 }
 
 // intermediateVertexToOcw (:138-188) into M.wn / M.ws; returns the number of edges, -1 on overflow.
-// The stem blacklisting side effect (:164-169) has no reader in independent-source mode and is not performed.
-__device__ inline int buildWalk(const TileMem &M, uint32_t t, uint32_t src) {
+// The stem blacklisting side effect (:164-169) has no reader in independent-source mode and is performed in mode V only
+// (G.blStampNext != nullptr): every vertex the reference blacklists gets the stamp `now` of this source.
+__device__ inline int buildWalk(const GraphDev &G, const TileMem &M, uint32_t t, uint32_t src, int32_t now) {
     int32_t *pa = M.pa, *pb = M.pb;
     const int P = tracePath(M, t, src, pa);
     if (P < 0) return -1;
@@ -321,6 +322,7 @@ __device__ inline int buildWalk(const TileMem &M, uint32_t t, uint32_t src) {
     while (((pa[endPath + 1] >> 1) == (pb[endTwin + 1] >> 1)) && endPath > 0 && endTwin > 0) {
         endPath--;
         endTwin--;
+        if (G.blStampNext) atomicMin(&G.blStampNext[pa[endPath + 1] >> 1], now); // blacklist_[path[endPath].v] = true (:168)
     }
     if ((pa[endPath + 1] >> 1) != (pb[endTwin + 1] >> 1)) {
         endPath++;
@@ -329,6 +331,24 @@ __device__ inline int buildWalk(const TileMem &M, uint32_t t, uint32_t src) {
     for (int i = 0; i <= endPath; ++i) addEdge(pa[i + 1] >> 1, ((pa[i] ^ pa[i + 1]) & 1) == 0);
     for (int i = endTwin; i >= 0; --i) addEdge(pb[i] >> 1, ((pb[i] ^ pb[i + 1]) & 1) == 0);
     return W;
+}
+
+// Mode V, end of a source that completed in this tier: remember whether it found nothing, and if so do what
+// `if (intermediateVertices_.empty()) blacklistIntReachable(originalId(source))` (ocw_seperator.cpp:113-114, 363-382)
+// does at the source vertex itself: blacklist it unconditionally and blacklist its not-yet-blacklisted neighbours over
+// integral edges (weight exactly 0.0 or 1.0).  The rest of that depth-first search -- the flood of this source's stamp
+// through integral edges -- is floodStampsKernel's job (ocw_kernels.cuh), for all sources of the sweep at once.
+template <int TW>
+__device__ inline void verbatimSourceDone(const Tile<TW> &T, const GraphDev &G, const uint32_t src, const int32_t now, const bool empty) {
+    if (T.lane == 0) G.srcEmpty[now] = empty ? 1 : 0;
+    if (!empty) return;
+    const uint32_t u = src >> 1;
+    if (T.lane == 0) atomicMin(&G.blStampNext[u], now);
+    for (long long a = G.rowptr[u] + T.lane; a < G.rowptr[u + 1]; a += TW) {
+        const Arc arc = G.arcs[a];
+        const uint32_t v = (uint32_t)arc.nbr & 0x7FFFFFFFu;
+        if ((arc.w == 0.0 || arc.w == 1.0) && arc.nbr >= 0 && !stampedBefore(G, v, now)) atomicMin(&G.blStampNext[v], now);
+    }
 }
 
 } // namespace smsgpu

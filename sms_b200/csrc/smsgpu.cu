@@ -183,6 +183,10 @@ struct smsgpu_ctx {
     smsgpu_params lastParams{};
     smsgpu_stats stats{};
 
+    // SMSGPU_MODE_VERBATIM: two stamp arrays (previous / current sweep), per-source "found nothing" flags, work list
+    DevBuf vStampA, vStampB, vEmpty, vEmptyB0, vActive, vFlags;
+    long long vActiveCount = 0;
+
     // multi-GPU
     void *ncclComm = nullptr;
     int commRank = 0, commSize = 1;
@@ -540,7 +544,7 @@ void smsgpu_destroy(smsgpu_ctx *ctx) {
                      &ctx->fin.src, &ctx->fin.seq, &ctx->fin.viol, &ctx->scFin.off, &ctx->scFin.node, &ctx->scFin.eid,
                      &ctx->scFin.stay, &ctx->scFin.ncross, &ctx->scFin.src, &ctx->scFin.viol, &ctx->scNodes[0], &ctx->scNodes[1], &ctx->scEids[0],
                      &ctx->scEids[1], &ctx->scFlag[0], &ctx->scFlag[1], &ctx->scStay[0], &ctx->scStay[1], &ctx->gCounts,
-                     &ctx->pBlock, &ctx->mBlocks, &ctx->mNode, &ctx->mEid, &ctx->mStay, &ctx->mOff, &ctx->mLen, &ctx->mSrc,
+                     &ctx->pBlock, &ctx->mBlocks, &ctx->vStampA, &ctx->vStampB, &ctx->vEmpty, &ctx->vEmptyB0, &ctx->vActive, &ctx->vFlags, &ctx->mNode, &ctx->mEid, &ctx->mStay, &ctx->mOff, &ctx->mLen, &ctx->mSrc,
                      &ctx->mSeq, &ctx->mValid};
     for (auto *b : dev) b->release();
     PinBuf *pin[] = {&ctx->hX, &ctx->hBl, &ctx->hCounters, &ctx->hHeavy, &ctx->host.off, &ctx->host.node, &ctx->host.eid,
@@ -879,11 +883,21 @@ int separateLocal(smsgpu_ctx *ctx, const smsgpu_params &P) {
         CU(ctx->labHops.ensure((size_t)ctx->labCap * 4));
         CU(ctx->labDist.ensure((size_t)ctx->labCap * 8));
     }
-    GraphDev G{ctx->n, ctx->m, ctx->dRowptr.as<int64_t>(), ctx->dArcs.as<Arc>()};
+    GraphDev G{ctx->n, ctx->m, ctx->dRowptr.as<int64_t>(), ctx->dArcs.as<Arc>(), nullptr, nullptr, nullptr};
     long long rawCuts = 0, rawNodes = 0;
+    // One sweep over the sources: every tier in turn until each source has finished somewhere; raw walks in the arena.
+    // wl0 == nullptr: all local sources, issued by the history of the previous round (independent-source mode's one and
+    // only sweep); else the given work list, no history (the sweeps of SMSGPU_MODE_VERBATIM).
+    auto sweep = [&](const int32_t *wl0, long long nw0, const bool plain) -> int {
     for (int attempt = 0;; ++attempt) {
         if (attempt > 4) return fail(ctx, SMSGPU_ERR_INTERNAL, "raw arena kept overflowing");
         CU(cudaMemsetAsync(dc, 0, 24 * sizeof(unsigned long long), st));
+        if (G.blStampNext) { // mode V: this sweep's stamps start from the round's initial blacklist
+            initStampsKernel<<<ctx->smCount * 4, 256, 0, st>>>(ctx->n, ctx->blPtr, G.blStampNext);
+            CU(cudaGetLastError());
+            CU(cudaMemsetAsync(G.srcEmpty, 0, (size_t)std::max<long long>(nsrc, 1), st));
+            ctx->stats.total_launches += 1;
+        }
         CU(cudaMemsetAsync(ctx->srcTier.p, 0xFF, (size_t)std::max<long long>(nsrc, 1), st));
         CU(cudaMemsetAsync(ctx->srcWork.p, 0, (size_t)std::max<long long>(nsrc, 1) * 4, st)); // skipped sources: no work
         RawOut R{};
@@ -920,9 +934,9 @@ int separateLocal(smsgpu_ctx *ctx, const smsgpu_params &P) {
         SP.debugFlags = P.debug_flags;
         SP.queueCounter = dc + 8;
         SP.runSlot = 4;
-        long long nwork = nsrc;
-        const int32_t *worklist = nullptr;
-        if (ctx->useHistory && ctx->haveOrder) worklist = ctx->srcOrder.as<int32_t>(); // longest first (previous round)
+        long long nwork = plain ? nsrc : nw0;
+        const int32_t *worklist = plain ? nullptr : wl0;
+        if (plain && ctx->useHistory && ctx->haveOrder) worklist = ctx->srcOrder.as<int32_t>(); // longest first (previous round)
         int firstTier = P.start_tier;
         if (ctx->useHistory && ctx->skipTier0 > 0 && firstTier == 0) firstTier = 1;
         int32_t *ovfBufs[2] = {ctx->ovfA.as<int32_t>(), ctx->ovfB.as<int32_t>()};
@@ -965,12 +979,12 @@ int separateLocal(smsgpu_ctx *ctx, const smsgpu_params &P) {
         // with as many CTAs as they have sources for; tier 1 fills the rest of the GPU with everything else.  Run one
         // after the other, tier 2 is a tail of a few thousand long searches on an otherwise idle GPU.
         long long heavy = 0;
-        if (worklist && ctx->heavyPending) {
+        if (plain && worklist && ctx->heavyPending) {
             CU(cudaEventSynchronize(ctx->heavyEv));
             ctx->heavyPairs = (long long)*ctx->hHeavy.as<unsigned int>();
             ctx->heavyPending = false;
         }
-        if (worklist && ctx->overlapHeavy && firstTier == 1 && ctx->heavyPairs > 0 && kNumTiers > 2 && ctx->tier[2].caps.nbuckets) {
+        if (plain && worklist && ctx->overlapHeavy && firstTier == 1 && ctx->heavyPairs > 0 && kNumTiers > 2 && ctx->tier[2].caps.nbuckets) {
             heavy = std::min<long long>(2 * ctx->heavyPairs, nsrc & ~1ll);
             if (int rc = ensureTierScratch(ctx, 1)) return rc;
             if (int rc = ensureTierScratch(ctx, 2)) return rc;
@@ -1064,7 +1078,7 @@ int separateLocal(smsgpu_ctx *ctx, const smsgpu_params &P) {
             redo = true;
         }
         if (redo) continue;
-        if (ctx->useHistory && nsrc > 0) {
+        if (plain && ctx->useHistory && nsrc > 0) {
             // tier 0 (shared memory) is skipped for the next 15 rounds when it completed fewer than 1/4 of its sources
             if (tierRan[0])
                 ctx->skipTier0 = (done[0] * 4 < nsrc) ? 15 : 0;
@@ -1086,8 +1100,8 @@ int separateLocal(smsgpu_ctx *ctx, const smsgpu_params &P) {
             ctx->haveOrder = true;
         }
         ctx->stats.sources_run = (long long)hc[4] + heavyRun;
-        ctx->stats.arcs_scanned = (long long)hc[2];
-        ctx->stats.settled = (long long)hc[3];
+        ctx->stats.arcs_scanned += (long long)hc[2]; // summed over the sweeps of mode V
+        ctx->stats.settled += (long long)hc[3];
         ctx->stats.mirrored_sources = (long long)hc[6];
         ctx->stats.mirrored_arcs = (long long)hc[7];
         ctx->stats.raw_walks = rawCuts;
@@ -1101,6 +1115,99 @@ int separateLocal(smsgpu_ctx *ctx, const smsgpu_params &P) {
         float hms = 0; // the overlapped launch ran beside tier 1: the tier times no longer add up to the search time
         if (heavyRan && cudaEventElapsedTime(&hms, ctx->tierEv[8], ctx->tierEv[9]) == cudaSuccess) ctx->stats.ms_tier[2] += hms;
         break;
+    }
+    return 0;
+    }; // sweep
+
+    if (P.mode == SMSGPU_MODE_INDEPENDENT) {
+        if (int rc = sweep(nullptr, nsrc, true)) return rc;
+    } else {
+        // ---- SMSGPU_MODE_VERBATIM: the sequential sweep as the fixed point of independent sweeps over time stamps --------
+        // (include/smsgpu.h; CPU statement of the same scheme: oracle/ocw_oracle.hpp stampBegin...)
+        if (ctx->nranks != 1) return fail(ctx, SMSGPU_ERR_ARG, "SMSGPU_MODE_VERBATIM runs on one GPU (the stamps are positions in the whole source list)");
+        const size_t nb = (size_t)std::max<long long>(nsrc, 1);
+        CU(ctx->vStampA.ensure((size_t)ctx->n * 4));
+        CU(ctx->vStampB.ensure((size_t)ctx->n * 4));
+        CU(ctx->vEmpty.ensure(nb));
+        CU(ctx->vEmptyB0.ensure(nb));
+        CU(ctx->vActive.ensure(nb * 4));
+        CU(ctx->vFlags.ensure(4 * sizeof(unsigned int)));
+        int32_t *cur = ctx->vStampA.as<int32_t>(), *next = ctx->vStampB.as<int32_t>();
+        unsigned int *flags = ctx->vFlags.as<unsigned int>(); // [0] flood changed, [1] stamps differ, [2] active count
+        unsigned int hf[4] = {0, 0, 0, 0};
+        initStampsKernel<<<ctx->smCount * 4, 256, 0, st>>>(ctx->n, ctx->blPtr, cur);
+        CU(cudaGetLastError());
+        const bool savedMirror = ctx->pairsMirror;
+        ctx->pairsMirror = false; // the two sides of a vertex sit at different times: each is searched
+        bool shortcut = !(std::getenv("SMSGPU_VERBATIM_FULL") && std::getenv("SMSGPU_VERBATIM_FULL")[0] == '1');
+        bool verifying = false;
+        const int32_t *active = nullptr;
+        long long nactive = nsrc;
+        const int32_t *srcList = ctx->explicitSources ? ctx->dSources.as<int32_t>() : nullptr;
+        const unsigned gv = (unsigned)ctx->smCount * 8;
+        int rcV = 0;
+        for (long long sweepNo = 1;; ++sweepNo) {
+            if (sweepNo > std::max<long long>(nsrc, 1) + 2) {
+                rcV = fail(ctx, SMSGPU_ERR_INTERNAL, "the stamps did not reach a fixed point in %lld sweeps", sweepNo - 1);
+                break;
+            }
+            const bool full = active == nullptr;
+            G.blStamp = cur;
+            G.blStampNext = next;
+            G.srcEmpty = ctx->vEmpty.as<uint8_t>();
+            if ((rcV = sweep(active, nactive, false))) break;
+            ctx->stats.verbatim_sweeps = sweepNo;
+            auto cuv = [&](cudaError_t e) { return e == cudaSuccess ? 0 : fail(ctx, SMSGPU_ERR_CUDA, "mode V: %s", cudaGetErrorString(e)); };
+            if (!full) {
+                reseedEmptySourcesKernel<<<gv, 256, 0, st>>>(G, nsrc, srcList, ctx->vEmptyB0.as<uint8_t>());
+                ctx->stats.total_launches += 1;
+            }
+            for (long long pass = 0;; ++pass) { // flood of the empty sources' stamps over integral edges
+                if ((rcV = cuv(cudaMemsetAsync(flags, 0, 8, st)))) break;
+                floodStampsKernel<<<gv, 256, 0, st>>>(G, flags);
+                ctx->stats.total_launches += 1;
+                if ((rcV = cuv(cudaMemcpyAsync(hf, flags, 4, cudaMemcpyDeviceToHost, st)))) break;
+                if ((rcV = cuv(cudaStreamSynchronize(st)))) break;
+                if (!hf[0]) break;
+                if (pass > ctx->n + 2) {
+                    rcV = fail(ctx, SMSGPU_ERR_INTERNAL, "stamp flood did not settle");
+                    break;
+                }
+            }
+            if (rcV) break;
+            compareStampsKernel<<<gv, 256, 0, st>>>(ctx->n, cur, next, flags + 1);
+            ctx->stats.total_launches += 1;
+            if (sweepNo == 1 && shortcut) { // sources that found nothing against the initial blacklist never find anything
+                if ((rcV = cuv(cudaMemcpyAsync(ctx->vEmptyB0.p, ctx->vEmpty.p, nb, cudaMemcpyDeviceToDevice, st)))) break;
+                if ((rcV = cuv(cudaMemsetAsync(flags + 2, 0, 4, st)))) break;
+                activeSourcesKernel<<<gv, 256, 0, st>>>(nsrc, ctx->vEmptyB0.as<uint8_t>(), ctx->vActive.as<int32_t>(), flags + 2);
+                ctx->stats.total_launches += 1;
+            }
+            if ((rcV = cuv(cudaMemcpyAsync(hf, flags, 12, cudaMemcpyDeviceToHost, st)))) break;
+            if ((rcV = cuv(cudaStreamSynchronize(st)))) break;
+            if (sweepNo == 1 && shortcut) ctx->vActiveCount = (long long)hf[2];
+            std::swap(cur, next);
+            if (std::getenv("SMSGPU_DEBUG_OVF"))
+                std::fprintf(stderr, "[smsgpu] mode V sweep %lld (%s, %lld sources): stamps %s\n", sweepNo, full ? "full" : "active set", nactive,
+                             hf[1] ? "changed" : "reproduced");
+            if (!hf[1]) {
+                if (full) break; // a full sweep reproduced the stamps it read: its walks are the sequential sweep's
+                verifying = true; // the active set has converged: one full sweep has to confirm it
+                active = nullptr;
+                nactive = nsrc;
+                continue;
+            }
+            if (verifying) shortcut = false; // the confirmation failed (never observed): full sweeps from here on
+            if (shortcut && !verifying) {
+                active = ctx->vActive.as<int32_t>();
+                nactive = ctx->vActiveCount;
+            } else {
+                active = nullptr;
+                nactive = nsrc;
+            }
+        }
+        ctx->pairsMirror = savedMirror;
+        if (rcV) return rcV;
     }
     CU(cudaEventRecord(ctx->ev[2], st));
 
