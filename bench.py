@@ -42,6 +42,10 @@ WORKLOADS = {
     "torus3d20": (lambda: I.torus3d(20), "config 3: 20x20x20 toroidal grid (8k nodes, 24k edges), iid U(0,1) x*"),
     "random20k": (lambda: I.random_graph(20_000, 80_000, seed=7), "config 4: random graph 20k nodes / 80k edges, iid U(0,1) x*"),
 }
+DENSE_N = 500  # complete graph K_500: 124 750 edges, 20 708 500 triangles (the K6 workload)
+WORKLOADS["dense"] = (lambda: I.from_edges(f"K{DENSE_N}", DENSE_N, np.stack(np.triu_indices(DENSE_N, 1), axis=1)),
+                      f"dense instance: complete graph K_{DENSE_N}, all C({DENSE_N},3) triangles, iid U(0,1) x*: one triangle-inequality scan per step "
+                      "(TriangleSeparator::getViolatedTriangles, triangles.hpp:34-53)")
 WORKLOADS_N = {"random1m": 1_000_000, "torus100": 10_000, "torus3d20": 8_000, "random20k": 20_000}
 # sources the reference arm times per step (bounded, seeded sample; the reference costs O(n) per source: at 1M nodes
 # ~2.5 ms each, so 2048 sources are ~5 s of CPU work per step; SURVEY 7.3-9 asks for >= 1024).  The small configs run
@@ -51,6 +55,9 @@ REF_SAMPLE = {"random1m": 2048, "torus100": 10_000, "torus3d20": 8_000, "random2
 
 # dram bytes of the search of one full round, from the committed ncu capture (per launch; see roofline.traffic_note)
 TRAFFIC_NCU = {"random1m": round(165.588185e9 * 1254134233 / 329005693)}  # 165.59 GB for the capture's 329.0 M (reference-equivalent) settled nodes
+
+
+XSTAR_NOTE = {"fixed": "", "fresh": "; a NEW iid U(0,1) x* every step", "replay": "; x* sequence from the cutting loop (HiGHS root LP iterates, one per step)"}
 
 
 def peaks():
@@ -124,13 +131,37 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------------------------------
 # reference arm / cpu baseline: the unmodified reference on host cores
 # ------------------------------------------------------------------------------------------------------------------
+LPSEQ = {"torus100": "lpseq_torus2d_100.npz", "torus3d20": "lpseq_torus3d_20.npz", "random20k": "lpseq_random20k.npz"}
+
+
+def xstar_sequence(name: str, inst, mode: str, count: int):
+    """The x* the timed steps feed, in order (step k uses entry k mod len):
+      fixed   one iid U(0,1) point (seed 1), the same every step -- the mandated config-5 input
+      fresh   a new iid U(0,1) point every step (seeds 1, 2, ...): nothing the previous round learnt about ball sizes
+              carries over except what the graph itself determines
+      replay  the logged x* sequence of the HiGHS root cutting loop on this instance (tests/golden/lpseq_*.npz,
+              generated by tests/golden/make_lp_golden.py): x* changes every step the way a cutting loop changes it"""
+    if mode == "fixed":
+        return [I.xstar_uniform(inst.m, seed=1)]
+    if mode == "fresh":
+        return [I.xstar_uniform(inst.m, seed=1 + k) for k in range(max(1, min(count, 8)))]
+    path = os.path.join(ROOT, "tests", "golden", LPSEQ.get(name, "-"))
+    if not os.path.exists(path):
+        raise SystemExit(f"bench.py: no logged LP sequence for workload {name} ({path})")
+    g = np.load(path)
+    if int(g["n"]) != inst.n or not np.array_equal(g["eu"], inst.eu) or not np.array_equal(g["ev"], inst.ev):
+        raise SystemExit(f"bench.py: {path} was logged on a different instance")
+    return [np.ascontiguousarray(x) for x in g["xs"]]
+
+
 def _ref_worker(args):
     """One process = one separator (graph built once per call, outside the timed part) over its slice of the sample.
     Returns (set-up s, sum of per-source s, sum of squares, max per-source s, sources timed, walks)."""
-    name, srcs, seed = args
+    name, srcs, xmode, xidx = args
     from oracle import oracle_py  # checker library, executed here as the timed CPU baseline only
     inst = WORKLOADS[name][0]()
-    x = I.xstar_uniform(inst.m, seed=seed)
+    seq = xstar_sequence(name, inst, xmode, xidx + 1)
+    x = seq[xidx % len(seq)]
     eng = oracle_py.ref() if oracle_py.have_ref() else oracle_py.orc()
     # mode "V": the verbatim loop of ConshdlrOscw::sepaOddCycles (conshdlr_oscw.cpp:188-195) -- what the reference
     # actually executes per round; no per-source blacklist re-initialisation is charged to it
@@ -138,7 +169,7 @@ def _ref_worker(args):
     return (*s.timing, s.n_walks)
 
 
-def reference_round(name: str, sample: int, procs: int, pool=None):
+def reference_round(name: str, sample: int, procs: int, pool=None, xmode: str = "fixed", xidx: int = 0):
     """Times the reference on `sample` seeded sources of the workload's round and extrapolates to the full round:
 
         round seconds = set-up (m x updateEdgeWeight + blacklist reset: ONCE per round, not multiplied)
@@ -154,7 +185,7 @@ def reference_round(name: str, sample: int, procs: int, pool=None):
     rng = np.random.default_rng(12345)
     srcs = np.sort(rng.choice(n, sample, replace=False)) if sample < n else np.arange(n)
     chunks = [c for c in np.array_split(srcs, procs) if len(c)]
-    jobs = [(name, c, 1) for c in chunks]
+    jobs = [(name, c, xmode, xidx) for c in chunks]
     res = [_ref_worker(j) for j in jobs] if (pool is None or procs == 1) else pool.map(_ref_worker, jobs)
     setup = statistics.mean(r[0] for r in res)
     tsum = sum(r[1] for r in res)
@@ -168,19 +199,98 @@ def reference_round(name: str, sample: int, procs: int, pool=None):
             "walks": int(sum(r[5] for r in res))}
 
 
+def _ref_dense_worker(args):
+    lo, hi = args
+    from oracle import oracle_py
+    inst = WORKLOADS["dense"][0]()
+    eng = oracle_py.ref() if oracle_py.have_ref() else oracle_py.orc()
+    # the reference's list order on a complete graph (small_ccs.cpp:18-43): u < x < y ascending, triangle {x, u, y}
+    tri = dense_triangles(DENSE_N, lo, hi)
+    nv, setup, scan = eng.small_cycle_scan_timed(inst, I.xstar_uniform(inst.m, seed=1), tri)
+    return setup, scan, hi - lo, nv
+
+
+def dense_triangles(c, lo, hi):
+    """triangles lo..hi-1 of computeSmallCCs' list on the complete graph K_c with adjacency in ascending order"""
+    out = np.empty((hi - lo, 3), np.int32)
+    k = 0
+    idx = 0
+    for u in range(c):
+        cnt_u = (c - 1 - u) * (c - 2 - u) // 2
+        if idx + cnt_u <= lo:
+            idx += cnt_u
+            continue
+        for x in range(u + 1, c):
+            cnt_x = c - 1 - x
+            if idx + cnt_x <= lo:
+                idx += cnt_x
+                continue
+            ys = np.arange(x + 1, c)
+            a, b = max(lo - idx, 0), min(hi - idx, cnt_x)
+            if b > a:
+                out[k:k + b - a, 0] = x
+                out[k:k + b - a, 1] = u
+                out[k:k + b - a, 2] = ys[a:b]
+                k += b - a
+            idx += cnt_x
+            if idx >= hi:
+                return out
+    return out
+
+
+def reference_dense_round(sample: int, procs: int, pool=None):
+    """the reference's TriangleSeparator on `sample` triangles of the dense workload, `procs` processes with a slice each;
+    round = the m updateWeights (once) + mean triangle cost x all triangles / procs"""
+    from oracle import oracle_py
+    T = DENSE_N * (DENSE_N - 1) * (DENSE_N - 2) // 6
+    sample = min(sample, T)
+    per = sample // procs
+    start = np.random.default_rng(7).integers(0, T - per, size=procs)
+    jobs = [(int(a), int(a) + per) for a in start]
+    res = [_ref_dense_worker(j) for j in jobs] if (pool is None or procs == 1) else pool.map(_ref_dense_worker, jobs)
+    setup = statistics.mean(r[0] for r in res)
+    mean = sum(r[1] for r in res) / sum(r[2] for r in res)
+    return {"seconds": setup + mean * T / procs, "setup_s": setup, "mean_triangle_s": mean, "triangles_timed": per * procs, "T": T,
+            "procs": procs, "kind": "reference" if oracle_py.have_ref() else "port"}
+
+
+def run_reference_arm_dense(args):
+    import multiprocessing as mp
+    procs = os.cpu_count() or 1
+    runs = []
+    with mp.get_context("spawn").Pool(procs) as pool:
+        for it in range(args.warmup + args.steps):
+            r = reference_dense_round(1_600_000, procs, pool)
+            if it >= args.warmup:
+                runs.append(r)
+    sec = statistics.mean(r["seconds"] for r in runs)
+    r0 = runs[-1]
+    line = {"impl": "reference", "metric": "triangle-inequality scans/sec (K6 rounds/s)", "value": 1.0 / sec, "unit": "rounds/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic", "config": {"workload": WORKLOADS["dense"][1], "name": "dense"},
+            "cpu_baseline": {"value": 1.0 / sec, "unit": "rounds/s", "cores": procs, "kind": r0["kind"],
+                             "sample": f"{r0['triangles_timed']} of {r0['T']} triangles per step over {procs} processes; round = {r0['setup_s'] * 1e3:.1f} ms "
+                                       f"(m updateWeights, once) + {r0['mean_triangle_s'] * 1e9:.0f} ns per triangle x {r0['T']} / {procs} cores"},
+            "e2e": {"value": 1.0 / sec, "unit": "rounds/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+    return 0
+
+
 def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
+    if args.workload == "dense":
+        return run_reference_arm_dense(args)
     import multiprocessing as mp
     procs = os.cpu_count() or 1
     sample = REF_SAMPLE[args.workload]
     ctx = mp.get_context("spawn")
     runs = []
     with ctx.Pool(procs) as pool:
-        pool.map(_ref_worker, [(args.workload, np.arange(2), 1)] * procs)  # page in the libraries once per worker
+        pool.map(_ref_worker, [(args.workload, np.arange(2), "fixed", 0)] * procs)  # page in the libraries once per worker
         for it in range(args.warmup + args.steps):
-            r = reference_round(args.workload, sample, procs, pool)
+            r = reference_round(args.workload, sample, procs, pool, args.xstar, max(it - args.warmup, 0))
             if it >= args.warmup:
                 runs.append(r)
     sec = statistics.mean(r["seconds"] for r in runs)
@@ -192,7 +302,7 @@ def run_reference_arm(args):
         "impl": "reference", "metric": "odd-cycle separation rounds/sec", "value": val, "unit": "rounds/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": WORKLOADS[args.workload][1], "name": args.workload,
+        "config": {"workload": WORKLOADS[args.workload][1] + XSTAR_NOTE[args.xstar], "name": args.workload, "xstar": args.xstar,
                    "mode": "V (the reference's own sequential sweep, conshdlr_oscw.cpp:188-195) within each process slice; "
                            "the GPU arm runs mode I (independent sources), which is MORE work (no source is skipped "
                            "because an earlier one blacklisted it)"},
@@ -244,18 +354,27 @@ def time_rounds(ctx, torch, dist, world, steps, warmup, step_fn, flush):
     return dt, per
 
 
+_INST = {}  # instances built once per process
+
+
 def measure_workload(name, args, torch, dist, rank, world, device, full=True):
     from sms_b200 import capi
-    inst = WORKLOADS[name][0]()
-    x = I.xstar_uniform(inst.m, seed=1)
+    if name not in _INST:
+        _INST[name] = WORKLOADS[name][0]()
+    inst = _INST[name]
+    xs = xstar_sequence(name, inst, getattr(args, "xstar", "fixed"), args.steps + args.warmup)
+    x = xs[0]
     bl = inst.root_blacklist()
+    os.environ.pop("SMSGPU_NO_HISTORY", None)
+    if getattr(args, "no_history", False):
+        os.environ["SMSGPU_NO_HISTORY"] = "1"  # read when the context is created
     ctx = capi.Context(inst.n, inst.rowptr, inst.col, inst.eid, device=device)
     if world > 1:
         uid = [ctx.nccl_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(uid, src=0)
         ctx.comm_init(uid[0], rank, world)
     ctx.set_sources(None, rank, world)
-    p = ctx.params(dedup=1)
+    p = ctx.params(dedup=1, mode=getattr(args, "mode", 0))
     import ctypes as C
     lib = ctx.lib
     # L2 flush buffer (> 126 MB), written between timed iterations
@@ -265,13 +384,16 @@ def measure_workload(name, args, torch, dist, rank, world, device, full=True):
         flush_buf.zero_()
 
     # ---- value leg: inputs resident in HBM, result left on the device ----
-    dx = torch.from_numpy(x).cuda()
+    dxs = [torch.from_numpy(v).cuda() for v in xs]
     dbl = torch.from_numpy(bl).cuda()
     torch.cuda.synchronize()
+    kstep = [0, 0]
     agg = {"ms_search": 0.0, "arcs": 0, "settled": 0, "launches": 0, "search_launches": 0, "n": 0, "ms_dev": 0.0,
            "ms_weights": 0.0, "ms_dedup": 0.0}
 
     def step_dev():
+        dx = dxs[kstep[0] % len(dxs)]
+        kstep[0] += 1
         ctx.set_round_input_device(dx.data_ptr(), dbl.data_ptr())
         ctx._check(lib.smsgpu_separate_async(ctx.h, C.byref(p)))
         return None
@@ -284,6 +406,11 @@ def measure_workload(name, args, torch, dist, rank, world, device, full=True):
         step_dev()
     torch.cuda.synchronize()
     sampler.wait_first()
+    kstep[0] = 0  # the timed steps walk through the sequence from its start
+    if len(xs) > 1:  # ... behind one round on its last entry, so that step 0 also meets the history of ANOTHER x*
+        kstep[0] = len(xs) - 1
+        step_dev()
+        kstep[0] = 0
     dt, _ = time_rounds(ctx, torch, dist, world, args.steps, 0, step_dev, flush)
     clocks = sampler.stop()
     # per-round device stats of the last round (events on the library's own stream)
@@ -310,7 +437,8 @@ def measure_workload(name, args, torch, dist, rank, world, device, full=True):
         hx, hbl = ctx.input_buffers()
 
         def step_host():
-            np.copyto(hx, x)
+            np.copyto(hx, xs[kstep[1] % len(xs)])
+            kstep[1] += 1
             np.copyto(hbl, bl)
             ctx.set_round_input(hx, hbl)
             if rank == 0:
@@ -342,6 +470,89 @@ def measure_workload(name, args, torch, dist, rank, world, device, full=True):
     return res
 
 
+def measure_dense(args, torch, device):
+    """K6: one triangle-inequality scan over all triangles of the dense workload per step"""
+    from sms_b200 import build, capi
+    inst = WORKLOADS["dense"][0]()
+    x = I.xstar_uniform(inst.m, seed=1)
+    ctx = capi.Context(inst.n, inst.rowptr, inst.col, inst.eid, device=device)
+    t0 = time.perf_counter()
+    T, _ = ctx.small_cycles_enumerate(False)  # scip_initsol: once per solve, not part of a round
+    t_enum = time.perf_counter() - t0
+    assert T == DENSE_N * (DENSE_N - 1) * (DENSE_N - 2) // 6
+    flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    dx = torch.from_numpy(x).cuda()
+    dbl = torch.zeros(inst.n, dtype=torch.uint8, device="cuda")
+    hx, hbl = ctx.input_buffers()
+    import ctypes as C
+    lib = ctx.lib
+    sampler = ClockSampler(device)
+    sampler.start()
+
+    def step_dev():  # x* resident, walks left on the device
+        ctx.set_round_input_device(dx.data_ptr(), dbl.data_ptr())
+        ctx._check(lib.smsgpu_small_cycles_scan_device(ctx.h, 3))
+
+    def step_host():  # x* from the host, walks back on the host
+        np.copyto(hx, x)
+        ctx.set_round_input(hx, hbl)
+        return ctx.small_cycles_scan_nocopy(3)
+
+    for _ in range(max(args.warmup, 3)):
+        flush_buf.zero_()
+        step_dev()
+    torch.cuda.synchronize()
+    sampler.wait_first()
+    ms_scan, ms_gather = [], []
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        flush_buf.zero_()
+        step_dev()
+        tm = ctx.small_cycles_timing()  # CUDA events on the library's stream (the scan call waits for the counts)
+        ms_scan.append(tm["ms_scan"])
+        ms_gather.append(tm["ms_gather"])
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    clocks = sampler.stop()
+    for _ in range(2):
+        flush_buf.zero_()
+        step_host()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        flush_buf.zero_()
+        U, N = step_host()
+    torch.cuda.synchronize()
+    dt2 = time.perf_counter() - t0
+    ctx.close()
+    peak, peak_src = peaks()
+    sec = dt / args.steps
+    k_scan = statistics.mean(ms_scan) * 1e-3
+    alg_scan = 12.0 * T + 8.0 * inst.m + 1.0 * T  # 3 edge ids per triangle + x* once + the code byte
+    out_bytes = U * (12 + 12 + 3 + 4 + 4 + 8 + 8)
+    line = {"metric": "triangle-inequality scans/sec (K6 rounds/s)", "value": 1.0 / sec, "unit": "rounds/s", "n_gpus": 1, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": WORKLOADS["dense"][1], "name": "dense", "n": inst.n, "m": inst.m, "triangles": T, "violated": U,
+                       "l2": "256 MiB buffer rewritten between timed iterations; the list itself is 12 B x T = %.0f MB" % (12.0 * T / 1e6),
+                       "enumeration_ms_once": t_enum * 1e3, "lib_source_hash": build.built_hash()},
+            "gtriangles_per_s": T / sec / 1e9,
+            "kernel_ms": {"scan": statistics.mean(ms_scan), "rank_and_gather": statistics.mean(ms_gather)},
+            "roofline": {"bound": "hbm", "kernel": "smallCycleScanKernel<3>", "achieved": alg_scan / k_scan / 1e9, "peak": peak, "unit": "GB/s",
+                         "frac": alg_scan / k_scan / 1e9 / peak, "traffic": None, "peak_source": peak_src, "algorithmic_bytes": alg_scan,
+                         "whole_scan": {"algorithmic_bytes": alg_scan + out_bytes, "note": "scan + rank + gather of the violated walks (51 B each out, 24 B each re-read)",
+                                        "achieved": (alg_scan + out_bytes) / ((statistics.mean(ms_scan) + statistics.mean(ms_gather)) * 1e-3) / 1e9}},
+            "e2e": {"value": args.steps / dt2, "unit": "rounds/s", "h2d_bytes_per_step": inst.m * 8 + inst.n, "d2h_bytes_per_step": int(out_bytes + 8)},
+            "gpu_launches": 6 * args.steps, "clocks": clocks}
+    if not args.no_cpu_baseline:
+        r = reference_dense_round(400_000, 1)
+        line["cpu_baseline"] = {"value": 1.0 / r["seconds"], "unit": "rounds/s", "cores": 1, "kind": r["kind"],
+                                "sample": f"{r['triangles_timed']} of {r['T']} triangles, 1 thread; round = {r['setup_s'] * 1e3:.1f} ms (m updateWeights, once) + "
+                                          f"{r['mean_triangle_s'] * 1e9:.0f} ns per triangle x {r['T']}"}
+    print(json.dumps(line))
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -349,6 +560,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--workload", default="random1m", choices=sorted(WORKLOADS))
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--xstar", default="fixed", choices=["fixed", "fresh", "replay"], help="x* of the timed steps (see xstar_sequence)")
+    ap.add_argument("--no-history", action="store_true", help="the engine forgets the previous round (issue order, tier decisions): every round is a first round")
+    ap.add_argument("--mode", type=int, default=0, choices=[0, 1], help="0: independent sources (default); 1: the reference's sequential sweep (SMSGPU_MODE_VERBATIM, 1 GPU)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extra", action="store_true", help="skip the secondary torus100 measurement")
     args = ap.parse_args()
@@ -371,12 +585,27 @@ def main():
 
     from sms_b200 import build
     build.build()
+    if args.workload == "dense":
+        if world > 1:
+            raise SystemExit("the dense (K6) workload is a single-GPU scan")
+        return measure_dense(args, torch, local)
     res = measure_workload(args.workload, args, torch, dist, rank, world, local, full=True)
     extra = {}
-    if world == 1 and not args.no_extra and args.workload != "torus100":
-        r2 = measure_workload("torus100", argparse.Namespace(steps=50, warmup=5), torch, dist, rank, world, local, full=True)
+    if world == 1 and not args.no_extra and args.workload == "random1m" and args.xstar == "fixed" and args.mode == 0 and not args.no_history:
+        # the same engine away from its best case (the headline feeds the SAME x* every step, so the previous round predicts
+        # the issue order and the tier of every source exactly): a new x* every step, and no memory of the previous round
+        ns = argparse.Namespace
+        r3 = measure_workload("random1m", ns(steps=3, warmup=3, xstar="fresh", no_history=False, mode=0), torch, dist, rank, world, local, full=False)
+        extra["random1m_new_xstar_every_step"] = {"rounds_per_s_device": 3 / r3["dt"], "ms_search_last": r3["ms_search"], "tier_sources_last": r3["stats"]["tier_sources"]}
+        r4 = measure_workload("random1m", ns(steps=3, warmup=3, xstar="fixed", no_history=True, mode=0), torch, dist, rank, world, local, full=False)
+        extra["random1m_no_history"] = {"rounds_per_s_device": 3 / r4["dt"], "ms_search_last": r4["ms_search"], "tier_sources_last": r4["stats"]["tier_sources"]}
+        r2 = measure_workload("torus100", ns(steps=50, warmup=5, xstar="fixed", no_history=False, mode=0), torch, dist, rank, world, local, full=True)
         extra["torus100"] = {"rounds_per_s_device": 50 / r2["dt"], "rounds_per_s_e2e": 50 / r2["e2e_dt"],
                              "ms_search": r2["ms_search"], "unique_cuts": r2["ncuts"], "arcs_scanned": r2["arcs"]}
+        if os.path.exists(os.path.join(ROOT, "tests", "golden", LPSEQ["torus100"])):
+            r5 = measure_workload("torus100", ns(steps=30, warmup=3, xstar="replay", no_history=False, mode=0), torch, dist, rank, world, local, full=True)
+            extra["torus100_lp_replay"] = {"workload": "100x100 torus" + XSTAR_NOTE["replay"] + ", 30 LP solves", "rounds_per_s_device": 30 / r5["dt"],
+                                           "rounds_per_s_e2e": 30 / r5["e2e_dt"], "ms_search_last": r5["ms_search"], "tier_sources_last": r5["stats"]["tier_sources"]}
     if len(set(res["cut_hashes"])) != 1:
         if rank == 0:
             print(f"bench.py: the ranks returned DIFFERENT cut lists: {res['cut_hashes']}", file=sys.stderr)
@@ -396,8 +625,12 @@ def main():
             "metric": "odd-cycle separation rounds/sec", "value": 1.0 / sec, "unit": "rounds/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": WORKLOADS[args.workload][1], "name": args.workload, "n": res["n"], "m": res["m"],
-                       "sources": res["n"], "mode": "I (independent sources), canonical ties, dedup on; twin sources (v,0)/(v,1) searched once when tie-free; issue order from the previous (warm-up) round",
+            "config": {"workload": WORKLOADS[args.workload][1] + XSTAR_NOTE[args.xstar], "name": args.workload, "xstar": args.xstar,
+                       "history": "off (every round is a first round)" if args.no_history else "on (issue order / tier decisions from the previous round)",
+                       "n": res["n"], "m": res["m"],
+                       "sources": res["n"],
+                       "mode": ("V (the reference's sequential sweep as a fixed point of stamped sweeps), canonical ties, dedup on" if args.mode == 1 else
+                                "I (independent sources), canonical ties, dedup on; twin sources (v,0)/(v,1) searched once when tie-free"),
                        "l2": "256 MiB buffer rewritten between timed iterations; arc array alone is 16 B x 2m",
                        "parallelism": f"source pairs cyclic over {world} GPU(s), graph replicated",
                        # blake2b-64 of the final (off, node, eid, is_stay, src) arrays; identical on every rank (checked:
@@ -411,7 +644,7 @@ def main():
             "unique_cuts": res["ncuts"],
             "kernel_ms": {"weights": res["ms_weights"], "search": res["ms_search"], "dedup_and_merge": res["ms_dedup"],
                           "device_total": res["ms_total_device"]},
-            "tier_sources": res["stats"]["tier_sources"],
+            "tier_sources": res["stats"]["tier_sources"], "verbatim_sweeps": int(res["stats"].get("verbatim_sweeps", 0)),
             "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                          "traffic": TRAFFIC_NCU.get(args.workload), "peak_source": peak_src,
                          "kernel": "ocwSearchPairsKernel (tier 1; tiers 0/2: ocwSearchKernel)",
@@ -425,8 +658,10 @@ def main():
             "clocks": res["clocks"],
             "extra": extra,
         }
+        if extra:  # the driver keeps `config`: the measurements away from the headline's best case travel with it
+            line["config"]["other_inputs"] = extra
         if world == 1 and not args.no_cpu_baseline:
-            r = reference_round(args.workload, min(REF_SAMPLE[args.workload], 1024), 1)
+            r = reference_round(args.workload, min(REF_SAMPLE[args.workload], 1024), 1, None, args.xstar, 0)
             line["cpu_baseline"] = {"value": 1.0 / r["seconds"], "unit": "rounds/s", "cores": 1, "kind": r["kind"],
                                     "sample": f"{r['sources_timed']} seeded sources of {r['n']}, 1 thread (the reference is single-threaded), mode V; "
                                               f"round = set-up {r['setup_s'] * 1e3:.1f} ms (once) + mean source {r['mean_source_s'] * 1e3:.4f} ms x {r['n']}",

@@ -168,8 +168,18 @@ int smsgpu_get_src_stats(smsgpu_ctx *ctx, int64_t *nsrc, const int64_t **arcs, c
  * in the order addTriangle / addFourHole received them.  The scan uses the x* of the last set_round_input and
  * returns walks in list order through smsgpu_get_small_cycle_cuts (same layout as smsgpu_cuts; src = list index). */
 int smsgpu_small_cycles_set(smsgpu_ctx *ctx, int k, int64_t T, const int32_t *cycles);
+/* The lists themselves, computed on the device: replaces SmallChordlessCycles::computeSmallCCs (src/graph/small_ccs.cpp:18-43,
+ * called from ConshdlrTriangles::scip_initsol, src/conshdlr/conshdlr_triangles.cpp:193-203, and ConshdlrHoles).  Triangles
+ * {x, u, y} and (want_holes) chordless four-cycles {x, u, y, z}, in the reference's list order; both lists are registered
+ * as smsgpu_small_cycles_set would.  smsgpu_small_cycles_get returns a host copy of a registered list. */
+int smsgpu_small_cycles_enumerate(smsgpu_ctx *ctx, int want_holes, int64_t *ntriangles, int64_t *nholes);
+int smsgpu_small_cycles_get(smsgpu_ctx *ctx, int k, int64_t *T, const int32_t **cycles);
 int smsgpu_small_cycles_scan(smsgpu_ctx *ctx, int k);
+int smsgpu_small_cycles_scan_device(smsgpu_ctx *ctx, int k); /* same, the walks stay on the device (bench "value" leg) */
 int smsgpu_get_small_cycle_cuts(smsgpu_ctx *ctx, int k, smsgpu_cuts *out);
+/* device times of the last scan (CUDA events on the context's stream): the scan kernel, the ranking + gather of the
+ * violated cycles, the device-to-host copy of the walks */
+int smsgpu_small_cycles_timing(smsgpu_ctx *ctx, double *ms_scan, double *ms_gather, double *ms_d2h);
 
 /* ---- multi-GPU: one context per GPU (one process per GPU under torchrun, or one thread per GPU inside a
  * single SCIP process).  After smsgpu_comm_init every smsgpu_separate ends with an NCCL all-gather of the

@@ -209,18 +209,24 @@ void *orc_small_cycle_scan(int64_t n, int64_t m, const int32_t *eu, const int32_
     std::vector<double> xc(x, x + m);
     for (auto &v : xc) v = std::min(std::max(0., v), 1.);
     std::vector<orc::Walk> out;
+    auto t0 = std::chrono::steady_clock::now();
     if (K == 3) {
         std::vector<std::array<int64_t, 3>> c(ncycles);
         for (int64_t i = 0; i < ncycles; ++i)
             for (int k = 0; k < 3; ++k) c[i][k] = cycles[3 * i + k];
+        t0 = std::chrono::steady_clock::now();
         out = orc::violatedSmallCycles<3>(g, c, xc);
     } else {
         std::vector<std::array<int64_t, 4>> c(ncycles);
         for (int64_t i = 0; i < ncycles; ++i)
             for (int k = 0; k < 4; ++k) c[i][k] = cycles[4 * i + k];
+        t0 = std::chrono::steady_clock::now();
         out = orc::violatedSmallCycles<4>(g, c, xc);
     }
-    return packWalks(out);
+    auto *r = packWalks(out);
+    r->secondsSources = r->seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    r->sourcesTimed = ncycles;
+    return r;
 }
 
 } // extern "C"

@@ -191,6 +191,14 @@ class _Lib:
                                         cycles.shape[0])
         return self._unpack(h, 0, False).walks()
 
+    def small_cycle_scan_timed(self, inst, x, cycles):
+        """(number of violated cycles, set-up seconds = the m updateWeights of a round, scan seconds)"""
+        cycles = _c(cycles, np.int32)
+        K = cycles.shape[1]
+        h = self._f("small_cycle_scan")(inst.n, inst.m, inst.eu, inst.ev, _c(x, np.float64), K, cycles.reshape(-1), cycles.shape[0])
+        s = self._unpack(h, 0, False)
+        return s.ncuts, s.timing[0], s.timing[1]
+
 
 def _c(a, dt):
     return np.ascontiguousarray(a, dtype=dt)

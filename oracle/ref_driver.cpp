@@ -29,6 +29,7 @@
 #include "sms/conshdlr/triangles.hpp"
 #include "sms/graph/small_ccs.hpp"
 
+#include <chrono>
 #include "sweep_common.hpp"
 
 namespace {
@@ -169,19 +170,41 @@ void *ref_small_cycle_scan(int64_t n, int64_t m, const int32_t *eu, const int32_
     std::vector<sms::OddClosedWalk> out;
     // Both separators construct an EMPTY weighted graph and rely on setWeight() inserting the edge
     // (NetworKit Graph::setWeight adds a missing edge, Graph.cpp:856-877).
+    // Timed like one round of the handler (conshdlr_triangles.cpp:86-93): the m updateWeights (set-up, once per round) and
+    // getViolated... (the scan); registering the list (scip_initsol) is not part of a round.
+    std::vector<double> xe(m);
+    for (int64_t e = 0; e < m; ++e) xe[e] = x[g.edgeId(eu[e], ev[e])];
+    double tSetup = 0, tScan = 0;
+    auto now = [] { return std::chrono::steady_clock::now(); };
+    auto secs = [](auto a, auto b) { return std::chrono::duration<double>(b - a).count(); };
     if (K == 3) {
         sms::TriangleSeparator ts(&g);
-        for (int64_t e = 0; e < m; ++e) ts.updateWeights(eu[e], ev[e], x[g.edgeId(eu[e], ev[e])]);
+        for (int64_t e = 0; e < m; ++e) ts.updateWeights(eu[e], ev[e], xe[e]); // inserts the edges
         for (int64_t i = 0; i < ncycles; ++i) ts.addTriangle(cycles[3 * i], cycles[3 * i + 1], cycles[3 * i + 2]);
+        auto t0 = now();
+        for (int64_t e = 0; e < m; ++e) ts.updateWeights(eu[e], ev[e], xe[e]);
+        auto t1 = now();
         out = ts.getViolatedTriangles();
+        tSetup = secs(t0, t1);
+        tScan = secs(t1, now());
     } else {
         sms::HoleSeparator hs(&g);
-        for (int64_t e = 0; e < m; ++e) hs.updateWeights(eu[e], ev[e], x[g.edgeId(eu[e], ev[e])]);
+        for (int64_t e = 0; e < m; ++e) hs.updateWeights(eu[e], ev[e], xe[e]);
         for (int64_t i = 0; i < ncycles; ++i)
             hs.addFourHole(cycles[4 * i], cycles[4 * i + 1], cycles[4 * i + 2], cycles[4 * i + 3]);
+        auto t0 = now();
+        for (int64_t e = 0; e < m; ++e) hs.updateWeights(eu[e], ev[e], xe[e]);
+        auto t1 = now();
         out = hs.getViolatedFourHoles();
+        tSetup = secs(t0, t1);
+        tScan = secs(t1, now());
     }
-    return packWalks(out);
+    auto *r = packWalks(out);
+    r->secondsSetup = tSetup;
+    r->secondsSources = tScan;
+    r->seconds = tSetup + tScan;
+    r->sourcesTimed = ncycles;
+    return r;
 }
 
 } // extern "C"

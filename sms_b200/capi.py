@@ -19,7 +19,7 @@ SYMBOLS = [
     "smsgpu_create", "smsgpu_destroy", "smsgpu_last_error", "smsgpu_abi_version", "smsgpu_default_params",
     "smsgpu_set_round_input", "smsgpu_input_buffers", "smsgpu_set_round_input_device", "smsgpu_set_sources", "smsgpu_separate",
     "smsgpu_separate_async", "smsgpu_fetch_cuts", "smsgpu_get_cuts", "smsgpu_get_stats", "smsgpu_get_labels",
-    "smsgpu_get_src_stats", "smsgpu_small_cycles_set", "smsgpu_small_cycles_scan", "smsgpu_get_small_cycle_cuts",
+    "smsgpu_get_src_stats", "smsgpu_small_cycles_set", "smsgpu_small_cycles_enumerate", "smsgpu_small_cycles_get", "smsgpu_small_cycles_scan", "smsgpu_small_cycles_scan_device", "smsgpu_get_small_cycle_cuts", "smsgpu_small_cycles_timing",
     "smsgpu_nccl_unique_id", "smsgpu_comm_init", "smsgpu_comm_destroy",
 ]
 
@@ -138,8 +138,12 @@ def load_library(path: str | None = None) -> C.CDLL:
     lib.smsgpu_get_src_stats.argtypes = [vp, C.POINTER(i64), C.POINTER(C.POINTER(i64)), C.POINTER(C.POINTER(i64)),
                                          C.POINTER(C.POINTER(C.c_int32))]
     lib.smsgpu_small_cycles_set.argtypes = [vp, i32, i64, vp]
+    lib.smsgpu_small_cycles_enumerate.argtypes = [vp, i32, C.POINTER(i64), C.POINTER(i64)]
+    lib.smsgpu_small_cycles_get.argtypes = [vp, i32, C.POINTER(i64), C.POINTER(C.POINTER(C.c_int32))]
     lib.smsgpu_small_cycles_scan.argtypes = [vp, i32]
+    lib.smsgpu_small_cycles_scan_device.argtypes = [vp, i32]
     lib.smsgpu_get_small_cycle_cuts.argtypes = [vp, i32, C.POINTER(CutsStruct)]
+    lib.smsgpu_small_cycles_timing.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)]
     lib.smsgpu_nccl_unique_id.argtypes = [vp]
     lib.smsgpu_comm_init.argtypes = [vp, vp, i32, i32]
     lib.smsgpu_comm_destroy.argtypes = [vp]
@@ -297,11 +301,35 @@ class Context:
         self._check(self.lib.smsgpu_small_cycles_set(self.h, k, c.shape[0] if c.ndim == 2 else 0, c.ctypes.data))
         return k
 
+    def small_cycles_enumerate(self, want_holes: bool = True):
+        """computeSmallCCs on the device; returns (number of triangles, number of four-holes); both lists are registered"""
+        nt, nh = C.c_int64(), C.c_int64()
+        self._check(self.lib.smsgpu_small_cycles_enumerate(self.h, 1 if want_holes else 0, C.byref(nt), C.byref(nh)))
+        return int(nt.value), int(nh.value)
+
+    def small_cycles_get(self, k: int) -> np.ndarray:
+        n = C.c_int64()
+        p = C.POINTER(C.c_int32)()
+        self._check(self.lib.smsgpu_small_cycles_get(self.h, k, C.byref(n), C.byref(p)))
+        return _arr(p, int(n.value) * k, np.int32).reshape(-1, k)
+
     def small_cycles_scan(self, k: int) -> Cuts:
         self._check(self.lib.smsgpu_small_cycles_scan(self.h, k))
         cs = CutsStruct()
         self._check(self.lib.smsgpu_get_small_cycle_cuts(self.h, k, C.byref(cs)))
         return _cuts_from_struct(cs)
+
+    def small_cycles_scan_nocopy(self, k: int):
+        """the scan through the C ABI without building numpy copies (bench); returns (violated cycles, walk nodes)"""
+        self._check(self.lib.smsgpu_small_cycles_scan(self.h, k))
+        cs = CutsStruct()
+        self._check(self.lib.smsgpu_get_small_cycle_cuts(self.h, k, C.byref(cs)))
+        return int(cs.ncuts), int(cs.nnodes)
+
+    def small_cycles_timing(self):
+        a, b, c = C.c_double(), C.c_double(), C.c_double()
+        self._check(self.lib.smsgpu_small_cycles_timing(self.h, C.byref(a), C.byref(b), C.byref(c)))
+        return {"ms_scan": a.value, "ms_gather": b.value, "ms_d2h": c.value}
 
     # ---- multi GPU ----
     def nccl_unique_id(self) -> bytes:

@@ -13,15 +13,18 @@ namespace smsgpu {
 // and folds the round's blacklist (ocw_seperator.hpp:25-28) into the arc.  One thread per 4 consecutive arcs:
 // 128-bit loads of col / eid, four 128-bit stores.
 __global__ void __launch_bounds__(256) dcWeightsKernel(const long long narcs, const int32_t *__restrict__ col,
-                                                       const int32_t *__restrict__ eid, const double *__restrict__ x,
-                                                       const uint8_t *__restrict__ bl, Arc *__restrict__ arcs) {
+                                                       const int32_t *__restrict__ eid, const uint32_t *__restrict__ rowpack,
+                                                       const double *__restrict__ x, const uint8_t *__restrict__ bl,
+                                                       Arc *__restrict__ arcs) {
     const long long nquads = narcs >> 2;
     const long long stride = (long long)gridDim.x * blockDim.x;
     for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < nquads; q += stride) {
         const int4 c = reinterpret_cast<const int4 *>(col)[q];
         const int4 e = reinterpret_cast<const int4 *>(eid)[q];
+        const uint4 r = reinterpret_cast<const uint4 *>(rowpack)[q];
         const int cs[4] = {c.x, c.y, c.z, c.w};
         const int es[4] = {e.x, e.y, e.z, e.w};
+        const uint32_t rs[4] = {r.x, r.y, r.z, r.w};
         double ws[4];
         int bs[4];
 #pragma unroll
@@ -33,7 +36,7 @@ __global__ void __launch_bounds__(256) dcWeightsKernel(const long long narcs, co
         for (int k = 0; k < 4; ++k) {
             Arc a;
             a.nbr = cs[k] | (bs[k] ? (int32_t)0x80000000 : 0);
-            a.eid = es[k];
+            a.row = rs[k];
             a.w = clamp01(ws[k]);
             arcs[4 * q + k] = a;
         }
@@ -44,8 +47,8 @@ __global__ void __launch_bounds__(256) dcWeightsKernel(const long long narcs, co
         Arc a;
         const int c = col[t];
         a.nbr = c | (bl[c] ? (int32_t)0x80000000 : 0);
-        a.eid = eid[t];
-        a.w = clamp01(x[a.eid]);
+        a.row = rowpack[t];
+        a.w = clamp01(x[eid[t]]);
         arcs[t] = a;
     }
 }

@@ -48,6 +48,7 @@ struct PairsParams {
     float scaleU;         // bucket map: u = (float)dist * scaleU; 0 selects the linear map
     float scaleB;         // bucket = (2^u - 1) * scaleB   (linear map: dist * scaleB)
     int mirror;           // 1: twin sources (v,0)/(v,1) are searched once when no id tie-break occurred
+    uint32_t rowShift;    // Arc::row = first arc | degree << rowShift; a saturated degree field means "read rowinfo"
 };
 
 // The per-source working memory (label table, predecessors, queue) is touched once or twice per source and is far
@@ -594,12 +595,13 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
             }
             const double best0 = best; // conservative (>= the running value) for pruning / queue admission
             bool act = run && (c0 + tl < dg);
-            uint32_t nbr = 0;
+            uint32_t nbr = 0, rowp = 0;
             double w = 0.0;
             uint2 nrow = make_uint2(0u, 0u);
             if (act) {
                 const Arc arc = G.arcs[rb + c0 + tl];
                 nbr = (uint32_t)arc.nbr & 0x7FFFFFFFu;
+                rowp = arc.row;
                 w = arc.w;
                 act = arc.nbr >= 0;    // blacklisted neighbours are skipped (:98-99)
                 if (G.blStamp && act) act = !stampedBefore(G, nbr, nowIdx); // mode V: blacklisted by an earlier source
@@ -754,8 +756,12 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
             PCLK(6);
             // ---- store the label, retire superseded keys, push the new ones ---------------------------------------
             bool ovf = false, dirty = false;
-            // the row of the neighbour travels with its key: one 8-byte read per PUSHING lane (about one per settled node)
-            if ((accS && 2 * dS <= best0) || (accX && 2 * dX <= best0)) nrow = Q.rowinfo[nbr];
+            // the row of the neighbour travels with its key; it came with the arc (Arc::row), the row record is read only
+            // when the degree did not fit the packed field
+            if ((accS && 2 * dS <= best0) || (accX && 2 * dX <= best0)) {
+                nrow = make_uint2(rowp & ((1u << Q.rowShift) - 1u), rowp >> Q.rowShift);
+                if (nrow.y == (0xFFFFFFFFu >> Q.rowShift)) nrow = Q.rowinfo[nbr];
+            }
             if (accS || accX) {
                 if (hNew >= 0xFFFFu) ovf = true; // hops share a word with the queue position in this engine
 #pragma unroll

@@ -19,11 +19,14 @@ namespace smsgpu {
 // One CSR adjacency entry in HBM, rebuilt every round by K1 (dc_weights): 16 B, one 128-bit load per arc scan.
 //   nbr : neighbour's original vertex id, bit 31 set when the neighbour is blacklisted this round
 //         (folds the `if (blacklist_[neighbor]) continue` of ocw_seperator.cpp:98-99 into the arc)
-//   eid : NetworKit edge id
+//   row : the NEIGHBOUR's adjacency row, packed: first arc | degree << rowShift (degree saturates at the field's
+//         maximum, which then means "read the row record").  A relaxation that pushes the neighbour into the queue
+//         needs its row for the queue entry; carried by the arc it costs no dependent load (pairs engine).
 //   w   : stay weight = clamp(x*[eid], 0, 1) (ocw_seperator.cpp:25-35); the cross weight 1.0 - w is computed
+// The NetworKit edge id of the arc is needed only when a walk is written out; it lives in GraphDev::eid.
 struct __align__(16) Arc {
     int32_t nbr;
-    int32_t eid;
+    uint32_t row;
     double w;
 };
 
@@ -59,6 +62,7 @@ struct GraphDev {
     int64_t n, m;
     const int64_t *rowptr; // n+1
     const Arc *arcs;       // 2m, adjacency order of the reference graph
+    const int32_t *eid;    // 2m, NetworKit edge id of every adjacency entry (walk output only)
     // SMSGPU_MODE_VERBATIM only (all three null in independent-source mode): the reference's blacklist as a function of
     // time.  stamp[v] = position in the source list of the FIRST source that blacklists v (-1: blacklisted from the
     // start, kNeverStamp: never); the source at position `now` sees v blacklisted iff stamp[v] < now.

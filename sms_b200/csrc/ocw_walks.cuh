@@ -228,7 +228,7 @@ __device__ inline void extractCycles(const GraphDev &G, TileMem &M, SrcState &S,
         if (cs || ce) continue;
         const bool crossing = ch[3] & 1, inner = (ch[3] & 2) != 0;
         const long long ca = (long long)((uint32_t)ch[3] >> 2);
-        const int32_t chordEid = G.arcs[ca].eid;
+        const int32_t chordEid = G.eid[ca];
         const int wlen = ch[2];
         long long cut, off;
         const bool ok = emitReserve(E, wlen, cut, off);
@@ -248,12 +248,12 @@ __device__ inline void extractCycles(const GraphDev &G, TileMem &M, SrcState &S,
             pos++;
         };
         if (inner) {
-            for (int k = start; k < end; ++k) put(c[k], G.arcs[warc[k + 1]].eid, st[k]);
+            for (int k = start; k < end; ++k) put(c[k], G.eid[warc[k + 1]], st[k]);
             put(c[end], chordEid, crossing ? 0 : 1);
         } else {
-            for (int k = 0; k < start; ++k) put(c[k], G.arcs[warc[k + 1]].eid, st[k]);
+            for (int k = 0; k < start; ++k) put(c[k], G.eid[warc[k + 1]], st[k]);
             put(c[start], chordEid, crossing ? 0 : 1);
-            for (int k = end; k < len; ++k) put(c[k], G.arcs[warc[k + 1]].eid, st[k]);
+            for (int k = end; k < len; ++k) put(c[k], G.eid[warc[k + 1]], st[k]);
         }
         if (ncov > covCap) {
             S.overflow = 1;
@@ -266,7 +266,7 @@ __device__ inline void extractCycles(const GraphDev &G, TileMem &M, SrcState &S,
         if (emitReserve(E, len, cut, off))
             for (int k = 0; k < len; ++k) {
                 E.R->node[off + k] = c[k];
-                E.R->eid[off + k] = G.arcs[warc[k + 1]].eid;
+                E.R->eid[off + k] = G.eid[warc[k + 1]];
                 E.R->stay[off + k] = (uint8_t)st[k];
             }
     }

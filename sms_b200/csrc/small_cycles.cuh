@@ -32,16 +32,10 @@ __global__ void __launch_bounds__(256) resolveCycleEidsKernel(const long long T,
     }
 }
 
-// flag[t] = 1 if violated; stayMask[t] bit i = edge i (nodes[i] -> nodes[i+1 mod K]) is a stay edge
+// violatedOddSelectionClosedWalk (src/graph/odd_closed_walk.cpp:8-65) on the K clamped weights of one cycle.
+// Returns 0 when the cycle yields no violated inequality, else 0x80 | stay mask (bit i: edge i is a stay edge).
 template <int K>
-__global__ void __launch_bounds__(256) smallCycleScanKernel(const long long T, const int32_t *__restrict__ eids,
-                                                            const double *__restrict__ x, int32_t *__restrict__ flag,
-                                                            uint8_t *__restrict__ stayMask, double *__restrict__ viol) {
-    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= T) return;
-    double w[K];
-#pragma unroll
-    for (int i = 0; i < K; ++i) w[i] = clamp01(__ldg(x + eids[K * t + i]));
+__device__ __forceinline__ unsigned oddSelectionCode(const double (&w)[K], double &length) {
     double curLength = 0;
     unsigned cross = 0;
     double lightestCross = 1, heaviestStay = 0;
@@ -75,43 +69,225 @@ __global__ void __launch_bounds__(256) smallCycleScanKernel(const long long T, c
         else
             none = true;
     }
-    flag[t] = none ? 0 : 1;
-    if (!none) {
-        stayMask[t] = (uint8_t)(~cross & ((1u << K) - 1u));
-        double len = 0;
+    if (none) return 0u;
+    double len = 0;
 #pragma unroll
-        for (int i = 0; i < K; ++i) len += ((cross >> i) & 1u) ? 1 - w[i] : w[i];
-        viol[t] = 1.0 - len;
+    for (int i = 0; i < K; ++i) len += ((cross >> i) & 1u) ? 1 - w[i] : w[i];
+    length = len;
+    return 0x80u | (~cross & ((1u << K) - 1u));
+}
+
+// The scan is two passes over the list, kSmallTile cycles per CTA:
+//   pass 1  K edge ids in (12 / 16 B per cycle, the only mandatory traffic), K gathers of x* (L2 resident), ONE code byte
+//           out per cycle and one count per CTA;
+//   (exclusive scan of the per-CTA counts: T / 1024 words)
+//   pass 2  re-reads the code bytes, ranks the violated cycles inside the CTA (list order) and writes their walks.
+constexpr int kSmallBlock = 256, kSmallItems = 4, kSmallTile = kSmallBlock * kSmallItems;
+
+template <int K>
+__global__ void __launch_bounds__(kSmallBlock) smallCycleScanKernel(const long long T, const int32_t *__restrict__ eids,
+                                                                    const double *__restrict__ x, uint8_t *__restrict__ code,
+                                                                    int32_t *__restrict__ tileCount) {
+    const long long base = (long long)blockIdx.x * kSmallTile;
+    int mine = 0;
+#pragma unroll
+    for (int it = 0; it < kSmallItems; ++it) {
+        const long long t = base + it * kSmallBlock + threadIdx.x;
+        if (t >= T) continue;
+        double w[K];
+#pragma unroll
+        for (int i = 0; i < K; ++i) w[i] = clamp01(__ldg(x + eids[K * t + i]));
+        double len;
+        const unsigned c = oddSelectionCode<K>(w, len);
+        code[t] = (uint8_t)c;
+        mine += c ? 1 : 0;
+    }
+    // CTA total
+    __shared__ int warpSum[kSmallBlock / 32];
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) mine += __shfl_xor_sync(0xFFFFFFFFu, mine, off);
+    if ((threadIdx.x & 31) == 0) warpSum[threadIdx.x >> 5] = mine;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int tot = 0;
+#pragma unroll
+        for (int k = 0; k < kSmallBlock / 32; ++k) tot += warpSum[k];
+        tileCount[blockIdx.x] = tot;
     }
 }
 
 template <int K>
-__global__ void __launch_bounds__(256) smallCycleGatherKernel(const long long T, const int32_t *__restrict__ nodes,
-                                                              const int32_t *__restrict__ eids,
-                                                              const int32_t *__restrict__ flag,
-                                                              const uint8_t *__restrict__ stayMask,
-                                                              const double *__restrict__ viol,
-                                                              const long long *__restrict__ pos, int32_t *oNode,
-                                                              int32_t *oEid, uint8_t *oStay, int32_t *oNcross, int32_t *oSrc,
-                                                              double *oViol, long long *oOff) {
-    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= T || !flag[t]) return;
-    const long long k = pos[t];
-    const unsigned sm = stayMask[t];
-    int nc = 0;
+__global__ void __launch_bounds__(kSmallBlock) smallCycleGatherKernel(const long long T, const int32_t *__restrict__ nodes,
+                                                                      const int32_t *__restrict__ eids,
+                                                                      const double *__restrict__ x, const uint8_t *__restrict__ code,
+                                                                      const long long *__restrict__ tileBase, int32_t *oNode,
+                                                                      int32_t *oEid, uint8_t *oStay, int32_t *oNcross, int32_t *oSrc,
+                                                                      double *oViol, long long *oOff) {
+    __shared__ int warpSum[kSmallBlock / 32];
+    __shared__ int carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    const long long base = (long long)blockIdx.x * kSmallTile;
+    const long long out0 = tileBase[blockIdx.x];
+    const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
+    for (int it = 0; it < kSmallItems; ++it) {
+        const long long t = base + it * kSmallBlock + threadIdx.x;
+        const unsigned c = t < T ? code[t] : 0u;
+        const int v = c ? 1 : 0;
+        int incl = v;
 #pragma unroll
-    for (int i = 0; i < K; ++i) {
-        oNode[K * k + i] = nodes[K * t + i];
-        oEid[K * k + i] = eids[K * t + i];
-        const int s = (sm >> i) & 1u;
-        oStay[K * k + i] = (uint8_t)s;
-        nc += 1 - s;
+        for (int off = 1; off < 32; off <<= 1) {
+            const int a = __shfl_up_sync(0xFFFFFFFFu, incl, off);
+            if (lane >= off) incl += a;
+        }
+        if (lane == 31) warpSum[wrp] = incl;
+        __syncthreads();
+        int before = carry;
+        for (int k = 0; k < wrp; ++k) before += warpSum[k];
+        if (v) {
+            const long long k = out0 + before + incl - 1;
+            const unsigned sm = c & 0x7Fu;
+            int nc = 0;
+            double w[K];
+#pragma unroll
+            for (int i = 0; i < K; ++i) {
+                const int32_t e = eids[K * t + i];
+                w[i] = clamp01(__ldg(x + e));
+                oNode[K * k + i] = nodes[K * t + i];
+                oEid[K * k + i] = e;
+                const int s = (sm >> i) & 1u;
+                oStay[K * k + i] = (uint8_t)s;
+                nc += 1 - s;
+            }
+            double len = 0; // same summation order as the scan's
+#pragma unroll
+            for (int i = 0; i < K; ++i) len += ((sm >> i) & 1u) ? w[i] : 1 - w[i];
+            oNcross[k] = nc;
+            oSrc[k] = (int32_t)t;
+            oViol[k] = 1.0 - len;
+            oOff[k] = (long long)K * k;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            int tot = 0;
+#pragma unroll
+            for (int k = 0; k < kSmallBlock / 32; ++k) tot += warpSum[k];
+            carry += tot;
+        }
+        __syncthreads();
     }
-    oNcross[k] = nc;
-    oSrc[k] = (int32_t)t;
-    oViol[k] = viol[t];
-    oOff[k] = (long long)K * k;
-    if (k == pos[T] - 1) oOff[k + 1] = (long long)K * (k + 1);
+}
+// oOff[U] = K * U
+__global__ void smallCycleTailKernel(long long *oOff, const long long U, const int K) { oOff[U] = (long long)K * U; }
+
+// ---- enumeration: replaces SmallChordlessCycles::computeSmallCCs (src/graph/small_ccs.cpp:18-43) -----------------------
+//   for u ascending, for x in adj(u) with x > u, for y in adj(u) with y > x (both in adjacency order):
+//     hasEdge(x, y)  -> triangle {x, u, y}
+//     else for z in adj(x) (adjacency order) with z > u and !hasEdge(u, z): hasEdge(z, y) -> four-hole {x, u, y, z}
+// The reference's list order is therefore lexicographic in (arc index of (u, x), position of y, position of z), and
+// the arc index is the unit of work: one WARP per arc, lanes over the positions of y, 32 at a time, in order.  Two
+// passes with the same traversal: COUNT (per arc, then an exclusive scan gives every arc its slice of the two lists)
+// and FILL.  hasEdge is a binary search in a per-row SORTED copy of the adjacency (the reference scans the row).
+__device__ __forceinline__ bool sortedHasEdge(const long long *__restrict__ rowptr, const int32_t *__restrict__ colSorted,
+                                              const int32_t u, const int32_t v) {
+    long long lo = rowptr[u], hi = rowptr[u + 1];
+    while (lo < hi) {
+        const long long mid = (lo + hi) >> 1;
+        const int32_t c = colSorted[mid];
+        if (c == v) return true;
+        if (c < v)
+            lo = mid + 1;
+        else
+            hi = mid;
+    }
+    return false;
+}
+
+template <bool FILL>
+__global__ void __launch_bounds__(256) enumerateSmallCyclesKernel(const long long narcs, const int32_t *__restrict__ arcSrc,
+                                                                  const long long *__restrict__ rowptr,
+                                                                  const int32_t *__restrict__ col,
+                                                                  const int32_t *__restrict__ colSorted,
+                                                                  int32_t *__restrict__ triCount, int32_t *__restrict__ holeCount,
+                                                                  const long long *__restrict__ triBase,
+                                                                  const long long *__restrict__ holeBase,
+                                                                  int32_t *__restrict__ tri, int32_t *__restrict__ holes,
+                                                                  const int wantHoles) {
+    const int lane = threadIdx.x & 31;
+    const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+    for (long long ai = warp; ai < narcs; ai += nwarps) {
+        const int32_t u = arcSrc[ai], x = col[ai];
+        if (x <= u) {
+            if (!FILL && lane == 0) {
+                triCount[ai] = 0;
+                holeCount[ai] = 0;
+            }
+            continue;
+        }
+        long long tpos = FILL ? triBase[ai] : 0, hpos = FILL ? holeBase[ai] : 0;
+        int tsum = 0, hsum = 0;
+        const long long ub = rowptr[u], ue = rowptr[u + 1], xb = rowptr[x], xe = rowptr[x + 1];
+        for (long long b0 = ub; b0 < ue; b0 += 32) {
+            const long long b = b0 + lane;
+            const int32_t y = b < ue ? col[b] : -1;
+            int t = 0, h = 0;
+            bool isTri = false;
+            if (y > x) {
+                isTri = sortedHasEdge(rowptr, colSorted, x, y);
+                if (isTri) {
+                    t = 1;
+                } else if (wantHoles) {
+                    for (long long c = xb; c < xe; ++c) {
+                        const int32_t z = col[c];
+                        if (z <= u || sortedHasEdge(rowptr, colSorted, u, z)) continue;
+                        if (sortedHasEdge(rowptr, colSorted, z, y)) ++h;
+                    }
+                }
+            }
+            // exclusive prefix over the lanes: this lane's slice inside the chunk
+            int tp = t, hp = h;
+#pragma unroll
+            for (int off = 1; off < 32; off <<= 1) {
+                const int a = __shfl_up_sync(0xFFFFFFFFu, tp, off), c = __shfl_up_sync(0xFFFFFFFFu, hp, off);
+                if (lane >= off) {
+                    tp += a;
+                    hp += c;
+                }
+            }
+            const int ttot = __shfl_sync(0xFFFFFFFFu, tp, 31), htot = __shfl_sync(0xFFFFFFFFu, hp, 31);
+            if (FILL) {
+                if (isTri) {
+                    const long long o = 3 * (tpos + tp - t);
+                    tri[o] = x;
+                    tri[o + 1] = u;
+                    tri[o + 2] = y;
+                } else if (h > 0) {
+                    long long o = 4 * (hpos + hp - h);
+                    for (long long c = xb; c < xe; ++c) {
+                        const int32_t z = col[c];
+                        if (z <= u || sortedHasEdge(rowptr, colSorted, u, z)) continue;
+                        if (sortedHasEdge(rowptr, colSorted, z, y)) {
+                            holes[o] = x;
+                            holes[o + 1] = u;
+                            holes[o + 2] = y;
+                            holes[o + 3] = z;
+                            o += 4;
+                        }
+                    }
+                }
+                tpos += ttot;
+                hpos += htot;
+            } else {
+                tsum += ttot;
+                hsum += htot;
+            }
+        }
+        if (!FILL && lane == 0) {
+            triCount[ai] = tsum;
+            holeCount[ai] = hsum;
+        }
+    }
 }
 
 } // namespace smsgpu

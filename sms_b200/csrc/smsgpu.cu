@@ -123,6 +123,8 @@ struct smsgpu_ctx {
     DevBuf dRowptr, dCol, dEid, dArcs;
     DevBuf dPairsArgs;        // PairsKArgs of the launch in flight
     DevBuf dRowinfo;          // uint2[n] {first arc, degree}: pairs engine (tier 1)
+    DevBuf dRowpack;          // uint32[2m] Arc::row of every adjacency entry (static; K1 copies it into the arc records)
+    uint32_t rowShift = 31;   // Arc::row = first arc | degree << rowShift
     bool pairs = false;       // tier 1 runs the pairs engine (ocw_search_pairs.cuh)
     float pairsScaleU = 0.f;  // bucket map of the pairs engine (PairsParams)
     float pairsScaleB = 0.f;
@@ -174,11 +176,18 @@ struct smsgpu_ctx {
     bool haveLabels = false, haveSrcStats = false;
 
     // small cycles (k = 3, 4)
-    DevBuf scNodes[2], scEids[2], scFlag[2], scStay[2];
+    DevBuf scNodes[2], scEids[2], scCode;
+    cudaEvent_t scEv[4]{};
+    double scMs[3] = {0, 0, 0}; // last scan: scan kernel, (count scan +) gather kernels, D2H of the walks
     long long scCount[2] = {0, 0};
     CutListHost scHost[2];
     CutListDev scFin;
-    PinBuf scTmp;
+    PinBuf scTmp, scListHost[2];
+    // enumeration of the small cycles (smsgpu_small_cycles_enumerate)
+    std::vector<int64_t> hRowptr; // host copy of the CSR (enumeration set-up)
+    std::vector<int32_t> hCol;
+    DevBuf dArcSrc, dColSorted, eHoleBase;
+    bool enumReady = false;
 
     smsgpu_params lastParams{};
     smsgpu_stats stats{};
@@ -272,7 +281,7 @@ cudaError_t launchSearch(smsgpu_ctx *c, int tierIdx, const GraphDev &G, const Se
         if (e != cudaSuccess) return e;
         e = cudaMemcpyAsync(c->dPairsArgs.p, &K, sizeof K, cudaMemcpyHostToDevice, st); // pageable source: staged before return
         if (e != cudaSuccess) return e;
-        const PairsParams Q{c->dPairsArgs.as<PairsKArgs>(), c->dRowinfo.as<uint2>(), c->pairsScaleU, c->pairsScaleB, c->pairsMirror ? 1 : 0};
+        const PairsParams Q{c->dPairsArgs.as<PairsKArgs>(), c->dRowinfo.as<uint2>(), c->pairsScaleU, c->pairsScaleB, c->pairsMirror ? 1 : 0, c->rowShift};
         ocwSearchPairsKernel<<<ctas, 128, t.smemBytes, st>>>(G, Q, P, R, t.caps, t.scratch.as<unsigned char>());
         return cudaGetLastError();
     }
@@ -436,6 +445,8 @@ int smsgpu_create(smsgpu_ctx **out, int64_t n, int64_t m, const int64_t *rowptr,
     ctx->device = device;
     ctx->n = n;
     ctx->m = m;
+    ctx->hRowptr.assign(rowptr, rowptr + n + 1);
+    ctx->hCol.assign(col, col + 2 * m);
     auto bail = [&](int code) {
         g_createError = ctx->err;
         smsgpu_destroy(ctx);
@@ -461,6 +472,7 @@ int smsgpu_create(smsgpu_ctx **out, int64_t n, int64_t m, const int64_t *rowptr,
     CUB(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
     for (auto &e : ctx->ev) CUB(cudaEventCreate(&e));
     for (auto &e : ctx->tierEv) CUB(cudaEventCreate(&e));
+    for (auto &e : ctx->scEv) CUB(cudaEventCreate(&e));
     {
         int prLow = 0, prHigh = 0; // its CTAs take free SM slots before tier 1's
         CUB(cudaDeviceGetStreamPriorityRange(&prLow, &prHigh));
@@ -477,6 +489,22 @@ int smsgpu_create(smsgpu_ctx **out, int64_t n, int64_t m, const int64_t *rowptr,
     if (m > 0) {
         CUB(cudaMemcpyAsync(ctx->dCol.p, col, (size_t)2 * m * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
         CUB(cudaMemcpyAsync(ctx->dEid.p, eid, (size_t)2 * m * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
+    }
+    {
+        // Arc::row of every adjacency entry: the neighbour's first arc in the low rowShift bits, its degree above
+        // (saturated: the all-ones field sends the reader to the row record)
+        uint32_t shift = 1;
+        while (shift < 31 && (1ll << shift) < std::max<int64_t>(2 * m, 2)) ++shift;
+        ctx->rowShift = shift;
+        const uint32_t degMax = 0xFFFFFFFFu >> shift;
+        std::vector<uint32_t> rp((size_t)std::max<int64_t>(2 * m, 4), 0u);
+        for (int64_t a = 0; a < 2 * m; ++a) {
+            const int64_t v = col[a];
+            const uint64_t deg = (uint64_t)(rowptr[v + 1] - rowptr[v]);
+            rp[(size_t)a] = (uint32_t)rowptr[v] | ((uint32_t)std::min<uint64_t>(deg, degMax) << shift);
+        }
+        CUB(ctx->dRowpack.ensure(rp.size() * sizeof(uint32_t)));
+        CUB(cudaMemcpy(ctx->dRowpack.p, rp.data(), rp.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
     }
     CUB(ctx->dX.ensure((size_t)std::max<int64_t>(m, 1) * sizeof(double)));
     CUB(ctx->dBl.ensure((size_t)n));
@@ -516,6 +544,31 @@ int smsgpu_create(smsgpu_ctx **out, int64_t n, int64_t m, const int64_t *rowptr,
             }
         }
     }
+    // The arc records are the one array every search shares; everything else the searches touch is private working memory
+    // that streams through L2 once or twice.  With SMSGPU_L2_PERSIST=1 the arc array gets an access-policy window with
+    // the persisting property on both streams (as much of it as the device lets persist), so that the streaming
+    // working-memory traffic cannot evict it.  Off by default: the carve-out is a device-wide limit.
+    if (const char *ep = std::getenv("SMSGPU_L2_PERSIST")) {
+        if (ep[0] == '1' && m > 0) {
+            const size_t arcBytes = (size_t)2 * m * sizeof(Arc);
+            const size_t persist = std::min<size_t>((size_t)prop.persistingL2CacheMaxSize, arcBytes);
+            const size_t window = std::min<size_t>((size_t)prop.accessPolicyMaxWindowSize, arcBytes);
+            if (persist > 0 && window > 0) {
+                CUB(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, persist));
+                cudaStreamAttrValue av{};
+                av.accessPolicyWindow.base_ptr = ctx->dArcs.p;
+                av.accessPolicyWindow.num_bytes = window;
+                av.accessPolicyWindow.hitRatio = (float)std::min(1.0, (double)persist / (double)window);
+                av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+                av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+                CUB(cudaStreamSetAttribute(ctx->stream, cudaStreamAttributeAccessPolicyWindow, &av));
+                CUB(cudaStreamSetAttribute(ctx->stream2, cudaStreamAttributeAccessPolicyWindow, &av));
+                if (std::getenv("SMSGPU_DEBUG_OVF"))
+                    std::fprintf(stderr, "[smsgpu] L2 persisting window: %zu of %zu arc bytes (L2 %d MB, max persisting %d MB, max window %d MB)\n",
+                                 persist, arcBytes, prop.l2CacheSize >> 20, prop.persistingL2CacheMaxSize >> 20, prop.accessPolicyMaxWindowSize >> 20);
+            }
+        }
+    }
     if (const char *eh = std::getenv("SMSGPU_NO_HISTORY")) ctx->useHistory = !(eh[0] == '1');
     if (const char *eo = std::getenv("SMSGPU_NO_OVERLAP")) ctx->overlapHeavy = !(eo[0] == '1');
     configureTiers(ctx);
@@ -533,7 +586,7 @@ void smsgpu_destroy(smsgpu_ctx *ctx) {
     smsgpu_comm_destroy(ctx);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     if (ctx->stream2) cudaStreamSynchronize(ctx->stream2);
-    DevBuf *dev[] = {&ctx->dPairsArgs, &ctx->dRowinfo, &ctx->dRowptr, &ctx->dCol, &ctx->dEid, &ctx->dArcs, &ctx->dX, &ctx->dBl, &ctx->dSources,
+    DevBuf *dev[] = {&ctx->dPairsArgs, &ctx->dRowinfo, &ctx->dRowpack, &ctx->dRowptr, &ctx->dCol, &ctx->dEid, &ctx->dArcs, &ctx->dX, &ctx->dBl, &ctx->dSources,
                      &ctx->tier[0].scratch, &ctx->tier[1].scratch, &ctx->tier[2].scratch, &ctx->tier[3].scratch, &ctx->rNode, &ctx->rEid,
                      &ctx->rStay, &ctx->rCutOff, &ctx->rCutLen, &ctx->rCutSrc, &ctx->rCutSeq, &ctx->rCutTier, &ctx->rValid,
                      &ctx->labSrc, &ctx->labNode, &ctx->labHops, &ctx->labDist, &ctx->srcTier, &ctx->srcArcs,
@@ -543,13 +596,13 @@ void smsgpu_destroy(smsgpu_ctx *ctx) {
                      &ctx->wBlockSums, &ctx->fin.off, &ctx->fin.node, &ctx->fin.eid, &ctx->fin.stay, &ctx->fin.ncross,
                      &ctx->fin.src, &ctx->fin.seq, &ctx->fin.viol, &ctx->scFin.off, &ctx->scFin.node, &ctx->scFin.eid,
                      &ctx->scFin.stay, &ctx->scFin.ncross, &ctx->scFin.src, &ctx->scFin.viol, &ctx->scNodes[0], &ctx->scNodes[1], &ctx->scEids[0],
-                     &ctx->scEids[1], &ctx->scFlag[0], &ctx->scFlag[1], &ctx->scStay[0], &ctx->scStay[1], &ctx->gCounts,
-                     &ctx->pBlock, &ctx->mBlocks, &ctx->vStampA, &ctx->vStampB, &ctx->vEmpty, &ctx->vEmptyB0, &ctx->vActive, &ctx->vFlags, &ctx->mNode, &ctx->mEid, &ctx->mStay, &ctx->mOff, &ctx->mLen, &ctx->mSrc,
+                     &ctx->scEids[1], &ctx->gCounts,
+                     &ctx->pBlock, &ctx->mBlocks, &ctx->dArcSrc, &ctx->dColSorted, &ctx->eHoleBase, &ctx->scCode, &ctx->vStampA, &ctx->vStampB, &ctx->vEmpty, &ctx->vEmptyB0, &ctx->vActive, &ctx->vFlags, &ctx->mNode, &ctx->mEid, &ctx->mStay, &ctx->mOff, &ctx->mLen, &ctx->mSrc,
                      &ctx->mSeq, &ctx->mValid};
     for (auto *b : dev) b->release();
     PinBuf *pin[] = {&ctx->hX, &ctx->hBl, &ctx->hCounters, &ctx->hHeavy, &ctx->host.off, &ctx->host.node, &ctx->host.eid,
                      &ctx->host.stay, &ctx->host.ncross, &ctx->host.src, &ctx->host.viol, &ctx->hLabOff, &ctx->hLabNode,
-                     &ctx->hLabDist, &ctx->hLabHops, &ctx->hSrcArcs, &ctx->hSrcSettled, &ctx->hSrcTier, &ctx->scTmp,
+                     &ctx->hLabDist, &ctx->hLabHops, &ctx->hSrcArcs, &ctx->hSrcSettled, &ctx->hSrcTier, &ctx->scTmp, &ctx->scListHost[0], &ctx->scListHost[1],
                      &ctx->hGCounts};
     for (auto *b : pin) b->release();
     for (int k = 0; k < 2; ++k) {
@@ -560,6 +613,8 @@ void smsgpu_destroy(smsgpu_ctx *ctx) {
     for (auto &e : ctx->ev)
         if (e) cudaEventDestroy(e);
     for (auto &e : ctx->tierEv)
+        if (e) cudaEventDestroy(e);
+    for (auto &e : ctx->scEv)
         if (e) cudaEventDestroy(e);
     if (ctx->joinEv) cudaEventDestroy(ctx->joinEv);
     if (ctx->heavyEv) cudaEventDestroy(ctx->heavyEv);
@@ -797,6 +852,7 @@ int runDedup(smsgpu_ctx *ctx, const CutView &V, long long totalNodes, bool canon
 }
 
 int mergeAcrossRanks(smsgpu_ctx *ctx, bool dedup, int localRc); // multi-GPU part below
+int registerSmallCycles(smsgpu_ctx *ctx, int k, int64_t T);
 int separateLocal(smsgpu_ctx *ctx, const smsgpu_params &P);
 
 } // namespace
@@ -852,7 +908,8 @@ int separateLocal(smsgpu_ctx *ctx, const smsgpu_params &P) {
     // ---- K1 ----
     if (ctx->arcsDirty && ctx->m > 0) {
         dcWeightsKernel<<<std::min<unsigned>(gridFor((2 * ctx->m + 3) / 4, 256), (unsigned)ctx->smCount * 16), 256, 0, st>>>(
-            2 * ctx->m, ctx->dCol.as<int32_t>(), ctx->dEid.as<int32_t>(), ctx->xPtr, ctx->blPtr, ctx->dArcs.as<Arc>());
+            2 * ctx->m, ctx->dCol.as<int32_t>(), ctx->dEid.as<int32_t>(), ctx->dRowpack.as<uint32_t>(), ctx->xPtr, ctx->blPtr,
+            ctx->dArcs.as<Arc>());
         CU(cudaGetLastError());
         ctx->stats.total_launches += 1;
     }
@@ -883,7 +940,7 @@ int separateLocal(smsgpu_ctx *ctx, const smsgpu_params &P) {
         CU(ctx->labHops.ensure((size_t)ctx->labCap * 4));
         CU(ctx->labDist.ensure((size_t)ctx->labCap * 8));
     }
-    GraphDev G{ctx->n, ctx->m, ctx->dRowptr.as<int64_t>(), ctx->dArcs.as<Arc>(), nullptr, nullptr, nullptr};
+    GraphDev G{ctx->n, ctx->m, ctx->dRowptr.as<int64_t>(), ctx->dArcs.as<Arc>(), ctx->dEid.as<int32_t>(), nullptr, nullptr, nullptr};
     long long rawCuts = 0, rawNodes = 0;
     // One sweep over the sources: every tier in turn until each source has finished somewhere; raw walks in the arena.
     // wl0 == nullptr: all local sources, issued by the history of the previous round (independent-source mode's one and
@@ -1387,13 +1444,21 @@ int smsgpu_small_cycles_set(smsgpu_ctx *ctx, int k, int64_t T, const int32_t *cy
     const int s = k - 3;
     for (int64_t i = 0; i < T * k; ++i)
         if (cycles[i] < 0 || cycles[i] >= ctx->n) return fail(ctx, SMSGPU_ERR_ARG, "cycle vertex out of range");
+    CU(ctx->scNodes[s].ensure((size_t)std::max<int64_t>(T * k, 4) * 4));
+    if (T > 0) CU(cudaMemcpyAsync(ctx->scNodes[s].p, cycles, (size_t)T * k * 4, cudaMemcpyHostToDevice, ctx->stream));
+    return registerSmallCycles(ctx, k, T);
+}
+
+} // extern "C"
+
+namespace {
+// the list of k-cycles sits in ctx->scNodes[k - 3] (device): resolve its edge ids once, size the scan's buffers
+int registerSmallCycles(smsgpu_ctx *ctx, int k, int64_t T) {
+    const int s = k - 3;
     ctx->scCount[s] = T;
     CU(ctx->scNodes[s].ensure((size_t)std::max<int64_t>(T * k, 4) * 4));
     CU(ctx->scEids[s].ensure((size_t)std::max<int64_t>(T * k, 4) * 4));
-    CU(ctx->scFlag[s].ensure((size_t)std::max<int64_t>(T, 1) * 4));
-    CU(ctx->scStay[s].ensure((size_t)std::max<int64_t>(T, 1)));
     if (T == 0) return SMSGPU_OK;
-    CU(cudaMemcpyAsync(ctx->scNodes[s].p, cycles, (size_t)T * k * 4, cudaMemcpyHostToDevice, ctx->stream));
     unsigned long long *dc = ctx->counters.as<unsigned long long>();
     CU(cudaMemsetAsync(dc + 14, 0, 8, ctx->stream));
     int *missing = reinterpret_cast<int *>(dc + 14);
@@ -1415,8 +1480,89 @@ int smsgpu_small_cycles_set(smsgpu_ctx *ctx, int k, int64_t T, const int32_t *cy
     }
     return SMSGPU_OK;
 }
+} // namespace
 
-int smsgpu_small_cycles_scan(smsgpu_ctx *ctx, int k) {
+extern "C" {
+
+// SmallChordlessCycles::computeSmallCCs (src/graph/small_ccs.cpp:18-43) on the device: triangles, and chordless
+// four-cycles when want_holes, in the reference's list order; both lists are registered for the scan.
+int smsgpu_small_cycles_enumerate(smsgpu_ctx *ctx, int want_holes, int64_t *ntriangles, int64_t *nholes) {
+    if (!ctx) return SMSGPU_ERR_ARG;
+    CU(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const long long narcs = 2 * ctx->m;
+    if (ntriangles) *ntriangles = 0;
+    if (nholes) *nholes = 0;
+    if (narcs == 0) {
+        if (int rc = registerSmallCycles(ctx, 3, 0)) return rc;
+        return want_holes ? registerSmallCycles(ctx, 4, 0) : SMSGPU_OK;
+    }
+    if (!ctx->enumReady) { // owner vertex of every arc + per-row sorted adjacency (hasEdge = binary search), built once
+        std::vector<int32_t> src((size_t)narcs), sorted(ctx->hCol);
+        for (long long u = 0; u < ctx->n; ++u) {
+            std::fill(src.begin() + ctx->hRowptr[u], src.begin() + ctx->hRowptr[u + 1], (int32_t)u);
+            std::sort(sorted.begin() + ctx->hRowptr[u], sorted.begin() + ctx->hRowptr[u + 1]);
+        }
+        CU(ctx->dArcSrc.ensure((size_t)narcs * 4));
+        CU(ctx->dColSorted.ensure((size_t)narcs * 4));
+        CU(cudaMemcpy(ctx->dArcSrc.p, src.data(), (size_t)narcs * 4, cudaMemcpyHostToDevice));
+        CU(cudaMemcpy(ctx->dColSorted.p, sorted.data(), (size_t)narcs * 4, cudaMemcpyHostToDevice));
+        ctx->enumReady = true;
+    }
+    CU(ctx->wCnt.ensure((size_t)(narcs + 1) * 4));
+    CU(ctx->wCursor.ensure((size_t)(narcs + 1) * 4));
+    CU(ctx->wBase.ensure((size_t)(narcs + 2) * 8));
+    CU(ctx->eHoleBase.ensure((size_t)(narcs + 2) * 8));
+    const unsigned grid = (unsigned)std::min<long long>((narcs + 7) / 8, (long long)ctx->smCount * 32);
+    int32_t *triCnt = ctx->wCnt.as<int32_t>(), *holeCnt = ctx->wCursor.as<int32_t>();
+    long long *triBase = ctx->wBase.as<long long>(), *holeBase = ctx->eHoleBase.as<long long>();
+    enumerateSmallCyclesKernel<false><<<grid, 256, 0, st>>>(narcs, ctx->dArcSrc.as<int32_t>(), ctx->dRowptr.as<long long>(),
+                                                            ctx->dCol.as<int32_t>(), ctx->dColSorted.as<int32_t>(), triCnt, holeCnt,
+                                                            nullptr, nullptr, nullptr, nullptr, want_holes ? 1 : 0);
+    CU(cudaGetLastError());
+    if (int rc = exclusiveScan(ctx, triCnt, narcs, triBase)) return rc;
+    if (int rc = exclusiveScan(ctx, holeCnt, narcs, holeBase)) return rc;
+    long long tot[2] = {0, 0};
+    CU(cudaMemcpyAsync(&tot[0], triBase + narcs, 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(&tot[1], holeBase + narcs, 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    if (tot[0] * 3 >= (1ll << 31) || tot[1] * 4 >= (1ll << 31)) return fail(ctx, SMSGPU_ERR_ARG, "more than 2^31 cycle vertices (%lld triangles, %lld holes)", tot[0], tot[1]);
+    CU(ctx->scNodes[0].ensure((size_t)std::max<long long>(tot[0] * 3, 4) * 4));
+    CU(ctx->scNodes[1].ensure((size_t)std::max<long long>(tot[1] * 4, 4) * 4));
+    if (tot[0] + tot[1] > 0) {
+        enumerateSmallCyclesKernel<true><<<grid, 256, 0, st>>>(narcs, ctx->dArcSrc.as<int32_t>(), ctx->dRowptr.as<long long>(),
+                                                               ctx->dCol.as<int32_t>(), ctx->dColSorted.as<int32_t>(), nullptr, nullptr,
+                                                               triBase, holeBase, ctx->scNodes[0].as<int32_t>(),
+                                                               ctx->scNodes[1].as<int32_t>(), want_holes ? 1 : 0);
+        CU(cudaGetLastError());
+    }
+    if (int rc = registerSmallCycles(ctx, 3, tot[0])) return rc;
+    if (want_holes)
+        if (int rc = registerSmallCycles(ctx, 4, tot[1])) return rc;
+    if (ntriangles) *ntriangles = tot[0];
+    if (nholes) *nholes = want_holes ? tot[1] : 0;
+    return SMSGPU_OK;
+}
+
+// host copy of the registered list of k-cycles (vertex ids, k per cycle), e.g. after smsgpu_small_cycles_enumerate
+int smsgpu_small_cycles_get(smsgpu_ctx *ctx, int k, int64_t *T, const int32_t **cycles) {
+    if (!ctx || !T || !cycles) return SMSGPU_ERR_ARG;
+    if (k != 3 && k != 4) return fail(ctx, SMSGPU_ERR_ARG, "k must be 3 or 4");
+    CU(cudaSetDevice(ctx->device));
+    const int s = k - 3;
+    const long long cnt = ctx->scCount[s];
+    CU(ctx->scListHost[s].ensure((size_t)std::max<long long>(cnt * k, 1) * 4));
+    if (cnt > 0) {
+        CU(cudaMemcpyAsync(ctx->scListHost[s].p, ctx->scNodes[s].p, (size_t)cnt * k * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        CU(cudaStreamSynchronize(ctx->stream));
+    }
+    *T = cnt;
+    *cycles = ctx->scListHost[s].as<int32_t>();
+    return SMSGPU_OK;
+}
+
+// device part of the scan: codes, ranks, the violated walks in ctx->scFin; returns with the number of violated cycles known
+static int smallCyclesScanDevice(smsgpu_ctx *ctx, int k, long long *Uout) {
     if (!ctx) return SMSGPU_ERR_ARG;
     if (k != 3 && k != 4) return fail(ctx, SMSGPU_ERR_ARG, "k must be 3 or 4");
     if (!ctx->haveInput) return fail(ctx, SMSGPU_ERR_STATE, "small_cycles_scan before set_round_input");
@@ -1424,23 +1570,26 @@ int smsgpu_small_cycles_scan(smsgpu_ctx *ctx, int k) {
     const int s = k - 3;
     const long long T = ctx->scCount[s];
     cudaStream_t st = ctx->stream;
-    CutListHost &H = ctx->scHost[s];
-    H.ncuts = H.nnodes = 0;
-    CU(H.off.ensure(8));
-    H.off.as<int64_t>()[0] = 0;
+    *Uout = 0;
+    ctx->scMs[0] = ctx->scMs[1] = ctx->scMs[2] = 0.0;
+    ctx->scFin.ncuts = ctx->scFin.nnodes = 0;
     if (T == 0) return SMSGPU_OK;
-    CU(ctx->wViol.ensure((size_t)T * 8));
-    CU(ctx->wBase.ensure((size_t)(T + 2) * 8));
+    const long long ntiles = (T + kSmallTile - 1) / kSmallTile;
+    CU(ctx->scCode.ensure((size_t)T));
+    CU(ctx->wCnt.ensure((size_t)(ntiles + 1) * 4));
+    CU(ctx->wBase.ensure((size_t)(ntiles + 2) * 8));
+    CU(cudaEventRecord(ctx->scEv[0], st));
     if (k == 3)
-        smallCycleScanKernel<3><<<gridFor(T, 256), 256, 0, st>>>(T, ctx->scEids[s].as<int32_t>(), ctx->xPtr, ctx->scFlag[s].as<int32_t>(),
-                                                                ctx->scStay[s].as<uint8_t>(), ctx->wViol.as<double>());
+        smallCycleScanKernel<3><<<(unsigned)ntiles, kSmallBlock, 0, st>>>(T, ctx->scEids[s].as<int32_t>(), ctx->xPtr, ctx->scCode.as<uint8_t>(),
+                                                                        ctx->wCnt.as<int32_t>());
     else
-        smallCycleScanKernel<4><<<gridFor(T, 256), 256, 0, st>>>(T, ctx->scEids[s].as<int32_t>(), ctx->xPtr, ctx->scFlag[s].as<int32_t>(),
-                                                                ctx->scStay[s].as<uint8_t>(), ctx->wViol.as<double>());
+        smallCycleScanKernel<4><<<(unsigned)ntiles, kSmallBlock, 0, st>>>(T, ctx->scEids[s].as<int32_t>(), ctx->xPtr, ctx->scCode.as<uint8_t>(),
+                                                                        ctx->wCnt.as<int32_t>());
     CU(cudaGetLastError());
-    if (int rc = exclusiveScan(ctx, ctx->scFlag[s].as<int32_t>(), T, ctx->wBase.as<long long>())) return rc;
+    CU(cudaEventRecord(ctx->scEv[1], st));
+    if (int rc = exclusiveScan(ctx, ctx->wCnt.as<int32_t>(), ntiles, ctx->wBase.as<long long>())) return rc;
     long long U = 0;
-    CU(cudaMemcpyAsync(&U, ctx->wBase.as<long long>() + T, 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(&U, ctx->wBase.as<long long>() + ntiles, 8, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     CutListDev &F = ctx->scFin;
     CU(F.off.ensure((size_t)(U + 1) * 8));
@@ -1450,28 +1599,62 @@ int smsgpu_small_cycles_scan(smsgpu_ctx *ctx, int k) {
     CU(F.ncross.ensure((size_t)std::max<long long>(U, 1) * 4));
     CU(F.src.ensure((size_t)std::max<long long>(U, 1) * 4));
     CU(F.viol.ensure((size_t)std::max<long long>(U, 1) * 8));
-    CU(H.off.ensure((size_t)(U + 1) * 8));
-    CU(H.node.ensure((size_t)std::max<long long>(U * k, 1) * 4));
-    CU(H.eid.ensure((size_t)std::max<long long>(U * k, 1) * 4));
-    CU(H.stay.ensure((size_t)std::max<long long>(U * k, 1)));
-    CU(H.ncross.ensure((size_t)std::max<long long>(U, 1) * 4));
-    CU(H.src.ensure((size_t)std::max<long long>(U, 1) * 4));
-    CU(H.viol.ensure((size_t)std::max<long long>(U, 1) * 8));
-    H.off.as<int64_t>()[0] = 0;
     if (U > 0) {
         if (k == 3)
-            smallCycleGatherKernel<3><<<gridFor(T, 256), 256, 0, st>>>(
-                T, ctx->scNodes[s].as<int32_t>(), ctx->scEids[s].as<int32_t>(), ctx->scFlag[s].as<int32_t>(),
-                ctx->scStay[s].as<uint8_t>(), ctx->wViol.as<double>(), ctx->wBase.as<long long>(), F.node.as<int32_t>(),
-                F.eid.as<int32_t>(), F.stay.as<uint8_t>(), F.ncross.as<int32_t>(), F.src.as<int32_t>(), F.viol.as<double>(),
-                F.off.as<long long>());
+            smallCycleGatherKernel<3><<<(unsigned)ntiles, kSmallBlock, 0, st>>>(
+                T, ctx->scNodes[s].as<int32_t>(), ctx->scEids[s].as<int32_t>(), ctx->xPtr, ctx->scCode.as<uint8_t>(),
+                ctx->wBase.as<long long>(), F.node.as<int32_t>(), F.eid.as<int32_t>(), F.stay.as<uint8_t>(), F.ncross.as<int32_t>(),
+                F.src.as<int32_t>(), F.viol.as<double>(), F.off.as<long long>());
         else
-            smallCycleGatherKernel<4><<<gridFor(T, 256), 256, 0, st>>>(
-                T, ctx->scNodes[s].as<int32_t>(), ctx->scEids[s].as<int32_t>(), ctx->scFlag[s].as<int32_t>(),
-                ctx->scStay[s].as<uint8_t>(), ctx->wViol.as<double>(), ctx->wBase.as<long long>(), F.node.as<int32_t>(),
-                F.eid.as<int32_t>(), F.stay.as<uint8_t>(), F.ncross.as<int32_t>(), F.src.as<int32_t>(), F.viol.as<double>(),
-                F.off.as<long long>());
+            smallCycleGatherKernel<4><<<(unsigned)ntiles, kSmallBlock, 0, st>>>(
+                T, ctx->scNodes[s].as<int32_t>(), ctx->scEids[s].as<int32_t>(), ctx->xPtr, ctx->scCode.as<uint8_t>(),
+                ctx->wBase.as<long long>(), F.node.as<int32_t>(), F.eid.as<int32_t>(), F.stay.as<uint8_t>(), F.ncross.as<int32_t>(),
+                F.src.as<int32_t>(), F.viol.as<double>(), F.off.as<long long>());
+        smallCycleTailKernel<<<1, 1, 0, st>>>(F.off.as<long long>(), U, k);
         CU(cudaGetLastError());
+    }
+    CU(cudaEventRecord(ctx->scEv[2], st));
+    F.ncuts = U;
+    F.nnodes = U * k;
+    *Uout = U;
+    return SMSGPU_OK;
+}
+static void smallCyclesTimes(smsgpu_ctx *ctx, bool withD2h) {
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, ctx->scEv[0], ctx->scEv[1]) == cudaSuccess) ctx->scMs[0] = ms;
+    if (cudaEventElapsedTime(&ms, ctx->scEv[1], ctx->scEv[2]) == cudaSuccess) ctx->scMs[1] = ms;
+    if (withD2h && cudaEventElapsedTime(&ms, ctx->scEv[2], ctx->scEv[3]) == cudaSuccess) ctx->scMs[2] = ms;
+    (void)cudaGetLastError();
+}
+
+int smsgpu_small_cycles_scan_device(smsgpu_ctx *ctx, int k) {
+    long long U = 0;
+    if (int rc = smallCyclesScanDevice(ctx, k, &U)) return rc;
+    if (ctx->scCount[k - 3] > 0) {
+        CU(cudaStreamSynchronize(ctx->stream));
+        smallCyclesTimes(ctx, false);
+    }
+    return SMSGPU_OK;
+}
+
+int smsgpu_small_cycles_scan(smsgpu_ctx *ctx, int k) {
+    long long U = 0;
+    if (int rc = smallCyclesScanDevice(ctx, k, &U)) return rc;
+    const int s = k - 3;
+    cudaStream_t st = ctx->stream;
+    CutListHost &H = ctx->scHost[s];
+    CutListDev &F = ctx->scFin;
+    H.ncuts = H.nnodes = 0;
+    CU(H.off.ensure((size_t)(U + 1) * 8));
+    H.off.as<int64_t>()[0] = 0;
+    if (ctx->scCount[s] == 0) return SMSGPU_OK;
+    if (U > 0) {
+        CU(H.node.ensure((size_t)U * k * 4));
+        CU(H.eid.ensure((size_t)U * k * 4));
+        CU(H.stay.ensure((size_t)U * k));
+        CU(H.ncross.ensure((size_t)U * 4));
+        CU(H.src.ensure((size_t)U * 4));
+        CU(H.viol.ensure((size_t)U * 8));
         CU(cudaMemcpyAsync(H.off.p, F.off.p, (size_t)(U + 1) * 8, cudaMemcpyDeviceToHost, st));
         CU(cudaMemcpyAsync(H.node.p, F.node.p, (size_t)U * k * 4, cudaMemcpyDeviceToHost, st));
         CU(cudaMemcpyAsync(H.eid.p, F.eid.p, (size_t)U * k * 4, cudaMemcpyDeviceToHost, st));
@@ -1479,10 +1662,20 @@ int smsgpu_small_cycles_scan(smsgpu_ctx *ctx, int k) {
         CU(cudaMemcpyAsync(H.ncross.p, F.ncross.p, (size_t)U * 4, cudaMemcpyDeviceToHost, st));
         CU(cudaMemcpyAsync(H.src.p, F.src.p, (size_t)U * 4, cudaMemcpyDeviceToHost, st));
         CU(cudaMemcpyAsync(H.viol.p, F.viol.p, (size_t)U * 8, cudaMemcpyDeviceToHost, st));
-        CU(cudaStreamSynchronize(st));
     }
+    CU(cudaEventRecord(ctx->scEv[3], st));
+    CU(cudaStreamSynchronize(st));
+    smallCyclesTimes(ctx, true);
     H.ncuts = U;
     H.nnodes = U * k;
+    return SMSGPU_OK;
+}
+
+int smsgpu_small_cycles_timing(smsgpu_ctx *ctx, double *ms_scan, double *ms_gather, double *ms_d2h) {
+    if (!ctx) return SMSGPU_ERR_ARG;
+    if (ms_scan) *ms_scan = ctx->scMs[0];
+    if (ms_gather) *ms_gather = ctx->scMs[1];
+    if (ms_d2h) *ms_d2h = ctx->scMs[2];
     return SMSGPU_OK;
 }
 

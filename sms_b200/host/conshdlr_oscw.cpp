@@ -127,7 +127,7 @@ SCIP_RETCODE ConshdlrOscw::sepaOddCycles(SCIP *scip, SCIP_CONSHDLR *conshdlr, SC
     try {
         ocwSeparator_.setRoundInput(xByEid_.data(), blacklist_.data());
         // sources 0..n-1 as the reference issues them (:188-195); blacklisted ones are skipped on the device
-        walks = ocwSeparator_.separateRound(nullptr, 0, /*dedup=*/true);
+        walks = ocwSeparator_.separateRound(nullptr, 0, /*dedup=*/true, sweepMode_, deviceMinEfficacy_);
     } catch (const std::exception &e) {
         SCIPerrorMessage("cycleparity: GPU separation failed: %s\n", e.what());
         return SCIP_ERROR;
@@ -135,11 +135,16 @@ SCIP_RETCODE ConshdlrOscw::sepaOddCycles(SCIP *scip, SCIP_CONSHDLR *conshdlr, SC
     roundsRun_++;
     cutsFromDevice_ += walks.size();
 
-    // rows (reference :196-243).  The list is ordered by (first-finding source, emission index); after a CUTOFF the
-    // reference still finishes the walks of the current source and then stops.
-    int32_t cutoffSrc = -1;
+    // rows (reference :188-243).  The list is ordered by (first-finding source, emission index).  The reference's protocol,
+    // kept as it is: the loop over the sources stops in front of the next source once the result is CUTOFF (:188), the walks of
+    // the current source are still processed, and a later efficacious row of that source that is feasible overwrites CUTOFF
+    // with SEPARATED (:231-237); efficacy is always asked for the LP solution (sol = nullptr, :221/232) even in CONSSEPASOL.
+    int32_t curSrc = -1;
     for (const auto &ocw : walks) {
-        if (*result == SCIP_CUTOFF && ocw.sourceIndex() != cutoffSrc) break;
+        if (ocw.sourceIndex() != curSrc) {
+            if (*result == SCIP_CUTOFF) break;
+            curSrc = ocw.sourceIndex();
+        }
         const SCIP_Real lhs = -SCIPinfinity(scip);
         const unsigned int rhs = ocw.numCrosses() - 1;
         SCIP_ROW *row;
@@ -151,19 +156,14 @@ SCIP_RETCODE ConshdlrOscw::sepaOddCycles(SCIP *scip, SCIP_CONSHDLR *conshdlr, SC
         }
         SCIP_CALL(SCIPflushRowExtensions(scip, row));
         if (sepaCutpool_) {
-            if (SCIPisCutEfficacious(scip, sol, row)) {
+            if (SCIPisCutEfficacious(scip, nullptr, row)) {
                 SCIP_CALL(SCIPaddPoolCut(scip, row));
                 *result = SCIP_SEPARATED;
             }
-        } else if (SCIPisCutEfficacious(scip, sol, row)) {
+        } else if (SCIPisCutEfficacious(scip, nullptr, row)) {
             SCIP_Bool infeasible;
             SCIP_CALL(SCIPaddRow(scip, row, TRUE, &infeasible));
-            if (infeasible) {
-                *result = SCIP_CUTOFF;
-                cutoffSrc = ocw.sourceIndex();
-            } else if (*result != SCIP_CUTOFF) {
-                *result = SCIP_SEPARATED;
-            }
+            *result = infeasible ? SCIP_CUTOFF : SCIP_SEPARATED;
         }
         SCIP_CALL(SCIPreleaseRow(scip, &row));
     }

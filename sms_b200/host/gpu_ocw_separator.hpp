@@ -21,6 +21,7 @@
 #include <cstdint>
 #include <stdexcept>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "smsgpu.h"
@@ -121,12 +122,16 @@ public:
     }
     // The loop of conshdlr_oscw.cpp:188-195 in one call.  sources == nullptr: doubled ids 0..n-1 as the handler
     // issues them; sources whose id is blacklisted are skipped on the device (ocw_seperator.cpp:334).
-    std::vector<GpuOddClosedWalk> separateRound(const int32_t *sources = nullptr, int64_t nsrc = 0, bool dedup = true) {
+    // mode: SMSGPU_MODE_INDEPENDENT / SMSGPU_MODE_VERBATIM; minEfficacy: device pre-filter (0 = keep everything)
+    std::vector<GpuOddClosedWalk> separateRound(const int32_t *sources = nullptr, int64_t nsrc = 0, bool dedup = true,
+                                                int mode = SMSGPU_MODE_INDEPENDENT, double minEfficacy = 0.) {
         flush();
         check(smsgpu_set_sources(ctx_, sources, nsrc, 0, 1));
         smsgpu_params p;
         smsgpu_default_params(&p);
         p.dedup = dedup ? 1 : 0;
+        p.mode = mode;
+        p.min_efficacy = minEfficacy;
         check(smsgpu_separate(ctx_, &p));
         smsgpu_cuts c;
         check(smsgpu_get_cuts(ctx_, &c));
@@ -140,6 +145,25 @@ public:
         smsgpu_stats s;
         smsgpu_get_stats(ctx_, &s);
         return s;
+    }
+    // ---- small cycles (K6) on this context: used by GpuSmallCycleSeparator below -------------------------------------
+    // SmallChordlessCycles::computeSmallCCs (src/graph/small_ccs.cpp:18-43) on the device; both lists get registered
+    std::pair<int64_t, int64_t> enumerateSmallCycles(bool wantHoles) {
+        int64_t nt = 0, nh = 0;
+        check(smsgpu_small_cycles_enumerate(ctx_, wantHoles ? 1 : 0, &nt, &nh));
+        return {nt, nh};
+    }
+    void setSmallCycles(int k, const std::vector<int32_t> &flat) { check(smsgpu_small_cycles_set(ctx_, k, static_cast<int64_t>(flat.size()) / k, flat.data())); }
+    std::vector<GpuOddClosedWalk> scanSmallCycles(int k) {
+        flush();
+        check(smsgpu_small_cycles_scan(ctx_, k));
+        smsgpu_cuts c;
+        check(smsgpu_get_small_cycle_cuts(ctx_, k, &c));
+        std::vector<GpuOddClosedWalk> out;
+        out.reserve(static_cast<size_t>(c.ncuts));
+        for (int64_t i = 0; i < c.ncuts; ++i)
+            out.emplace_back(c.node + c.off[i], c.eid + c.off[i], c.is_stay + c.off[i], c.off[i + 1] - c.off[i], c.violation[i], c.src[i]);
+        return out;
     }
     smsgpu_ctx *context() const { return ctx_; }
     int64_t numberOfNodes() const { return n_; }
@@ -174,6 +198,55 @@ private:
     std::vector<uint8_t> blacklist_;
     bool dirty_ = true;
 };
+
+// sms::TriangleSeparator (include/sms/conshdlr/triangles.hpp:12-54) for K = 3 and sms::HoleSeparator
+// (include/sms/conshdlr/holes.hpp) for K = 4 over the C ABI: same constructor argument, updateWeights / addTriangle /
+// addFourHole / getViolatedTriangles / getViolatedFourHoles; the walks come back in list order like the reference's.
+// Added: enumerate(), the device version of the SmallChordlessCycles run the handlers do in scip_initsol.
+template <int K>
+class GpuSmallCycleSeparator {
+    static_assert(K == 3 || K == 4, "triangles or four-holes");
+
+public:
+    template <class GraphT>
+    explicit GpuSmallCycleSeparator(GraphT const *const originalGraph, int device = 0) : gpu_(*originalGraph, device) {}
+    void updateWeights(uint64_t u, uint64_t v, double w) { gpu_.updateWeights(u, v, w); } // clamped on the device like triangles.hpp:27
+    void updateEdgeWeight(uint64_t edgeId, double w) { gpu_.updateEdgeWeight(edgeId, w); }
+    void addTriangle(uint64_t u, uint64_t v, uint64_t w) {
+        static_assert(K == 3, "addTriangle is the triangle separator's");
+        for (uint64_t a : {u, v, w}) list_.push_back(static_cast<int32_t>(a));
+        registered_ = false;
+    }
+    void addFourHole(uint64_t a, uint64_t b, uint64_t c, uint64_t d) {
+        static_assert(K == 4, "addFourHole is the hole separator's");
+        for (uint64_t v : {a, b, c, d}) list_.push_back(static_cast<int32_t>(v));
+        registered_ = false;
+    }
+    // scip_initsol: the whole list from the device (replaces the SmallChordlessCycles loop + addTriangle calls)
+    int64_t enumerate() {
+        const auto cnt = gpu_.enumerateSmallCycles(K == 4);
+        list_.clear();
+        registered_ = true; // the enumeration registered it
+        return K == 3 ? cnt.first : cnt.second;
+    }
+    std::vector<GpuOddClosedWalk> getViolated() {
+        if (!registered_) {
+            gpu_.setSmallCycles(K, list_);
+            registered_ = true;
+        }
+        return gpu_.scanSmallCycles(K);
+    }
+    std::vector<GpuOddClosedWalk> getViolatedTriangles() { return getViolated(); }
+    std::vector<GpuOddClosedWalk> getViolatedFourHoles() { return getViolated(); }
+    GpuOcwSeparator &context() { return gpu_; }
+
+private:
+    GpuOcwSeparator gpu_;
+    std::vector<int32_t> list_;
+    bool registered_ = false;
+};
+using GpuTriangleSeparator = GpuSmallCycleSeparator<3>;
+using GpuHoleSeparator = GpuSmallCycleSeparator<4>;
 
 } // namespace sms
 

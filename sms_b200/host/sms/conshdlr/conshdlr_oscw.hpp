@@ -27,6 +27,8 @@ private:
     // Statistics (the reference keeps totalConstructedCycleLength_, conshdlr_oscw.hpp:30)
     uint64_t totalConstructedCycleLength_ = 0;
     uint64_t roundsRun_ = 0, cutsFromDevice_ = 0;
+    int sweepMode_ = 0;
+    double deviceMinEfficacy_ = 0.;
 
 public:
     explicit ConshdlrOscw(Scip *scip, const NetworKit::Graph *sepGraph);
@@ -42,6 +44,11 @@ public:
     scip::ObjProbCloneable *SCIP_DECL_CONSHDLRCLONE(clone) override;
     SCIP_Bool iscloneable() const override { return TRUE; }
 
+    // SMSGPU_MODE_INDEPENDENT (default) or SMSGPU_MODE_VERBATIM: which sweep contract the device runs (include/smsgpu.h)
+    void setSweepMode(int mode) { sweepMode_ = mode; }
+    // efficacy pre-filter on the device (smsgpu_params::min_efficacy); BasicOcwSolver would pass the value it sets for
+    // separating/minefficacyroot (src/solver/basic_ocw.cpp:244).  0 = off; SCIPisCutEfficacious still decides every survivor.
+    void setDeviceMinEfficacy(double e) { deviceMinEfficacy_ = e; }
     uint64_t totalConstructedCycleLength() const { return totalConstructedCycleLength_; }
     uint64_t roundsRun() const { return roundsRun_; }
     uint64_t cutsFromDevice() const { return cutsFromDevice_; }

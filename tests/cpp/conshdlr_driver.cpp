@@ -5,6 +5,7 @@
 // Prints one line per row SCIP received: "<pool|lp> <name> <rhs> <len> eid:coef ..." and "result <code>".
 // Exit code 3: the handler could not be constructed (e.g. no CUDA device -- there is no CPU fallback).
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <fstream>
 #include <iostream>
@@ -36,6 +37,7 @@ int main(int argc, char **argv) {
         in >> u;
         prob.nodeToVar(u)->lbLocal = prob.nodeToVar(u)->ubLocal = 1.;
     }
+    if (argc > 3) scip.infeasibleAtAddRow = std::atol(argv[3]); // test hook: this SCIPaddRow call reports `infeasible`
     sms::ConshdlrOscw *h = nullptr;
     try {
         h = new sms::ConshdlrOscw(&scip, &g);

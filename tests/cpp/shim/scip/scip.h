@@ -82,6 +82,7 @@ struct Scip {
     std::vector<SCIP_ROW> poolCuts, lpRows;     /* what SCIPaddPoolCut / SCIPaddRow received, in call order */
     long nRowsCreated = 0, nRowsReleased = 0, nAddVar = 0;
     bool nextAddRowInfeasible = false;          /* test hook for the CUTOFF branch */
+    long infeasibleAtAddRow = -1, nAddRow = 0;  /* test hook: the k-th SCIPaddRow call (0-based) reports infeasible */
 };
 typedef struct Scip SCIP;
 
@@ -169,7 +170,8 @@ inline SCIP_RETCODE SCIPaddPoolCut(SCIP *scip, SCIP_ROW *row) {
 }
 inline SCIP_RETCODE SCIPaddRow(SCIP *scip, SCIP_ROW *row, SCIP_Bool, SCIP_Bool *infeasible) {
     scip->lpRows.push_back(*row);
-    *infeasible = scip->nextAddRowInfeasible ? TRUE : FALSE;
+    *infeasible = (scip->nextAddRowInfeasible || scip->nAddRow == scip->infeasibleAtAddRow) ? TRUE : FALSE;
+    scip->nAddRow++;
     return SCIP_OKAY;
 }
 inline SCIP_RETCODE SCIPreleaseRow(SCIP *scip, SCIP_ROW **row) {
