@@ -595,13 +595,18 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
             }
             const double best0 = best; // conservative (>= the running value) for pruning / queue admission
             bool act = run && (c0 + tl < dg);
-            uint32_t nbr = 0, rowp = 0;
+            uint32_t nbr = 0;
+#ifdef SMSGPU_PAIRS_ROW_IN_ARC
+            uint32_t rowp = 0;
+#endif
             double w = 0.0;
             uint2 nrow = make_uint2(0u, 0u);
             if (act) {
                 const Arc arc = G.arcs[rb + c0 + tl];
                 nbr = (uint32_t)arc.nbr & 0x7FFFFFFFu;
+#ifdef SMSGPU_PAIRS_ROW_IN_ARC
                 rowp = arc.row;
+#endif
                 w = arc.w;
                 act = arc.nbr >= 0;    // blacklisted neighbours are skipped (:98-99)
                 if (G.blStamp && act) act = !stampedBefore(G, nbr, nowIdx); // mode V: blacklisted by an earlier source
@@ -756,11 +761,16 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
             PCLK(6);
             // ---- store the label, retire superseded keys, push the new ones ---------------------------------------
             bool ovf = false, dirty = false;
-            // the row of the neighbour travels with its key; it came with the arc (Arc::row), the row record is read only
-            // when the degree did not fit the packed field
+            // the row of the neighbour travels with its key: one 8-byte read per PUSHING lane (about one per settled node).
+            // The arc record carries the same information packed (Arc::row), but keeping it live across the probe costs the
+            // hot loop registers: measured 490 -> 520 ms per round (profiles/README.md, round 2), so the row record is read.
             if ((accS && 2 * dS <= best0) || (accX && 2 * dX <= best0)) {
+#ifdef SMSGPU_PAIRS_ROW_IN_ARC
                 nrow = make_uint2(rowp & ((1u << Q.rowShift) - 1u), rowp >> Q.rowShift);
                 if (nrow.y == (0xFFFFFFFFu >> Q.rowShift)) nrow = Q.rowinfo[nbr];
+#else
+                nrow = Q.rowinfo[nbr];
+#endif
             }
             if (accS || accX) {
                 if (hNew >= 0xFFFFu) ovf = true; // hops share a word with the queue position in this engine

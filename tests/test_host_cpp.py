@@ -137,15 +137,17 @@ def test_cutoff_protocol_of_the_reference(driver, orc, tmp_path):
     """conshdlr_oscw.cpp:188-243 with sepacutpool = FALSE: SCIPaddRow reports `infeasible` for one row.  The reference sets
     CUTOFF, still processes the remaining walks of the SAME source (a later feasible row of that source turns the result
     back into SEPARATED), and stops in front of the next source only while the result is CUTOFF."""
-    inst = I.torus2d(8)
-    x = I.xstar_uniform(inst.m, seed=2)
+    for inst, x in ((I.random_graph(300, 1200, seed=4), None), (I.torus3d(5), None), (I.torus2d(8), None)):
+        x = I.xstar_lp_like(inst.m, seed=2)
+        rows = ordered_rows(inst, x, inst.root_blacklist(), orc)
+        srcs = [r[0] for r in rows]
+        last_of_source = [k for k in range(len(rows)) if k + 1 == len(rows) or srcs[k + 1] != srcs[k]]
+        inner = [k for k in range(len(rows) - 1) if srcs[k + 1] == srcs[k]]
+        if len(last_of_source) > 2 and inner:
+            break
+    assert len(last_of_source) > 2 and inner, "the instance must have sources with several cuts and several sources"
     p = str(tmp_path / "i.txt")
     write_instance(p, inst, x, cutpool=0)
-    rows = ordered_rows(inst, x, inst.root_blacklist(), orc)
-    srcs = [r[0] for r in rows]
-    last_of_source = [k for k in range(len(rows)) if k + 1 == len(rows) or srcs[k + 1] != srcs[k]]
-    inner = [k for k in range(len(rows) - 1) if srcs[k + 1] == srcs[k]]
-    assert last_of_source and inner, "the instance must have sources with several cuts and several sources"
     CUTOFF, SEPARATED = 7, 8
     for k in (last_of_source[0], last_of_source[len(last_of_source) // 2], inner[0], inner[-1]):
         rc, out, err = run(driver, p, "sepalp", k)
