@@ -1,0 +1,776 @@
+// "Runs" engine of K2 (tier 3, the last tier): one source per CTA, and the CTA settles a whole RUN of queue keys at once.
+//
+// Why.  An LP point of a cutting loop is 70 - 100 % exact 0 / 1 values, so in the double cover most arcs cost exactly 0 and
+// a search is a breadth-first flood of zero-distance components: thousands of queue keys share the same (dist, hops)
+// and differ only in the id.  The bucket engines of tiers 1 / 2 give such a source up at once (no bucket holds a
+// thousand keys of equal distance); the one-key-at-a-time heap engine that used to be the last tier then settled them
+// at ~2.5 us per node on a single warp (torus 100x100, root LP iterates: the round was the critical path of one
+// 20 000-node search).  Measured on those inputs (oracle statistics): a search of 20 000 settled nodes
+// has ~100 distinct (dist, hops) values, a random 20k-node graph with LP-like x* settles 22 000 nodes in 8.
+//
+// What.  runDijsktra of the reference (src/graph/ocw_seperator.cpp:37-112) in the canonical order (dist, hops, doubled id),
+// event for event, like the other engines -- but advanced run by run.  A RUN is the set of all queue keys with the
+// minimal (dist, hops) = (d, h), in id order.  Facts that make a run processable in parallel:
+//   * every offer a run member makes has hops h + 1, so no relaxation of the run can put a key INTO the run or improve the
+//     label of another member: the run is known completely when it starts;
+//   * what one member's relaxations do to a neighbour depends only on that neighbour's label (both sides of a vertex sit
+//     in one entry), so offers to DIFFERENT vertices commute; offers to the same vertex are applied in the sequential
+//     order (member id, adjacency position, stay before cross) by one thread;
+//   * the one thing that is a history -- bestDist / bestHopDist / the list of intermediates (:71-82) -- is replayed
+//     serially over the events (label improvements whose D = dist[t] + dist[t^1] can matter), sorted into that same order;
+//   * the loop condition of :88-90 is tested before every extraction: the target's position in the run is known up front
+//     (the run is cut there); `2 d > bestDist` can become true in the middle of a run only through the replay, in which
+//     case the chunk of members being processed is rolled back (undo log) and redone up to that member -- it ends the search.
+// A run is processed in chunks of at most kRunOfferCap arcs: (1) one thread per arc computes the offer, (2) the offers are
+// sorted by (target vertex, sequence number) in shared memory, (3) one thread per target vertex applies its offers in order,
+// emits events and queue keys, (4) the events are sorted by sequence number and replayed by one thread.
+//
+// The queue is an unsorted pool of keys in HBM with tombstones (a per-node position array lets a superseded key be killed
+// directly), scanned by the whole CTA once per run for the minimal (dist, hops) and once to collect the members.
+// Labels live in a dense table indexed by vertex (O(n) per CTA, reset through the touched list), laid out like the other
+// engines' tiles, so that selection of intermediates, walk extraction and chord repair are the shared code of ocw_walks.cuh.
+#pragma once
+#include "ocw_search_fast.cuh"
+#include "ocw_walks.cuh"
+
+namespace smsgpu {
+
+constexpr int kRunThreads = 256;
+constexpr uint32_t kRunOfferCap = 2048; // arcs per chunk (sort buffers in shared memory)
+
+
+// per-CTA scratch behind the tile (global memory)
+struct RunScratch {
+    uint32_t *run;     // [runCap] members of the current run (doubled ids, sorted)
+    uint32_t *qpos;    // [2n] pool position of a node's live key, kNoQpos
+    uint32_t *offNbr;  // [cap] per offer: target vertex
+    uint32_t *offCur;  // [cap] the member (doubled id) that makes it
+    double *offW;      // [cap] stay weight of the arc
+    uint32_t *undoVtx; // [cap] per segment (target vertex) of the chunk: undo log
+    Entry *undoEntry;
+    uint2 *undoPred, *undoQpos;
+    uint32_t *evNode;  // [2 cap] events: doubled id of the improved node
+    uint32_t *evSeq;   //   sequence number 2 * offer + (cross ? 1 : 0)
+    uint32_t *evH;
+    double *evD;
+    uint32_t runCap;
+};
+__host__ __device__ inline size_t runScratchBytes(const long long n) {
+    size_t rc = 2;
+    while (rc < (size_t)(2 * n + 2)) rc <<= 1; // power of two: the member list is sorted with a bitonic network
+    size_t b = rc * 4 + (size_t)(2 * n + 2) * 4;
+    b += (size_t)kRunOfferCap * (4 + 4 + 8 + 4 + 32 + 8 + 8);
+    b += (size_t)2 * kRunOfferCap * (4 + 4 + 4 + 8);
+    return (b + 255) & ~(size_t)255;
+}
+__device__ inline void carveRunScratch(RunScratch &X, unsigned char *p, const long long n) {
+    uint32_t rc = 2;
+    while (rc < (uint32_t)(2 * n + 2)) rc <<= 1;
+    X.runCap = rc;
+    // 8-byte members first
+    X.offW = reinterpret_cast<double *>(p);
+    p += (size_t)kRunOfferCap * 8;
+    X.evD = reinterpret_cast<double *>(p);
+    p += (size_t)2 * kRunOfferCap * 8;
+    X.undoEntry = reinterpret_cast<Entry *>(p);
+    p += (size_t)kRunOfferCap * 32;
+    X.undoPred = reinterpret_cast<uint2 *>(p);
+    p += (size_t)kRunOfferCap * 8;
+    X.undoQpos = reinterpret_cast<uint2 *>(p);
+    p += (size_t)kRunOfferCap * 8;
+    X.run = reinterpret_cast<uint32_t *>(p);
+    p += (size_t)rc * 4;
+    X.qpos = reinterpret_cast<uint32_t *>(p);
+    p += (size_t)(2 * n + 2) * 4;
+    X.offNbr = reinterpret_cast<uint32_t *>(p);
+    p += (size_t)kRunOfferCap * 4;
+    X.offCur = reinterpret_cast<uint32_t *>(p);
+    p += (size_t)kRunOfferCap * 4;
+    X.undoVtx = reinterpret_cast<uint32_t *>(p);
+    p += (size_t)kRunOfferCap * 4;
+    X.evNode = reinterpret_cast<uint32_t *>(p);
+    p += (size_t)2 * kRunOfferCap * 4;
+    X.evSeq = reinterpret_cast<uint32_t *>(p);
+    p += (size_t)2 * kRunOfferCap * 4;
+    X.evH = reinterpret_cast<uint32_t *>(p);
+}
+
+// state of the search shared by the CTA
+struct RunShared {
+    double best, runD;
+    unsigned long long minHi, minLo;
+    uint32_t bestHop, histN, poolN, touchedN, runLen, runH, nev, nseg;
+    long long arcs, settled;
+    int overflow, done, cutoff;
+    uint32_t src;
+    int32_t srcIdx;
+    long long wi;
+    int skip;
+};
+
+// block-wide bitonic sort of n (a power of two) 64-bit keys in shared memory, ascending
+__device__ inline void bitonicSortShared(unsigned long long *k, const uint32_t n) {
+    for (uint32_t size = 2; size <= n; size <<= 1) {
+        for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
+            __syncthreads();
+            for (uint32_t t = threadIdx.x; t < (n >> 1); t += blockDim.x) {
+                const uint32_t lo = 2 * t - (t & (stride - 1));
+                const uint32_t hi = lo + stride;
+                const bool up = (lo & size) == 0;
+                const unsigned long long a = k[lo], b = k[hi];
+                if ((a > b) == up) {
+                    k[lo] = b;
+                    k[hi] = a;
+                }
+            }
+        }
+    }
+    __syncthreads();
+}
+// the same on 32-bit keys in global memory (member lists too long for shared memory)
+__device__ inline void bitonicSortGlobal32(uint32_t *k, const uint32_t n) {
+    for (uint32_t size = 2; size <= n; size <<= 1) {
+        for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
+            __syncthreads();
+            for (uint32_t t = threadIdx.x; t < (n >> 1); t += blockDim.x) {
+                const uint32_t lo = 2 * t - (t & (stride - 1));
+                const uint32_t hi = lo + stride;
+                const bool up = (lo & size) == 0;
+                const uint32_t a = k[lo], b = k[hi];
+                if ((a > b) == up) {
+                    k[lo] = b;
+                    k[hi] = a;
+                }
+            }
+        }
+    }
+    __syncthreads();
+}
+__device__ __forceinline__ uint32_t nextPow2(uint32_t v) {
+    uint32_t p = 2;
+    while (p < v) p <<= 1;
+    return p;
+}
+
+// One chunk of the current run: members run[mlo .. mhi) -- or, when arcHi > arcLo, the arcs [arcLo, arcHi) of the single
+// member run[mlo] (a row longer than the chunk capacity).  `offs` (shared) holds the exclusive prefix of the members' degrees.
+// Returns (in sh.cutoff) the rank of the member after whose events 2 d > bestDist became true, or -1.
+__device__ inline void runChunk(const GraphDev &G, TileMem &M, RunScratch &X, RunShared &sh, unsigned long long *keys, uint32_t *offs,
+                                const uint32_t mlo, const uint32_t mhi, const uint32_t arcLo, const uint32_t arcHi,
+                                const uint32_t noffers, const int32_t now, const uint32_t snapPool, const bool lastOfRun) {
+    const double d = sh.runD;
+    const uint32_t hNew = sh.runH + 1;
+    const double best0 = sh.best; // conservative (>= the running value) for pruning / queue admission, as in the other engines
+    const uint32_t nm = mhi - mlo;
+    // ---- (1) offers: one thread per arc -------------------------------------------------------------------------------
+    int myArcs = 0;
+    for (uint32_t j = threadIdx.x; j < noffers; j += blockDim.x) {
+        uint32_t r, a;
+        if (arcHi > arcLo) {
+            r = 0;
+            a = arcLo + j;
+        } else { // member of offer j: the last r with offs[r] <= j
+            uint32_t lo = 0, hi = nm;
+            while (hi - lo > 1) {
+                const uint32_t mid = (lo + hi) >> 1;
+                if (offs[mid] <= j)
+                    lo = mid;
+                else
+                    hi = mid;
+            }
+            r = lo;
+            a = j - offs[r];
+        }
+        const uint32_t cur = X.run[mlo + r];
+        const Arc arc = G.arcs[G.rowptr[cur >> 1] + a];
+        const uint32_t nbr = (uint32_t)arc.nbr & 0x7FFFFFFFu;
+        bool act = arc.nbr >= 0; // blacklisted neighbours are skipped (:98-99)
+        if (G.blStamp && act) act = !stampedBefore(G, nbr, now);
+        myArcs += act ? 1 : 0;
+        X.offNbr[j] = nbr;
+        X.offCur[j] = cur;
+        X.offW[j] = arc.w;
+        keys[j] = act ? (((unsigned long long)nbr << 32) | j) : ~0ull; // skipped arcs sort behind everything
+    }
+    const uint32_t np = nextPow2(noffers);
+    for (uint32_t j = noffers + threadIdx.x; j < np; j += blockDim.x) keys[j] = ~0ull;
+    if (myArcs) atomicAdd(reinterpret_cast<unsigned long long *>(&sh.arcs), (unsigned long long)myArcs);
+    if (threadIdx.x == 0) {
+        sh.nev = 0;
+        sh.nseg = 0;
+        sh.cutoff = -1;
+    }
+    // ---- (2) group by target vertex, in sequence order ------------------------------------------------------------------
+    bitonicSortShared(keys, np);
+    // ---- (3) one thread per target vertex: updatePaths (:59-84) for its offers, in order -------------------------------
+    for (uint32_t p = threadIdx.x; p < noffers; p += blockDim.x) {
+        const unsigned long long kp = keys[p];
+        if (kp == ~0ull) continue;
+        const uint32_t v = (uint32_t)(kp >> 32);
+        if (p > 0 && (uint32_t)(keys[p - 1] >> 32) == v) continue; // not the first offer to v
+        Entry e = loadEntry(&M.tab[v]);
+        const Entry old = e;
+        const uint2 oldPred = make_uint2(M.pred[2 * v], M.pred[2 * v + 1]);
+        const bool fresh = e.key == kEmptyKey;
+        uint32_t pr0 = oldPred.x, pr1 = oldPred.y;
+        bool ch0 = false, ch1 = false;
+        for (uint32_t q = p; q < noffers; ++q) {
+            const unsigned long long kq = keys[q];
+            if ((uint32_t)(kq >> 32) != v) break;
+            const uint32_t j = (uint32_t)kq;
+            const uint32_t cur = X.offCur[j];
+            const uint32_t side = cur & 1u;
+            const double w = X.offW[j];
+            const double dS = d + w, dX = d + (1.0 - w);
+            const bool creatS = dS + d <= best0, creatX = dX + d <= best0; // label pruning, see ocw_search.cuh
+            double dA = side ? e.d1 : e.d0, dB = side ? e.d0 : e.d1;
+            uint32_t hA = side ? e.h1 : e.h0, hB = side ? e.h0 : e.h1;
+            bool accS, accX;
+            if (dA >= kUnlabelled)
+                accS = dS < kInfDist && (creatS || dS + dB <= best0);
+            else
+                accS = (dA == dS) ? (hNew < hA) : (dS < dA);
+            if (accS) {
+                dA = dS;
+                hA = hNew;
+                const double D = dA + dB;
+                if (D <= best0) {
+                    const uint32_t k = atomicAdd(&sh.nev, 1u);
+                    X.evNode[k] = 2 * v + side;
+                    X.evSeq[k] = 2 * j;
+                    X.evD[k] = D;
+                    X.evH[k] = hA + hB;
+                }
+            }
+            if (dB >= kUnlabelled)
+                accX = dX < kInfDist && (creatX || dX + dA <= best0);
+            else
+                accX = (dB == dX) ? (hNew < hB) : (dX < dB);
+            if (accX) {
+                dB = dX;
+                hB = hNew;
+                const double D = dB + dA;
+                if (D <= best0) {
+                    const uint32_t k = atomicAdd(&sh.nev, 1u);
+                    X.evNode[k] = 2 * v + (side ^ 1u);
+                    X.evSeq[k] = 2 * j + 1;
+                    X.evD[k] = D;
+                    X.evH[k] = hB + hA;
+                }
+            }
+            if (accS || accX) {
+                if (side) {
+                    e.d1 = dA;
+                    e.h1 = hA;
+                    e.d0 = dB;
+                    e.h0 = hB;
+                } else {
+                    e.d0 = dA;
+                    e.h0 = hA;
+                    e.d1 = dB;
+                    e.h1 = hB;
+                }
+                if (accS) {
+                    (side ? pr1 : pr0) = cur;
+                    (side ? ch1 : ch0) = true;
+                }
+                if (accX) {
+                    (side ? pr0 : pr1) = cur;
+                    (side ? ch0 : ch1) = true;
+                }
+            }
+        }
+        if (!(ch0 || ch1)) continue;
+        // undo log of this vertex (a chunk is rolled back when the search ends in its middle)
+        const uint32_t sidx = atomicAdd(&sh.nseg, 1u);
+        X.undoVtx[sidx] = v;
+        X.undoEntry[sidx] = old;
+        X.undoPred[sidx] = oldPred;
+        const uint2 oldQ = fresh ? make_uint2(kNoQpos, kNoQpos) : make_uint2(X.qpos[2 * v], X.qpos[2 * v + 1]);
+        X.undoQpos[sidx] = oldQ;
+        e.key = v;
+        if (fresh) {
+            e.flags = 0;
+            const uint32_t ti = atomicAdd(&sh.touchedN, 1u);
+            if (ti < M.caps.touchedCap)
+                M.touched[ti] = v;
+            else
+                sh.overflow = 1;
+        }
+        storeEntry(&M.tab[v], e);
+        M.pred[2 * v] = pr0;
+        M.pred[2 * v + 1] = pr1;
+        // queue: the superseded key dies, the new one is appended if the node can still be extracted
+        uint32_t nq0 = oldQ.x, nq1 = oldQ.y;
+#pragma unroll
+        for (int sd = 0; sd < 2; ++sd) {
+            if (!(sd ? ch1 : ch0)) continue;
+            const uint32_t oq = sd ? oldQ.y : oldQ.x;
+            if (oq != kNoQpos) M.heap[oq].hi = kDeadKey;
+            const double dn = sd ? e.d1 : e.d0;
+            uint32_t nq = kNoQpos;
+            if (2 * dn <= best0) {
+                nq = atomicAdd(&sh.poolN, 1u);
+                if (nq < M.caps.heapCap) {
+                    HeapEnt ke;
+                    ke.hi = (unsigned long long)__double_as_longlong(dn);
+                    ke.lo = ((unsigned long long)hNew << 32) | (2 * v + sd);
+                    M.heap[nq] = ke;
+                } else {
+                    sh.overflow = 1;
+                    nq = kNoQpos;
+                }
+            }
+            (sd ? nq1 : nq0) = nq;
+        }
+        X.qpos[2 * v] = nq0;
+        X.qpos[2 * v + 1] = nq1;
+    }
+    __syncthreads();
+    // ---- (4) the record logic (:71-82), serially, in the sequential order of the events --------------------------------
+    const uint32_t nev = sh.nev;
+    if (nev > 0) {
+        const uint32_t ne2 = nextPow2(nev);
+        for (uint32_t k = threadIdx.x; k < ne2; k += blockDim.x) keys[k] = k < nev ? (((unsigned long long)X.evSeq[k] << 32) | k) : ~0ull;
+        bitonicSortShared(keys, ne2);
+        if (threadIdx.x == 0) {
+            double best = sh.best;
+            uint32_t bestHop = sh.bestHop, histN = sh.histN;
+            int cutoff = -1;
+            uint32_t curRank = 0xFFFFFFFFu;
+            for (uint32_t q = 0; q < nev; ++q) {
+                const uint32_t k = (uint32_t)keys[q];
+                const uint32_t j = X.evSeq[k] >> 1;
+                // rank of the member that made this offer (members are distinct ids in ascending order)
+                uint32_t r = 0;
+                if (arcHi <= arcLo) {
+                    uint32_t lo = 0, hi = nm;
+                    while (hi - lo > 1) {
+                        const uint32_t mid = (lo + hi) >> 1;
+                        if (offs[mid] <= j)
+                            lo = mid;
+                        else
+                            hi = mid;
+                    }
+                    r = lo;
+                }
+                if (r != curRank) { // the loop condition in front of member r: 2 d <= bestDist (:90)
+                    if (curRank != 0xFFFFFFFFu && 2 * d > best) {
+                        cutoff = (int)curRank;
+                        break;
+                    }
+                    curRank = r;
+                }
+                const double D = X.evD[k];
+                const uint32_t H = X.evH[k];
+                bool push = false;
+                if (D < best || (D == best && H < bestHop)) {
+                    best = D;
+                    bestHop = H;
+                    push = true;
+                } else if (D == best && H < 2 * bestHop) {
+                    push = true;
+                }
+                if (push) {
+                    if (histN >= M.caps.histCap) {
+                        sh.overflow = 1;
+                        break;
+                    }
+                    M.hist[histN++] = X.evNode[k];
+                }
+            }
+            // ended in front of a later member of this chunk (or of this run): everything after member `cutoff` is undone
+            if (cutoff < 0 && 2 * d > best && curRank != 0xFFFFFFFFu && (curRank + 1 < nm || !lastOfRun) && arcHi <= arcLo) cutoff = (int)curRank;
+            if (cutoff >= 0 && (uint32_t)cutoff + 1 >= nm) { // nothing of this chunk lies behind it: the search just ends here
+                sh.done = 1;
+                cutoff = -1;
+            }
+            if (cutoff < 0) {
+                sh.best = best;
+                sh.bestHop = bestHop;
+                sh.histN = histN;
+            }
+            sh.cutoff = cutoff;
+        }
+        __syncthreads();
+    }
+    if (sh.cutoff >= 0) { // roll the chunk back; the caller redoes members [mlo, mlo + cutoff] and ends the search
+        const uint32_t nseg = sh.nseg;
+        for (uint32_t s = threadIdx.x; s < nseg; s += blockDim.x) {
+            const uint32_t v = X.undoVtx[s];
+            const Entry old = X.undoEntry[s];
+            storeEntry(&M.tab[v], old);
+            M.pred[2 * v] = X.undoPred[s].x;
+            M.pred[2 * v + 1] = X.undoPred[s].y;
+            const uint2 oq = X.undoQpos[s];
+            X.qpos[2 * v] = oq.x;
+            X.qpos[2 * v + 1] = oq.y;
+            if (oq.x != kNoQpos) { // revive the keys this chunk killed
+                HeapEnt ke;
+                ke.hi = (unsigned long long)__double_as_longlong(old.d0);
+                ke.lo = ((unsigned long long)old.h0 << 32) | (2 * v);
+                M.heap[oq.x] = ke;
+            }
+            if (oq.y != kNoQpos) {
+                HeapEnt ke;
+                ke.hi = (unsigned long long)__double_as_longlong(old.d1);
+                ke.lo = ((unsigned long long)old.h1 << 32) | (2 * v + 1);
+                M.heap[oq.y] = ke;
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) sh.poolN = snapPool;
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(kRunThreads) ocwSearchRunsKernel(const GraphDev G, const SearchParams P, const RawOut R, const TileCaps caps,
+                                                                   unsigned char *scratch) {
+    __shared__ RunShared sh;
+    __shared__ unsigned long long keys[2 * kRunOfferCap]; // offers: <= cap keys; events: <= 2 cap keys; member sort: 4 cap ids
+    __shared__ uint32_t offs[kRunOfferCap + 1];
+    __shared__ unsigned long long redHi[kRunThreads / 32], redLo[kRunThreads / 32];
+    const size_t tb = tileBytes(caps), xb = runScratchBytes(G.n);
+    unsigned char *tile = scratch + (size_t)blockIdx.x * (tb + xb);
+    TileMem M;
+    carveTileMem(M, tile, caps);
+    RunScratch X;
+    carveRunScratch(X, tile + tb, G.n);
+    const Tile<32> T;
+    const long long total = P.worklist ? P.nwork : P.nsrc;
+    const int maxInter = min(P.maxInter, 16);
+    uint32_t sel[16];
+    long long accArcs = 0, accSettled = 0, accSources = 0;
+
+    while (true) {
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            const long long wi = (long long)atomicAdd(P.queueCounter, 1ull);
+            sh.wi = wi;
+            sh.skip = 0;
+            if (wi < total) {
+                const int32_t srcIdx = P.worklist ? P.worklist[wi] : (int32_t)wi;
+                const uint32_t src = P.sources ? (uint32_t)P.sources[srcIdx]
+                                               : (uint32_t)(((((long long)(srcIdx >> 1)) * P.srcStride + P.srcBegin) << 1) | (srcIdx & 1));
+                sh.srcIdx = srcIdx;
+                sh.src = src;
+                // `if (blacklist_[currentSource_]) return {}` -- indexed with the DOUBLED id (ocw_seperator.cpp:334, quirk A.7.1)
+                if ((long long)src < G.n && (G.blStamp ? stampedBefore(G, src, srcIdx) : P.blacklist[src] != 0)) sh.skip = 1;
+                if ((long long)(src >> 1) >= G.n) sh.skip = 1;
+            }
+        }
+        __syncthreads();
+        if (sh.wi >= total) break;
+        if (sh.skip) continue;
+        const uint32_t src = sh.src;
+        const int32_t srcIdx = sh.srcIdx;
+        const uint32_t target = src ^ 1u;
+        // ---- distances_[source] = 0, hopDistances_[source] = 0, heap.push(source)   (:54-57) ----------------------------
+        if (threadIdx.x == 0) {
+            Entry e = emptyEntry();
+            e.key = src >> 1;
+            if (src & 1u) {
+                e.d1 = 0.0;
+                e.h1 = 0;
+            } else {
+                e.d0 = 0.0;
+                e.h0 = 0;
+            }
+            storeEntry(&M.tab[src >> 1], e);
+            M.touched[0] = src >> 1;
+            X.qpos[src] = 0;
+            X.qpos[src ^ 1u] = kNoQpos;
+            HeapEnt k0;
+            k0.hi = 0ull;
+            k0.lo = (unsigned long long)src;
+            M.heap[0] = k0;
+            sh.best = P.bestInit;
+            sh.bestHop = 0;
+            sh.histN = 0;
+            sh.poolN = 1;
+            sh.touchedN = 1;
+            sh.arcs = 0;
+            sh.settled = 0;
+            sh.overflow = 0;
+            sh.done = 0;
+        }
+        __syncthreads();
+
+        while (!sh.done && !sh.overflow) {
+            // ---- the minimal key of the pool: 128-bit lexicographic minimum over the live keys -------------------------------
+            const uint32_t poolN = sh.poolN;
+            unsigned long long mhi = ~0ull, mlo = ~0ull;
+            for (uint32_t i = threadIdx.x; i < poolN; i += blockDim.x) {
+                const HeapEnt k = M.heap[i];
+                if (k.hi != kDeadKey && keyLess(k.hi, k.lo, mhi, mlo)) {
+                    mhi = k.hi;
+                    mlo = k.lo;
+                }
+            }
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) {
+                const unsigned long long ohi = __shfl_xor_sync(0xFFFFFFFFu, mhi, off), olo = __shfl_xor_sync(0xFFFFFFFFu, mlo, off);
+                if (keyLess(ohi, olo, mhi, mlo)) {
+                    mhi = ohi;
+                    mlo = olo;
+                }
+            }
+            if ((threadIdx.x & 31) == 0) {
+                redHi[threadIdx.x >> 5] = mhi;
+                redLo[threadIdx.x >> 5] = mlo;
+            }
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                for (int w = 1; w < kRunThreads / 32; ++w)
+                    if (keyLess(redHi[w], redLo[w], mhi, mlo)) {
+                        mhi = redHi[w];
+                        mlo = redLo[w];
+                    }
+                sh.minHi = mhi;
+                sh.minLo = mlo;
+                sh.runLen = 0;
+                // loop condition of ocw_seperator.cpp:88-90 for the first member of the run
+                const double dmin = __longlong_as_double((long long)mhi);
+                if (mhi == ~0ull || (uint32_t)mlo == target || 2 * dmin > sh.best) sh.done = 1;
+                sh.runD = dmin;
+                sh.runH = (uint32_t)(mlo >> 32);
+            }
+            __syncthreads();
+            if (sh.done) break;
+            // ---- collect the run: every live key with the minimal (dist, hops); the keys leave the pool -------------------
+            {
+                const unsigned long long dhi = sh.minHi;
+                const uint32_t hmin = sh.runH;
+                for (uint32_t i = threadIdx.x; i < poolN; i += blockDim.x) {
+                    const HeapEnt k = M.heap[i];
+                    if (k.hi == dhi && (uint32_t)(k.lo >> 32) == hmin) {
+                        const uint32_t pos = atomicAdd(&sh.runLen, 1u);
+                        if (pos < X.runCap) X.run[pos] = (uint32_t)k.lo;
+                        M.heap[i].hi = kDeadKey;
+                        X.qpos[(uint32_t)k.lo] = kNoQpos;
+                    }
+                }
+            }
+            __syncthreads();
+            uint32_t runLen = sh.runLen;
+            SMS_CHK(runLen >= 1 && runLen <= X.runCap);
+            // ---- in id order; the target ends the run in front of itself (:89) ------------------------------------------------
+            if (runLen > 1) {
+                const uint32_t np = nextPow2(runLen);
+                if (np <= 4 * kRunOfferCap) {
+                    uint32_t *k32 = reinterpret_cast<uint32_t *>(keys);
+                    for (uint32_t i = threadIdx.x; i < np; i += blockDim.x) k32[i] = i < runLen ? X.run[i] : 0xFFFFFFFFu;
+                    // 32-bit bitonic network in shared memory
+                    for (uint32_t size = 2; size <= np; size <<= 1)
+                        for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
+                            __syncthreads();
+                            for (uint32_t t = threadIdx.x; t < (np >> 1); t += blockDim.x) {
+                                const uint32_t lo = 2 * t - (t & (stride - 1)), hi = lo + stride;
+                                const bool up = (lo & size) == 0;
+                                const uint32_t a = k32[lo], b = k32[hi];
+                                if ((a > b) == up) {
+                                    k32[lo] = b;
+                                    k32[hi] = a;
+                                }
+                            }
+                        }
+                    __syncthreads();
+                    for (uint32_t i = threadIdx.x; i < runLen; i += blockDim.x) X.run[i] = k32[i];
+                } else {
+                    for (uint32_t i = runLen + threadIdx.x; i < np; i += blockDim.x) X.run[i] = 0xFFFFFFFFu;
+                    bitonicSortGlobal32(X.run, np);
+                }
+                __syncthreads();
+            }
+            bool endsAtTarget = false;
+            {
+                // position of the target in the sorted run, if it is a member (binary search by every thread: uniform)
+                uint32_t lo = 0, hi = runLen;
+                while (lo < hi) {
+                    const uint32_t mid = (lo + hi) >> 1;
+                    if (X.run[mid] < target)
+                        lo = mid + 1;
+                    else
+                        hi = mid;
+                }
+                if (lo < runLen && X.run[lo] == target) {
+                    endsAtTarget = true;
+                    runLen = lo; // members behind the target are never extracted; the search ends when the target is on top
+                }
+            }
+            // ---- the members, chunk by chunk ----------------------------------------------------------------------------------
+            uint32_t m0 = 0;
+            while (m0 < runLen && !sh.done && !sh.overflow) {
+                // settled bits + prefix of the degrees of the next members, as many as fit a chunk
+                const uint32_t window = min(runLen - m0, kRunOfferCap);
+                __syncthreads();
+                for (uint32_t i = threadIdx.x; i < window; i += blockDim.x) { // degrees first (in parallel), then their prefix
+                    const uint32_t u = X.run[m0 + i] >> 1;
+                    offs[i] = (uint32_t)(G.rowptr[u + 1] - G.rowptr[u]);
+                }
+                __syncthreads();
+                if (threadIdx.x == 0) {
+                    uint32_t acc = 0, cnt = 0;
+                    for (; cnt < window; ++cnt) {
+                        const uint32_t deg = offs[cnt];
+                        if (cnt > 0 && acc + deg > kRunOfferCap) break;
+                        offs[cnt] = acc;
+                        acc += deg;
+                        if (acc > kRunOfferCap) { // a single row longer than a chunk: processed in pieces
+                            cnt = 1;
+                            break;
+                        }
+                    }
+                    offs[cnt] = acc;
+                    sh.nseg = cnt; // (re-used as a mailbox: members in this chunk)
+                    sh.nev = acc;  //                        offers in this chunk
+                }
+                __syncthreads();
+                const uint32_t cnt = sh.nseg, tot = sh.nev;
+                const bool lastOfRun = (m0 + cnt >= runLen) && !endsAtTarget;
+                __syncthreads();
+                const uint32_t snapPool = sh.poolN, snapTouched = sh.touchedN;
+                const long long snapArcs = sh.arcs;
+                if (tot <= kRunOfferCap) {
+                    if (tot > 0) runChunk(G, M, X, sh, keys, offs, m0, m0 + cnt, 0, 0, tot, srcIdx, snapPool, lastOfRun);
+                    __syncthreads();
+                    int c = tot > 0 ? sh.cutoff : -1;
+                    if (c >= 0) {
+                        // the search ends behind member m0 + c: redo the chunk up to it (no cutoff possible this time)
+                        __syncthreads();
+                        if (threadIdx.x == 0) {
+                            sh.touchedN = snapTouched;
+                            sh.arcs = snapArcs;
+                        }
+                        __syncthreads();
+                        const uint32_t cnt2 = (uint32_t)c + 1;
+                        const uint32_t tot2 = offs[cnt2];
+                        if (tot2 > 0) runChunk(G, M, X, sh, keys, offs, m0, m0 + cnt2, 0, 0, tot2, srcIdx, sh.poolN, true);
+                        __syncthreads();
+                        SMS_CHK(sh.cutoff < 0);
+                        if (threadIdx.x == 0) {
+                            sh.settled += cnt2;
+                            sh.done = 1;
+                        }
+                        for (uint32_t i = threadIdx.x; i < cnt2; i += blockDim.x) {
+                            const uint32_t id = X.run[m0 + i];
+                            atomicOr(&M.tab[id >> 1].flags, 1u << (id & 1u));
+                        }
+                        __syncthreads();
+                        break;
+                    }
+                    if (threadIdx.x == 0) sh.settled += cnt;
+                    for (uint32_t i = threadIdx.x; i < cnt; i += blockDim.x) {
+                        const uint32_t id = X.run[m0 + i];
+                        atomicOr(&M.tab[id >> 1].flags, 1u << (id & 1u));
+                    }
+                } else {
+                    // one member with a long row: its arcs in pieces (offers of one member never meet at a vertex)
+                    for (uint32_t a0 = 0; a0 < tot && !sh.overflow; a0 += kRunOfferCap) {
+                        const uint32_t a1 = min(a0 + kRunOfferCap, tot);
+                        __syncthreads();
+                        runChunk(G, M, X, sh, keys, offs, m0, m0 + 1, a0, a1, a1 - a0, srcIdx, sh.poolN, lastOfRun);
+                        __syncthreads();
+                    }
+                    if (threadIdx.x == 0) {
+                        sh.settled += 1;
+                        const uint32_t id = X.run[m0];
+                        M.tab[id >> 1].flags |= 1u << (id & 1u);
+                    }
+                }
+                __syncthreads();
+                m0 += cnt;
+                // the loop condition in front of the next member (:90); within a chunk the replay has tested it already
+                if (threadIdx.x == 0 && 2 * sh.runD > sh.best && (m0 < runLen || endsAtTarget)) sh.done = 1;
+                __syncthreads();
+            }
+            if (endsAtTarget) {
+                __syncthreads();
+                if (threadIdx.x == 0) sh.done = 1;
+                __syncthreads();
+            }
+        }
+        __syncthreads();
+
+        // ---- everything after the search: the code shared with the other engines, by the first warp --------------------------
+        SrcState S;
+        S.best = sh.best;
+        S.bestHop = (double)sh.bestHop;
+        S.histN = sh.histN;
+        S.heapN = 0;
+        S.touchedN = min(sh.touchedN, M.caps.touchedCap);
+        S.arcs = sh.arcs;
+        S.settled = sh.settled;
+        S.steps = 0;
+        S.loads = 0;
+        S.overflow = sh.overflow;
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            if (!S.overflow && S.histN > 0) {
+                const int nsel = selectIntermediates<32>(T, M, S, maxInter, sel);
+                if (!S.overflow && T.lane == 0) {
+                    Emitter E;
+                    E.R = &R;
+                    E.srcIdx = srcIdx;
+                    E.seq = 0;
+                    E.tier = P.tier;
+                    for (int r = 0; r < nsel; ++r) {
+                        const int W = buildWalk(G, M, sel[r], src, srcIdx);
+                        if (W < 0) {
+                            S.overflow = 1;
+                            break;
+                        }
+                        simpleOddCyclesAndExtract(G, M, S, E, W);
+                        if (S.overflow) break;
+                    }
+                }
+                S.overflow = T.shfl(S.overflow, 0);
+            }
+            if (!S.overflow && G.blStampNext) verbatimSourceDone<32>(T, G, src, srcIdx, S.histN == 0);
+            if (!S.overflow) {
+                if (P.exportLabels) {
+                    for (uint32_t i = T.lane; i < S.touchedN; i += 32) {
+                        const Entry e = loadEntry(&M.tab[M.touched[i]]);
+#pragma unroll
+                        for (int sd = 0; sd < 2; ++sd) {
+                            const double dd = sd ? e.d1 : e.d0;
+                            if (dd >= kUnlabelled) continue;
+                            const long long li = (long long)atomicAdd(&R.counters[5], 1ull);
+                            if (li < R.labCap) {
+                                R.labSrc[li] = srcIdx;
+                                R.labNode[li] = (int32_t)(2 * e.key + sd);
+                                R.labDist[li] = dd;
+                                R.labHops[li] = (int32_t)(sd ? e.h1 : e.h0);
+                            }
+                        }
+                    }
+                }
+                if (T.lane == 0) {
+                    R.srcTier[srcIdx] = (int8_t)P.tier;
+                    if (R.srcWork) R.srcWork[srcIdx] = (uint32_t)min(S.settled, 0xFFFFFFFFll);
+                    if (R.srcArcs) {
+                        R.srcArcs[srcIdx] = S.arcs;
+                        R.srcSettled[srcIdx] = S.settled;
+                    }
+                    accArcs += S.arcs;
+                    accSettled += S.settled;
+                    accSources++;
+                }
+            } else if (T.lane == 0) {
+                const unsigned long long k = atomicAdd(P.ovfCount, 1ull);
+                P.ovfList[k] = srcIdx;
+            }
+        }
+        __syncthreads();
+        // leave the table clean for the next source
+        const uint32_t tn = min(sh.touchedN, M.caps.touchedCap);
+        for (uint32_t i = threadIdx.x; i < tn; i += blockDim.x) storeEntry(&M.tab[M.touched[i]], emptyEntry());
+    }
+    if (threadIdx.x == 0 && accSources) {
+        atomicAdd(&R.counters[2], (unsigned long long)accArcs);
+        atomicAdd(&R.counters[3], (unsigned long long)accSettled);
+        atomicAdd(&R.counters[P.runSlot], (unsigned long long)accSources);
+    }
+}
+
+} // namespace smsgpu

@@ -91,6 +91,7 @@ struct TierCfg {
     size_t smemBytes = 0;   // dynamic shared memory per CTA (tier 0: whole tiles, tier 1: hot words)
     bool hotInSmem = false; // fast engine: where the bucket counters and the presence bitmap live
     bool pairs = false;     // pairs engine: two tiles per warp
+    bool runs = false;      // runs engine (ocw_search_runs.cuh): one tile per CTA of kRunThreads threads
     uint64_t stampNext = 0; // fast engine: stamps handed out so far for this scratch (ocw_search_fast.cuh)
     DevBuf scratch;
     bool ready = false;
@@ -286,6 +287,10 @@ cudaError_t launchSearch(smsgpu_ctx *c, int tierIdx, const GraphDev &G, const Se
         return cudaGetLastError();
     }
     if (t.caps.nbuckets) return launchSearchT<false, true>(c, t, G, P, R, st, ctas);
+    if (t.runs) {
+        ocwSearchRunsKernel<<<ctas, kRunThreads, 0, st>>>(G, P, R, t.caps, t.scratch.as<unsigned char>());
+        return cudaGetLastError();
+    }
     return launchSearchT<false, false>(c, t, G, P, R, st, ctas);
 }
 template <bool SMEM, bool FAST>
@@ -367,14 +372,30 @@ void configureTiers(smsgpu_ctx *c) {
         t.caps = TileCaps{(uint32_t)n, 0, 1, (uint32_t)n + (uint32_t)tw, big, big,
                           (uint32_t)std::min<uint64_t>(2 * n + 2, 1u << 28),
                           (uint32_t)std::min<uint64_t>(4 * m + 16, 1u << 22)};
+        // the runs engine (a CTA per source, whole runs of equal (dist, hops) settled at once); SMSGPU_RUNS=0 puts the
+        // one-key-at-a-time heap engine back (kept for comparison and tested)
+        const char *er = std::getenv("SMSGPU_RUNS");
+        t.runs = !(er && er[0] == '0');
     }
 }
 
 int ensureTierScratch(smsgpu_ctx *ctx, int ti) {
     TierCfg &t = ctx->tier[ti];
     if (t.ready) return 0;
-    const size_t tb = tileBytes(t.caps) + (t.hotInSmem ? 0 : hotBytes(t.caps)); // tile stride
-    if (ti >= 2) { // large tiles: as many as fit in a quarter of the free memory, at most the resident warps
+    const size_t tb = tileBytes(t.caps) + (t.hotInSmem ? 0 : hotBytes(t.caps)) + (t.runs ? runScratchBytes(ctx->n) : 0); // tile stride
+    if (t.runs) { // one tile per CTA: as many CTAs as can be resident, as far as a quarter of the free memory goes
+        size_t freeB = 0, totalB = 0;
+        CU(cudaMemGetInfo(&freeB, &totalB));
+        int perSm = 1;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, ocwSearchRunsKernel, kRunThreads, 0) != cudaSuccess) {
+            (void)cudaGetLastError();
+            perSm = 1;
+        }
+        long long nt = std::min<long long>((long long)((freeB / 4) / tb), (long long)ctx->smCount * std::max(perSm, 1));
+        if (nt < 1) return fail(ctx, SMSGPU_ERR_NOMEM, "runs tier needs %zu bytes per tile, %zu free", tb, freeB);
+        t.ctas = (int)nt;
+        t.ntiles = nt;
+    } else if (ti >= 2) { // large tiles: as many as fit in a quarter of the free memory, at most the resident warps
         size_t freeB = 0, totalB = 0;
         CU(cudaMemGetInfo(&freeB, &totalB));
         long long nt = (long long)((freeB / 4) / tb);
