@@ -85,9 +85,23 @@ def build(force: bool = False, verbose: bool = False, debug: bool = False) -> st
     return LIB
 
 
+def build_variant(name: str, flags: list[str]) -> str:
+    """Experiment builds (profiles/README.md): csrc/libsmsgpu_<name>.so with extra nvcc flags, selected at run time with
+    SMSGPU_LIB=<path>.  Never the default library."""
+    out = os.path.join(CSRC, f"libsmsgpu_{name}.so")
+    cmd = [_nvcc(), *NVCC_FLAGS, *flags, "-o", out, *[os.path.join(CSRC, s) for s in SOURCES], "-ldl"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("nvcc failed:\n" + r.stdout + r.stderr)
+    return out
+
+
 if __name__ == "__main__":
     import sys
-    if "--debug" in sys.argv:
+    if "--variant" in sys.argv:
+        i = sys.argv.index("--variant")
+        print(build_variant(sys.argv[i + 1], sys.argv[i + 2:]))
+    elif "--debug" in sys.argv:
         print(build(debug=True))
     else:
         print(build(force=True, verbose=True))

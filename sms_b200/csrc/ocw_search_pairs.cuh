@@ -235,6 +235,9 @@ __device__ __noinline__ int finishSourcePairs(const PairsKArgs *K, unsigned char
 #define PCLK(i_) ((void)0)
 #endif
 
+// VERB: SMSGPU_MODE_VERBATIM (time-stamped blacklist); a template parameter so that the independent-source build of the hot
+// loop carries none of its tests (measured: the run-time test cost the 1M-source round 1.5 %)
+template <bool VERB>
 __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
     ocwSearchPairsKernel(const GraphDev G, const PairsParams Q, const SearchParams P, const RawOut R, const TileCaps caps,
                          unsigned char *scratch) {
@@ -338,7 +341,7 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
                     const int32_t i0 = P.worklist ? P.worklist[w32] : (int32_t)w32;
                     const uint32_t s0 = P.sources ? (uint32_t)P.sources[i0] : (uint32_t)(((((long long)(i0 >> 1)) * P.srcStride + P.srcBegin) << 1) | (i0 & 1));
                     // `if (blacklist_[currentSource_]) return {}` -- indexed with the DOUBLED id (ocw_seperator.cpp:334)
-                    const bool skip0 = ((long long)s0 < G.n && (G.blStamp ? stampedBefore(G, s0, i0) : P.blacklist[s0] != 0)) || (long long)(s0 >> 1) >= G.n;
+                    const bool skip0 = ((long long)s0 < G.n && (VERB ? stampedBefore(G, s0, i0) : P.blacklist[s0] != 0)) || (long long)(s0 >> 1) >= G.n;
                     if (second) { // skip test already passed when the item was fetched
                         wi = w32;
                         src = s0;
@@ -350,7 +353,7 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
                         if (have1) {
                             const int32_t i1 = P.worklist ? P.worklist[w32 + 1] : (int32_t)(w32 + 1);
                             s1 = P.sources ? (uint32_t)P.sources[i1] : (uint32_t)(((((long long)(i1 >> 1)) * P.srcStride + P.srcBegin) << 1) | (i1 & 1));
-                            have1 = !(((long long)s1 < G.n && (G.blStamp ? stampedBefore(G, s1, i1) : P.blacklist[s1] != 0)) || (long long)(s1 >> 1) >= G.n);
+                            have1 = !(((long long)s1 < G.n && (VERB ? stampedBefore(G, s1, i1) : P.blacklist[s1] != 0)) || (long long)(s1 >> 1) >= G.n);
                         }
                         if (!skip0) {
                             wi = w32;
@@ -527,7 +530,7 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
         const uint32_t hNew = (uint32_t)(clo >> 32) + 1;
         const uint32_t stamp = P.stampBase + wi + 1u;
         int32_t nowIdx = 0; // mode V: position of this half's source in the source list (its time stamp)
-        if (G.blStamp && run) nowIdx = P.worklist ? P.worklist[wi] : (int32_t)wi;
+        if (VERB && run) nowIdx = P.worklist ? P.worklist[wi] : (int32_t)wi;
 
         PCLK(2);
         // ---- (4b) bucket exhausted by this extraction: find the next one and issue its loads NOW, so that they are in
@@ -609,7 +612,7 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
 #endif
                 w = arc.w;
                 act = arc.nbr >= 0;    // blacklisted neighbours are skipped (:98-99)
-                if (G.blStamp && act) act = !stampedBefore(G, nbr, nowIdx); // mode V: blacklisted by an earlier source
+                if (VERB && act) act = !stampedBefore(G, nbr, nowIdx); // mode V: blacklisted by an earlier source
             }
             arcsN += __popc((__ballot_sync(FULL, act) >> gbase) & 0xFFFFu);
             PCLK(4);

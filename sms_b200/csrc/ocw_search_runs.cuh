@@ -36,7 +36,23 @@
 namespace smsgpu {
 
 constexpr int kRunThreads = 256;
-constexpr uint32_t kRunOfferCap = 2048; // arcs per chunk (sort buffers in shared memory)
+constexpr uint32_t kRunOfferCap = 1024; // arcs per chunk (sort buffers in shared memory)
+
+#ifdef SMSGPU_RUNS_CLOCKS // instrumentation build: cycles per phase of a chunk, accumulated by thread 0 of CTA 0
+__device__ unsigned long long g_runClk[16];
+#define RCLK(i_)                                                                     \
+    do {                                                                             \
+        if (threadIdx.x == 0 && blockIdx.x == 0) {                                   \
+            const long long now_ = clock64();                                        \
+            atomicAdd(&g_runClk[i_], (unsigned long long)(now_ - rclkLast));         \
+            rclkLast = now_;                                                         \
+        }                                                                            \
+    } while (0)
+#define RCLK_DECL long long rclkLast = clock64()
+#else
+#define RCLK(i_) ((void)0)
+#define RCLK_DECL ((void)0)
+#endif
 
 
 // per-CTA scratch behind the tile (global memory)
@@ -162,6 +178,7 @@ __device__ inline void runChunk(const GraphDev &G, TileMem &M, RunScratch &X, Ru
     const uint32_t hNew = sh.runH + 1;
     const double best0 = sh.best; // conservative (>= the running value) for pruning / queue admission, as in the other engines
     const uint32_t nm = mhi - mlo;
+    RCLK_DECL;
     // ---- (1) offers: one thread per arc -------------------------------------------------------------------------------
     int myArcs = 0;
     for (uint32_t j = threadIdx.x; j < noffers; j += blockDim.x) {
@@ -201,7 +218,9 @@ __device__ inline void runChunk(const GraphDev &G, TileMem &M, RunScratch &X, Ru
         sh.cutoff = -1;
     }
     // ---- (2) group by target vertex, in sequence order ------------------------------------------------------------------
+    RCLK(0);
     bitonicSortShared(keys, np);
+    RCLK(1);
     // ---- (3) one thread per target vertex: updatePaths (:59-84) for its offers, in order -------------------------------
     for (uint32_t p = threadIdx.x; p < noffers; p += blockDim.x) {
         const unsigned long long kp = keys[p];
@@ -327,23 +346,109 @@ __device__ inline void runChunk(const GraphDev &G, TileMem &M, RunScratch &X, Ru
         X.qpos[2 * v + 1] = nq1;
     }
     __syncthreads();
-    // ---- (4) the record logic (:71-82), serially, in the sequential order of the events --------------------------------
+    RCLK(2);
+    // ---- (4) the record logic (:71-82) in the sequential order of the events ------------------------------------------------
+    // bestDist in front of an event is min(bestDist before the chunk, D of every earlier event): a prefix minimum, computed
+    // in parallel.  Only events with D <= that value can touch the record (or end the search); they are replayed serially by
+    // one thread from shared memory -- bestHopDist and the list of intermediates are a true history.
+    RCLK(3);
     const uint32_t nev = sh.nev;
     if (nev > 0) {
         const uint32_t ne2 = nextPow2(nev);
         for (uint32_t k = threadIdx.x; k < ne2; k += blockDim.x) keys[k] = k < nev ? (((unsigned long long)X.evSeq[k] << 32) | k) : ~0ull;
         bitonicSortShared(keys, ne2);
+        RCLK(4);
+        constexpr int IT = 4;
+        __shared__ double wMin[kRunThreads / 32];
+        __shared__ uint32_t wCnt[kRunThreads / 32];
+        __shared__ double carryMin;
+        __shared__ uint32_t carryCnt;
+        __shared__ int stopReplay;
+        __shared__ double sD[kRunThreads * IT];
+        __shared__ uint32_t sH[kRunThreads * IT], sNode[kRunThreads * IT], sRank[kRunThreads * IT];
         if (threadIdx.x == 0) {
-            double best = sh.best;
-            uint32_t bestHop = sh.bestHop, histN = sh.histN;
-            int cutoff = -1;
-            uint32_t curRank = 0xFFFFFFFFu;
-            for (uint32_t q = 0; q < nev; ++q) {
-                const uint32_t k = (uint32_t)keys[q];
-                const uint32_t j = X.evSeq[k] >> 1;
-                // rank of the member that made this offer (members are distinct ids in ascending order)
+            carryMin = sh.best;
+            carryCnt = 0;
+            stopReplay = 0;
+        }
+        __syncthreads();
+        const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
+        for (uint32_t base = 0; base < nev; base += kRunThreads * IT) {
+            uint32_t kk[IT];
+            double dd[IT];
+#pragma unroll
+            for (int i = 0; i < IT; ++i) {
+                const uint32_t q = base + threadIdx.x * IT + i;
+                kk[i] = q < nev ? (uint32_t)keys[q] : 0u;
+                dd[i] = q < nev ? X.evD[kk[i]] : 8.0; // 8.0: larger than any D
+            }
+            double tmin = dd[0];
+#pragma unroll
+            for (int i = 1; i < IT; ++i) tmin = fmin(tmin, dd[i]);
+            double incl = tmin; // inclusive prefix minimum over the lanes, then exclusive over the threads of the CTA
+#pragma unroll
+            for (int off = 1; off < 32; off <<= 1) {
+                const double o = __shfl_up_sync(0xFFFFFFFFu, incl, off);
+                if (lane >= off) incl = fmin(incl, o);
+            }
+            double excl = __shfl_up_sync(0xFFFFFFFFu, incl, 1);
+            if (lane == 0) excl = 8.0;
+            if (lane == 31) wMin[wrp] = incl;
+            __syncthreads(); // (also: every thread has read its keys before the candidates overwrite the front of the array)
+            double before = fmin(carryMin, excl);
+            for (int w = 0; w < wrp; ++w) before = fmin(before, wMin[w]);
+            bool cand[IT];
+            int nc = 0;
+#pragma unroll
+            for (int i = 0; i < IT; ++i) {
+                const uint32_t q = base + threadIdx.x * IT + i;
+                cand[i] = q < nev && dd[i] <= before;
+                nc += cand[i] ? 1 : 0;
+                before = fmin(before, dd[i]);
+            }
+            int cincl = nc;
+#pragma unroll
+            for (int off = 1; off < 32; off <<= 1) {
+                const int o = __shfl_up_sync(0xFFFFFFFFu, cincl, off);
+                if (lane >= off) cincl += o;
+            }
+            if (lane == 31) wCnt[wrp] = (uint32_t)cincl;
+            __syncthreads();
+            uint32_t pos = carryCnt + (uint32_t)(cincl - nc);
+            for (int w = 0; w < wrp; ++w) pos += wCnt[w];
+#pragma unroll
+            for (int i = 0; i < IT; ++i)
+                if (cand[i]) keys[pos++] = kk[i]; // in place: the write position never passes the events already consumed
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                double m = carryMin;
+                uint32_t c = carryCnt;
+                for (int w = 0; w < kRunThreads / 32; ++w) {
+                    m = fmin(m, wMin[w]);
+                    c += wCnt[w];
+                }
+                carryMin = m;
+                carryCnt = c;
+            }
+            __syncthreads();
+        }
+        RCLK(5);
+        const uint32_t ncand = carryCnt;
+        // thread 0's view of the record across the batches
+        double best = sh.best;
+        uint32_t bestHop = sh.bestHop, histN = sh.histN;
+        bool drop = false;
+        int cutoff = -1;
+        for (uint32_t base = 0; base < ncand && !stopReplay; base += kRunThreads * IT) {
+            const uint32_t nb = min(ncand - base, (uint32_t)(kRunThreads * IT));
+            for (uint32_t i = threadIdx.x; i < nb; i += blockDim.x) {
+                const uint32_t k = (uint32_t)keys[base + i];
+                sD[i] = X.evD[k];
+                sH[i] = X.evH[k];
+                sNode[i] = X.evNode[k];
                 uint32_t r = 0;
-                if (arcHi <= arcLo) {
+                if (arcHi <= arcLo) { // rank of the member that made the offer
+                    const uint32_t j = X.evSeq[k] >> 1;
                     uint32_t lo = 0, hi = nm;
                     while (hi - lo > 1) {
                         const uint32_t mid = (lo + hi) >> 1;
@@ -354,45 +459,54 @@ __device__ inline void runChunk(const GraphDev &G, TileMem &M, RunScratch &X, Ru
                     }
                     r = lo;
                 }
-                if (r != curRank) { // the loop condition in front of member r: 2 d <= bestDist (:90)
-                    if (curRank != 0xFFFFFFFFu && 2 * d > best) {
-                        cutoff = (int)curRank;
-                        break;
+                sRank[i] = r;
+            }
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                for (uint32_t i = 0; i < nb; ++i) {
+                    const double D = sD[i];
+                    const uint32_t H = sH[i];
+                    bool push = false;
+                    if (D < best || (D == best && H < bestHop)) {
+                        best = D;
+                        bestHop = H;
+                        push = true;
+                    } else if (D == best && H < 2 * bestHop) {
+                        push = true;
                     }
-                    curRank = r;
-                }
-                const double D = X.evD[k];
-                const uint32_t H = X.evH[k];
-                bool push = false;
-                if (D < best || (D == best && H < bestHop)) {
-                    best = D;
-                    bestHop = H;
-                    push = true;
-                } else if (D == best && H < 2 * bestHop) {
-                    push = true;
-                }
-                if (push) {
-                    if (histN >= M.caps.histCap) {
-                        sh.overflow = 1;
-                        break;
+                    if (push) {
+                        if (histN >= M.caps.histCap) {
+                            sh.overflow = 1;
+                            stopReplay = 1;
+                            break;
+                        }
+                        M.hist[histN++] = sNode[i];
                     }
-                    M.hist[histN++] = X.evNode[k];
+                    if (!drop && 2 * d > best) {
+                        // bestDist fell below 2 d: the loop condition (:90) fails in front of the NEXT member.  If that member is
+                        // part of this chunk, its offers (already applied) have to go: roll back, redo up to this member.
+                        drop = true;
+                        if (sRank[i] + 1 < nm) {
+                            cutoff = (int)sRank[i];
+                            stopReplay = 1;
+                            break;
+                        }
+                    }
                 }
             }
-            // ended in front of a later member of this chunk (or of this run): everything after member `cutoff` is undone
-            if (cutoff < 0 && 2 * d > best && curRank != 0xFFFFFFFFu && (curRank + 1 < nm || !lastOfRun) && arcHi <= arcLo) cutoff = (int)curRank;
-            if (cutoff >= 0 && (uint32_t)cutoff + 1 >= nm) { // nothing of this chunk lies behind it: the search just ends here
-                sh.done = 1;
-                cutoff = -1;
-            }
-            if (cutoff < 0) {
+            __syncthreads();
+        }
+        if (threadIdx.x == 0) {
+            if (cutoff < 0 && !sh.overflow) {
                 sh.best = best;
                 sh.bestHop = bestHop;
                 sh.histN = histN;
+                if (drop && !lastOfRun) sh.done = 1; // the next member of the run is never extracted
             }
             sh.cutoff = cutoff;
         }
         __syncthreads();
+        RCLK(6);
     }
     if (sh.cutoff >= 0) { // roll the chunk back; the caller redoes members [mlo, mlo + cutoff] and ends the search
         const uint32_t nseg = sh.nseg;

@@ -275,7 +275,8 @@ cudaError_t launchSearch(smsgpu_ctx *c, int tierIdx, const GraphDev &G, const Se
     const int ctas = ctasCap > 0 ? std::min(ctasCap, t.ctas) : t.ctas;
     if (tierIdx == 0) return launchSearchT<true, false>(c, t, G, P, R, st, ctas);
     if (t.pairs) {
-        cudaError_t e = cudaFuncSetAttribute(ocwSearchPairsKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t.smemBytes);
+        auto kern = G.blStamp ? ocwSearchPairsKernel<true> : ocwSearchPairsKernel<false>;
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t.smemBytes);
         if (e != cudaSuccess) return e;
         PairsKArgs K{G, P, R, t.caps};
         e = c->dPairsArgs.ensure(sizeof K);
@@ -283,7 +284,7 @@ cudaError_t launchSearch(smsgpu_ctx *c, int tierIdx, const GraphDev &G, const Se
         e = cudaMemcpyAsync(c->dPairsArgs.p, &K, sizeof K, cudaMemcpyHostToDevice, st); // pageable source: staged before return
         if (e != cudaSuccess) return e;
         const PairsParams Q{c->dPairsArgs.as<PairsKArgs>(), c->dRowinfo.as<uint2>(), c->pairsScaleU, c->pairsScaleB, c->pairsMirror ? 1 : 0, c->rowShift};
-        ocwSearchPairsKernel<<<ctas, 128, t.smemBytes, st>>>(G, Q, P, R, t.caps, t.scratch.as<unsigned char>());
+        kern<<<ctas, 128, t.smemBytes, st>>>(G, Q, P, R, t.caps, t.scratch.as<unsigned char>());
         return cudaGetLastError();
     }
     if (t.caps.nbuckets) return launchSearchT<false, true>(c, t, G, P, R, st, ctas);
@@ -350,8 +351,8 @@ void configureTiers(smsgpu_ctx *c) {
                 const int pairTiles = 2 * (128 / 32);
                 t.smemBytes = hotBytes(t.caps) * pairTiles + (128 / 32) * kPairsSaveWords * sizeof(uint32_t);
                 int nb2 = 0;
-                cudaFuncSetAttribute(ocwSearchPairsKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t.smemBytes);
-                if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb2, ocwSearchPairsKernel, 128, t.smemBytes) != cudaSuccess) {
+                cudaFuncSetAttribute(ocwSearchPairsKernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t.smemBytes);
+                if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb2, ocwSearchPairsKernel<false>, 128, t.smemBytes) != cudaSuccess) {
                     (void)cudaGetLastError();
                     nb2 = 1;
                 }
@@ -1298,6 +1299,17 @@ int separateLocal(smsgpu_ctx *ctx, const smsgpu_params &P) {
     CutView V{ctx->rNode.as<int32_t>(), ctx->rEid.as<int32_t>(), ctx->rStay.as<uint8_t>(), ctx->rCutOff.as<int32_t>(),
               ctx->rCutLen.as<int32_t>(), ctx->rCutSrc.as<int32_t>(), ctx->rCutSeq.as<int32_t>(), ctx->rValid.as<uint8_t>(),
               rawCuts};
+#ifdef SMSGPU_RUNS_CLOCKS
+    {
+        unsigned long long h[16];
+        if (cudaMemcpyFromSymbol(h, g_runClk, sizeof h) == cudaSuccess) {
+            std::fprintf(stderr, "[smsgpu] runs engine, CTA 0, cycles: offers %llu | sort %llu | apply %llu | - %llu | event sort %llu | prefix-min %llu | replay %llu\n", h[0],
+                         h[1], h[2], h[3], h[4], h[5], h[6]);
+            std::memset(h, 0, sizeof h);
+            cudaMemcpyToSymbol(g_runClk, h, sizeof h);
+        }
+    }
+#endif
     return runDedup(ctx, V, rawNodes, P.dedup != 0, P.dedup != 0, ctx->nranks, ctx->rank, ctx->nsrcGlobal, P.min_efficacy);
 }
 
