@@ -16,14 +16,15 @@
 //   * what one member's relaxations do to a neighbour depends only on that neighbour's label (both sides of a vertex sit
 //     in one entry), so offers to DIFFERENT vertices commute; offers to the same vertex are applied in the sequential
 //     order (member id, adjacency position, stay before cross) by one thread;
-//   * the one thing that is a history -- bestDist / bestHopDist / the list of intermediates (:71-82) -- is replayed
-//     serially over the events (label improvements whose D = dist[t] + dist[t^1] can matter), sorted into that same order;
+//   * the one thing that is a history -- bestDist / bestHopDist / the list of intermediates (:71-82) -- is a function of the
+//     events (label improvements whose D = dist[t] + dist[t^1] can matter) in sequential order: (bestDist, bestHopDist) in front
+//     of an event is the lexicographic minimum of (D, H) over the earlier ones, so the whole record logic is a parallel scan;
 //   * the loop condition of :88-90 is tested before every extraction: the target's position in the run is known up front
 //     (the run is cut there); `2 d > bestDist` can become true in the middle of a run only through the replay, in which
 //     case the chunk of members being processed is rolled back (undo log) and redone up to that member -- it ends the search.
-// A run is processed in chunks of at most kRunOfferCap arcs: (1) one thread per arc computes the offer, (2) the offers are
-// sorted by (target vertex, sequence number) in shared memory, (3) one thread per target vertex applies its offers in order,
-// emits events and queue keys, (4) the events are sorted by sequence number and replayed by one thread.
+// A run is processed in chunks of at most kRunOfferCap arcs, in three parallel phases (runChunk): the offers, one thread per
+// arc, dropped at once unless they can improve the target's label; the surviving offers of a target vertex applied in order by
+// one thread; the record logic as a lexicographic prefix minimum over the events.
 //
 // The queue is an unsorted pool of keys in HBM with tombstones (a per-node position array lets a superseded key be killed
 // directly), scanned by the whole CTA once per run for the minimal (dist, hops) and once to collect the members.
@@ -59,35 +60,23 @@ __device__ unsigned long long g_runClk[16];
 struct RunScratch {
     uint32_t *run;     // [runCap] members of the current run (doubled ids, sorted)
     uint32_t *qpos;    // [2n] pool position of a node's live key, kNoQpos
-    uint32_t *offNbr;  // [cap] per offer: target vertex
-    uint32_t *offCur;  // [cap] the member (doubled id) that makes it
-    double *offW;      // [cap] stay weight of the arc
-    uint32_t *undoVtx; // [cap] per segment (target vertex) of the chunk: undo log
+    uint32_t *undoVtx; // [cap] per target vertex of the chunk: undo log (label, predecessors, queue positions before the chunk)
     Entry *undoEntry;
     uint2 *undoPred, *undoQpos;
-    uint32_t *evNode;  // [2 cap] events: doubled id of the improved node
-    uint32_t *evSeq;   //   sequence number 2 * offer + (cross ? 1 : 0)
-    uint32_t *evH;
-    double *evD;
     uint32_t runCap;
 };
 __host__ __device__ inline size_t runScratchBytes(const long long n) {
     size_t rc = 2;
     while (rc < (size_t)(2 * n + 2)) rc <<= 1; // power of two: the member list is sorted with a bitonic network
     size_t b = rc * 4 + (size_t)(2 * n + 2) * 4;
-    b += (size_t)kRunOfferCap * (4 + 4 + 8 + 4 + 32 + 8 + 8);
-    b += (size_t)2 * kRunOfferCap * (4 + 4 + 4 + 8);
+    b += (size_t)kRunOfferCap * (4 + 32 + 8 + 8);
     return (b + 255) & ~(size_t)255;
 }
 __device__ inline void carveRunScratch(RunScratch &X, unsigned char *p, const long long n) {
     uint32_t rc = 2;
     while (rc < (uint32_t)(2 * n + 2)) rc <<= 1;
     X.runCap = rc;
-    // 8-byte members first
-    X.offW = reinterpret_cast<double *>(p);
-    p += (size_t)kRunOfferCap * 8;
-    X.evD = reinterpret_cast<double *>(p);
-    p += (size_t)2 * kRunOfferCap * 8;
+    // 16-byte members first
     X.undoEntry = reinterpret_cast<Entry *>(p);
     p += (size_t)kRunOfferCap * 32;
     X.undoPred = reinterpret_cast<uint2 *>(p);
@@ -98,17 +87,7 @@ __device__ inline void carveRunScratch(RunScratch &X, unsigned char *p, const lo
     p += (size_t)rc * 4;
     X.qpos = reinterpret_cast<uint32_t *>(p);
     p += (size_t)(2 * n + 2) * 4;
-    X.offNbr = reinterpret_cast<uint32_t *>(p);
-    p += (size_t)kRunOfferCap * 4;
-    X.offCur = reinterpret_cast<uint32_t *>(p);
-    p += (size_t)kRunOfferCap * 4;
     X.undoVtx = reinterpret_cast<uint32_t *>(p);
-    p += (size_t)kRunOfferCap * 4;
-    X.evNode = reinterpret_cast<uint32_t *>(p);
-    p += (size_t)2 * kRunOfferCap * 4;
-    X.evSeq = reinterpret_cast<uint32_t *>(p);
-    p += (size_t)2 * kRunOfferCap * 4;
-    X.evH = reinterpret_cast<uint32_t *>(p);
 }
 
 // state of the search shared by the CTA
@@ -124,26 +103,7 @@ struct RunShared {
     int skip;
 };
 
-// block-wide bitonic sort of n (a power of two) 64-bit keys in shared memory, ascending
-__device__ inline void bitonicSortShared(unsigned long long *k, const uint32_t n) {
-    for (uint32_t size = 2; size <= n; size <<= 1) {
-        for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
-            __syncthreads();
-            for (uint32_t t = threadIdx.x; t < (n >> 1); t += blockDim.x) {
-                const uint32_t lo = 2 * t - (t & (stride - 1));
-                const uint32_t hi = lo + stride;
-                const bool up = (lo & size) == 0;
-                const unsigned long long a = k[lo], b = k[hi];
-                if ((a > b) == up) {
-                    k[lo] = b;
-                    k[hi] = a;
-                }
-            }
-        }
-    }
-    __syncthreads();
-}
-// the same on 32-bit keys in global memory (member lists too long for shared memory)
+// block-wide bitonic sort of n (a power of two) 32-bit keys in global memory, ascending (member lists too long for shared memory)
 __device__ inline void bitonicSortGlobal32(uint32_t *k, const uint32_t n) {
     for (uint32_t size = 2; size <= n; size <<= 1) {
         for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
@@ -168,78 +128,153 @@ __device__ __forceinline__ uint32_t nextPow2(uint32_t v) {
     return p;
 }
 
-// One chunk of the current run: members run[mlo .. mhi) -- or, when arcHi > arcLo, the arcs [arcLo, arcHi) of the single
-// member run[mlo] (a row longer than the chunk capacity).  `offs` (shared) holds the exclusive prefix of the members' degrees.
-// Returns (in sh.cutoff) the rank of the member after whose events 2 d > bestDist became true, or -1.
-__device__ inline void runChunk(const GraphDev &G, TileMem &M, RunScratch &X, RunShared &sh, unsigned long long *keys, uint32_t *offs,
-                                const uint32_t mlo, const uint32_t mhi, const uint32_t arcLo, const uint32_t arcHi,
-                                const uint32_t noffers, const int32_t now, const uint32_t snapPool, const bool lastOfRun) {
+// Shared memory of a CTA (dynamic): everything a chunk needs between its phases.
+constexpr uint32_t kRunHashSlots = 2 * kRunOfferCap;
+constexpr uint32_t kRunHashShift = 32 - 11; // log2(kRunHashSlots) = 11
+static_assert(kRunHashSlots == 2048, "kRunHashShift assumes 2048 slots");
+constexpr uint16_t kRunNil = 0xFFFFu;
+struct RunSmem {
+    double sW[kRunOfferCap];              // surviving offers: stay weight of the arc
+    double evD[2 * kRunOfferCap];         // events, slot 2 j + (cross ? 1 : 0) of arc j: D (8.0 = no event); j order = sequential order
+    uint32_t evH[2 * kRunOfferCap];       //   H
+    uint32_t evNode[2 * kRunOfferCap];    //   doubled id of the improved node
+    uint32_t offs[kRunOfferCap + 1];      // exclusive prefix of the degrees of the chunk's members
+    uint32_t mCur[kRunOfferCap];          // per member: doubled id
+    uint32_t mRow[kRunOfferCap];          //             first arc of its row
+    uint32_t sNbr[kRunOfferCap];          // surviving offers: target vertex
+    uint32_t hKey[kRunHashSlots];         // offers grouped by target vertex: open addressing, kEmptyKey = free
+    uint16_t hHead[kRunHashSlots];        //   head of the vertex' list of surviving offers
+    uint16_t sNext[kRunOfferCap];         //   next offer of the same vertex
+    uint16_t sRank[kRunOfferCap];         // surviving offers: rank of the member that makes it
+    uint16_t sJ[kRunOfferCap];            //                   arc index in the chunk (the sequence number)
+};
+
+struct LexMin { // (D, H) lexicographic minimum: bestDist / bestHopDist after a sequence of events (:73-76)
+    double d;
+    uint32_t h;
+};
+__device__ __forceinline__ LexMin lexmin(const LexMin a, const LexMin b) { return (b.d < a.d || (b.d == a.d && b.h < a.h)) ? b : a; }
+
+// One chunk of the current run: the members with ranks [0, nm) described by S.mCur / S.mRow / S.offs -- or, when arcHi > arcLo,
+// the arcs [arcLo, arcHi) of the single member of rank 0 (a row longer than the chunk capacity).
+//   (1) one thread per arc: the offer, tested against the target's CURRENT label.  Labels only improve, so an offer that cannot
+//       improve the label now never will: it is dropped here (most arcs of a flood point at nodes that are labelled already).
+//       Survivors are hung into a shared-memory hash list of their target vertex.
+//   (2) one thread per target vertex: updatePaths (:59-84) for its surviving offers in sequential order (arc index in the chunk =
+//       (member id, adjacency position) order); label, predecessor, queue key; events into the slots of their arcs.
+//   (3) the record logic (:71-82): bestDist / bestHopDist in front of an event is the lexicographic prefix minimum of (D, H) over
+//       the event slots -- a parallel scan; an event is recorded iff D < bestDist or D == bestDist and H < 2 bestHopDist; the recorded
+//       ones are appended to the list of intermediates in slot order.  The same scan tells where 2 d > bestDist becomes true.
+// sh.cutoff: rank of the member behind which the search ends when later members of the chunk have to be undone, else -1.
+__device__ inline void runChunk(const GraphDev &G, TileMem &M, RunScratch &X, RunShared &sh, RunSmem &S, const uint32_t nm,
+                                const uint32_t arcLo, const uint32_t arcHi, const uint32_t noffers, const int32_t now,
+                                const uint32_t snapPool, const bool lastOfRun) {
     const double d = sh.runD;
     const uint32_t hNew = sh.runH + 1;
     const double best0 = sh.best; // conservative (>= the running value) for pruning / queue admission, as in the other engines
-    const uint32_t nm = mhi - mlo;
+    const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
+    __shared__ uint32_t nSurv, firstDrop;
+    __shared__ double wD[kRunThreads / 32];
+    __shared__ uint32_t wH[kRunThreads / 32], wC[kRunThreads / 32];
     RCLK_DECL;
-    // ---- (1) offers: one thread per arc -------------------------------------------------------------------------------
+    for (uint32_t i = threadIdx.x; i < kRunHashSlots; i += blockDim.x) {
+        S.hKey[i] = kEmptyKey;
+        S.hHead[i] = kRunNil;
+    }
+    if (threadIdx.x == 0) {
+        nSurv = 0;
+        firstDrop = 0xFFFFFFFFu;
+        sh.nseg = 0;
+        sh.cutoff = -1;
+    }
+    __syncthreads();
+    // ---- (1) offers ---------------------------------------------------------------------------------------------------------
     int myArcs = 0;
     for (uint32_t j = threadIdx.x; j < noffers; j += blockDim.x) {
-        uint32_t r, a;
-        if (arcHi > arcLo) {
-            r = 0;
-            a = arcLo + j;
-        } else { // member of offer j: the last r with offs[r] <= j
+        uint32_t r = 0, a = arcLo + j;
+        if (arcHi <= arcLo) { // member of arc j: the last rank with offs[rank] <= j
             uint32_t lo = 0, hi = nm;
             while (hi - lo > 1) {
                 const uint32_t mid = (lo + hi) >> 1;
-                if (offs[mid] <= j)
+                if (S.offs[mid] <= j)
                     lo = mid;
                 else
                     hi = mid;
             }
             r = lo;
-            a = j - offs[r];
+            a = j - S.offs[r];
         }
-        const uint32_t cur = X.run[mlo + r];
-        const Arc arc = G.arcs[G.rowptr[cur >> 1] + a];
+        S.evD[2 * j] = 8.0; // no event (larger than any D)
+        S.evD[2 * j + 1] = 8.0;
+        const uint32_t cur = S.mCur[r];
+        const Arc arc = G.arcs[S.mRow[r] + a];
         const uint32_t nbr = (uint32_t)arc.nbr & 0x7FFFFFFFu;
         bool act = arc.nbr >= 0; // blacklisted neighbours are skipped (:98-99)
         if (G.blStamp && act) act = !stampedBefore(G, nbr, now);
-        myArcs += act ? 1 : 0;
-        X.offNbr[j] = nbr;
-        X.offCur[j] = cur;
-        X.offW[j] = arc.w;
-        keys[j] = act ? (((unsigned long long)nbr << 32) | j) : ~0ull; // skipped arcs sort behind everything
+        if (!act) continue;
+        myArcs++;
+        const Entry e = loadEntry(&M.tab[nbr]);
+        const uint32_t side = cur & 1u;
+        const double w = arc.w;
+        const double dS = d + w, dX = d + (1.0 - w);
+        const double dA = side ? e.d1 : e.d0, dB = side ? e.d0 : e.d1;
+        const uint32_t hA = side ? e.h1 : e.h0, hB = side ? e.h0 : e.h1;
+        // can the offer be accepted at all?  A side without a label accepts iff the label could still matter (label pruning, see
+        // ocw_search.cuh): d_offer + d <= best or d_offer + dist[twin] <= best, where the twin's label can only fall to >= d here.
+        const bool sS = dA >= kUnlabelled ? (dS < kInfDist && dS + fmin(dB, d) <= best0) : ((dA == dS) ? (hNew < hA) : (dS < dA));
+        const bool sX = dB >= kUnlabelled ? (dX < kInfDist && dX + fmin(dA, d) <= best0) : ((dB == dX) ? (hNew < hB) : (dX < dB));
+        if (!(sS || sX)) continue;
+        const uint32_t sv = atomicAdd(&nSurv, 1u);
+        S.sNbr[sv] = nbr;
+        S.sW[sv] = w;
+        S.sRank[sv] = (uint16_t)r;
+        S.sJ[sv] = (uint16_t)j;
+        uint32_t hs = (nbr * 0x9E3779B1u) >> kRunHashShift;
+        while (true) {
+            const uint32_t old = atomicCAS(&S.hKey[hs], kEmptyKey, nbr);
+            if (old == kEmptyKey || old == nbr) break;
+            hs = (hs + 1) & (kRunHashSlots - 1);
+        }
+        // push onto the vertex' list (16-bit exchange through the containing word)
+        uint32_t *word = reinterpret_cast<uint32_t *>(S.hHead) + (hs >> 1);
+        const uint32_t shft = (hs & 1u) * 16u;
+        uint32_t seen = *word, want;
+        do {
+            want = (seen & ~(0xFFFFu << shft)) | (sv << shft);
+            const uint32_t got = atomicCAS(word, seen, want);
+            if (got == seen) break;
+            seen = got;
+        } while (true);
+        S.sNext[sv] = (uint16_t)((seen >> shft) & 0xFFFFu);
     }
-    const uint32_t np = nextPow2(noffers);
-    for (uint32_t j = noffers + threadIdx.x; j < np; j += blockDim.x) keys[j] = ~0ull;
     if (myArcs) atomicAdd(reinterpret_cast<unsigned long long *>(&sh.arcs), (unsigned long long)myArcs);
-    if (threadIdx.x == 0) {
-        sh.nev = 0;
-        sh.nseg = 0;
-        sh.cutoff = -1;
-    }
-    // ---- (2) group by target vertex, in sequence order ------------------------------------------------------------------
+    __syncthreads();
     RCLK(0);
-    bitonicSortShared(keys, np);
-    RCLK(1);
-    // ---- (3) one thread per target vertex: updatePaths (:59-84) for its offers, in order -------------------------------
-    for (uint32_t p = threadIdx.x; p < noffers; p += blockDim.x) {
-        const unsigned long long kp = keys[p];
-        if (kp == ~0ull) continue;
-        const uint32_t v = (uint32_t)(kp >> 32);
-        if (p > 0 && (uint32_t)(keys[p - 1] >> 32) == v) continue; // not the first offer to v
+    // ---- (2) one thread per target vertex -----------------------------------------------------------------------------------
+    for (uint32_t hs = threadIdx.x; hs < kRunHashSlots; hs += blockDim.x) {
+        const uint32_t v = S.hKey[hs];
+        if (v == kEmptyKey) continue;
         Entry e = loadEntry(&M.tab[v]);
         const Entry old = e;
         const uint2 oldPred = make_uint2(M.pred[2 * v], M.pred[2 * v + 1]);
         const bool fresh = e.key == kEmptyKey;
         uint32_t pr0 = oldPred.x, pr1 = oldPred.y;
         bool ch0 = false, ch1 = false;
-        for (uint32_t q = p; q < noffers; ++q) {
-            const unsigned long long kq = keys[q];
-            if ((uint32_t)(kq >> 32) != v) break;
-            const uint32_t j = (uint32_t)kq;
-            const uint32_t cur = X.offCur[j];
+        int last = -1;
+        while (true) { // the vertex' offers in ascending arc index
+            uint32_t bs = kRunNil, bj = 0xFFFFFFFFu;
+            for (uint32_t q = S.hHead[hs]; q != kRunNil; q = S.sNext[q]) {
+                const uint32_t jq = S.sJ[q];
+                if ((int)jq > last && jq < bj) {
+                    bj = jq;
+                    bs = q;
+                }
+            }
+            if (bs == kRunNil) break;
+            last = (int)bj;
+            const uint32_t cur = S.mCur[S.sRank[bs]];
             const uint32_t side = cur & 1u;
-            const double w = X.offW[j];
+            const double w = S.sW[bs];
             const double dS = d + w, dX = d + (1.0 - w);
             const bool creatS = dS + d <= best0, creatX = dX + d <= best0; // label pruning, see ocw_search.cuh
             double dA = side ? e.d1 : e.d0, dB = side ? e.d0 : e.d1;
@@ -254,11 +289,9 @@ __device__ inline void runChunk(const GraphDev &G, TileMem &M, RunScratch &X, Ru
                 hA = hNew;
                 const double D = dA + dB;
                 if (D <= best0) {
-                    const uint32_t k = atomicAdd(&sh.nev, 1u);
-                    X.evNode[k] = 2 * v + side;
-                    X.evSeq[k] = 2 * j;
-                    X.evD[k] = D;
-                    X.evH[k] = hA + hB;
+                    S.evD[2 * bj] = D;
+                    S.evH[2 * bj] = hA + hB;
+                    S.evNode[2 * bj] = 2 * v + side;
                 }
             }
             if (dB >= kUnlabelled)
@@ -270,11 +303,9 @@ __device__ inline void runChunk(const GraphDev &G, TileMem &M, RunScratch &X, Ru
                 hB = hNew;
                 const double D = dB + dA;
                 if (D <= best0) {
-                    const uint32_t k = atomicAdd(&sh.nev, 1u);
-                    X.evNode[k] = 2 * v + (side ^ 1u);
-                    X.evSeq[k] = 2 * j + 1;
-                    X.evD[k] = D;
-                    X.evH[k] = hB + hA;
+                    S.evD[2 * bj + 1] = D;
+                    S.evH[2 * bj + 1] = hB + hA;
+                    S.evNode[2 * bj + 1] = 2 * v + (side ^ 1u);
                 }
             }
             if (accS || accX) {
@@ -346,177 +377,122 @@ __device__ inline void runChunk(const GraphDev &G, TileMem &M, RunScratch &X, Ru
         X.qpos[2 * v + 1] = nq1;
     }
     __syncthreads();
-    RCLK(2);
-    // ---- (4) the record logic (:71-82) in the sequential order of the events ------------------------------------------------
-    // bestDist in front of an event is min(bestDist before the chunk, D of every earlier event): a prefix minimum, computed
-    // in parallel.  Only events with D <= that value can touch the record (or end the search); they are replayed serially by
-    // one thread from shared memory -- bestHopDist and the list of intermediates are a true history.
-    RCLK(3);
-    const uint32_t nev = sh.nev;
-    if (nev > 0) {
-        const uint32_t ne2 = nextPow2(nev);
-        for (uint32_t k = threadIdx.x; k < ne2; k += blockDim.x) keys[k] = k < nev ? (((unsigned long long)X.evSeq[k] << 32) | k) : ~0ull;
-        bitonicSortShared(keys, ne2);
-        RCLK(4);
-        constexpr int IT = 4;
-        __shared__ double wMin[kRunThreads / 32];
-        __shared__ uint32_t wCnt[kRunThreads / 32];
-        __shared__ double carryMin;
-        __shared__ uint32_t carryCnt;
-        __shared__ int stopReplay;
-        __shared__ double sD[kRunThreads * IT];
-        __shared__ uint32_t sH[kRunThreads * IT], sNode[kRunThreads * IT], sRank[kRunThreads * IT];
-        if (threadIdx.x == 0) {
-            carryMin = sh.best;
-            carryCnt = 0;
-            stopReplay = 0;
+    RCLK(1);
+    // ---- (3) the record logic over the event slots, in slot order ----------------------------------------------------------
+    constexpr int IT = 2 * kRunOfferCap / kRunThreads; // slots per thread
+    const uint32_t nslots = 2 * noffers;
+    LexMin run = {sh.best, sh.bestHop}; // (bestDist, bestHopDist) in front of the tile
+    uint32_t histBase = sh.histN;
+    uint32_t pushMask = 0, pushPos = 0;
+    {
+        double dd[IT];
+        uint32_t hh[IT];
+        LexMin agg = {8.0, 0xFFFFFFFFu};
+#pragma unroll
+        for (int i = 0; i < IT; ++i) {
+            const uint32_t q = threadIdx.x * IT + i;
+            dd[i] = q < nslots ? S.evD[q] : 8.0;
+            hh[i] = dd[i] < 8.0 ? S.evH[q] : 0xFFFFFFFFu;
+            agg = lexmin(agg, LexMin{dd[i], hh[i]});
+        }
+        // exclusive prefix (lexicographic minimum) over the threads of the CTA
+        LexMin incl = agg;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            LexMin o;
+            o.d = __shfl_up_sync(0xFFFFFFFFu, incl.d, off);
+            o.h = __shfl_up_sync(0xFFFFFFFFu, incl.h, off);
+            if (lane >= off) incl = lexmin(o, incl);
+        }
+        LexMin excl;
+        excl.d = __shfl_up_sync(0xFFFFFFFFu, incl.d, 1);
+        excl.h = __shfl_up_sync(0xFFFFFFFFu, incl.h, 1);
+        if (lane == 0) excl = LexMin{8.0, 0xFFFFFFFFu};
+        if (lane == 31) {
+            wD[wrp] = incl.d;
+            wH[wrp] = incl.h;
         }
         __syncthreads();
-        const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
-        for (uint32_t base = 0; base < nev; base += kRunThreads * IT) {
-            uint32_t kk[IT];
-            double dd[IT];
+        LexMin before = lexmin(run, excl);
+        for (int w = 0; w < wrp; ++w) before = lexmin(before, LexMin{wD[w], wH[w]});
+        int nc = 0;
 #pragma unroll
-            for (int i = 0; i < IT; ++i) {
-                const uint32_t q = base + threadIdx.x * IT + i;
-                kk[i] = q < nev ? (uint32_t)keys[q] : 0u;
-                dd[i] = q < nev ? X.evD[kk[i]] : 8.0; // 8.0: larger than any D
-            }
-            double tmin = dd[0];
-#pragma unroll
-            for (int i = 1; i < IT; ++i) tmin = fmin(tmin, dd[i]);
-            double incl = tmin; // inclusive prefix minimum over the lanes, then exclusive over the threads of the CTA
-#pragma unroll
-            for (int off = 1; off < 32; off <<= 1) {
-                const double o = __shfl_up_sync(0xFFFFFFFFu, incl, off);
-                if (lane >= off) incl = fmin(incl, o);
-            }
-            double excl = __shfl_up_sync(0xFFFFFFFFu, incl, 1);
-            if (lane == 0) excl = 8.0;
-            if (lane == 31) wMin[wrp] = incl;
-            __syncthreads(); // (also: every thread has read its keys before the candidates overwrite the front of the array)
-            double before = fmin(carryMin, excl);
-            for (int w = 0; w < wrp; ++w) before = fmin(before, wMin[w]);
-            bool cand[IT];
-            int nc = 0;
-#pragma unroll
-            for (int i = 0; i < IT; ++i) {
-                const uint32_t q = base + threadIdx.x * IT + i;
-                cand[i] = q < nev && dd[i] <= before;
-                nc += cand[i] ? 1 : 0;
-                before = fmin(before, dd[i]);
-            }
-            int cincl = nc;
-#pragma unroll
-            for (int off = 1; off < 32; off <<= 1) {
-                const int o = __shfl_up_sync(0xFFFFFFFFu, cincl, off);
-                if (lane >= off) cincl += o;
-            }
-            if (lane == 31) wCnt[wrp] = (uint32_t)cincl;
-            __syncthreads();
-            uint32_t pos = carryCnt + (uint32_t)(cincl - nc);
-            for (int w = 0; w < wrp; ++w) pos += wCnt[w];
-#pragma unroll
-            for (int i = 0; i < IT; ++i)
-                if (cand[i]) keys[pos++] = kk[i]; // in place: the write position never passes the events already consumed
-            __syncthreads();
-            if (threadIdx.x == 0) {
-                double m = carryMin;
-                uint32_t c = carryCnt;
-                for (int w = 0; w < kRunThreads / 32; ++w) {
-                    m = fmin(m, wMin[w]);
-                    c += wCnt[w];
+        for (int i = 0; i < IT; ++i) {
+            if (dd[i] < 8.0) {
+                // `if (D < bestDist || (D == bestDist && H < bestHopDist)) {...; push} else if (D == bestDist && H < 2 bestHopDist) push`
+                const bool push = dd[i] < before.d || (dd[i] == before.d && hh[i] < 2 * before.h);
+                if (push) {
+                    pushMask |= 1u << i;
+                    nc++;
                 }
-                carryMin = m;
-                carryCnt = c;
+                before = lexmin(before, LexMin{dd[i], hh[i]});
+                if (2 * d > before.d) atomicMin(&firstDrop, threadIdx.x * IT + i); // the loop condition (:90) fails behind this member
             }
-            __syncthreads();
         }
-        RCLK(5);
-        const uint32_t ncand = carryCnt;
-        // thread 0's view of the record across the batches
-        double best = sh.best;
-        uint32_t bestHop = sh.bestHop, histN = sh.histN;
-        bool drop = false;
-        int cutoff = -1;
-        for (uint32_t base = 0; base < ncand && !stopReplay; base += kRunThreads * IT) {
-            const uint32_t nb = min(ncand - base, (uint32_t)(kRunThreads * IT));
-            for (uint32_t i = threadIdx.x; i < nb; i += blockDim.x) {
-                const uint32_t k = (uint32_t)keys[base + i];
-                sD[i] = X.evD[k];
-                sH[i] = X.evH[k];
-                sNode[i] = X.evNode[k];
-                uint32_t r = 0;
-                if (arcHi <= arcLo) { // rank of the member that made the offer
-                    const uint32_t j = X.evSeq[k] >> 1;
+        int cincl = nc;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const int o = __shfl_up_sync(0xFFFFFFFFu, cincl, off);
+            if (lane >= off) cincl += o;
+        }
+        if (lane == 31) wC[wrp] = (uint32_t)cincl;
+        __syncthreads();
+        pushPos = (uint32_t)(cincl - nc);
+        for (int w = 0; w < wrp; ++w) pushPos += wC[w];
+        if (threadIdx.x == 0) {
+            LexMin tot = run;
+            uint32_t np = 0;
+            for (int w = 0; w < kRunThreads / 32; ++w) {
+                tot = lexmin(tot, LexMin{wD[w], wH[w]});
+                np += wC[w];
+            }
+            int cutoff = -1;
+            bool drop = false;
+            if (firstDrop != 0xFFFFFFFFu) {
+                drop = true;
+                if (arcHi <= arcLo) { // rank of the member whose event made 2 d > bestDist true
+                    const uint32_t j = firstDrop >> 1;
                     uint32_t lo = 0, hi = nm;
                     while (hi - lo > 1) {
                         const uint32_t mid = (lo + hi) >> 1;
-                        if (offs[mid] <= j)
+                        if (S.offs[mid] <= j)
                             lo = mid;
                         else
                             hi = mid;
                     }
-                    r = lo;
-                }
-                sRank[i] = r;
-            }
-            __syncthreads();
-            if (threadIdx.x == 0) {
-                for (uint32_t i = 0; i < nb; ++i) {
-                    const double D = sD[i];
-                    const uint32_t H = sH[i];
-                    bool push = false;
-                    if (D < best || (D == best && H < bestHop)) {
-                        best = D;
-                        bestHop = H;
-                        push = true;
-                    } else if (D == best && H < 2 * bestHop) {
-                        push = true;
-                    }
-                    if (push) {
-                        if (histN >= M.caps.histCap) {
-                            sh.overflow = 1;
-                            stopReplay = 1;
-                            break;
-                        }
-                        M.hist[histN++] = sNode[i];
-                    }
-                    if (!drop && 2 * d > best) {
-                        // bestDist fell below 2 d: the loop condition (:90) fails in front of the NEXT member.  If that member is
-                        // part of this chunk, its offers (already applied) have to go: roll back, redo up to this member.
-                        drop = true;
-                        if (sRank[i] + 1 < nm) {
-                            cutoff = (int)sRank[i];
-                            stopReplay = 1;
-                            break;
-                        }
-                    }
+                    if (lo + 1 < nm) cutoff = (int)lo; // later members of this chunk were never extracted: roll back, redo up to here
                 }
             }
-            __syncthreads();
-        }
-        if (threadIdx.x == 0) {
-            if (cutoff < 0 && !sh.overflow) {
-                sh.best = best;
-                sh.bestHop = bestHop;
-                sh.histN = histN;
-                if (drop && !lastOfRun) sh.done = 1; // the next member of the run is never extracted
+            if (cutoff < 0) {
+                if (histBase + np > M.caps.histCap) {
+                    sh.overflow = 1;
+                } else {
+                    sh.best = tot.d;
+                    sh.bestHop = tot.h;
+                    sh.histN = histBase + np;
+                    if (drop && !lastOfRun) sh.done = 1; // the next member of the run is never extracted
+                }
             }
             sh.cutoff = cutoff;
         }
         __syncthreads();
-        RCLK(6);
+        if (sh.cutoff < 0 && !sh.overflow) { // append the recorded events to the list of intermediates, in slot order
+#pragma unroll
+            for (int i = 0; i < IT; ++i)
+                if (pushMask & (1u << i)) M.hist[histBase + pushPos++] = S.evNode[threadIdx.x * IT + i];
+        }
     }
-    if (sh.cutoff >= 0) { // roll the chunk back; the caller redoes members [mlo, mlo + cutoff] and ends the search
+    __syncthreads();
+    RCLK(2);
+    if (sh.cutoff >= 0) { // roll the chunk back; the caller redoes the members up to rank `cutoff` and ends the search
         const uint32_t nseg = sh.nseg;
-        for (uint32_t s = threadIdx.x; s < nseg; s += blockDim.x) {
-            const uint32_t v = X.undoVtx[s];
-            const Entry old = X.undoEntry[s];
+        for (uint32_t k = threadIdx.x; k < nseg; k += blockDim.x) {
+            const uint32_t v = X.undoVtx[k];
+            const Entry old = X.undoEntry[k];
             storeEntry(&M.tab[v], old);
-            M.pred[2 * v] = X.undoPred[s].x;
-            M.pred[2 * v + 1] = X.undoPred[s].y;
-            const uint2 oq = X.undoQpos[s];
+            M.pred[2 * v] = X.undoPred[k].x;
+            M.pred[2 * v + 1] = X.undoPred[k].y;
+            const uint2 oq = X.undoQpos[k];
             X.qpos[2 * v] = oq.x;
             X.qpos[2 * v + 1] = oq.y;
             if (oq.x != kNoQpos) { // revive the keys this chunk killed
@@ -536,13 +512,14 @@ __device__ inline void runChunk(const GraphDev &G, TileMem &M, RunScratch &X, Ru
         if (threadIdx.x == 0) sh.poolN = snapPool;
         __syncthreads();
     }
+    RCLK(3);
 }
 
 __global__ void __launch_bounds__(kRunThreads) ocwSearchRunsKernel(const GraphDev G, const SearchParams P, const RawOut R, const TileCaps caps,
                                                                    unsigned char *scratch) {
+    extern __shared__ __align__(16) unsigned char runSmemRaw[];
+    RunSmem &S = *reinterpret_cast<RunSmem *>(runSmemRaw);
     __shared__ RunShared sh;
-    __shared__ unsigned long long keys[2 * kRunOfferCap]; // offers: <= cap keys; events: <= 2 cap keys; member sort: 4 cap ids
-    __shared__ uint32_t offs[kRunOfferCap + 1];
     __shared__ unsigned long long redHi[kRunThreads / 32], redLo[kRunThreads / 32];
     const size_t tb = tileBytes(caps), xb = runScratchBytes(G.n);
     unsigned char *tile = scratch + (size_t)blockIdx.x * (tb + xb);
@@ -672,7 +649,7 @@ __global__ void __launch_bounds__(kRunThreads) ocwSearchRunsKernel(const GraphDe
             if (runLen > 1) {
                 const uint32_t np = nextPow2(runLen);
                 if (np <= 4 * kRunOfferCap) {
-                    uint32_t *k32 = reinterpret_cast<uint32_t *>(keys);
+                    uint32_t *k32 = reinterpret_cast<uint32_t *>(S.evD); // 2 cap doubles = 4 cap ids of scratch
                     for (uint32_t i = threadIdx.x; i < np; i += blockDim.x) k32[i] = i < runLen ? X.run[i] : 0xFFFFFFFFu;
                     // 32-bit bitonic network in shared memory
                     for (uint32_t size = 2; size <= np; size <<= 1)
@@ -718,24 +695,27 @@ __global__ void __launch_bounds__(kRunThreads) ocwSearchRunsKernel(const GraphDe
                 // settled bits + prefix of the degrees of the next members, as many as fit a chunk
                 const uint32_t window = min(runLen - m0, kRunOfferCap);
                 __syncthreads();
-                for (uint32_t i = threadIdx.x; i < window; i += blockDim.x) { // degrees first (in parallel), then their prefix
-                    const uint32_t u = X.run[m0 + i] >> 1;
-                    offs[i] = (uint32_t)(G.rowptr[u + 1] - G.rowptr[u]);
+                for (uint32_t i = threadIdx.x; i < window; i += blockDim.x) { // ids, rows and degrees first (in parallel), then the prefix
+                    const uint32_t id = X.run[m0 + i];
+                    const long long rb = G.rowptr[id >> 1];
+                    S.mCur[i] = id;
+                    S.mRow[i] = (uint32_t)rb;
+                    S.offs[i] = (uint32_t)(G.rowptr[(id >> 1) + 1] - rb);
                 }
                 __syncthreads();
                 if (threadIdx.x == 0) {
                     uint32_t acc = 0, cnt = 0;
                     for (; cnt < window; ++cnt) {
-                        const uint32_t deg = offs[cnt];
+                        const uint32_t deg = S.offs[cnt];
                         if (cnt > 0 && acc + deg > kRunOfferCap) break;
-                        offs[cnt] = acc;
+                        S.offs[cnt] = acc;
                         acc += deg;
                         if (acc > kRunOfferCap) { // a single row longer than a chunk: processed in pieces
                             cnt = 1;
                             break;
                         }
                     }
-                    offs[cnt] = acc;
+                    S.offs[cnt] = acc;
                     sh.nseg = cnt; // (re-used as a mailbox: members in this chunk)
                     sh.nev = acc;  //                        offers in this chunk
                 }
@@ -746,7 +726,7 @@ __global__ void __launch_bounds__(kRunThreads) ocwSearchRunsKernel(const GraphDe
                 const uint32_t snapPool = sh.poolN, snapTouched = sh.touchedN;
                 const long long snapArcs = sh.arcs;
                 if (tot <= kRunOfferCap) {
-                    if (tot > 0) runChunk(G, M, X, sh, keys, offs, m0, m0 + cnt, 0, 0, tot, srcIdx, snapPool, lastOfRun);
+                    if (tot > 0) runChunk(G, M, X, sh, S, cnt, 0, 0, tot, srcIdx, snapPool, lastOfRun);
                     __syncthreads();
                     int c = tot > 0 ? sh.cutoff : -1;
                     if (c >= 0) {
@@ -758,8 +738,8 @@ __global__ void __launch_bounds__(kRunThreads) ocwSearchRunsKernel(const GraphDe
                         }
                         __syncthreads();
                         const uint32_t cnt2 = (uint32_t)c + 1;
-                        const uint32_t tot2 = offs[cnt2];
-                        if (tot2 > 0) runChunk(G, M, X, sh, keys, offs, m0, m0 + cnt2, 0, 0, tot2, srcIdx, sh.poolN, true);
+                        const uint32_t tot2 = S.offs[cnt2];
+                        if (tot2 > 0) runChunk(G, M, X, sh, S, cnt2, 0, 0, tot2, srcIdx, sh.poolN, true);
                         __syncthreads();
                         SMS_CHK(sh.cutoff < 0);
                         if (threadIdx.x == 0) {
@@ -783,7 +763,7 @@ __global__ void __launch_bounds__(kRunThreads) ocwSearchRunsKernel(const GraphDe
                     for (uint32_t a0 = 0; a0 < tot && !sh.overflow; a0 += kRunOfferCap) {
                         const uint32_t a1 = min(a0 + kRunOfferCap, tot);
                         __syncthreads();
-                        runChunk(G, M, X, sh, keys, offs, m0, m0 + 1, a0, a1, a1 - a0, srcIdx, sh.poolN, lastOfRun);
+                        runChunk(G, M, X, sh, S, 1, a0, a1, a1 - a0, srcIdx, sh.poolN, lastOfRun);
                         __syncthreads();
                     }
                     if (threadIdx.x == 0) {

@@ -289,7 +289,9 @@ cudaError_t launchSearch(smsgpu_ctx *c, int tierIdx, const GraphDev &G, const Se
     }
     if (t.caps.nbuckets) return launchSearchT<false, true>(c, t, G, P, R, st, ctas);
     if (t.runs) {
-        ocwSearchRunsKernel<<<ctas, kRunThreads, 0, st>>>(G, P, R, t.caps, t.scratch.as<unsigned char>());
+        cudaError_t e = cudaFuncSetAttribute(ocwSearchRunsKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RunSmem));
+        if (e != cudaSuccess) return e;
+        ocwSearchRunsKernel<<<ctas, kRunThreads, sizeof(RunSmem), st>>>(G, P, R, t.caps, t.scratch.as<unsigned char>());
         return cudaGetLastError();
     }
     return launchSearchT<false, false>(c, t, G, P, R, st, ctas);
@@ -388,7 +390,8 @@ int ensureTierScratch(smsgpu_ctx *ctx, int ti) {
         size_t freeB = 0, totalB = 0;
         CU(cudaMemGetInfo(&freeB, &totalB));
         int perSm = 1;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, ocwSearchRunsKernel, kRunThreads, 0) != cudaSuccess) {
+        cudaFuncSetAttribute(ocwSearchRunsKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RunSmem));
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, ocwSearchRunsKernel, kRunThreads, sizeof(RunSmem)) != cudaSuccess) {
             (void)cudaGetLastError();
             perSm = 1;
         }
@@ -1303,8 +1306,8 @@ int separateLocal(smsgpu_ctx *ctx, const smsgpu_params &P) {
     {
         unsigned long long h[16];
         if (cudaMemcpyFromSymbol(h, g_runClk, sizeof h) == cudaSuccess) {
-            std::fprintf(stderr, "[smsgpu] runs engine, CTA 0, cycles: offers %llu | sort %llu | apply %llu | - %llu | event sort %llu | prefix-min %llu | replay %llu\n", h[0],
-                         h[1], h[2], h[3], h[4], h[5], h[6]);
+            std::fprintf(stderr, "[smsgpu] runs engine, CTA 0, cycles: offers + grouping %llu | apply %llu | record logic %llu | rollback %llu\n", h[0], h[1],
+                         h[2], h[3]);
             std::memset(h, 0, sizeof h);
             cudaMemcpyToSymbol(g_runClk, h, sizeof h);
         }
