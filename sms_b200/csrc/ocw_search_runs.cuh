@@ -50,9 +50,11 @@ __device__ unsigned long long g_runClk[16];
         }                                                                            \
     } while (0)
 #define RCLK_DECL long long rclkLast = clock64()
+#define RCLK_RESET rclkLast = clock64()
 #else
 #define RCLK(i_) ((void)0)
 #define RCLK_DECL ((void)0)
+#define RCLK_RESET ((void)0)
 #endif
 
 
@@ -60,6 +62,7 @@ __device__ unsigned long long g_runClk[16];
 struct RunScratch {
     uint32_t *run;     // [runCap] members of the current run (doubled ids, sorted)
     uint32_t *qpos;    // [2n] pool position of a node's live key, kNoQpos
+    uint32_t *bits;    // [(2n + 31) / 32] bitmap over the doubled ids (sorting long runs); all zero between uses
     uint32_t *undoVtx; // [cap] per target vertex of the chunk: undo log (label, predecessors, queue positions before the chunk)
     Entry *undoEntry;
     uint2 *undoPred, *undoQpos;
@@ -68,7 +71,7 @@ struct RunScratch {
 __host__ __device__ inline size_t runScratchBytes(const long long n) {
     size_t rc = 2;
     while (rc < (size_t)(2 * n + 2)) rc <<= 1; // power of two: the member list is sorted with a bitonic network
-    size_t b = rc * 4 + (size_t)(2 * n + 2) * 4;
+    size_t b = rc * 4 + (size_t)(2 * n + 2) * 4 + (size_t)((2 * n + 31) / 32 + 1) * 4;
     b += (size_t)kRunOfferCap * (4 + 32 + 8 + 8);
     return (b + 255) & ~(size_t)255;
 }
@@ -87,6 +90,8 @@ __device__ inline void carveRunScratch(RunScratch &X, unsigned char *p, const lo
     p += (size_t)rc * 4;
     X.qpos = reinterpret_cast<uint32_t *>(p);
     p += (size_t)(2 * n + 2) * 4;
+    X.bits = reinterpret_cast<uint32_t *>(p);
+    p += (size_t)((2 * n + 31) / 32 + 1) * 4;
     X.undoVtx = reinterpret_cast<uint32_t *>(p);
 }
 
@@ -147,6 +152,8 @@ struct RunSmem {
     uint16_t sNext[kRunOfferCap];         //   next offer of the same vertex
     uint16_t sRank[kRunOfferCap];         // surviving offers: rank of the member that makes it
     uint16_t sJ[kRunOfferCap];            //                   arc index in the chunk (the sequence number)
+    uint16_t gSlot[kRunOfferCap];         // hash slots in use (one per target vertex with a surviving offer)
+    uint16_t aRank[kRunOfferCap];         // per arc of the chunk: rank of its member
 };
 
 struct LexMin { // (D, H) lexicographic minimum: bestDist / bestHopDist after a sequence of events (:73-76)
@@ -173,7 +180,7 @@ __device__ inline void runChunk(const GraphDev &G, TileMem &M, RunScratch &X, Ru
     const uint32_t hNew = sh.runH + 1;
     const double best0 = sh.best; // conservative (>= the running value) for pruning / queue admission, as in the other engines
     const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
-    __shared__ uint32_t nSurv, firstDrop;
+    __shared__ uint32_t nSurv, nGroups, firstDrop;
     __shared__ double wD[kRunThreads / 32];
     __shared__ uint32_t wH[kRunThreads / 32], wC[kRunThreads / 32];
     RCLK_DECL;
@@ -183,77 +190,97 @@ __device__ inline void runChunk(const GraphDev &G, TileMem &M, RunScratch &X, Ru
     }
     if (threadIdx.x == 0) {
         nSurv = 0;
+        nGroups = 0;
         firstDrop = 0xFFFFFFFFu;
         sh.nseg = 0;
         sh.cutoff = -1;
     }
     __syncthreads();
     // ---- (1) offers ---------------------------------------------------------------------------------------------------------
+    // kRunOfferCap / kRunThreads arcs per thread, the loads of all of them in flight together: arc records first, then the labels
     int myArcs = 0;
-    for (uint32_t j = threadIdx.x; j < noffers; j += blockDim.x) {
-        uint32_t r = 0, a = arcLo + j;
-        if (arcHi <= arcLo) { // member of arc j: the last rank with offs[rank] <= j
-            uint32_t lo = 0, hi = nm;
-            while (hi - lo > 1) {
-                const uint32_t mid = (lo + hi) >> 1;
-                if (S.offs[mid] <= j)
-                    lo = mid;
-                else
-                    hi = mid;
+    {
+        constexpr int IA = kRunOfferCap / kRunThreads;
+        uint32_t rr[IA], nb[IA];
+        double ww[IA];
+        bool act[IA];
+#pragma unroll
+        for (int i = 0; i < IA; ++i) {
+            const uint32_t j = threadIdx.x + i * kRunThreads;
+            act[i] = false;
+            rr[i] = 0;
+            nb[i] = 0;
+            ww[i] = 0.0;
+            if (j >= noffers) continue;
+            uint32_t r = 0, a = arcLo + j;
+            if (arcHi <= arcLo) { // member of arc j
+                r = S.aRank[j];
+                a = j - S.offs[r];
             }
-            r = lo;
-            a = j - S.offs[r];
+            S.evD[2 * j] = 8.0; // no event (larger than any D)
+            S.evD[2 * j + 1] = 8.0;
+            const Arc arc = G.arcs[S.mRow[r] + a];
+            rr[i] = r;
+            nb[i] = (uint32_t)arc.nbr & 0x7FFFFFFFu;
+            ww[i] = arc.w;
+            act[i] = arc.nbr >= 0; // blacklisted neighbours are skipped (:98-99)
         }
-        S.evD[2 * j] = 8.0; // no event (larger than any D)
-        S.evD[2 * j + 1] = 8.0;
-        const uint32_t cur = S.mCur[r];
-        const Arc arc = G.arcs[S.mRow[r] + a];
-        const uint32_t nbr = (uint32_t)arc.nbr & 0x7FFFFFFFu;
-        bool act = arc.nbr >= 0; // blacklisted neighbours are skipped (:98-99)
-        if (G.blStamp && act) act = !stampedBefore(G, nbr, now);
-        if (!act) continue;
-        myArcs++;
-        const Entry e = loadEntry(&M.tab[nbr]);
-        const uint32_t side = cur & 1u;
-        const double w = arc.w;
-        const double dS = d + w, dX = d + (1.0 - w);
-        const double dA = side ? e.d1 : e.d0, dB = side ? e.d0 : e.d1;
-        const uint32_t hA = side ? e.h1 : e.h0, hB = side ? e.h0 : e.h1;
-        // can the offer be accepted at all?  A side without a label accepts iff the label could still matter (label pruning, see
-        // ocw_search.cuh): d_offer + d <= best or d_offer + dist[twin] <= best, where the twin's label can only fall to >= d here.
-        const bool sS = dA >= kUnlabelled ? (dS < kInfDist && dS + fmin(dB, d) <= best0) : ((dA == dS) ? (hNew < hA) : (dS < dA));
-        const bool sX = dB >= kUnlabelled ? (dX < kInfDist && dX + fmin(dA, d) <= best0) : ((dB == dX) ? (hNew < hB) : (dX < dB));
-        if (!(sS || sX)) continue;
-        const uint32_t sv = atomicAdd(&nSurv, 1u);
-        S.sNbr[sv] = nbr;
-        S.sW[sv] = w;
-        S.sRank[sv] = (uint16_t)r;
-        S.sJ[sv] = (uint16_t)j;
-        uint32_t hs = (nbr * 0x9E3779B1u) >> kRunHashShift;
-        while (true) {
-            const uint32_t old = atomicCAS(&S.hKey[hs], kEmptyKey, nbr);
-            if (old == kEmptyKey || old == nbr) break;
-            hs = (hs + 1) & (kRunHashSlots - 1);
+        Entry ee[IA];
+#pragma unroll
+        for (int i = 0; i < IA; ++i) {
+            if (G.blStamp && act[i]) act[i] = !stampedBefore(G, nb[i], now);
+            if (act[i]) ee[i] = loadEntry(&M.tab[nb[i]]);
         }
-        // push onto the vertex' list (16-bit exchange through the containing word)
-        uint32_t *word = reinterpret_cast<uint32_t *>(S.hHead) + (hs >> 1);
-        const uint32_t shft = (hs & 1u) * 16u;
-        uint32_t seen = *word, want;
-        do {
-            want = (seen & ~(0xFFFFu << shft)) | (sv << shft);
-            const uint32_t got = atomicCAS(word, seen, want);
-            if (got == seen) break;
-            seen = got;
-        } while (true);
-        S.sNext[sv] = (uint16_t)((seen >> shft) & 0xFFFFu);
+#pragma unroll
+        for (int i = 0; i < IA; ++i) {
+            if (!act[i]) continue;
+            myArcs++;
+            const uint32_t j = threadIdx.x + i * kRunThreads;
+            const Entry &e = ee[i];
+            const uint32_t nbr = nb[i];
+            const uint32_t side = S.mCur[rr[i]] & 1u;
+            const double w = ww[i];
+            const double dS = d + w, dX = d + (1.0 - w);
+            const double dA = side ? e.d1 : e.d0, dB = side ? e.d0 : e.d1;
+            const uint32_t hA = side ? e.h1 : e.h0, hB = side ? e.h0 : e.h1;
+            // can the offer be accepted at all?  A side without a label accepts iff the label could still matter (label pruning, see
+            // ocw_search.cuh): d_offer + d <= best or d_offer + dist[twin] <= best, where the twin's label can only fall to >= d here.
+            const bool sS = dA >= kUnlabelled ? (dS < kInfDist && dS + fmin(dB, d) <= best0) : ((dA == dS) ? (hNew < hA) : (dS < dA));
+            const bool sX = dB >= kUnlabelled ? (dX < kInfDist && dX + fmin(dA, d) <= best0) : ((dB == dX) ? (hNew < hB) : (dX < dB));
+            if (!(sS || sX)) continue;
+            const uint32_t sv = atomicAdd(&nSurv, 1u);
+            S.sNbr[sv] = nbr;
+            S.sW[sv] = w;
+            S.sRank[sv] = (uint16_t)rr[i];
+            S.sJ[sv] = (uint16_t)j;
+            uint32_t hs = (nbr * 0x9E3779B1u) >> kRunHashShift;
+            while (true) {
+                const uint32_t old = atomicCAS(&S.hKey[hs], kEmptyKey, nbr);
+                if (old == kEmptyKey) S.gSlot[atomicAdd(&nGroups, 1u)] = (uint16_t)hs; // first offer to this vertex in the chunk
+                if (old == kEmptyKey || old == nbr) break;
+                hs = (hs + 1) & (kRunHashSlots - 1);
+            }
+            // push onto the vertex' list (16-bit exchange through the containing word)
+            uint32_t *word = reinterpret_cast<uint32_t *>(S.hHead) + (hs >> 1);
+            const uint32_t shft = (hs & 1u) * 16u;
+            uint32_t seen = *word, want;
+            do {
+                want = (seen & ~(0xFFFFu << shft)) | (sv << shft);
+                const uint32_t got = atomicCAS(word, seen, want);
+                if (got == seen) break;
+                seen = got;
+            } while (true);
+            S.sNext[sv] = (uint16_t)((seen >> shft) & 0xFFFFu);
+        }
     }
     if (myArcs) atomicAdd(reinterpret_cast<unsigned long long *>(&sh.arcs), (unsigned long long)myArcs);
     __syncthreads();
     RCLK(0);
     // ---- (2) one thread per target vertex -----------------------------------------------------------------------------------
-    for (uint32_t hs = threadIdx.x; hs < kRunHashSlots; hs += blockDim.x) {
+    const uint32_t ngroups = nGroups;
+    for (uint32_t g = threadIdx.x; g < ngroups; g += blockDim.x) {
+        const uint32_t hs = S.gSlot[g];
         const uint32_t v = S.hKey[hs];
-        if (v == kEmptyKey) continue;
         Entry e = loadEntry(&M.tab[v]);
         const Entry old = e;
         const uint2 oldPred = make_uint2(M.pred[2 * v], M.pred[2 * v + 1]);
@@ -515,7 +542,10 @@ __device__ inline void runChunk(const GraphDev &G, TileMem &M, RunScratch &X, Ru
     RCLK(3);
 }
 
-__global__ void __launch_bounds__(kRunThreads) ocwSearchRunsKernel(const GraphDev G, const SearchParams P, const RawOut R, const TileCaps caps,
+#ifndef SMSGPU_RUNS_MIN_CTAS
+#define SMSGPU_RUNS_MIN_CTAS 2
+#endif
+__global__ void __launch_bounds__(kRunThreads, SMSGPU_RUNS_MIN_CTAS) ocwSearchRunsKernel(const GraphDev G, const SearchParams P, const RawOut R, const TileCaps caps,
                                                                    unsigned char *scratch) {
     extern __shared__ __align__(16) unsigned char runSmemRaw[];
     RunSmem &S = *reinterpret_cast<RunSmem *>(runSmemRaw);
@@ -532,6 +562,7 @@ __global__ void __launch_bounds__(kRunThreads) ocwSearchRunsKernel(const GraphDe
     const int maxInter = min(P.maxInter, 16);
     uint32_t sel[16];
     long long accArcs = 0, accSettled = 0, accSources = 0;
+    for (uint32_t w = threadIdx.x; w < (uint32_t)((2 * G.n + 31) >> 5) + 1; w += blockDim.x) X.bits[w] = 0u;
 
     while (true) {
         __syncthreads();
@@ -587,7 +618,9 @@ __global__ void __launch_bounds__(kRunThreads) ocwSearchRunsKernel(const GraphDe
         }
         __syncthreads();
 
+        RCLK_DECL;
         while (!sh.done && !sh.overflow) {
+            RCLK_RESET;
             // ---- the minimal key of the pool: 128-bit lexicographic minimum over the live keys -------------------------------
             const uint32_t poolN = sh.poolN;
             unsigned long long mhi = ~0ull, mlo = ~0ull;
@@ -628,6 +661,7 @@ __global__ void __launch_bounds__(kRunThreads) ocwSearchRunsKernel(const GraphDe
             }
             __syncthreads();
             if (sh.done) break;
+            RCLK(4);
             // ---- collect the run: every live key with the minimal (dist, hops); the keys leave the pool -------------------
             {
                 const unsigned long long dhi = sh.minHi;
@@ -645,8 +679,43 @@ __global__ void __launch_bounds__(kRunThreads) ocwSearchRunsKernel(const GraphDe
             __syncthreads();
             uint32_t runLen = sh.runLen;
             SMS_CHK(runLen >= 1 && runLen <= X.runCap);
+            RCLK(5);
             // ---- in id order; the target ends the run in front of itself (:89) ------------------------------------------------
-            if (runLen > 1) {
+            const uint32_t nwords = (uint32_t)((2 * G.n + 31) >> 5);
+            if (runLen > 1 && (runLen > 4 * kRunOfferCap || nwords <= 16 * runLen)) {
+                // a long run: the members are distinct ids below 2n, so "sorting" is marking a bitmap and reading it in order
+                for (uint32_t i = threadIdx.x; i < runLen; i += blockDim.x) {
+                    const uint32_t id = X.run[i];
+                    atomicOr(&X.bits[id >> 5], 1u << (id & 31));
+                }
+                __syncthreads();
+                const uint32_t per = (nwords + blockDim.x - 1) / blockDim.x;
+                const uint32_t w0 = min(threadIdx.x * per, nwords), w1 = min(w0 + per, nwords);
+                uint32_t cntb = 0;
+                for (uint32_t w = w0; w < w1; ++w) cntb += __popc(X.bits[w]);
+                uint32_t incl = cntb;
+#pragma unroll
+                for (int off = 1; off < 32; off <<= 1) {
+                    const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, incl, off);
+                    if ((threadIdx.x & 31) >= off) incl += o;
+                }
+                __shared__ uint32_t bSum[kRunThreads / 32];
+                if ((threadIdx.x & 31) == 31) bSum[threadIdx.x >> 5] = incl;
+                __syncthreads();
+                uint32_t pos = incl - cntb;
+                for (uint32_t w = 0; w < (threadIdx.x >> 5); ++w) pos += bSum[w];
+                for (uint32_t w = w0; w < w1; ++w) {
+                    uint32_t bits = X.bits[w];
+                    if (!bits) continue;
+                    X.bits[w] = 0u; // left clean for the next run
+                    while (bits) {
+                        const int b = __ffs(bits) - 1;
+                        bits &= bits - 1;
+                        X.run[pos++] = 32u * w + (uint32_t)b;
+                    }
+                }
+                __syncthreads();
+            } else if (runLen > 1) {
                 const uint32_t np = nextPow2(runLen);
                 if (np <= 4 * kRunOfferCap) {
                     uint32_t *k32 = reinterpret_cast<uint32_t *>(S.evD); // 2 cap doubles = 4 cap ids of scratch
@@ -673,6 +742,7 @@ __global__ void __launch_bounds__(kRunThreads) ocwSearchRunsKernel(const GraphDe
                 }
                 __syncthreads();
             }
+            RCLK(6);
             bool endsAtTarget = false;
             {
                 // position of the target in the sorted run, if it is a member (binary search by every thread: uniform)
@@ -703,23 +773,67 @@ __global__ void __launch_bounds__(kRunThreads) ocwSearchRunsKernel(const GraphDe
                     S.offs[i] = (uint32_t)(G.rowptr[(id >> 1) + 1] - rb);
                 }
                 __syncthreads();
-                if (threadIdx.x == 0) {
-                    uint32_t acc = 0, cnt = 0;
-                    for (; cnt < window; ++cnt) {
-                        const uint32_t deg = S.offs[cnt];
-                        if (cnt > 0 && acc + deg > kRunOfferCap) break;
-                        S.offs[cnt] = acc;
-                        acc += deg;
-                        if (acc > kRunOfferCap) { // a single row longer than a chunk: processed in pieces
-                            cnt = 1;
-                            break;
+                {
+                    // exclusive prefix of the degrees over the window (block scan), and how many members fit a chunk
+                    constexpr int IW = kRunOfferCap / kRunThreads;
+                    __shared__ uint32_t wSum[kRunThreads / 32];
+                    uint32_t dg[IW], tsum = 0;
+                    const uint32_t deg0 = S.offs[0]; // (degree of the first member: needed when its row alone exceeds a chunk)
+#pragma unroll
+                    for (int i = 0; i < IW; ++i) {
+                        const uint32_t q = threadIdx.x * IW + i;
+                        dg[i] = q < window ? S.offs[q] : 0u;
+                        tsum += dg[i];
+                    }
+                    uint32_t incl = tsum;
+#pragma unroll
+                    for (int off = 1; off < 32; off <<= 1) {
+                        const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, incl, off);
+                        if ((threadIdx.x & 31) >= off) incl += o;
+                    }
+                    if ((threadIdx.x & 31) == 31) wSum[threadIdx.x >> 5] = incl;
+                    if (threadIdx.x == 0) {
+                        sh.nseg = 0;
+                        sh.nev = 0;
+                    }
+                    __syncthreads();
+                    uint32_t run0 = incl - tsum;
+                    for (uint32_t w = 0; w < (threadIdx.x >> 5); ++w) run0 += wSum[w];
+                    uint32_t fit = 0, last = 0;
+#pragma unroll
+                    for (int i = 0; i < IW; ++i) {
+                        const uint32_t q = threadIdx.x * IW + i;
+                        if (q < window) {
+                            S.offs[q] = run0;
+                            run0 += dg[i];
+                            if (run0 <= kRunOfferCap) {
+                                fit++;
+                                last = run0;
+                            }
                         }
                     }
-                    S.offs[cnt] = acc;
-                    sh.nseg = cnt; // (re-used as a mailbox: members in this chunk)
-                    sh.nev = acc;  //                        offers in this chunk
+                    if (fit) {
+                        atomicAdd(&sh.nseg, fit);  // members whose rows fit completely (a prefix of the window: the sums are monotone)
+                        atomicMax(&sh.nev, last);  // arcs of those members
+                    }
+                    __syncthreads();
+                    if (threadIdx.x == 0) {
+                        if (sh.nseg == 0) { // the first row alone is longer than a chunk: processed in pieces
+                            sh.nseg = 1;
+                            sh.nev = deg0;
+                        }
+                    }
+                    __syncthreads();
+                    if (threadIdx.x == 0) S.offs[sh.nseg] = sh.nev;
+                    __syncthreads();
+                    if (sh.nev <= kRunOfferCap) { // rank of the member of every arc of the chunk
+                        const uint32_t nmem = sh.nseg;
+                        for (uint32_t r = threadIdx.x; r < nmem; r += blockDim.x)
+                            for (uint32_t j = S.offs[r]; j < S.offs[r + 1]; ++j) S.aRank[j] = (uint16_t)r;
+                    }
                 }
                 __syncthreads();
+                RCLK(7);
                 const uint32_t cnt = sh.nseg, tot = sh.nev;
                 const bool lastOfRun = (m0 + cnt >= runLen) && !endsAtTarget;
                 __syncthreads();
@@ -773,6 +887,7 @@ __global__ void __launch_bounds__(kRunThreads) ocwSearchRunsKernel(const GraphDe
                     }
                 }
                 __syncthreads();
+                RCLK_RESET;
                 m0 += cnt;
                 // the loop condition in front of the next member (:90); within a chunk the replay has tested it already
                 if (threadIdx.x == 0 && 2 * sh.runD > sh.best && (m0 < runLen || endsAtTarget)) sh.done = 1;
@@ -786,6 +901,7 @@ __global__ void __launch_bounds__(kRunThreads) ocwSearchRunsKernel(const GraphDe
         }
         __syncthreads();
 
+        RCLK_RESET;
         // ---- everything after the search: the code shared with the other engines, by the first warp --------------------------
         SrcState S;
         S.best = sh.best;
@@ -856,9 +972,11 @@ __global__ void __launch_bounds__(kRunThreads) ocwSearchRunsKernel(const GraphDe
             }
         }
         __syncthreads();
+        RCLK(8);
         // leave the table clean for the next source
         const uint32_t tn = min(sh.touchedN, M.caps.touchedCap);
         for (uint32_t i = threadIdx.x; i < tn; i += blockDim.x) storeEntry(&M.tab[M.touched[i]], emptyEntry());
+        RCLK(9);
     }
     if (threadIdx.x == 0 && accSources) {
         atomicAdd(&R.counters[2], (unsigned long long)accArcs);
