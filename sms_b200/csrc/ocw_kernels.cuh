@@ -268,22 +268,16 @@ __global__ void __launch_bounds__(128, FAST ? SMSGPU_FAST_MIN_CTAS : 1) ocwSearc
         else
             searchSource<TW>(T, G, M, S, src, P.bestInit, srcIdx);
         if (!S.overflow && S.histN > 0) {
-            const int nsel = selectIntermediates<TW>(T, M, S, maxInter, sel);
-            if (!S.overflow && T.lane == 0) {
+            int nsel = selectIntermediates<TW>(T, M, S, maxInter, sel);
+            if (!S.overflow) { // (uniform: selectIntermediates decides on uniform values)
                 Emitter E;
                 E.R = &R;
                 E.srcIdx = srcIdx;
                 E.seq = 0;
                 E.tier = P.tier;
-                for (int r = 0; r < nsel; ++r) {
-                    const int W = buildWalk(G, M, sel[r], src, srcIdx);
-                    if (W < 0) {
-                        S.overflow = 1;
-                        break;
-                    }
-                    simpleOddCyclesAndExtract(G, M, S, E, W);
-                    if (S.overflow) break;
-                }
+#pragma unroll
+                for (int r = 0; r < 16; ++r) sel[r] = T.shfl(sel[r], 0); // lane 0 holds the selection
+                walksOfSource(G, M, S, E, sel, nsel, src, srcIdx);
             }
             S.overflow = T.shfl(S.overflow, 0);
         }

@@ -115,7 +115,9 @@ __device__ __noinline__ int finishSourcePairs(const PairsKArgs *K, unsigned char
     const int maxInter = min(P.maxInter, 16);
     if (!S.overflow && S.histN > 0) {
         const int nsel = selectIntermediates<32>(T, M, S, maxInter, sel);
-        if (!S.overflow && T.lane == 0) {
+        if (!S.overflow) { // all 32 lanes (the chord search is spread over them); lane 0 owns the emitter
+#pragma unroll
+            for (int r = 0; r < 16; ++r) sel[r] = T.shfl(sel[r], 0); // lane 0 holds the selection
             // srcIdx2 >= 0: the twin source (other side of the same vertex) gets the same walks -- its search is the mirror
             // image of this one, and a walk is a sequence of ORIGINAL vertices and stay/cross flags.  The cuts of the first
             // pass are logged and copied; only if there are more than the log holds, the walks are built a second time.
@@ -135,29 +137,22 @@ __device__ __noinline__ int finishSourcePairs(const PairsKArgs *K, unsigned char
                     E.logCap = kLog;
                 }
                 if (pass == 1 && nlogged <= kLog) { // copy
-                    for (int i = 0; i < nlogged; ++i) {
-                        long long cut, off;
-                        if (emitReserve(E, logLen[i], cut, off) && logCut[i] >= 0) {
-                            const long long so = R.cutOff[logCut[i]];
-                            for (int k = 0; k < logLen[i]; ++k) {
-                                R.node[off + k] = R.node[so + k];
-                                R.eid[off + k] = R.eid[so + k];
-                                R.stay[off + k] = R.stay[so + k];
+                    if (T.lane == 0)
+                        for (int i = 0; i < nlogged; ++i) {
+                            long long cut, off;
+                            if (emitReserve(E, logLen[i], cut, off) && logCut[i] >= 0) {
+                                const long long so = R.cutOff[logCut[i]];
+                                for (int k = 0; k < logLen[i]; ++k) {
+                                    R.node[off + k] = R.node[so + k];
+                                    R.eid[off + k] = R.eid[so + k];
+                                    R.stay[off + k] = R.stay[so + k];
+                                }
                             }
                         }
-                    }
                     break;
                 }
-                for (int r = 0; r < nsel; ++r) {
-                    const int W = buildWalk(G, M, sel[r], src, srcIdx);
-                    if (W < 0) {
-                        S.overflow = 1;
-                        break;
-                    }
-                    simpleOddCyclesAndExtract(G, M, S, E, W);
-                    if (S.overflow) break;
-                }
-                nlogged = E.nlog;
+                walksOfSource(G, M, S, E, sel, nsel, src, srcIdx);
+                nlogged = T.shfl(E.nlog, 0);
             }
         }
         S.overflow = T.shfl(S.overflow, 0);

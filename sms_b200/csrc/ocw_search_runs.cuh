@@ -180,7 +180,7 @@ __device__ inline void runChunk(const GraphDev &G, TileMem &M, RunScratch &X, Ru
     const uint32_t hNew = sh.runH + 1;
     const double best0 = sh.best; // conservative (>= the running value) for pruning / queue admission, as in the other engines
     const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
-    __shared__ uint32_t nSurv, nGroups, firstDrop;
+    __shared__ uint32_t nSurv, nGroups, firstDrop, chunkArcs;
     __shared__ double wD[kRunThreads / 32];
     __shared__ uint32_t wH[kRunThreads / 32], wC[kRunThreads / 32];
     RCLK_DECL;
@@ -190,6 +190,7 @@ __device__ inline void runChunk(const GraphDev &G, TileMem &M, RunScratch &X, Ru
     }
     if (threadIdx.x == 0) {
         nSurv = 0;
+        chunkArcs = 0;
         nGroups = 0;
         firstDrop = 0xFFFFFFFFu;
         sh.nseg = 0;
@@ -273,8 +274,12 @@ __device__ inline void runChunk(const GraphDev &G, TileMem &M, RunScratch &X, Ru
             S.sNext[sv] = (uint16_t)((seen >> shft) & 0xFFFFu);
         }
     }
-    if (myArcs) atomicAdd(reinterpret_cast<unsigned long long *>(&sh.arcs), (unsigned long long)myArcs);
+    // arcs scanned: one 32-bit shared-memory atomic per warp (a 64-bit one is a compare-and-swap loop: it was 16 % of the
+    // kernel's stall samples, profiles/r02_runs_tier3_random20k_lplike_4k.md)
+    myArcs = __reduce_add_sync(0xFFFFFFFFu, myArcs);
+    if (lane == 0 && myArcs) atomicAdd(&chunkArcs, (uint32_t)myArcs);
     __syncthreads();
+    if (threadIdx.x == 0) sh.arcs += chunkArcs;
     RCLK(0);
     // ---- (2) one thread per target vertex -----------------------------------------------------------------------------------
     const uint32_t ngroups = nGroups;
@@ -918,21 +923,15 @@ __global__ void __launch_bounds__(kRunThreads, SMSGPU_RUNS_MIN_CTAS) ocwSearchRu
         if (threadIdx.x < 32) {
             if (!S.overflow && S.histN > 0) {
                 const int nsel = selectIntermediates<32>(T, M, S, maxInter, sel);
-                if (!S.overflow && T.lane == 0) {
+                if (!S.overflow) {
                     Emitter E;
                     E.R = &R;
                     E.srcIdx = srcIdx;
                     E.seq = 0;
                     E.tier = P.tier;
-                    for (int r = 0; r < nsel; ++r) {
-                        const int W = buildWalk(G, M, sel[r], src, srcIdx);
-                        if (W < 0) {
-                            S.overflow = 1;
-                            break;
-                        }
-                        simpleOddCyclesAndExtract(G, M, S, E, W);
-                        if (S.overflow) break;
-                    }
+#pragma unroll
+                    for (int r = 0; r < 16; ++r) sel[r] = T.shfl(sel[r], 0); // lane 0 holds the selection
+                    walksOfSource(G, M, S, E, sel, nsel, src, srcIdx);
                 }
                 S.overflow = T.shfl(S.overflow, 0);
             }

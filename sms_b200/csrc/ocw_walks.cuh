@@ -123,84 +123,118 @@ __device__ inline int tracePath(const TileMem &M, uint32_t t, uint32_t src, int3
 }
 
 // extractCycles (:229-328) on the closed walk c[0..len] (c[len] == c[0]) with stay flags st[0..len).
+// Called by all 32 lanes of the warp with identical arguments (E and the serial parts belong to lane 0): the arcs of the
+// walk's edges and the chord search -- for every position i, every arc of c[i], the first earlier position of its end
+// point: O(len^2 deg) loads -- are spread over the lanes; the candidates come out in the reference's order (position,
+// adjacency position, inner before outer) through a warp prefix sum.  Lane 0 then sorts and emits as before.
 __device__ inline void extractCycles(const GraphDev &G, TileMem &M, SrcState &S, Emitter &E, const int32_t *c,
                                      const int32_t *st, const int len) {
+    constexpr unsigned FULL = 0xFFFFFFFFu;
+    const int lane = threadIdx.x & 31;
     int32_t *warc = M.warc; // warc[i]: arc (in the row of c[i]) of the edge c[i-1] - c[i], i = 1..len
     int32_t *crs = M.crs;
     double *plen = M.plen;
-    // prefix sums (:242-250)
-    int numCross = 0;
-    double pathLength = 0.;
-    crs[0] = 0;
-    plen[0] = 0.;
-    for (int i = 1; i <= len; ++i) {
-        numCross += st[i - 1] ? 0 : 1;
+    // prefix sums (:242-250): the arcs in parallel, the sums serially (the order of the additions is the reference's)
+    for (int i = 1 + lane; i <= len; i += 32) {
         const long long a = findArc(G, c[i], c[i - 1]);
         SMS_CHK(a >= 0);
         SMS_CHK(i <= 2 * (int)M.caps.walkCap + 1);
         warc[i] = (int32_t)a;
-        const double w = G.arcs[a].w;
-        pathLength += st[i - 1] ? w : 1 - w;
-        crs[i] = numCross;
-        plen[i] = pathLength;
+        plen[i] = G.arcs[a].w; // the edge's weight for now, the prefix sum below
     }
+    __syncwarp(FULL);
+    if (lane == 0) {
+        int numCross = 0;
+        double pathLength = 0.;
+        crs[0] = 0;
+        plen[0] = 0.;
+        for (int i = 1; i <= len; ++i) {
+            numCross += st[i - 1] ? 0 : 1;
+            const double w = plen[i];
+            pathLength += st[i - 1] ? w : 1 - w;
+            crs[i] = numCross;
+            plen[i] = pathLength;
+        }
+    }
+    __syncwarp(FULL);
     // good chords (:254-306)
     int nch = 0;
+    const double total = plen[len];
     for (int i = 2; i < len; ++i) {
-        const int32_t cur = c[i];
-        for (long long a = G.rowptr[cur]; a < G.rowptr[cur + 1]; ++a) {
-            const Arc arc = G.arcs[a];
-            const int32_t nb = arc.nbr & 0x7FFFFFFF;
-            if (nb == c[i - 1] || nb == c[i + 1]) continue;
-            int j = -1;
-            for (int k = 0; k < i; ++k)
-                if (c[k] == nb) {
-                    j = k;
-                    break;
-                }
-            if (j < 0) continue;
-            const int innerCrossingDif = crs[i] - crs[j];
-            const double innerLen = plen[i] - plen[j];
-            const double outerLen = plen[len] - innerLen;
-            // weights_[edgeId(c[i], c[j])]: first arc of c[i] towards c[j]
-            const long long ca = findArc(G, cur, nb);
-            SMS_CHK(ca >= 0);
-            const double x = G.arcs[ca].w;
+        const int32_t cur = c[i], prv = c[i - 1], nxt = c[i + 1];
+        const long long rb = G.rowptr[cur], re = G.rowptr[cur + 1];
+        for (long long base = rb; base < re; base += 32) {
+            const long long a = base + lane;
             int f0 = -1, l0 = 0, f1 = -1, l1 = 0; // flags: bit0 crossing, bit1 inner
-            if ((innerCrossingDif % 2) == 0) {
-                if (innerLen - x < 0) {
-                    f0 = 1 | 2;
-                    l0 = i - j + 1;
-                }
-                if (outerLen + x < 1) {
-                    f1 = 0;
-                    l1 = len - i + j + 1;
-                }
-            } else {
-                if (innerLen + x < 1) {
-                    f0 = 2;
-                    l0 = i - j + 1;
-                }
-                if (outerLen - x < 0) {
-                    f1 = 1;
-                    l1 = len - i + j + 1;
+            if (a < re) {
+                const Arc arc = G.arcs[a];
+                const int32_t nb = arc.nbr & 0x7FFFFFFF;
+                if (nb != prv && nb != nxt) {
+                    int j = -1;
+                    for (int k = 0; k < i; ++k)
+                        if (c[k] == nb) {
+                            j = k;
+                            break;
+                        }
+                    if (j >= 0) {
+                        const int innerCrossingDif = crs[i] - crs[j];
+                        const double innerLen = plen[i] - plen[j];
+                        const double outerLen = total - innerLen;
+                        // weights_[edgeId(c[i], c[j])]: the first arc of c[i] towards c[j] -- this one, the graph is simple
+                        const double x = arc.w;
+                        if ((innerCrossingDif % 2) == 0) {
+                            if (innerLen - x < 0) {
+                                f0 = 1 | 2;
+                                l0 = i - j + 1;
+                            }
+                            if (outerLen + x < 1) {
+                                f1 = 0;
+                                l1 = len - i + j + 1;
+                            }
+                        } else {
+                            if (innerLen + x < 1) {
+                                f0 = 2;
+                                l0 = i - j + 1;
+                            }
+                            if (outerLen - x < 0) {
+                                f1 = 1;
+                                l1 = len - i + j + 1;
+                            }
+                        }
+                        // the chord's start position j rides in the flags' high bits until the candidate is written
+                        if (f0 >= 0) f0 |= j << 8;
+                        if (f1 >= 0) f1 |= j << 8;
+                    }
                 }
             }
+            const int cnt = (f0 >= 0 ? 1 : 0) + (f1 >= 0 ? 1 : 0);
+            int incl = cnt;
+#pragma unroll
+            for (int off = 1; off < 32; off <<= 1) {
+                const int o = __shfl_up_sync(FULL, incl, off);
+                if (lane >= off) incl += o;
+            }
+            const int tot = __shfl_sync(FULL, incl, 31);
+            if (tot == 0) continue;
+            if (nch + tot > (int)M.caps.chordCap) {
+                S.overflow = 1;
+                return;
+            }
+            int pos = nch + incl - cnt;
             for (int q = 0; q < 2; ++q) {
                 const int f = q ? f1 : f0;
                 if (f < 0) continue;
-                if (nch >= (int)M.caps.chordCap) {
-                    S.overflow = 1;
-                    return;
-                }
-                int32_t *ch = M.chords + 4 * nch++;
-                ch[0] = j;
+                int32_t *ch = M.chords + 4 * pos++;
+                ch[0] = f >> 8;
                 ch[1] = i;
                 ch[2] = q ? l1 : l0;
-                ch[3] = (int32_t)((uint32_t)f | ((uint32_t)ca << 2)); // 2m < 2^30 checked at create
+                ch[3] = (int32_t)((uint32_t)(f & 3) | ((uint32_t)a << 2)); // 2m < 2^30 checked at create
             }
+            nch += tot;
         }
     }
+    __syncwarp(FULL);
+    if (lane != 0) return; // the rest is serial: lane 0 (the caller re-converges the warp)
     // stable sort by resulting length (:309; canonical: stable)
     for (int a = 1; a < nch; ++a) {
         int32_t t0 = M.chords[4 * a], t1 = M.chords[4 * a + 1], t2 = M.chords[4 * a + 2], t3 = M.chords[4 * a + 3];
@@ -272,8 +306,10 @@ __device__ inline void extractCycles(const GraphDev &G, TileMem &M, SrcState &S,
     }
 }
 
-// simpleOddCycles (:202-227) on the closed walk wn[0..W], then extractCycles on every piece
+// simpleOddCycles (:202-227) on the closed walk wn[0..W], then extractCycles on every piece.  All 32 lanes, identical
+// control flow (every lane reads the same walk); S.overflow is made uniform after every piece.
 __device__ inline void simpleOddCyclesAndExtract(const GraphDev &G, TileMem &M, SrcState &S, Emitter &E, const int W) {
+    constexpr unsigned FULL = 0xFFFFFFFFu;
     const int32_t *wn = M.wn, *ws = M.ws;
     int lastLeft = -1;
     bool any = false;
@@ -289,12 +325,18 @@ __device__ inline void simpleOddCyclesAndExtract(const GraphDev &G, TileMem &M, 
             lastLeft = pp;
             if (i - lastLeft > 2) {
                 extractCycles(G, M, S, E, wn + lastLeft, ws + lastLeft, i - lastLeft);
+                __syncwarp(FULL);
+                S.overflow = __shfl_sync(FULL, S.overflow, 0);
                 if (S.overflow) return;
                 any = true;
             }
         }
     }
-    if (!any) extractCycles(G, M, S, E, wn, ws, W);
+    if (!any) {
+        extractCycles(G, M, S, E, wn, ws, W);
+        __syncwarp(FULL);
+        S.overflow = __shfl_sync(FULL, S.overflow, 0);
+    }
 }
 
 // intermediateVertexToOcw (:138-188) into M.wn / M.ws; returns the number of edges, -1 on overflow.
@@ -331,6 +373,25 @@ __device__ inline int buildWalk(const GraphDev &G, const TileMem &M, uint32_t t,
     for (int i = 0; i <= endPath; ++i) addEdge(pa[i + 1] >> 1, ((pa[i] ^ pa[i + 1]) & 1) == 0);
     for (int i = endTwin; i >= 0; --i) addEdge(pb[i] >> 1, ((pb[i] ^ pb[i + 1]) & 1) == 0);
     return W;
+}
+
+// The walks of one source: intermediateVertexToOcw -> simpleOddCycles -> extractCycles for each selected intermediate
+// (ocw_seperator.cpp:341-358).  All 32 lanes; lane 0 owns the emitter.  Leaves S.overflow uniform.
+__device__ inline void walksOfSource(const GraphDev &G, TileMem &M, SrcState &S, Emitter &E, const uint32_t *sel, const int nsel,
+                                     const uint32_t src, const int32_t now) {
+    constexpr unsigned FULL = 0xFFFFFFFFu;
+    for (int r = 0; r < nsel; ++r) {
+        int W = 0;
+        if ((threadIdx.x & 31) == 0) W = buildWalk(G, M, sel[r], src, now);
+        __syncwarp(FULL);
+        W = __shfl_sync(FULL, W, 0);
+        if (W < 0) {
+            S.overflow = 1;
+            return;
+        }
+        simpleOddCyclesAndExtract(G, M, S, E, W);
+        if (S.overflow) return;
+    }
 }
 
 // Mode V, end of a source that completed in this tier: remember whether it found nothing, and if so do what
