@@ -127,7 +127,9 @@ void smsgpu_default_params(smsgpu_params *p);
 /* ---- per round input: replaces the m x updateWeights (ocw_seperator.cpp:25-35, called from
  * conshdlr_oscw.cpp:175-180) and the n x updateBlacklist (ocw_seperator.hpp:25-28, conshdlr_oscw.cpp:182-185).
  * x_by_eid[m] is the LP point indexed by edge id (clamped to [0,1] on the device); blacklist[n] is 1 for the
- * root and locally fixed vertices.  Host buffers; copied through pinned staging, asynchronously. */
+ * root and locally fixed vertices.  Host buffers; pageable ones are copied through pinned staging, page-locked ones
+ * (the context's own, below, or the caller's cudaHostAlloc / cudaHostRegister memory) are read by the DMA where they
+ * lie and must stay untouched until the round has been launched. */
 int smsgpu_set_round_input(smsgpu_ctx *ctx, const double *x_by_eid, const uint8_t *blacklist);
 /* The context's own pinned staging buffers (x[m], blacklist[n]).  A handler that gathers x* edge by edge
  * (SCIPgetSolVal per edge, conshdlr_oscw.cpp:175-180) writes straight into them and passes the same pointers to

@@ -653,12 +653,29 @@ int smsgpu_set_round_input(smsgpu_ctx *ctx, const double *x, const uint8_t *bl) 
     if (!ctx) return SMSGPU_ERR_ARG;
     if (!x || !bl) return fail(ctx, SMSGPU_ERR_ARG, "x_by_eid or blacklist is null");
     CU(cudaSetDevice(ctx->device));
-    // pageable -> pinned staging -> device, all on the context's stream
-    if (x != ctx->hX.p) std::memcpy(ctx->hX.p, x, (size_t)ctx->m * sizeof(double)); // smsgpu_input_buffers: already there
-    if (bl != ctx->hBl.p) std::memcpy(ctx->hBl.p, bl, (size_t)ctx->n);
+    // pageable -> pinned staging -> device, all on the context's stream.  No staging copy for the context's own buffers
+    // (smsgpu_input_buffers) nor for any other page-locked buffer of the caller (cudaHostAlloc / cudaHostRegister): the DMA
+    // reads it where it lies -- the caller must leave it alone until the round has been launched (smsgpu_separate*).
+    auto pinned = [](const void *p) {
+        cudaPointerAttributes a{};
+        if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+            (void)cudaGetLastError();
+            return false;
+        }
+        return a.type == cudaMemoryTypeHost;
+    };
+    const void *sx = x, *sb = bl;
+    if (x != ctx->hX.p && !pinned(x)) {
+        std::memcpy(ctx->hX.p, x, (size_t)ctx->m * sizeof(double));
+        sx = ctx->hX.p;
+    }
+    if (bl != ctx->hBl.p && !pinned(bl)) {
+        std::memcpy(ctx->hBl.p, bl, (size_t)ctx->n);
+        sb = ctx->hBl.p;
+    }
     CU(cudaEventRecord(ctx->ev[6], ctx->stream));
-    if (ctx->m) CU(cudaMemcpyAsync(ctx->dX.p, ctx->hX.p, (size_t)ctx->m * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
-    CU(cudaMemcpyAsync(ctx->dBl.p, ctx->hBl.p, (size_t)ctx->n, cudaMemcpyHostToDevice, ctx->stream));
+    if (ctx->m) CU(cudaMemcpyAsync(ctx->dX.p, sx, (size_t)ctx->m * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaMemcpyAsync(ctx->dBl.p, sb, (size_t)ctx->n, cudaMemcpyHostToDevice, ctx->stream));
     CU(cudaEventRecord(ctx->ev[7], ctx->stream));
     ctx->xPtr = ctx->dX.as<double>();
     ctx->blPtr = ctx->dBl.as<uint8_t>();
