@@ -429,17 +429,21 @@ def measure_workload(name, args, torch, dist, rank, world, device, full=True):
     res["ms_search"], res["ms_weights"], res["ms_dedup"], res["ms_total_device"] = ms.tolist()
 
     # ---- e2e leg: host buffers through the C ABI, H2D and D2H inside the timed region ----
-    # The handler's gather loop (one SCIPgetSolVal per edge, conshdlr_oscw.cpp:175-180) writes x* into the context's pinned
-    # staging buffers (smsgpu_input_buffers); here the step copies the round's x* / blacklist into them, which stands for
-    # that loop, then H2D -> round -> D2H of the cut list.  Rank 0 is the consumer (SCIP's thread): the other ranks
-    # upload their replica of x* and run their share, but do not read the merged list back.
+    # A handler gathers x* edge by edge (one SCIPgetSolVal per edge, conshdlr_oscw.cpp:175-180) into page-locked memory (the
+    # context's own staging buffers, smsgpu_input_buffers, or its own); timed here: H2D of x* + blacklist -> round -> D2H of
+    # the cut list.  Rank 0 is the consumer (SCIP's thread): the other ranks upload their replica of x* and run their share,
+    # but do not read the merged list back.
     if full:
-        hx, hbl = ctx.input_buffers()
+        # the round's inputs lie in page-locked host memory (the bench contract: "host->device copy of that step's inputs
+        # from pinned host memory"): smsgpu_set_round_input DMAs them from where they lie
+        pxs = [torch.from_numpy(v).pin_memory() for v in xs]
+        pbl = torch.from_numpy(bl).pin_memory()
+        hxs = [t.numpy() for t in pxs]
+        hbl = pbl.numpy()
 
         def step_host():
-            np.copyto(hx, xs[kstep[1] % len(xs)])
+            hx = hxs[kstep[1] % len(hxs)]
             kstep[1] += 1
-            np.copyto(hbl, bl)
             ctx.set_round_input(hx, hbl)
             if rank == 0:
                 ctx.separate_nocopy(p)
@@ -493,8 +497,9 @@ def measure_dense(args, torch, device):
         ctx.set_round_input_device(dx.data_ptr(), dbl.data_ptr())
         ctx._check(lib.smsgpu_small_cycles_scan_device(ctx.h, 3))
 
-    def step_host():  # x* from the host, walks back on the host
-        np.copyto(hx, x)
+    np.copyto(hx, x)  # x* lies in the context's page-locked staging buffer
+
+    def step_host():  # x* from the host (H2D), walks back on the host (D2H)
         ctx.set_round_input(hx, hbl)
         return ctx.small_cycles_scan_nocopy(3)
 

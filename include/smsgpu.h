@@ -71,7 +71,10 @@ typedef struct smsgpu_params {
  *   SMSGPU_MODE_VERBATIM     the cut list of the reference's own sequential sweep, reproduced exactly: the blacklist is
  *                            kept as a per-vertex TIME STAMP (index of the first source that blacklists the vertex), every
  *                            source reads "blacklisted before me", and the round is iterated to the fixed point of the
- *                            stamps (smsgpu_stats.verbatim_iterations sweeps).  Single GPU. */
+ *                            stamps (smsgpu_stats.verbatim_sweeps sweeps).  Single GPU.  Cost: several
+ *                            sweeps per round -- far ahead of the reference's CPU sweep on fractional x*, but on tie-heavy LP
+ *                            iterates (long dependency chains between consecutive sources, ~100 sweeps) BEHIND it; measured
+ *                            numbers in DESIGN.md section 5. */
 #define SMSGPU_MODE_INDEPENDENT 0
 #define SMSGPU_MODE_VERBATIM 1
 
