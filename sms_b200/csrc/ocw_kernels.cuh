@@ -188,9 +188,9 @@ __global__ void floodStampsKernel(const GraphDev G, unsigned int *changed) {
 // Sources known to find nothing whatever the blacklist (they found nothing against the round's INITIAL blacklist, and a
 // larger blacklist only removes walks) are not searched again in later sweeps; their writes are repeated here: nothing
 // when the source is blacklisted at its time (ocw_seperator.cpp:334), else the seed of blacklistIntReachable.
-__global__ void reseedEmptySourcesKernel(const GraphDev G, const long long nsrc, const int32_t *__restrict__ sources,
+__global__ void reseedEmptySourcesKernel(const GraphDev G, const long long lo, const long long hi, const int32_t *__restrict__ sources,
                                          const uint8_t *__restrict__ emptyB0) {
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nsrc; i += (long long)gridDim.x * blockDim.x) {
+    for (long long i = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += (long long)gridDim.x * blockDim.x) {
         if (!emptyB0[i]) continue;
         const int32_t now = (int32_t)i;
         const uint32_t src = sources ? (uint32_t)sources[i] : (uint32_t)i;
@@ -209,9 +209,13 @@ __global__ void reseedEmptySourcesKernel(const GraphDev G, const long long nsrc,
     }
 }
 // work list of the later sweeps: every source that is not known to be empty
-__global__ void activeSourcesKernel(const long long nsrc, const uint8_t *__restrict__ emptyB0, int32_t *list, unsigned int *count) {
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nsrc; i += (long long)gridDim.x * blockDim.x)
+__global__ void activeSourcesKernel(const long long lo, const long long hi, const uint8_t *__restrict__ emptyB0, int32_t *list,
+                                    unsigned int *count) {
+    for (long long i = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += (long long)gridDim.x * blockDim.x)
         if (!emptyB0[i]) list[atomicAdd(count, 1u)] = (int32_t)i;
+}
+__global__ void iotaKernel(const long long n, int32_t *out) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) out[i] = (int32_t)i;
 }
 __global__ void compareStampsKernel(const long long n, const int32_t *__restrict__ a, const int32_t *__restrict__ b, unsigned int *differ) {
     bool d = false;

@@ -194,7 +194,7 @@ struct smsgpu_ctx {
     smsgpu_stats stats{};
 
     // SMSGPU_MODE_VERBATIM: two stamp arrays (previous / current sweep), per-source "found nothing" flags, work list
-    DevBuf vStampA, vStampB, vEmpty, vEmptyB0, vActive, vFlags;
+    DevBuf vStampA, vStampB, vStampC, vIota, vEmpty, vEmptyB0, vActive, vFlags;
     long long vActiveCount = 0;
 
     // multi-GPU
@@ -622,7 +622,7 @@ void smsgpu_destroy(smsgpu_ctx *ctx) {
                      &ctx->fin.src, &ctx->fin.seq, &ctx->fin.viol, &ctx->scFin.off, &ctx->scFin.node, &ctx->scFin.eid,
                      &ctx->scFin.stay, &ctx->scFin.ncross, &ctx->scFin.src, &ctx->scFin.viol, &ctx->scNodes[0], &ctx->scNodes[1], &ctx->scEids[0],
                      &ctx->scEids[1], &ctx->gCounts,
-                     &ctx->pBlock, &ctx->mBlocks, &ctx->dArcSrc, &ctx->dColSorted, &ctx->eHoleBase, &ctx->scCode, &ctx->vStampA, &ctx->vStampB, &ctx->vEmpty, &ctx->vEmptyB0, &ctx->vActive, &ctx->vFlags, &ctx->mNode, &ctx->mEid, &ctx->mStay, &ctx->mOff, &ctx->mLen, &ctx->mSrc,
+                     &ctx->pBlock, &ctx->mBlocks, &ctx->dArcSrc, &ctx->dColSorted, &ctx->eHoleBase, &ctx->scCode, &ctx->vStampA, &ctx->vStampB, &ctx->vStampC, &ctx->vIota, &ctx->vEmpty, &ctx->vEmptyB0, &ctx->vActive, &ctx->vFlags, &ctx->mNode, &ctx->mEid, &ctx->mStay, &ctx->mOff, &ctx->mLen, &ctx->mSrc,
                      &ctx->mSeq, &ctx->mValid};
     for (auto *b : dev) b->release();
     PinBuf *pin[] = {&ctx->hX, &ctx->hBl, &ctx->hCounters, &ctx->hHeavy, &ctx->host.off, &ctx->host.node, &ctx->host.eid,
@@ -987,18 +987,35 @@ int separateLocal(smsgpu_ctx *ctx, const smsgpu_params &P) {
     // One sweep over the sources: every tier in turn until each source has finished somewhere; raw walks in the arena.
     // wl0 == nullptr: all local sources, issued by the history of the previous round (independent-source mode's one and
     // only sweep); else the given work list, no history (the sweeps of SMSGPU_MODE_VERBATIM).
+    // mode V, windowed: the sweep runs the sources [lo, hi) only; stamps, per-source flags and the walks of the windows in front
+    // of it are final and stay (stamps start from `base`, the arena counters from keepCuts / keepNodes)
+    struct {
+        bool on = false;
+        long long lo = 0, hi = 0, keepCuts = 0, keepNodes = 0;
+        const int32_t *base = nullptr;
+    } vw;
+    constexpr int kArenaGrew = 0x7A7A; // (internal) sweep(): the arena was re-allocated under a windowed mode-V round
     auto sweep = [&](const int32_t *wl0, long long nw0, const bool plain) -> int {
     for (int attempt = 0;; ++attempt) {
         if (attempt > 4) return fail(ctx, SMSGPU_ERR_INTERNAL, "raw arena kept overflowing");
         CU(cudaMemsetAsync(dc, 0, 24 * sizeof(unsigned long long), st));
-        if (G.blStampNext) { // mode V: this sweep's stamps start from the round's initial blacklist
-            initStampsKernel<<<ctx->smCount * 4, 256, 0, st>>>(ctx->n, ctx->blPtr, G.blStampNext);
-            CU(cudaGetLastError());
-            CU(cudaMemsetAsync(G.srcEmpty, 0, (size_t)std::max<long long>(nsrc, 1), st));
-            ctx->stats.total_launches += 1;
+        if (vw.on) {
+            hc[22] = (unsigned long long)vw.keepCuts;
+            hc[23] = (unsigned long long)vw.keepNodes;
+            CU(cudaMemcpyAsync(dc, hc + 22, 16, cudaMemcpyHostToDevice, st));
+            CU(cudaMemcpyAsync(G.blStampNext, vw.base, (size_t)ctx->n * 4, cudaMemcpyDeviceToDevice, st));
+            CU(cudaMemsetAsync(G.srcEmpty + vw.lo, 0, (size_t)(vw.hi - vw.lo), st));
+            CU(cudaMemsetAsync(ctx->srcTier.as<int8_t>() + vw.lo, 0xFF, (size_t)(vw.hi - vw.lo), st));
+        } else {
+            if (G.blStampNext) { // mode V, one window: this sweep's stamps start from the round's initial blacklist
+                initStampsKernel<<<ctx->smCount * 4, 256, 0, st>>>(ctx->n, ctx->blPtr, G.blStampNext);
+                CU(cudaGetLastError());
+                CU(cudaMemsetAsync(G.srcEmpty, 0, (size_t)std::max<long long>(nsrc, 1), st));
+                ctx->stats.total_launches += 1;
+            }
+            CU(cudaMemsetAsync(ctx->srcTier.p, 0xFF, (size_t)std::max<long long>(nsrc, 1), st));
+            CU(cudaMemsetAsync(ctx->srcWork.p, 0, (size_t)std::max<long long>(nsrc, 1) * 4, st)); // skipped sources: no work
         }
-        CU(cudaMemsetAsync(ctx->srcTier.p, 0xFF, (size_t)std::max<long long>(nsrc, 1), st));
-        CU(cudaMemsetAsync(ctx->srcWork.p, 0, (size_t)std::max<long long>(nsrc, 1) * 4, st)); // skipped sources: no work
         RawOut R{};
         R.node = ctx->rNode.as<int32_t>();
         R.eid = ctx->rEid.as<int32_t>();
@@ -1176,6 +1193,7 @@ int separateLocal(smsgpu_ctx *ctx, const smsgpu_params &P) {
             CU(ctx->labDist.ensure((size_t)ctx->labCap * 8));
             redo = true;
         }
+        if (redo && vw.on) return kArenaGrew;
         if (redo) continue;
         if (plain && ctx->useHistory && nsrc > 0) {
             // tier 0 (shared memory) is skipped for the next 15 rounds when it completed fewer than 1/4 of its sources
@@ -1231,80 +1249,119 @@ int separateLocal(smsgpu_ctx *ctx, const smsgpu_params &P) {
         CU(ctx->vEmptyB0.ensure(nb));
         CU(ctx->vActive.ensure(nb * 4));
         CU(ctx->vFlags.ensure(4 * sizeof(unsigned int)));
-        int32_t *cur = ctx->vStampA.as<int32_t>(), *next = ctx->vStampB.as<int32_t>();
+        CU(ctx->vStampC.ensure((size_t)ctx->n * 4));
+        CU(ctx->vIota.ensure(nb * 4));
+        int32_t *cur = ctx->vStampA.as<int32_t>(), *next = ctx->vStampB.as<int32_t>(), *base = ctx->vStampC.as<int32_t>();
         unsigned int *flags = ctx->vFlags.as<unsigned int>(); // [0] flood changed, [1] stamps differ, [2] active count
         unsigned int hf[4] = {0, 0, 0, 0};
-        initStampsKernel<<<ctx->smCount * 4, 256, 0, st>>>(ctx->n, ctx->blPtr, cur);
+        const unsigned gv = (unsigned)ctx->smCount * 8;
+        iotaKernel<<<gv, 256, 0, st>>>(nsrc, ctx->vIota.as<int32_t>());
         CU(cudaGetLastError());
         const bool savedMirror = ctx->pairsMirror;
         ctx->pairsMirror = false; // the two sides of a vertex sit at different times: each is searched
-        bool shortcut = !(std::getenv("SMSGPU_VERBATIM_FULL") && std::getenv("SMSGPU_VERBATIM_FULL")[0] == '1');
-        bool verifying = false;
-        const int32_t *active = nullptr;
-        long long nactive = nsrc;
+        const bool shortcutOn = !(std::getenv("SMSGPU_VERBATIM_FULL") && std::getenv("SMSGPU_VERBATIM_FULL")[0] == '1');
         const int32_t *srcList = ctx->explicitSources ? ctx->dSources.as<int32_t>() : nullptr;
-        const unsigned gv = (unsigned)ctx->smCount * 8;
+        // WINDOWS.  A source only reads stamps of EARLIER sources, so the list can be brought to its fixed point window by
+        // window, in order: the stamps of the finished windows are final (`base`), the sweeps of a window run its sources only.
+        // The sweeps a window needs are the length of the dependency chains INSIDE it, so short windows need few -- the work
+        // falls from (chain length of the whole list) x n to about (chain length of a window) x n.  Window = n / 16, at least
+        // 1024 sources (a sweep has ~10 launches and 4 host waits of fixed cost); SMSGPU_VERBATIM_WINDOW overrides, 0 = one window.
+        long long W = std::max<long long>(1024, (nsrc / 16 + 1) & ~1ll);
+        if (const char *ew = std::getenv("SMSGPU_VERBATIM_WINDOW")) W = std::atoll(ew);
+        if (W <= 0 || W > nsrc) W = std::max<long long>(nsrc, 1);
         int rcV = 0;
-        for (long long sweepNo = 1;; ++sweepNo) {
-            if (sweepNo > std::max<long long>(nsrc, 1) + 2) {
-                rcV = fail(ctx, SMSGPU_ERR_INTERNAL, "the stamps did not reach a fixed point in %lld sweeps", sweepNo - 1);
-                break;
-            }
-            const bool full = active == nullptr;
-            G.blStamp = cur;
-            G.blStampNext = next;
-            G.srcEmpty = ctx->vEmpty.as<uint8_t>();
-            if ((rcV = sweep(active, nactive, false))) break;
-            ctx->stats.verbatim_sweeps = sweepNo;
-            auto cuv = [&](cudaError_t e) { return e == cudaSuccess ? 0 : fail(ctx, SMSGPU_ERR_CUDA, "mode V: %s", cudaGetErrorString(e)); };
-            if (!full) {
-                reseedEmptySourcesKernel<<<gv, 256, 0, st>>>(G, nsrc, srcList, ctx->vEmptyB0.as<uint8_t>());
-                ctx->stats.total_launches += 1;
-            }
-            for (long long pass = 0;; ++pass) { // flood of the empty sources' stamps over integral edges
-                if ((rcV = cuv(cudaMemsetAsync(flags, 0, 8, st)))) break;
-                floodStampsKernel<<<gv, 256, 0, st>>>(G, flags);
-                ctx->stats.total_launches += 1;
-                if ((rcV = cuv(cudaMemcpyAsync(hf, flags, 4, cudaMemcpyDeviceToHost, st)))) break;
-                if ((rcV = cuv(cudaStreamSynchronize(st)))) break;
-                if (!hf[0]) break;
-                if (pass > ctx->n + 2) {
-                    rcV = fail(ctx, SMSGPU_ERR_INTERNAL, "stamp flood did not settle");
+        long long sweepsTotal = 0;
+        auto cuv = [&](cudaError_t e) { return e == cudaSuccess ? 0 : fail(ctx, SMSGPU_ERR_CUDA, "mode V: %s", cudaGetErrorString(e)); };
+        for (int restart = 0; restart < 4 && !rcV; ++restart) { // (restarted from the first window when the walk arena had to grow)
+        bool again = false;
+        initStampsKernel<<<ctx->smCount * 4, 256, 0, st>>>(ctx->n, ctx->blPtr, base);
+        if ((rcV = cuv(cudaGetLastError()))) break;
+        vw.keepCuts = vw.keepNodes = 0;
+        for (long long lo = 0; lo < nsrc && !rcV && !again; lo += W) {
+            const long long hi = std::min(nsrc, lo + W);
+            vw.on = W < nsrc;
+            vw.lo = lo;
+            vw.hi = hi;
+            vw.base = base;
+            if ((rcV = cuv(cudaMemcpyAsync(cur, base, (size_t)ctx->n * 4, cudaMemcpyDeviceToDevice, st)))) break;
+            bool shortcut = shortcutOn, verifying = false;
+            const int32_t *active = nullptr;
+            long long nactive = hi - lo;
+            for (long long sweepNo = 1;; ++sweepNo) {
+                if (sweepNo > (hi - lo) + 2) {
+                    rcV = fail(ctx, SMSGPU_ERR_INTERNAL, "the stamps did not reach a fixed point in %lld sweeps", sweepNo - 1);
                     break;
                 }
-            }
-            if (rcV) break;
-            compareStampsKernel<<<gv, 256, 0, st>>>(ctx->n, cur, next, flags + 1);
-            ctx->stats.total_launches += 1;
-            if (sweepNo == 1 && shortcut) { // sources that found nothing against the initial blacklist never find anything
-                if ((rcV = cuv(cudaMemcpyAsync(ctx->vEmptyB0.p, ctx->vEmpty.p, nb, cudaMemcpyDeviceToDevice, st)))) break;
-                if ((rcV = cuv(cudaMemsetAsync(flags + 2, 0, 4, st)))) break;
-                activeSourcesKernel<<<gv, 256, 0, st>>>(nsrc, ctx->vEmptyB0.as<uint8_t>(), ctx->vActive.as<int32_t>(), flags + 2);
+                const bool full = active == nullptr;
+                G.blStamp = cur;
+                G.blStampNext = next;
+                G.srcEmpty = ctx->vEmpty.as<uint8_t>();
+                rcV = sweep(full ? ctx->vIota.as<int32_t>() + lo : active, full ? hi - lo : nactive, false);
+                if (rcV == kArenaGrew) { // the arena was re-allocated: the walks of the finished windows are gone
+                    rcV = 0;
+                    again = true;
+                    break;
+                }
+                if (rcV) break;
+                ++sweepsTotal;
+                ctx->stats.verbatim_sweeps = sweepsTotal;
+                if (!full) {
+                    reseedEmptySourcesKernel<<<gv, 256, 0, st>>>(G, lo, hi, srcList, ctx->vEmptyB0.as<uint8_t>());
+                    ctx->stats.total_launches += 1;
+                }
+                for (long long pass = 0;; ++pass) { // flood of the empty sources' stamps over integral edges
+                    if ((rcV = cuv(cudaMemsetAsync(flags, 0, 8, st)))) break;
+                    floodStampsKernel<<<gv, 256, 0, st>>>(G, flags);
+                    ctx->stats.total_launches += 1;
+                    if ((rcV = cuv(cudaMemcpyAsync(hf, flags, 4, cudaMemcpyDeviceToHost, st)))) break;
+                    if ((rcV = cuv(cudaStreamSynchronize(st)))) break;
+                    if (!hf[0]) break;
+                    if (pass > ctx->n + 2) {
+                        rcV = fail(ctx, SMSGPU_ERR_INTERNAL, "stamp flood did not settle");
+                        break;
+                    }
+                }
+                if (rcV) break;
+                compareStampsKernel<<<gv, 256, 0, st>>>(ctx->n, cur, next, flags + 1);
                 ctx->stats.total_launches += 1;
+                if (sweepNo == 1 && shortcut) { // sources that found nothing against the stamps in front of the window never find anything
+                    if ((rcV = cuv(cudaMemcpyAsync(ctx->vEmptyB0.as<uint8_t>() + lo, ctx->vEmpty.as<uint8_t>() + lo, (size_t)(hi - lo),
+                                                   cudaMemcpyDeviceToDevice, st))))
+                        break;
+                    if ((rcV = cuv(cudaMemsetAsync(flags + 2, 0, 4, st)))) break;
+                    activeSourcesKernel<<<gv, 256, 0, st>>>(lo, hi, ctx->vEmptyB0.as<uint8_t>(), ctx->vActive.as<int32_t>(), flags + 2);
+                    ctx->stats.total_launches += 1;
+                }
+                if ((rcV = cuv(cudaMemcpyAsync(hf, flags, 12, cudaMemcpyDeviceToHost, st)))) break;
+                if ((rcV = cuv(cudaStreamSynchronize(st)))) break;
+                if (sweepNo == 1 && shortcut) ctx->vActiveCount = (long long)hf[2];
+                std::swap(cur, next);
+                if (std::getenv("SMSGPU_DEBUG_OVF"))
+                    std::fprintf(stderr, "[smsgpu] mode V window [%lld, %lld) sweep %lld (%s, %lld sources): stamps %s\n", lo, hi, sweepNo,
+                                 full ? "full" : "active set", full ? hi - lo : nactive, hf[1] ? "changed" : "reproduced");
+                if (!hf[1]) {
+                    if (full) break; // a full sweep of the window reproduced the stamps it read: its walks are the sequential sweep's
+                    verifying = true; // the active set has converged: one full sweep has to confirm it
+                    active = nullptr;
+                    continue;
+                }
+                if (verifying) shortcut = false; // the confirmation failed (never observed): full sweeps from here on
+                if (shortcut && !verifying) {
+                    active = ctx->vActive.as<int32_t>();
+                    nactive = ctx->vActiveCount;
+                } else {
+                    active = nullptr;
+                }
             }
-            if ((rcV = cuv(cudaMemcpyAsync(hf, flags, 12, cudaMemcpyDeviceToHost, st)))) break;
-            if ((rcV = cuv(cudaStreamSynchronize(st)))) break;
-            if (sweepNo == 1 && shortcut) ctx->vActiveCount = (long long)hf[2];
-            std::swap(cur, next);
-            if (std::getenv("SMSGPU_DEBUG_OVF"))
-                std::fprintf(stderr, "[smsgpu] mode V sweep %lld (%s, %lld sources): stamps %s\n", sweepNo, full ? "full" : "active set", nactive,
-                             hf[1] ? "changed" : "reproduced");
-            if (!hf[1]) {
-                if (full) break; // a full sweep reproduced the stamps it read: its walks are the sequential sweep's
-                verifying = true; // the active set has converged: one full sweep has to confirm it
-                active = nullptr;
-                nactive = nsrc;
-                continue;
-            }
-            if (verifying) shortcut = false; // the confirmation failed (never observed): full sweeps from here on
-            if (shortcut && !verifying) {
-                active = ctx->vActive.as<int32_t>();
-                nactive = ctx->vActiveCount;
-            } else {
-                active = nullptr;
-                nactive = nsrc;
-            }
+            if (rcV || again) break;
+            // the window is final: its stamps join the base, its walks stay in the arena
+            std::swap(base, cur);
+            vw.keepCuts = rawCuts;
+            vw.keepNodes = rawNodes;
         }
+        if (!again) break;
+        }
+        vw.on = false;
         ctx->pairsMirror = savedMirror;
         if (rcV) return rcV;
     }

@@ -124,3 +124,28 @@ def test_gpu_mode_v_with_fixed_vertices_and_a_permuted_source_list(orc):
         assert got.walks() == exp.walks()
     finally:
         sep.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("window", ["0", "37", "256"])
+def test_gpu_mode_v_windows(orc, window, monkeypatch):
+    """The fixed point is taken window by window of the source list (smsgpu.cu, mode V): any window length gives the
+    sequential sweep -- 0 = one window (the whole list), 37 = odd and tiny (many windows, twins split), 256."""
+    monkeypatch.setenv("SMSGPU_VERBATIM_WINDOW", window)
+    for mk, xf in ((lambda: I.torus2d(30), I.xstar_lp_like), (lambda: I.random_graph(3000, 12000, seed=11), I.xstar_uniform),
+                   (lambda: I.torus3d(6), I.xstar_half_integral)):
+        inst = mk()
+        x = xf(inst.m, seed=7)
+        bl = inst.root_blacklist()
+        exp = orc.sweep(inst, x, blacklist=bl, mode="V", canonical=True)
+        sep = _gpu_sep(inst)
+        try:
+            sep.setRoundInput(x, bl)
+            got = sep.separateRound(dedup=False, mode=1)
+            assert got.walks() == exp.walks(), f"{inst.name} window {window}"
+            st = sep.ctx.stats()
+            assert st["verbatim_sweeps"] >= 1
+            again = sep.separateRound(dedup=False, mode=1)  # a second round on the same context
+            assert again.walks() == exp.walks()
+        finally:
+            sep.close()
