@@ -196,6 +196,7 @@ struct smsgpu_ctx {
     // SMSGPU_MODE_VERBATIM: two stamp arrays (previous / current sweep), per-source "found nothing" flags, work list
     DevBuf vStampA, vStampB, vStampC, vIota, vEmpty, vEmptyB0, vActive, vFlags;
     long long vActiveCount = 0;
+    long long vWindow = 0; // mode V: window length chosen by the previous round (0: default rule)
 
     // multi-GPU
     void *ncclComm = nullptr;
@@ -742,6 +743,7 @@ int smsgpu_set_sources(smsgpu_ctx *ctx, const int32_t *sources, int64_t nsrc, in
         ctx->hSources.clear();
     }
     if (!same) { // the local index space changed
+        ctx->vWindow = 0;
         ctx->haveOrder = false;
         ctx->skipTier0 = 0;
         ctx->heavyPairs = 0;
@@ -1264,9 +1266,12 @@ int separateLocal(smsgpu_ctx *ctx, const smsgpu_params &P) {
         // WINDOWS.  A source only reads stamps of EARLIER sources, so the list can be brought to its fixed point window by
         // window, in order: the stamps of the finished windows are final (`base`), the sweeps of a window run its sources only.
         // The sweeps a window needs are the length of the dependency chains INSIDE it, so short windows need few -- the work
-        // falls from (chain length of the whole list) x n to about (chain length of a window) x n.  Window = n / 16, at least
-        // 1024 sources (a sweep has ~10 launches and 4 host waits of fixed cost); SMSGPU_VERBATIM_WINDOW overrides, 0 = one window.
-        long long W = std::max<long long>(1024, (nsrc / 16 + 1) & ~1ll);
+        // falls from (chain length of the whole list) x n to about (chain length of a window) x n.  But every sweep has a fixed
+        // cost (~10 launches, 4 host waits), so windows only pay when the chains are long or the sweeps heavy (measured: torus
+        // 100x100, LP iterates, 111 sweeps: 3.3 s -> 0.85 s per round with 10 windows; the same torus with uniform x*, 14 sweeps:
+        // 3.2 -> 13.7 ms).  Rule: one window, unless the list is long (> 200 000 sources: n / 16) or the previous round of this
+        // context needed >= 48 sweeps with one window (then n / 10, at least 1024).  SMSGPU_VERBATIM_WINDOW overrides, 0 = one.
+        long long W = ctx->vWindow > 0 ? ctx->vWindow : (nsrc > 200000 ? ((nsrc / 16 + 1) & ~1ll) : nsrc);
         if (const char *ew = std::getenv("SMSGPU_VERBATIM_WINDOW")) W = std::atoll(ew);
         if (W <= 0 || W > nsrc) W = std::max<long long>(nsrc, 1);
         int rcV = 0;
@@ -1362,6 +1367,7 @@ int separateLocal(smsgpu_ctx *ctx, const smsgpu_params &P) {
         if (!again) break;
         }
         vw.on = false;
+        if (!rcV && W >= nsrc && sweepsTotal >= 48 && nsrc >= 2048) ctx->vWindow = std::max<long long>(1024, (nsrc / 10 + 1) & ~1ll);
         ctx->pairsMirror = savedMirror;
         if (rcV) return rcV;
     }
