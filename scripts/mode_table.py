@@ -85,7 +85,9 @@ def main():
             cV, cI = canonical_set(sV.walks()), canonical_set(sI.walks())
             rV = canonical_set(orc.sweep(inst, x, blacklist=bl, mode="V", canonical=False).walks())
             rI = canonical_set(orc.sweep(inst, x, blacklist=bl, mode="I", canonical=False).walks())
-            _, info = orc.sweep_fixpoint(inst, x, blacklist=bl, canonical=True)
+            # sweeps of the stamped fixed point (CPU statement, one window); costs sweeps x a whole round: small instances only,
+            # the device's own counts for the large ones are in the bench lines (verbatim_sweeps)
+            info = orc.sweep_fixpoint(inst, x, blacklist=bl, canonical=True)[1] if inst.n <= 1000 else {"sweeps": None}
             bV = bI = b0 = None
             if g is not None and r is not None and inst.n <= 10000:
                 # the LP this point came from is not stored; the bound is taken over the cuts of THIS round only, added
