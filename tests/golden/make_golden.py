@@ -38,6 +38,9 @@ CASES = {
     "random_400_uniform": (lambda: I.random_graph(400, 1600, seed=3), lambda m: I.xstar_uniform(m, seed=4), True),
     "dense_150_uniform": (lambda: I.random_graph(150, 1500, seed=5), lambda m: I.xstar_uniform(m, seed=5), True),
     "torus2d_30_uniform": (lambda: I.torus2d(30), lambda m: I.xstar_uniform(m, seed=6), True),
+    # chord repair at work, but few enough good chords per cycle (<= 16) that the reference's std::sort of the chord list
+    # (introsort: insertion sort up to 16 elements, i.e. stable) leaves the emission order well defined -- unlike dense_150
+    "random_200_1300_uniform": (lambda: I.random_graph(200, 1300, seed=9), lambda m: I.xstar_uniform(m, seed=9), True),
     "torus2d_12_lp_like": (lambda: I.torus2d(12), lambda m: I.xstar_lp_like(m, seed=7), False),
     "random_400_lp_like": (lambda: I.random_graph(400, 1600, seed=3), lambda m: I.xstar_lp_like(m, seed=8), False),
 }
