@@ -186,6 +186,36 @@ int smsgpu_get_small_cycle_cuts(smsgpu_ctx *ctx, int k, smsgpu_cuts *out);
  * violated cycles, the device-to-host copy of the walks */
 int smsgpu_small_cycles_timing(smsgpu_ctx *ctx, double *ms_scan, double *ms_gather, double *ms_d2h);
 
+/* ---- the small-cycle scan without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same result as smsgpu_small_cycles_scan (the violated cycles of the list, in list order, same arrays as
+ * smsgpu_cuts with src = list index), but stateless and context free: every input and output is a DEVICE buffer of the
+ * caller, and the scan's scratch (one code byte per cycle + a count and a base per 1024 cycles) is a file-scope
+ * __device__ array of SMSGPU_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until exit.  The call issues
+ * no cudaMalloc / cudaFree / allocating library routine: three kernel launches on `stream` (a cudaStream_t, NULL = the
+ * default stream) of `device`, plus an 8-byte D2H copy and a stream synchronize only when h_count is given.
+ *   k               3 or 4
+ *   T               cycles in the list, 0 <= T <= SMSGPU_NOALLOC_MAX_CYCLES (larger: SMSGPU_ERR_ARG, nothing is launched)
+ *   d_cycles        [k*T] vertex ids, cycle by cycle (what smsgpu_small_cycles_get returns)
+ *   d_cycle_eids    [k*T] edge id of the edge (cycle[i], cycle[(i+1) % k]); every id must index d_x (not checked)
+ *   d_x             x* by edge id
+ *   out_capacity    violated cycles the output arrays can hold; d_node, d_eid, d_is_stay [k*out_capacity], d_n_cross, d_src,
+ *                   d_violation [out_capacity], d_off [out_capacity + 1].  Violated cycles beyond it are dropped (the first
+ *                   out_capacity in list order are kept), *d_count still reports all of them
+ *   d_count         (device) number of violated cycles;  h_count (host, may be NULL): the same, copied back
+ *   err, err_len    optional buffer for the message of a failed call
+ * Every call on a device shares the scratch array, which keeps the last call's contents (nothing in it needs clearing:
+ * each call writes every word it later reads).  Calls that overlap on the GPU -- two streams, two threads, two
+ * processes' worth of contexts are fine, two calls in flight on one device are not -- race on it.  The first call on
+ * a device resolves the array's device address (cudaGetSymbolAddress); make that call outside a graph capture. */
+#define SMSGPU_NOALLOC_MAX_CYCLES 4194304
+#define SMSGPU_NOALLOC_SCRATCH_BYTES 4243968
+int smsgpu_small_cycles_scan_noalloc(int device, void *stream, int k, int64_t T, const int32_t *d_cycles,
+                                     const int32_t *d_cycle_eids, const double *d_x, int64_t out_capacity, int32_t *d_node,
+                                     int32_t *d_eid, uint8_t *d_is_stay, int32_t *d_n_cross, int32_t *d_src,
+                                     double *d_violation, int64_t *d_off, int64_t *d_count, int64_t *h_count, char *err,
+                                     size_t err_len);
+
 /* ---- multi-GPU: one context per GPU (one process per GPU under torchrun, or one thread per GPU inside a
  * single SCIP process).  After smsgpu_comm_init every smsgpu_separate ends with an NCCL all-gather of the
  * per-GPU cut lists and a global dedup, so each rank returns the identical full list. */

@@ -20,6 +20,7 @@ SYMBOLS = [
     "smsgpu_set_round_input", "smsgpu_input_buffers", "smsgpu_set_round_input_device", "smsgpu_set_sources", "smsgpu_separate",
     "smsgpu_separate_async", "smsgpu_fetch_cuts", "smsgpu_get_cuts", "smsgpu_get_stats", "smsgpu_get_labels",
     "smsgpu_get_src_stats", "smsgpu_small_cycles_set", "smsgpu_small_cycles_enumerate", "smsgpu_small_cycles_get", "smsgpu_small_cycles_scan", "smsgpu_small_cycles_scan_device", "smsgpu_get_small_cycle_cuts", "smsgpu_small_cycles_timing",
+    "smsgpu_small_cycles_scan_noalloc",
     "smsgpu_nccl_unique_id", "smsgpu_comm_init", "smsgpu_comm_destroy",
 ]
 
@@ -144,6 +145,8 @@ def load_library(path: str | None = None) -> C.CDLL:
     lib.smsgpu_small_cycles_scan_device.argtypes = [vp, i32]
     lib.smsgpu_get_small_cycle_cuts.argtypes = [vp, i32, C.POINTER(CutsStruct)]
     lib.smsgpu_small_cycles_timing.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    lib.smsgpu_small_cycles_scan_noalloc.argtypes = [i32, vp, i32, i64, vp, vp, vp, i64, vp, vp, vp, vp, vp, vp, vp, vp,
+                                                     C.POINTER(i64), C.c_char_p, C.c_size_t]
     lib.smsgpu_nccl_unique_id.argtypes = [vp]
     lib.smsgpu_comm_init.argtypes = [vp, vp, i32, i32]
     lib.smsgpu_comm_destroy.argtypes = [vp]
@@ -163,6 +166,26 @@ def _cuts_from_struct(cs: CutsStruct) -> Cuts:
     return Cuts(off=_arr(cs.off, U + 1, np.int64), node=_arr(cs.node, N, np.int32), eid=_arr(cs.eid, N, np.int32),
                 is_stay=_arr(cs.is_stay, N, np.uint8), n_cross=_arr(cs.n_cross, U, np.int32), src=_arr(cs.src, U, np.int32),
                 violation=_arr(cs.violation, U, np.float64))
+
+
+NOALLOC_MAX_CYCLES = 4194304  # SMSGPU_NOALLOC_MAX_CYCLES
+
+
+def small_cycles_scan_noalloc(k: int, T: int, d_cycles: int, d_cycle_eids: int, d_x: int, out_capacity: int, d_node: int, d_eid: int,
+                              d_is_stay: int, d_n_cross: int, d_src: int, d_violation: int, d_off: int, d_count: int,
+                              device: int = 0, stream: int = 0, sync: bool = True, lib=None):
+    """smsgpu_small_cycles_scan_noalloc: the K6 scan on the caller's DEVICE buffers (raw addresses), no allocation inside.
+    Returns the number of violated cycles when `sync`, else None (the count is in *d_count once the stream gets there)."""
+    lib = lib or load_library()
+    err = C.create_string_buffer(512)
+    cnt = C.c_int64(-1)
+    rc = lib.smsgpu_small_cycles_scan_noalloc(device, stream or None, k, T, d_cycles or None, d_cycle_eids or None, d_x or None,
+                                              out_capacity, d_node or None, d_eid or None, d_is_stay or None, d_n_cross or None,
+                                              d_src or None, d_violation or None, d_off or None, d_count or None,
+                                              C.byref(cnt) if sync else None, err, len(err))
+    if rc != 0:
+        raise SmsGpuError(rc, err.value.decode(errors="replace"))
+    return int(cnt.value) if sync else None
 
 
 class Context:

@@ -2040,3 +2040,225 @@ int smsgpu_comm_destroy(smsgpu_ctx *ctx) {
 }
 
 } // extern "C"
+
+// =====================================================================================================================
+// K6 without any allocation: smsgpu_small_cycles_scan_noalloc (include/smsgpu.h).  No counterpart in the reference; added
+// for callers that cannot call cudaMalloc (CUDA graph capture, tight serving
+// loops, harnesses that forbid it).  Same scan / rank / gather as smallCyclesScanDevice above, but stateless: inputs and
+// outputs are the caller's device buffers, and the scratch of the scan (one code byte per cycle, one count and one base
+// per tile of 1024 cycles) lives in ONE file-scope device array of fixed size, which every GPU that loads the library
+// holds until exit.  Every call on a device shares that array: calls that overlap on the GPU race.
+// =====================================================================================================================
+#include <mutex>
+
+namespace {
+constexpr long long kNoallocMaxCycles = SMSGPU_NOALLOC_MAX_CYCLES;
+constexpr long long kNoallocMaxTiles = (kNoallocMaxCycles + kSmallTile - 1) / kSmallTile;
+static_assert(kNoallocMaxTiles <= 4096, "the tile scan below is one CTA of 1024 threads x 4 tiles");
+constexpr size_t kNoallocCodeBytes = ((size_t)kNoallocMaxCycles + 255) & ~(size_t)255;
+constexpr size_t kNoallocCountBytes = (((size_t)kNoallocMaxTiles + 1) * 4 + 255) & ~(size_t)255;
+constexpr size_t kNoallocBaseBytes = (((size_t)kNoallocMaxTiles + 2) * 8 + 255) & ~(size_t)255;
+constexpr size_t kNoallocScratchBytes = kNoallocCodeBytes + kNoallocCountBytes + kNoallocBaseBytes; // ~4.05 MiB
+static_assert(kNoallocScratchBytes == SMSGPU_NOALLOC_SCRATCH_BYTES, "include/smsgpu.h states the size of the array");
+} // namespace
+
+// In host code this name is a host-side stand-in, NOT a device address: the address the kernels get comes from
+// cudaGetSymbolAddress (noallocScratchOf), once per device.
+static __device__ __align__(256) unsigned char g_noallocScratch[kNoallocScratchBytes];
+
+namespace {
+// exclusive scan of the per-tile counts by one CTA (ntiles <= 4096), the total, and the closing offset of the walk list
+__global__ void __launch_bounds__(1024) noallocTileScanKernel(const int ntiles, const int32_t *__restrict__ cnt,
+                                                              long long *__restrict__ base, const long long cap, const int K,
+                                                              long long *__restrict__ oOff, long long *__restrict__ dCount) {
+    __shared__ long long warpSum[32];
+    const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
+    int v[4];
+    long long mine = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int t = 4 * (int)threadIdx.x + i;
+        v[i] = t < ntiles ? cnt[t] : 0;
+        mine += v[i];
+    }
+    long long incl = mine;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        const long long a = __shfl_up_sync(0xFFFFFFFFu, incl, off);
+        if (lane >= off) incl += a;
+    }
+    if (lane == 31) warpSum[wrp] = incl;
+    __syncthreads();
+    long long before = 0, total = 0;
+    for (int k = 0; k < 32; ++k) {
+        if (k < wrp) before += warpSum[k];
+        total += warpSum[k];
+    }
+    long long run = before + incl - mine;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int t = 4 * (int)threadIdx.x + i;
+        if (t < ntiles) base[t] = run;
+        run += v[i];
+    }
+    if (threadIdx.x == 0) {
+        base[ntiles] = total;
+        *dCount = total;
+        const long long kept = total < cap ? total : cap;
+        oOff[kept] = (long long)K * kept;
+    }
+}
+
+// smallCycleGatherKernel (small_cycles.cuh) with a bound on the output: violated cycles of list rank >= cap are dropped
+template <int K>
+__global__ void __launch_bounds__(kSmallBlock) noallocGatherKernel(const long long T, const int32_t *__restrict__ nodes,
+                                                                   const int32_t *__restrict__ eids, const double *__restrict__ x,
+                                                                   const uint8_t *__restrict__ code,
+                                                                   const long long *__restrict__ tileBase, const long long cap,
+                                                                   int32_t *oNode, int32_t *oEid, uint8_t *oStay, int32_t *oNcross,
+                                                                   int32_t *oSrc, double *oViol, long long *oOff) {
+    __shared__ int warpSum[kSmallBlock / 32];
+    const long long base = (long long)blockIdx.x * kSmallTile;
+    const long long out0 = tileBase[blockIdx.x];
+    if (out0 >= cap || tileBase[blockIdx.x + 1] == out0) return; // CTA uniform: nothing of this tile is kept
+    const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
+    int carry = 0; // violated cycles of the earlier items of this tile (every thread keeps its own copy)
+    for (int it = 0; it < kSmallItems; ++it) {
+        const long long t = base + it * kSmallBlock + threadIdx.x;
+        const unsigned c = t < T ? code[t] : 0u;
+        const int v = c ? 1 : 0;
+        int incl = v;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const int a = __shfl_up_sync(0xFFFFFFFFu, incl, off);
+            if (lane >= off) incl += a;
+        }
+        if (lane == 31) warpSum[wrp] = incl;
+        __syncthreads();
+        int before = carry, tot = 0;
+#pragma unroll
+        for (int k = 0; k < kSmallBlock / 32; ++k) {
+            if (k < wrp) before += warpSum[k];
+            tot += warpSum[k];
+        }
+        const long long k = out0 + before + incl - 1;
+        if (v && k < cap) {
+            const unsigned sm = c & 0x7Fu;
+            int nc = 0;
+            double w[K];
+#pragma unroll
+            for (int i = 0; i < K; ++i) {
+                const int32_t e = eids[K * t + i];
+                w[i] = clamp01(__ldg(x + e));
+                oNode[K * k + i] = nodes[K * t + i];
+                oEid[K * k + i] = e;
+                const int s = (sm >> i) & 1u;
+                oStay[K * k + i] = (uint8_t)s;
+                nc += 1 - s;
+            }
+            double len = 0; // same summation order as the scan's and as smallCycleGatherKernel's
+#pragma unroll
+            for (int i = 0; i < K; ++i) len += ((sm >> i) & 1u) ? w[i] : 1 - w[i];
+            oNcross[k] = nc;
+            oSrc[k] = (int32_t)t;
+            oViol[k] = 1.0 - len;
+            oOff[k] = (long long)K * k;
+        }
+        carry += tot;
+        __syncthreads(); // warpSum is rewritten by the next item
+    }
+}
+
+constexpr int kNoallocMaxDevices = 64;
+std::mutex g_noallocMutex;
+unsigned char *g_noallocPtr[kNoallocMaxDevices] = {};
+
+// device address of g_noallocScratch on `device` (which must be the current device), resolved once per device
+cudaError_t noallocScratchOf(const int device, unsigned char **out) {
+    std::lock_guard<std::mutex> lock(g_noallocMutex);
+    if (!g_noallocPtr[device]) {
+        void *p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_noallocScratch);
+        if (e != cudaSuccess) return e;
+        g_noallocPtr[device] = static_cast<unsigned char *>(p);
+    }
+    *out = g_noallocPtr[device];
+    return cudaSuccess;
+}
+
+int noallocFail(char *err, const size_t errLen, const int code, const char *fmt, ...) {
+    if (err && errLen > 0) {
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(err, errLen, fmt, ap);
+        va_end(ap);
+    }
+    return code;
+}
+} // namespace
+
+extern "C" int smsgpu_small_cycles_scan_noalloc(int device, void *stream, int k, int64_t T, const int32_t *d_cycles,
+                                                const int32_t *d_cycle_eids, const double *d_x, int64_t out_capacity,
+                                                int32_t *d_node, int32_t *d_eid, uint8_t *d_is_stay, int32_t *d_n_cross,
+                                                int32_t *d_src, double *d_violation, int64_t *d_off, int64_t *d_count,
+                                                int64_t *h_count, char *err, size_t err_len) {
+    if (err && err_len > 0) err[0] = 0;
+    if (k != 3 && k != 4) return noallocFail(err, err_len, SMSGPU_ERR_ARG, "k must be 3 or 4 (got %d)", k);
+    if (T < 0 || out_capacity < 0) return noallocFail(err, err_len, SMSGPU_ERR_ARG, "T and out_capacity must be >= 0");
+    if (T > kNoallocMaxCycles)
+        return noallocFail(err, err_len, SMSGPU_ERR_ARG,
+                           "T = %lld cycles exceeds SMSGPU_NOALLOC_MAX_CYCLES = %lld (the static scratch array holds no more; "
+                           "split the list or use smsgpu_small_cycles_scan)",
+                           (long long)T, kNoallocMaxCycles);
+    if (device < 0 || device >= kNoallocMaxDevices) return noallocFail(err, err_len, SMSGPU_ERR_ARG, "device %d out of range", device);
+    if (T > 0 && (!d_cycles || !d_cycle_eids || !d_x)) return noallocFail(err, err_len, SMSGPU_ERR_ARG, "null input pointer");
+    if (!d_off || !d_count) return noallocFail(err, err_len, SMSGPU_ERR_ARG, "d_off and d_count must not be null");
+    if (out_capacity > 0 && (!d_node || !d_eid || !d_is_stay || !d_n_cross || !d_src || !d_violation))
+        return noallocFail(err, err_len, SMSGPU_ERR_ARG, "null output pointer with out_capacity > 0");
+#define NA_CU(call)                                                                                              \
+    do {                                                                                                         \
+        const cudaError_t e_ = (call);                                                                           \
+        if (e_ != cudaSuccess) {                                                                                 \
+            (void)cudaGetLastError();                                                                            \
+            return noallocFail(err, err_len, SMSGPU_ERR_CUDA, "%s:%d %s: %s", __FILE__, __LINE__, #call,         \
+                               cudaGetErrorString(e_));                                                          \
+        }                                                                                                        \
+    } while (0)
+    NA_CU(cudaSetDevice(device));
+    unsigned char *scratch = nullptr;
+    NA_CU(noallocScratchOf(device, &scratch));
+    uint8_t *code = scratch;
+    int32_t *tileCount = reinterpret_cast<int32_t *>(scratch + kNoallocCodeBytes);
+    long long *tileBase = reinterpret_cast<long long *>(scratch + kNoallocCodeBytes + kNoallocCountBytes);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const long long ntiles = (T + kSmallTile - 1) / kSmallTile;
+    // Nothing in the scratch has to start at zero: the scan writes code[0, T) and tileCount[0, ntiles), the tile scan
+    // writes tileBase[0, ntiles], and only those ranges are read afterwards -- what an earlier call left behind is never seen.
+    if (ntiles > 0) {
+        if (k == 3)
+            smallCycleScanKernel<3><<<(unsigned)ntiles, kSmallBlock, 0, st>>>(T, d_cycle_eids, d_x, code, tileCount);
+        else
+            smallCycleScanKernel<4><<<(unsigned)ntiles, kSmallBlock, 0, st>>>(T, d_cycle_eids, d_x, code, tileCount);
+        NA_CU(cudaGetLastError());
+    }
+    noallocTileScanKernel<<<1, 1024, 0, st>>>((int)ntiles, tileCount, tileBase, out_capacity, k, reinterpret_cast<long long *>(d_off),
+                                             reinterpret_cast<long long *>(d_count));
+    NA_CU(cudaGetLastError());
+    if (ntiles > 0 && out_capacity > 0) {
+        if (k == 3)
+            noallocGatherKernel<3><<<(unsigned)ntiles, kSmallBlock, 0, st>>>(T, d_cycles, d_cycle_eids, d_x, code, tileBase, out_capacity, d_node,
+                                                                           d_eid, d_is_stay, d_n_cross, d_src, d_violation,
+                                                                           reinterpret_cast<long long *>(d_off));
+        else
+            noallocGatherKernel<4><<<(unsigned)ntiles, kSmallBlock, 0, st>>>(T, d_cycles, d_cycle_eids, d_x, code, tileBase, out_capacity, d_node,
+                                                                           d_eid, d_is_stay, d_n_cross, d_src, d_violation,
+                                                                           reinterpret_cast<long long *>(d_off));
+        NA_CU(cudaGetLastError());
+    }
+    if (h_count) {
+        NA_CU(cudaMemcpyAsync(h_count, d_count, 8, cudaMemcpyDeviceToHost, st));
+        NA_CU(cudaStreamSynchronize(st));
+    }
+#undef NA_CU
+    return SMSGPU_OK;
+}
