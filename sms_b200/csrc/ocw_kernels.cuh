@@ -5,6 +5,7 @@
 #pragma once
 #include "ocw_walks.cuh"
 #include "ocw_search_pairs.cuh"
+#include "ocw_search_lanes.cuh"
 #include "ocw_search_runs.cuh"
 
 namespace smsgpu {

@@ -1,0 +1,433 @@
+// "Lanes" engine of K2 (tier 1, in front of the pairs engine on long source lists): ONE SOURCE PER THREAD.
+//
+// Same search as every other engine -- runDijsktra of the reference (src/graph/ocw_seperator.cpp:37-112) in the
+// canonical order (dist, hops, doubled id), event for event -- written as plain sequential code: the statement of the
+// reference, with the reference's dense arrays replaced by a hashed label table and its heap by a monotone bucket queue.
+// Why: the warp-cooperative engines spend ~400 warp instructions per settled node on ballots, shuffles and predication
+// to keep 16 lanes busy with the ~9 arcs of a node, and have 7 000 searches in flight; the round is bound by the issue
+// slots and by two to three dependent DRAM round trips per step (profiles/r02_pairs_tier1_random1m_256k.md).  A thread
+// per source needs no cross-lane instruction at all, puts 32 independent searches behind every memory instruction, and
+// tens of thousands in flight; the round then is bound by DRAM sectors.
+//
+// Working memory of one search (a "tile", thread private, in HBM; bytes: lanesTileBytes):
+//   tab   Entry[tabCap]        label table, open addressing; a slot is occupied iff its `flags` word carries the stamp of
+//                              the search (nothing is cleared between searches); hop words = hops | queue position << 16
+//   q     32 B x (NB * 16 + park)  queue entries {dist, id, hops | first arc, degree, PREDECESSOR, -}: written once with
+//                              two 16-byte stores (a full sector: no read-modify-write in the memory system), never
+//                              moved, never overwritten -- the entry a label points to also holds its predecessor, so
+//                              there is no predecessor array (a 4-byte store into a random sector costs a sector read and
+//                              a sector write).  Labels that may not enter the queue (2 d > bestDist) get a "parked"
+//                              entry behind the buckets, for their predecessor.
+//   cnt   uint32[NB]           per bucket: entries appended << 16 | dead mask (bit i: position i extracted / superseded)
+//   hist  uint32[histCap]      intermediateVertices_ in push order
+// This header is the engine's sequential core and compiles for the host as well (tests/cpp/lanes_host.cu runs it on
+// the CPU against the oracle); the kernels around it are in ocw_search_lanes.cuh.
+#pragma once
+#include "ocw_types.cuh"
+#include <cstring>
+
+namespace smsgpu {
+
+constexpr uint32_t kLanesC = 16;               // queue positions per bucket (the dead mask has 16 bits)
+constexpr uint32_t kLanesNoQpos = 0xFFFFu;     // hop word >> 16: the label has no queue entry
+constexpr uint32_t kLanesPackedNone = 0xFFFFFFFFu;
+
+struct LanesCfg {
+    uint32_t tabCap, tabShift;  // label table slots (power of two), 32 - log2(tabCap)
+    uint32_t touchedCap;        // labels a search may create
+    uint32_t histCap;
+    uint32_t nbuckets;          // NB (multiple of 4); NB * kLanesC + parkCap <= 0xFFFF
+    uint32_t parkCap;
+    float scaleU, scaleB;       // bucket map of the pairs engine (ocw_search_pairs.cuh: bucketOf)
+    uint32_t rowShift;          // Arc::row = first arc | degree << rowShift
+};
+
+// result record of one tile's search, read by the finishing warp
+struct __align__(16) LanesRec {
+    uint32_t src;       // doubled id of the source searched
+    int32_t srcIdx;     // local source index; < 0: the tile has nothing to finish
+    int32_t twinIdx;    // second source of the work item (local index), or -1
+    uint32_t flags;     // bit 0: a capacity was hit (the source goes to the next engine); bit 1: an extraction broke a
+                        // (dist, hops) tie by id (the twin is not the mirror image); bit 2: the second source is the twin
+    double best;
+    uint32_t histN, touchedN, arcs, settled;
+    uint32_t stamp, parkN;
+    uint32_t pad[4];
+};
+static_assert(sizeof(LanesRec) == 64, "LanesRec is two sectors");
+
+struct LanesTile {
+    Entry *tab;
+    uint4 *q;       // two uint4 per entry
+    uint32_t *cnt;
+    uint32_t *hist;
+    LanesRec *rec;
+};
+
+__host__ __device__ inline size_t lanesTileBytes(const LanesCfg &c) {
+    size_t b = (size_t)c.tabCap * sizeof(Entry);
+    b += ((size_t)c.nbuckets * kLanesC + c.parkCap) * 32;
+    b += (size_t)c.nbuckets * sizeof(uint32_t);
+    b += (size_t)c.histCap * sizeof(uint32_t);
+    b = (b + 31) & ~(size_t)31;
+    b += sizeof(LanesRec);
+    return (b + 255) & ~(size_t)255;
+}
+__host__ __device__ inline LanesTile lanesCarve(unsigned char *base, const LanesCfg &c) {
+    LanesTile T;
+    unsigned char *p = base;
+    T.tab = reinterpret_cast<Entry *>(p);
+    p += (size_t)c.tabCap * sizeof(Entry);
+    T.q = reinterpret_cast<uint4 *>(p);
+    p += ((size_t)c.nbuckets * kLanesC + c.parkCap) * 32;
+    T.cnt = reinterpret_cast<uint32_t *>(p);
+    p += (size_t)c.nbuckets * sizeof(uint32_t);
+    T.hist = reinterpret_cast<uint32_t *>(p);
+    p += (size_t)c.histCap * sizeof(uint32_t);
+    p = base + (((size_t)(p - base) + 31) & ~(size_t)31);
+    T.rec = reinterpret_cast<LanesRec *>(p);
+    return T;
+}
+
+// ---- memory access: streaming hints on the thread-private working memory (it is touched once or twice and is far larger
+// than L2, the graph is shared by all searches), read-only path for the graph ----------------------------------------
+__host__ __device__ __forceinline__ uint4 lnLoad4(const uint4 *p) {
+#ifdef __CUDA_ARCH__
+    return __ldcs(p);
+#else
+    return *p;
+#endif
+}
+__host__ __device__ __forceinline__ void lnStore4(uint4 *p, const uint4 v) {
+#ifdef __CUDA_ARCH__
+    __stcs(p, v);
+#else
+    *p = v;
+#endif
+}
+__host__ __device__ __forceinline__ uint4 lnLoadRO4(const uint4 *p) {
+#ifdef __CUDA_ARCH__
+    return __ldg(p);
+#else
+    return *p;
+#endif
+}
+__host__ __device__ __forceinline__ double lnBitsToDouble(const uint32_t lo, const uint32_t hi) {
+#ifdef __CUDA_ARCH__
+    return __hiloint2double((int)hi, (int)lo);
+#else
+    const unsigned long long b = ((unsigned long long)hi << 32) | lo;
+    double d;
+    memcpy(&d, &b, 8);
+    return d;
+#endif
+}
+__host__ __device__ __forceinline__ unsigned long long lnDoubleBits(const double d) {
+#ifdef __CUDA_ARCH__
+    return (unsigned long long)__double_as_longlong(d);
+#else
+    unsigned long long b;
+    memcpy(&b, &d, 8);
+    return b;
+#endif
+}
+// Monotone (non-decreasing in d >= 0) bucket index: the pairs engine's map (ocw_search_pairs.cuh: bucketOf).  Only
+// monotonicity matters for the result; host and device need not agree bit for bit.
+__host__ __device__ __forceinline__ uint32_t lnBucketOf(const double d, const float scaleU, const float scaleB, const uint32_t nbm1) {
+#ifdef __CUDA_ARCH__
+    const float f = __double2float_rn(d);
+    uint32_t b;
+    if (scaleU > 0.f) {
+        const float y = __int_as_float(__float2int_rz(f * scaleU * 8388608.0f) + 0x3F800000);
+        b = __float2uint_rz((y - 1.0f) * scaleB);
+    } else {
+        b = __float2uint_rz(f * scaleB);
+    }
+    return min(b, nbm1);
+#else
+    const float f = (float)d;
+    uint32_t b;
+    if (scaleU > 0.f) {
+        const int bits = (int)(f * scaleU * 8388608.0f) + 0x3F800000;
+        float y;
+        memcpy(&y, &bits, 4);
+        b = (uint32_t)((y - 1.0f) * scaleB);
+    } else {
+        b = (uint32_t)(f * scaleB);
+    }
+    return b < nbm1 ? b : nbm1;
+#endif
+}
+
+struct LanesEntryRegs { // one label-table entry in registers
+    uint4 a, b;         // a = {d0 lo, d0 hi, d1 lo, d1 hi}, b = {key, h0, h1, flags}
+};
+__host__ __device__ __forceinline__ LanesEntryRegs lnLoadEntry(const Entry *p) {
+    LanesEntryRegs e;
+    e.a = lnLoad4(reinterpret_cast<const uint4 *>(p));
+    e.b = lnLoad4(reinterpret_cast<const uint4 *>(p) + 1);
+    return e;
+}
+
+// The search of one source.  `srow` = {first arc, degree} of the source's vertex.  Fills `rec` (src, flags bits 0-1,
+// best, histN, touchedN, arcs, settled, stamp, parkN); srcIdx / twinIdx / flag bit 2 belong to the caller.
+__host__ __device__ inline void lanesSearch(const Arc *__restrict__ arcs, const uint2 *__restrict__ rowinfo, const LanesCfg &C,
+                                            const LanesTile &T, const uint32_t src, const uint2 srow, const uint32_t stamp,
+                                            const double bestInit, LanesRec &rec) {
+    const uint32_t NB = C.nbuckets, tabMask = C.tabCap - 1u, parkBase = NB * kLanesC;
+    // ---- reset the bucket words, label and enqueue the source (:54-57) ---------------------------------------------
+    {
+        uint4 *c4 = reinterpret_cast<uint4 *>(T.cnt);
+        const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+        for (uint32_t i = 0; i < (NB >> 2); ++i) c4[i] = z;
+        const uint32_t s = ((src >> 1) * 0x9E3779B1u) >> C.tabShift;
+        const unsigned long long un = lnDoubleBits(kUnlabelled);
+        uint4 a = make_uint4((uint32_t)un, (uint32_t)(un >> 32), (uint32_t)un, (uint32_t)(un >> 32));
+        uint4 b = make_uint4(src >> 1, kLanesPackedNone, kLanesPackedNone, stamp);
+        if (src & 1u) {
+            a.z = 0u;
+            a.w = 0u;
+            b.z = 0u; // 0 hops, queue position 0
+        } else {
+            a.x = 0u;
+            a.y = 0u;
+            b.y = 0u;
+        }
+        lnStore4(reinterpret_cast<uint4 *>(T.tab + s), a);
+        lnStore4(reinterpret_cast<uint4 *>(T.tab + s) + 1, b);
+        lnStore4(T.q, make_uint4(0u, 0u, src, 0u));         // dist 0, id src, 0 hops
+        lnStore4(T.q + 1, make_uint4(srow.x, srow.y, src, 0u)); // row, predecessor: itself (never followed)
+        T.cnt[0] = 1u << 16;
+    }
+    double best = bestInit;
+    uint32_t bestHop = 0; // bestHopDist: a double in the reference (:52) that only ever holds small integers
+    uint32_t histN = 0, touchedN = 1, arcsN = 0, settledN = 0, parkN = 0;
+    bool overflow = false, tie = false;
+    uint32_t lo = 0; // bucket of the last extraction: keys never decrease
+
+    while (!overflow) {
+        // ---- first bucket at or after `lo` with a live key -------------------------------------------------------
+        uint32_t b = lo, word = 0, live = 0, app = 0;
+        for (; b < NB; ++b) {
+            word = T.cnt[b];
+            app = word >> 16;
+            live = ((1u << app) - 1u) & ~word;
+            if (live) break;
+        }
+        if (b >= NB) break; // queue empty (:88)
+        // ---- its minimum live key, (dist, hops, id) lexicographic; four entries per round trip ---------------------
+        unsigned long long mhi = ~0ull, mlo = ~0ull;
+        uint32_t mpos = 0, mfirst = 0, mdeg = 0;
+        bool mtie = false;
+        const uint4 *qb = T.q + 2 * (size_t)(b * kLanesC);
+        for (uint32_t p0 = 0; p0 < app; p0 += 4) {
+            uint4 k[4], r[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                k[j] = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
+                r[j] = make_uint4(0u, 0u, 0u, 0u);
+                if ((live >> (p0 + j)) & 1u) {
+                    k[j] = lnLoad4(qb + 2 * (p0 + j));
+                    r[j] = lnLoad4(qb + 2 * (p0 + j) + 1);
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                if (!((live >> (p0 + j)) & 1u)) continue;
+                const unsigned long long hi = ((unsigned long long)k[j].y << 32) | k[j].x;
+                const unsigned long long lw = ((unsigned long long)k[j].w << 32) | k[j].z; // hops << 32 | id
+                if (hi == mhi && (uint32_t)(lw >> 32) == (uint32_t)(mlo >> 32)) mtie = true; // equal (dist, hops): the id decides
+                if (hi < mhi || (hi == mhi && lw < mlo)) {
+                    if (hi != mhi || (uint32_t)(lw >> 32) != (uint32_t)(mlo >> 32)) mtie = false;
+                    mhi = hi;
+                    mlo = lw;
+                    mpos = p0 + j;
+                    mfirst = r[j].x;
+                    mdeg = r[j].y;
+                }
+            }
+        }
+        if (mtie) tie = true; // -> the twin's search is not the mirror image of this one
+        const uint32_t cur = (uint32_t)mlo, hc = (uint32_t)(mlo >> 32);
+        const double dc = lnBitsToDouble((uint32_t)mhi, (uint32_t)(mhi >> 32));
+        // loop condition of ocw_seperator.cpp:88-90
+        if (cur == (src ^ 1u) || 2 * dc > best) break;
+        T.cnt[b] = word | (1u << mpos); // extract_top: the position is dead from now on
+        settledN++;
+        lo = b;
+        const uint32_t side = cur & 1u, hNew = hc + 1u;
+        if (hNew >= 0xFFFFu) { // hops share a word with the queue position
+            overflow = true;
+            break;
+        }
+
+        // ---- relax the arcs of the settled node in adjacency order, four per round trip ----------------------------
+        for (uint32_t a0 = 0; a0 < mdeg && !overflow; a0 += 4) {
+            uint4 av[4];
+            LanesEntryRegs pe[4];
+            uint32_t home[4], wslot[4];
+            const uint32_t nb = (mdeg - a0) < 4u ? (mdeg - a0) : 4u;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                av[j] = make_uint4(0x80000000u, 0u, 0u, 0u);
+                if ((uint32_t)j < nb) av[j] = lnLoadRO4(reinterpret_cast<const uint4 *>(arcs + mfirst + a0 + j));
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                home[j] = ((av[j].x & 0x7FFFFFFFu) * 0x9E3779B1u) >> C.tabShift;
+                wslot[j] = 0xFFFFFFFFu;
+                pe[j].a = make_uint4(0u, 0u, 0u, 0u);
+                pe[j].b = make_uint4(0u, 0u, 0u, 0u);
+                if ((uint32_t)j < nb && !(av[j].x & 0x80000000u)) pe[j] = lnLoadEntry(T.tab + home[j]); // first probe, speculative
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                if ((uint32_t)j >= nb || overflow) continue;
+                if (av[j].x & 0x80000000u) continue; // blacklisted neighbours are skipped (:98-99)
+                const uint32_t nbr = av[j].x & 0x7FFFFFFFu;
+                const double w = lnBitsToDouble(av[j].z, av[j].w);
+                arcsN++;
+                if (touchedN + 1 > C.touchedCap) {
+                    overflow = true;
+                    continue;
+                }
+                const double dS = dc + w;         // totalStayDist  (:104)
+                const double dX = dc + (1.0 - w); // totalCrossDist (:107-108)
+                // label pruning (header of ocw_search.cuh) against the running bestDist
+                const bool creatS = dS + dc <= best, creatX = dX + dc <= best;
+                // ---- label table ----------------------------------------------------------------------------------
+                uint32_t s = home[j];
+                LanesEntryRegs e = pe[j];
+                {
+                    bool stale = false; // an earlier arc of this group wrote the slot after the speculative load
+#pragma unroll
+                    for (int jj = 0; jj < 4; ++jj)
+                        if (jj < j && wslot[jj] == s) stale = true;
+                    if (stale) e = lnLoadEntry(T.tab + s);
+                }
+                bool found = false, isNew = false;
+                while (true) {
+                    if (e.b.w != stamp) { // free slot
+                        isNew = creatS || creatX;
+                        break;
+                    }
+                    if (e.b.x == nbr) {
+                        found = true;
+                        break;
+                    }
+                    s = (s + 1u) & tabMask;
+                    e = lnLoadEntry(T.tab + s);
+                }
+                if (!found && !isNew) continue; // no label, and none may be created
+                double dA = kUnlabelled, dB = kUnlabelled;           // label of the side the stay arc reaches / of the other side
+                uint32_t pA = kLanesPackedNone, pB = kLanesPackedNone; // hops | queue position << 16
+                if (found) {
+                    const double e0 = lnBitsToDouble(e.a.x, e.a.y), e1 = lnBitsToDouble(e.a.z, e.a.w);
+                    dA = side ? e1 : e0;
+                    dB = side ? e0 : e1;
+                    pA = side ? e.b.z : e.b.y;
+                    pB = side ? e.b.y : e.b.z;
+                }
+                const bool hadA = dA < kUnlabelled, hadB = dB < kUnlabelled;
+                uint32_t hA = pA & 0xFFFFu, hB = pB & 0xFFFFu;
+                bool anyAcc = false;
+#pragma unroll
+                for (int k = 0; k < 2; ++k) { // updatePaths(stayNeighbor, ...) then updatePaths(crossNeighbor, ...)  (:59-84)
+                    const double d = k ? dX : dS;
+                    const bool had = k ? hadB : hadA;
+                    const double dOld = k ? dB : dA, dTw = k ? dA : dB;
+                    const uint32_t hOld = k ? hB : hA, hTw = k ? hA : hB;
+                    bool acc;
+                    if (!had)
+                        acc = d < kInfDist && ((k ? creatX : creatS) || d + dTw <= best);
+                    else
+                        acc = (dOld == d) ? (hNew < hOld) : (d < dOld);
+                    if (!acc || overflow) continue;
+                    anyAcc = true;
+                    const uint32_t sd = k ? (side ^ 1u) : side;
+                    // a superseded key leaves the queue (its position sits in the label's hop word)
+                    const uint32_t oldq = (k ? pB : pA) >> 16;
+                    if (had && oldq < parkBase) T.cnt[oldq / kLanesC] |= 1u << (oldq % kLanesC);
+                    // the new queue entry; only nodes that can still be extracted enter a bucket
+                    uint32_t qpos;
+                    uint4 kv = make_uint4(0u, 0u, 0u, 0u), rv = make_uint4(0u, 0u, cur, 0u);
+                    if (2 * d <= best) {
+                        const uint32_t bk = lnBucketOf(d, C.scaleU, C.scaleB, NB - 1u);
+                        const uint32_t cw = T.cnt[bk];
+                        const uint32_t pos = cw >> 16;
+                        if (pos >= kLanesC) {
+                            overflow = true; // a bucket is full
+                            continue;
+                        }
+                        T.cnt[bk] = cw + (1u << 16);
+                        qpos = bk * kLanesC + pos;
+                        const unsigned long long db = lnDoubleBits(d);
+                        kv = make_uint4((uint32_t)db, (uint32_t)(db >> 32), 2u * nbr + sd, hNew);
+                        uint32_t first = av[j].y & ((1u << C.rowShift) - 1u), deg = av[j].y >> C.rowShift;
+                        if (deg == (0xFFFFFFFFu >> C.rowShift)) { // saturated degree field: read the row record
+                            const uint2 ri = rowinfo[nbr];
+                            first = ri.x;
+                            deg = ri.y;
+                        }
+                        rv.x = first;
+                        rv.y = deg;
+                    } else {
+                        if (parkN >= C.parkCap) {
+                            overflow = true;
+                            continue;
+                        }
+                        qpos = parkBase + parkN++;
+                    }
+                    lnStore4(T.q + 2 * (size_t)qpos, kv);
+                    lnStore4(T.q + 2 * (size_t)qpos + 1, rv);
+                    const uint32_t pw = hNew | (qpos << 16);
+                    if (k) {
+                        dB = d;
+                        hB = hNew;
+                        pB = pw;
+                    } else {
+                        dA = d;
+                        hA = hNew;
+                        pA = pw;
+                    }
+                    // record logic (:71-82)
+                    const double D = d + dTw;
+                    const uint32_t H = hNew + hTw;
+                    bool push = false;
+                    if (D < best || (D == best && H < bestHop)) {
+                        best = D;
+                        bestHop = H;
+                        push = true;
+                    } else if (D == best && H < 2u * bestHop) {
+                        push = true;
+                    }
+                    if (push) {
+                        if (histN >= C.histCap) {
+                            overflow = true;
+                            continue;
+                        }
+                        T.hist[histN++] = 2u * nbr + sd;
+                    }
+                }
+                if (anyAcc) {
+                    const unsigned long long a0b = lnDoubleBits(side ? dB : dA), a1b = lnDoubleBits(side ? dA : dB);
+                    lnStore4(reinterpret_cast<uint4 *>(T.tab + s), make_uint4((uint32_t)a0b, (uint32_t)(a0b >> 32), (uint32_t)a1b, (uint32_t)(a1b >> 32)));
+                    lnStore4(reinterpret_cast<uint4 *>(T.tab + s) + 1, make_uint4(nbr, side ? pB : pA, side ? pA : pB, stamp));
+                    wslot[j] = s;
+                    if (isNew) touchedN++;
+                }
+            }
+        }
+    }
+    rec.src = src;
+    rec.flags = (overflow ? 1u : 0u) | (tie ? 2u : 0u);
+    rec.best = best;
+    rec.histN = histN;
+    rec.touchedN = touchedN;
+    rec.arcs = arcsN;
+    rec.settled = settledN;
+    rec.stamp = stamp;
+    rec.parkN = parkN;
+}
+
+} // namespace smsgpu

@@ -84,6 +84,10 @@ struct TileMem {
     uint32_t *bm;    // presence bitmap of the label table, one bit per slot
     uint32_t hopMask; // hop words: all 32 bits, except in the pairs engine (hops | queue position << 16)
     uint4 *qrow;     // pairs engine: its queue, two uint4 per entry: {dist bits, hops << 32 | id}, {first arc, degree, -, -}
+    // lanes engine (ocw_lanes_core.cuh; 0 / null elsewhere): a slot is occupied iff its flags word equals `stamp`; the
+    // predecessor of a label sits in the queue entry its hop word points to
+    uint32_t stamp;
+    const uint4 *lq;
 };
 
 __device__ inline void carveTileMem(TileMem &M, unsigned char *base, const TileCaps &c, unsigned char *hot = nullptr) {
@@ -92,6 +96,8 @@ __device__ inline void carveTileMem(TileMem &M, unsigned char *base, const TileC
     M.cl = nullptr;
     M.bm = nullptr;
     M.qrow = nullptr;
+    M.stamp = 0;
+    M.lq = nullptr;
     M.hopMask = c.pairs ? 0xFFFFu : 0xFFFFFFFFu;
     if (c.nbuckets) {
         M.cl = reinterpret_cast<uint32_t *>(hot);
@@ -162,6 +168,14 @@ __device__ __forceinline__ uint32_t homeSlot(const TileMem &M, uint32_t v) {
 // slot of original vertex v, or -1
 __device__ __forceinline__ int findSlot(const TileMem &M, uint32_t v) {
     uint32_t s = homeSlot(M, v);
+    if (M.stamp) { // lanes engine: occupied iff the entry carries the stamp of the search
+        while (true) {
+            const uint4 hb = reinterpret_cast<const uint4 *>(&M.tab[s])[1]; // {key, h0, h1, flags}
+            if (hb.w != M.stamp) return -1;
+            if (hb.x == v) return (int)s;
+            s = (s + 1) & M.tabMask;
+        }
+    }
     if (M.bm) { // fast engine: a slot is occupied iff its bit is set; entries of free slots hold garbage
         while (true) {
             if (!((M.bm[s >> 5] >> (s & 31)) & 1u)) return -1;
@@ -212,6 +226,10 @@ __device__ __forceinline__ bool keyLess(unsigned long long ahi, unsigned long lo
 }
 
 __device__ __forceinline__ uint32_t predOf(const TileMem &M, int slot, uint32_t side) {
+    if (M.lq) { // lanes engine: hop word = hops | queue position << 16; the entry there holds the predecessor
+        const uint32_t hw = side ? M.tab[slot].h1 : M.tab[slot].h0;
+        return M.lq[2 * (size_t)(hw >> 16) + 1].z;
+    }
     return M.pq ? M.pq[2 * slot + side].x : M.pred[2 * slot + side];
 }
 

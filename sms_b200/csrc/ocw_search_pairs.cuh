@@ -85,21 +85,20 @@ __device__ __forceinline__ uint32_t bucketOf(const double d, const float scaleU,
 
 // Everything after the search of one source, by all 32 lanes (same code path as ocwSearchKernel's tail).
 // Returns 1 when the source completed in this tier (its counters count), 0 when it overflowed.
-__device__ __noinline__ int finishSourcePairs(const PairsKArgs *K, unsigned char *tile, unsigned char *hot, const double best,
-                                              const uint32_t histN, const uint32_t touchedN, const uint32_t arcs,
-                                              const uint32_t settled, const int overflow, const uint32_t src,
-                                              const int32_t srcIdx, const int32_t twinIdx, const int mirrorOk) {
+// `M` is the source's working memory as the engine left it (pairs engine: carved from its tile below; lanes engine: built
+// by ocwLanesFinishKernel).
+__device__ __forceinline__ int finishSourceBody(const PairsKArgs *K, TileMem &M, const double best, const uint32_t histN,
+                                            const uint32_t touchedN, const uint32_t arcs, const uint32_t settled, const int overflow,
+                                            const uint32_t src, const int32_t srcIdx, const int32_t twinIdx, const int mirrorOk) {
     // twinIdx >= 0: the next entry of the source list is this source's twin (other side of the same vertex).  Its results
     // are emitted from this search when mirrorOk; if this source overflows, the twin goes to the next tier with it (its
     // search is the mirror image and would hit the same capacity).  Returns 0 / 1 / 2 = sources disposed of... see below.
     const int32_t srcIdx2 = (twinIdx >= 0 && mirrorOk && !overflow) ? twinIdx : -1;
     const Tile<32> T;
     const GraphDev G = K->G;
-    const TileCaps caps = K->caps;
+    const TileCaps caps = M.caps;
     const RawOut &R = K->R;
     const SearchParams &P = K->P;
-    TileMem M;
-    carveTileMem(M, tile, caps, hot);
     SrcState S;
     S.best = best;
     S.bestHop = 0.0;
@@ -162,7 +161,7 @@ __device__ __noinline__ int finishSourcePairs(const PairsKArgs *K, unsigned char
     if (!S.overflow) {
         if (P.exportLabels) {
             for (uint32_t i = T.lane; i < caps.tabCap; i += 32) {
-                if (!((M.bm[i >> 5] >> (i & 31)) & 1u)) continue;
+                if (M.bm ? !((M.bm[i >> 5] >> (i & 31)) & 1u) : (M.tab[i].flags != M.stamp)) continue;
                 const Entry e = loadEntry(&M.tab[i]);
 #pragma unroll
                 for (int sd = 0; sd < 2; ++sd) {
@@ -213,6 +212,21 @@ __device__ __noinline__ int finishSourcePairs(const PairsKArgs *K, unsigned char
     }
     T.sync();
     return counted; // 2: the twin is disposed of as well (mirrored, or sent to the next tier with this source)
+}
+
+__device__ __noinline__ int finishSourcePairs(const PairsKArgs *K, unsigned char *tile, unsigned char *hot, const double best,
+                                              const uint32_t histN, const uint32_t touchedN, const uint32_t arcs,
+                                              const uint32_t settled, const int overflow, const uint32_t src,
+                                              const int32_t srcIdx, const int32_t twinIdx, const int mirrorOk) {
+    TileMem M;
+    carveTileMem(M, tile, K->caps, hot);
+    return finishSourceBody(K, M, best, histN, touchedN, arcs, settled, overflow, src, srcIdx, twinIdx, mirrorOk);
+}
+// the same for working memory some other engine describes (lanes engine)
+__device__ __noinline__ int finishSourceMem(const PairsKArgs *K, TileMem &M, const double best, const uint32_t histN,
+                                            const uint32_t touchedN, const uint32_t arcs, const uint32_t settled, const int overflow,
+                                            const uint32_t src, const int32_t srcIdx, const int32_t twinIdx, const int mirrorOk) {
+    return finishSourceBody(K, M, best, histN, touchedN, arcs, settled, overflow, src, srcIdx, twinIdx, mirrorOk);
 }
 
 #ifndef SMSGPU_PAIRS_MIN_CTAS

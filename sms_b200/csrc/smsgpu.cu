@@ -130,6 +130,24 @@ struct smsgpu_ctx {
     float pairsScaleU = 0.f;  // bucket map of the pairs engine (PairsParams)
     float pairsScaleB = 0.f;
     bool pairsMirror = true;  // twin sources searched once (SMSGPU_MIRROR=0 turns it off)
+    // lanes engine (ocw_search_lanes.cuh): one source per THREAD, in front of the pairs engine on long source lists
+    int lanesMode = 0;                    // SMSGPU_LANES: 0 off, 1 on for every list, 2 on for lists of >= lanesMinSources entries
+    long long lanesMinSources = 200000;
+    long long lanesMaxTiles = 40960;      // SMSGPU_LANES_TILES: tiles (searches in flight) over all sets
+    int lanesSetsWanted = 2;              // SMSGPU_LANES_SETS: tile sets = streams that alternate batches
+    int lanesSets = 0;
+    long long lanesTilesPerSet = 0, lanesAllocWant = 0;
+    LanesCfg lanesCfg{};
+    TileCaps lanesFcaps{};
+    size_t lanesTileStride = 0, lanesWarpStride = 0;
+    int lanesFinishCtas = 0;
+    uint32_t lanesStamp = 0;
+    DevBuf lanesWarpScratch, dLanesArgs, ovfD;
+    void *lanesScratch = nullptr;
+    size_t lanesScratchBytes = 0;
+    cudaStream_t laneStream[4]{};
+    cudaEvent_t laneEv[4]{}, lanesForkEv = nullptr, lanesT0 = nullptr, lanesT1 = nullptr;
+    double lanesMs = 0.0;
     // round input
     DevBuf dX, dBl;
     const double *xPtr = nullptr;   // device pointer in use (own buffer or caller's)
@@ -420,6 +438,141 @@ int ensureTierScratch(smsgpu_ctx *ctx, int ti) {
     return 0;
 }
 
+
+// ---- lanes engine: working memory and one pass over a work list -----------------------------------------------------------
+// Tiles for `items` searches (at most lanesMaxTiles, at most 45 % of the free memory), in lanesSets sets.
+int ensureLanes(smsgpu_ctx *ctx, long long items) {
+    const TileCaps &pc = ctx->tier[1].caps;
+    LanesCfg C{};
+    C.tabCap = pc.tabCap;
+    C.tabShift = pc.tabShift;
+    C.touchedCap = pc.touchedCap;
+    C.histCap = pc.histCap;
+    C.nbuckets = (uint32_t)SMSGPU_PAIRS_BUCKETS;
+    C.parkCap = std::min<uint32_t>(8192u, 0xFFFFu - C.nbuckets * kLanesC - 1u);
+    C.scaleU = ctx->pairsScaleU;
+    C.scaleB = ctx->pairsScaleB;
+    C.rowShift = ctx->rowShift;
+    ctx->lanesCfg = C;
+    TileCaps F{};
+    F.tabCap = pc.tabCap;
+    F.tabShift = pc.tabShift;
+    F.dense = 0;
+    F.touchedCap = pc.touchedCap;
+    F.heapCap = pc.histCap; // selectIntermediates' key scratch
+    F.histCap = pc.histCap;
+    F.walkCap = pc.walkCap;
+    F.chordCap = pc.chordCap;
+    ctx->lanesFcaps = F;
+    const size_t stride = lanesTileBytes(C);
+    long long want = std::max<long long>(1, std::min<long long>(items, ctx->lanesMaxTiles));
+    int sets = (want >= 512) ? std::max(1, std::min(ctx->lanesSetsWanted, 4)) : 1;
+    long long perSet = (want + sets - 1) / sets;
+    perSet = (perSet + 127) & ~127ll; // whole CTAs of the search kernel
+    if (ctx->lanesScratch && ctx->lanesTileStride == stride && want <= ctx->lanesAllocWant) return 0; // what is there is enough (or all there can be)
+    if (ctx->lanesScratch) {
+        CU(cudaDeviceSynchronize());
+        cudaFree(ctx->lanesScratch);
+        ctx->lanesScratch = nullptr;
+        ctx->lanesScratchBytes = 0;
+    }
+    size_t freeB = 0, totalB = 0;
+    CU(cudaMemGetInfo(&freeB, &totalB));
+    const long long fit = (long long)((freeB / 100 * 45) / stride);
+    if (fit < 128) return fail(ctx, SMSGPU_ERR_NOMEM, "lanes engine needs %zu bytes per tile, %zu free", stride, freeB);
+    ctx->lanesAllocWant = want;
+    if (sets * perSet > fit) {
+        perSet = (fit / sets) & ~127ll;
+        if (perSet < 128) {
+            sets = 1;
+            perSet = fit & ~127ll;
+        }
+        ctx->lanesAllocWant = ctx->lanesMaxTiles; // all there can be
+    }
+    if (want >= ctx->lanesMaxTiles) ctx->lanesAllocWant = 1ll << 62;
+    const size_t bytes = (size_t)sets * (size_t)perSet * stride;
+    CU(cudaMalloc(&ctx->lanesScratch, bytes));
+    ctx->lanesScratchBytes = bytes;
+    CU(cudaMemsetAsync(ctx->lanesScratch, 0, bytes, ctx->stream)); // no entry carries a stamp
+    ctx->lanesStamp = 0;
+    ctx->lanesSets = sets;
+    ctx->lanesTilesPerSet = perSet;
+    ctx->lanesTileStride = stride;
+    // finishing warps: their walk scratch (table and history live in the tiles)
+    TileCaps sc = F;
+    sc.tabCap = 0;
+    sc.touchedCap = 0;
+    sc.histCap = 0;
+    ctx->lanesWarpStride = (tileBytes(sc) + 255) & ~(size_t)255;
+    ctx->lanesFinishCtas = (int)std::min<long long>((perSet + 3) / 4, (long long)ctx->smCount * 8);
+    CU(ctx->lanesWarpScratch.ensure((size_t)sets * (size_t)ctx->lanesFinishCtas * 4 * ctx->lanesWarpStride));
+    for (int k = 0; k < sets; ++k) {
+        if (!ctx->laneStream[k]) CU(cudaStreamCreateWithFlags(&ctx->laneStream[k], cudaStreamNonBlocking));
+        if (!ctx->laneEv[k]) CU(cudaEventCreateWithFlags(&ctx->laneEv[k], cudaEventDisableTiming));
+    }
+    if (!ctx->lanesForkEv) CU(cudaEventCreateWithFlags(&ctx->lanesForkEv, cudaEventDisableTiming));
+    if (!ctx->lanesT0) CU(cudaEventCreate(&ctx->lanesT0));
+    if (!ctx->lanesT1) CU(cudaEventCreate(&ctx->lanesT1));
+    if (std::getenv("SMSGPU_DEBUG_OVF"))
+        std::fprintf(stderr, "[smsgpu] lanes engine: %d sets x %lld tiles x %zu bytes = %.1f GB\n", sets, perSet, stride, (double)bytes / 1e9);
+    return 0;
+}
+
+// One pass of the lanes engine over wl[0 .. nw) (nullptr: all local sources): batches of tiles alternate between the lane
+// streams; everything is ordered behind `st` at the start and `st` waits for all of it at the end.  Sources that do not
+// finish here are appended to P.ovfList / P.ovfCount.
+int runLanes(smsgpu_ctx *ctx, const GraphDev &G, SearchParams P, const RawOut &R, const int32_t *wl, long long nw, cudaStream_t st) {
+    const int itemSize = ctx->pairsMirror ? 2 : 1;
+    const long long items = (nw + itemSize - 1) / itemSize;
+    if (int rc = ensureLanes(ctx, items)) return rc;
+    P.worklist = wl;
+    P.nwork = nw;
+    P.tier = 1;
+    PairsKArgs K{G, P, R, ctx->lanesFcaps};
+    CU(ctx->dLanesArgs.ensure(sizeof K));
+    CU(cudaMemcpyAsync(ctx->dLanesArgs.p, &K, sizeof K, cudaMemcpyHostToDevice, st)); // pageable source: staged before return
+    CU(cudaEventRecord(ctx->lanesT0, st));
+    CU(cudaEventRecord(ctx->lanesForkEv, st));
+    for (int k = 0; k < ctx->lanesSets; ++k) CU(cudaStreamWaitEvent(ctx->laneStream[k], ctx->lanesForkEv, 0));
+    const long long B = ctx->lanesTilesPerSet;
+    int batch = 0;
+    for (long long first = 0; first < items; first += B, ++batch) {
+        const int set = batch % ctx->lanesSets;
+        cudaStream_t s = ctx->laneStream[set];
+        if (++ctx->lanesStamp == 0) { // stamps exhausted (2^32 batches): forget every old entry
+            CU(cudaDeviceSynchronize());
+            CU(cudaMemsetAsync(ctx->lanesScratch, 0, ctx->lanesScratchBytes, s));
+            CU(cudaStreamSynchronize(s));
+            ctx->lanesStamp = 1;
+        }
+        LanesArgs A{};
+        A.cfg = ctx->lanesCfg;
+        A.rowinfo = ctx->dRowinfo.as<uint2>();
+        A.tiles = static_cast<unsigned char *>(ctx->lanesScratch) + (size_t)set * (size_t)B * ctx->lanesTileStride;
+        A.tileStride = ctx->lanesTileStride;
+        A.first = first;
+        A.count = std::min<long long>(B, items - first);
+        A.itemSize = itemSize;
+        A.stamp = ctx->lanesStamp;
+        A.kargs = ctx->dLanesArgs.as<PairsKArgs>();
+        A.warpScratch = ctx->lanesWarpScratch.as<unsigned char>() + (size_t)set * (size_t)ctx->lanesFinishCtas * 4 * ctx->lanesWarpStride;
+        A.warpScratchStride = ctx->lanesWarpStride;
+        A.fcaps = ctx->lanesFcaps;
+        ocwLanesSearchKernel<<<(unsigned)((A.count + SMSGPU_LANES_BLOCK - 1) / SMSGPU_LANES_BLOCK), SMSGPU_LANES_BLOCK, 0, s>>>(G, P, A);
+        CU(cudaGetLastError());
+        ocwLanesFinishKernel<<<(unsigned)std::min<long long>((A.count + 3) / 4, ctx->lanesFinishCtas), 128, 0, s>>>(A);
+        CU(cudaGetLastError());
+        ctx->stats.search_launches += 2;
+        ctx->stats.total_launches += 2;
+    }
+    for (int k = 0; k < ctx->lanesSets; ++k) {
+        CU(cudaEventRecord(ctx->laneEv[k], ctx->laneStream[k]));
+        CU(cudaStreamWaitEvent(st, ctx->laneEv[k], 0));
+    }
+    CU(cudaEventRecord(ctx->lanesT1, st));
+    return 0;
+}
+
 } // namespace
 
 extern "C" {
@@ -595,6 +748,10 @@ int smsgpu_create(smsgpu_ctx **out, int64_t n, int64_t m, const int64_t *rowptr,
             }
         }
     }
+    if (const char *el = std::getenv("SMSGPU_LANES")) ctx->lanesMode = el[0] == '1' ? 1 : (el[0] == '2' ? 2 : 0);
+    if (const char *el = std::getenv("SMSGPU_LANES_MIN")) ctx->lanesMinSources = std::atoll(el);
+    if (const char *el = std::getenv("SMSGPU_LANES_TILES")) ctx->lanesMaxTiles = std::max<long long>(128, std::atoll(el));
+    if (const char *el = std::getenv("SMSGPU_LANES_SETS")) ctx->lanesSetsWanted = std::max(1, std::min(4, std::atoi(el)));
     if (const char *eh = std::getenv("SMSGPU_NO_HISTORY")) ctx->useHistory = !(eh[0] == '1');
     if (const char *eo = std::getenv("SMSGPU_NO_OVERLAP")) ctx->overlapHeavy = !(eo[0] == '1');
     configureTiers(ctx);
@@ -642,6 +799,17 @@ void smsgpu_destroy(smsgpu_ctx *ctx) {
         if (e) cudaEventDestroy(e);
     for (auto &e : ctx->scEv)
         if (e) cudaEventDestroy(e);
+    for (auto &ls : ctx->laneStream)
+        if (ls) cudaStreamDestroy(ls);
+    for (auto &le : ctx->laneEv)
+        if (le) cudaEventDestroy(le);
+    if (ctx->lanesForkEv) cudaEventDestroy(ctx->lanesForkEv);
+    if (ctx->lanesT0) cudaEventDestroy(ctx->lanesT0);
+    if (ctx->lanesT1) cudaEventDestroy(ctx->lanesT1);
+    if (ctx->lanesScratch) cudaFree(ctx->lanesScratch);
+    ctx->lanesWarpScratch.release();
+    ctx->dLanesArgs.release();
+    ctx->ovfD.release();
     if (ctx->joinEv) cudaEventDestroy(ctx->joinEv);
     if (ctx->heavyEv) cudaEventDestroy(ctx->heavyEv);
     if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
@@ -1061,6 +1229,7 @@ int separateLocal(smsgpu_ctx *ctx, const smsgpu_params &P) {
         long long done[kNumTiers] = {0, 0, 0, 0};
         long long prevRun = 0;
         bool tierRan[kNumTiers] = {false, false, false, false};
+        bool lanesRan = false;
         // one search launch (no synchronisation): tier `ti` over `wl[0 .. nw)`, overflows appended to `ovf`
         auto launchTier = [&](int ti, const int32_t *wl, long long nw, int32_t *ovf, int ovfSlot, int queueSlot, int runSlot,
                               cudaStream_t s, int evIdx, int ctasCap) -> int {
@@ -1122,6 +1291,27 @@ int separateLocal(smsgpu_ctx *ctx, const smsgpu_params &P) {
             if (int rc = ensureTierScratch(ctx, ti)) return rc;
             const int which = ti & 1;
             if (heavy > 0 && ti >= 2) CU(cudaStreamWaitEvent(st, ctx->joinEv, 0)); // tier 2's tiles are in use until then
+            if (ti == 1 && plain && !G.blStampNext && ctx->tier[1].pairs &&
+                (ctx->lanesMode == 1 || (ctx->lanesMode == 2 && nwork >= ctx->lanesMinSources))) {
+                // the lanes engine (one source per thread) first; what it gives up -- a capacity hit, a second source that is
+                // not the mirror image of the first -- is the pairs engine's work list
+                CU(ctx->ovfD.ensure((size_t)std::max<long long>(nsrc, 1) * 4));
+                CU(cudaMemsetAsync(dc + 21, 0, 8, st));
+                SearchParams LQ = SP;
+                LQ.ovfList = ctx->ovfD.as<int32_t>();
+                LQ.ovfCount = dc + 21;
+                if (int rc = runLanes(ctx, G, LQ, R, worklist, nwork, st)) return rc;
+                CU(cudaMemcpyAsync(hc, dc, 24 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+                CU(cudaStreamSynchronize(st));
+                lanesRan = true;
+                if (std::getenv("SMSGPU_DEBUG_OVF"))
+                    std::fprintf(stderr, "[smsgpu] lanes engine: %lld sources in, %llu left for the pairs engine\n", nwork, hc[21]);
+                done[1] += (long long)hc[4] - prevRun;
+                prevRun = (long long)hc[4];
+                worklist = ctx->ovfD.as<int32_t>();
+                nwork = (long long)hc[21];
+                if (nwork == 0) continue;
+            }
             if (int rc = launchTier(ti, worklist, nwork, ovfBufs[which], 9 + which, 8, 4, st, 2 * ti, 0)) return rc;
             tierRan[ti] = true;
             CU(cudaMemcpyAsync(hc, dc, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
@@ -1231,6 +1421,8 @@ int separateLocal(smsgpu_ctx *ctx, const smsgpu_params &P) {
             ctx->stats.ms_tier[k] = 0.0;
             if (tierRan[k] && cudaEventElapsedTime(&tms, ctx->tierEv[2 * k], ctx->tierEv[2 * k + 1]) == cudaSuccess) ctx->stats.ms_tier[k] = tms;
         }
+        float lms = 0;
+        if (lanesRan && cudaEventElapsedTime(&lms, ctx->lanesT0, ctx->lanesT1) == cudaSuccess) ctx->stats.ms_tier[1] += lms;
         float hms = 0; // the overlapped launch ran beside tier 1: the tier times no longer add up to the search time
         if (heavyRan && cudaEventElapsedTime(&hms, ctx->tierEv[8], ctx->tierEv[9]) == cudaSuccess) ctx->stats.ms_tier[2] += hms;
         break;
