@@ -136,6 +136,7 @@ struct smsgpu_ctx {
     long long lanesMaxTiles = 40960;      // SMSGPU_LANES_TILES: tiles (searches in flight) over all sets
     int lanesSetsWanted = 2;              // SMSGPU_LANES_SETS: tile sets = streams that alternate batches
     int lanesSets = 0;
+    int lanesTabLg = 0, lanesBuckets = SMSGPU_PAIRS_BUCKETS, lanesPark = 8192; // SMSGPU_LANES_TABLG / _NB / _PARK
     long long lanesTilesPerSet = 0, lanesAllocWant = 0;
     LanesCfg lanesCfg{};
     TileCaps lanesFcaps{};
@@ -440,25 +441,30 @@ int ensureTierScratch(smsgpu_ctx *ctx, int ti) {
 
 
 // ---- lanes engine: working memory and one pass over a work list -----------------------------------------------------------
-// Tiles for `items` searches (at most lanesMaxTiles, at most 45 % of the free memory), in lanesSets sets.
+// Tiles for `items` searches (at most lanesMaxTiles, at most 60 % of the free memory), in lanesSets sets.
 int ensureLanes(smsgpu_ctx *ctx, long long items) {
     const TileCaps &pc = ctx->tier[1].caps;
     LanesCfg C{};
     C.tabCap = pc.tabCap;
     C.tabShift = pc.tabShift;
     C.touchedCap = pc.touchedCap;
+    if (ctx->lanesTabLg > 0 && (1u << ctx->lanesTabLg) < pc.tabCap) { // a smaller table: more tiles fit, larger balls go to the pairs engine
+        C.tabCap = 1u << ctx->lanesTabLg;
+        C.tabShift = 32 - (uint32_t)ctx->lanesTabLg;
+        C.touchedCap = std::min<uint32_t>(pc.touchedCap, C.tabCap / 4 * 3);
+    }
     C.histCap = pc.histCap;
-    C.nbuckets = (uint32_t)SMSGPU_PAIRS_BUCKETS;
-    C.parkCap = std::min<uint32_t>(8192u, 0xFFFFu - C.nbuckets * kLanesC - 1u);
+    C.nbuckets = (uint32_t)ctx->lanesBuckets;
+    C.parkCap = std::min<uint32_t>((uint32_t)ctx->lanesPark, 0xFFFFu - C.nbuckets * kLanesC - 1u);
     C.scaleU = ctx->pairsScaleU;
-    C.scaleB = ctx->pairsScaleB;
+    C.scaleB = ctx->pairsScaleB * ((float)ctx->lanesBuckets / (float)SMSGPU_PAIRS_BUCKETS); // the pairs engine's map over this engine's buckets
     C.rowShift = ctx->rowShift;
     ctx->lanesCfg = C;
     TileCaps F{};
-    F.tabCap = pc.tabCap;
-    F.tabShift = pc.tabShift;
+    F.tabCap = C.tabCap;
+    F.tabShift = C.tabShift;
     F.dense = 0;
-    F.touchedCap = pc.touchedCap;
+    F.touchedCap = C.touchedCap;
     F.heapCap = pc.histCap; // selectIntermediates' key scratch
     F.histCap = pc.histCap;
     F.walkCap = pc.walkCap;
@@ -478,7 +484,7 @@ int ensureLanes(smsgpu_ctx *ctx, long long items) {
     }
     size_t freeB = 0, totalB = 0;
     CU(cudaMemGetInfo(&freeB, &totalB));
-    const long long fit = (long long)((freeB / 100 * 45) / stride);
+    const long long fit = (long long)((freeB / 100 * 60) / stride);
     if (fit < 128) return fail(ctx, SMSGPU_ERR_NOMEM, "lanes engine needs %zu bytes per tile, %zu free", stride, freeB);
     ctx->lanesAllocWant = want;
     if (sets * perSet > fit) {
@@ -751,6 +757,9 @@ int smsgpu_create(smsgpu_ctx **out, int64_t n, int64_t m, const int64_t *rowptr,
     if (const char *el = std::getenv("SMSGPU_LANES")) ctx->lanesMode = el[0] == '1' ? 1 : (el[0] == '2' ? 2 : 0);
     if (const char *el = std::getenv("SMSGPU_LANES_MIN")) ctx->lanesMinSources = std::atoll(el);
     if (const char *el = std::getenv("SMSGPU_LANES_TILES")) ctx->lanesMaxTiles = std::max<long long>(128, std::atoll(el));
+    if (const char *el = std::getenv("SMSGPU_LANES_TABLG")) ctx->lanesTabLg = std::atoi(el) > 0 ? std::max(6, std::min(20, std::atoi(el))) : 0;
+    if (const char *el = std::getenv("SMSGPU_LANES_NB")) ctx->lanesBuckets = std::max(64, std::min(2048, std::atoi(el) & ~3));
+    if (const char *el = std::getenv("SMSGPU_LANES_PARK")) ctx->lanesPark = std::max(16, std::min(16384, std::atoi(el)));
     if (const char *el = std::getenv("SMSGPU_LANES_SETS")) ctx->lanesSetsWanted = std::max(1, std::min(4, std::atoi(el)));
     if (const char *eh = std::getenv("SMSGPU_NO_HISTORY")) ctx->useHistory = !(eh[0] == '1');
     if (const char *eo = std::getenv("SMSGPU_NO_OVERLAP")) ctx->overlapHeavy = !(eo[0] == '1');
