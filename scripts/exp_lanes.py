@@ -25,8 +25,12 @@ x = I.xstar_uniform(inst.m, seed=1)
 bl = inst.root_blacklist()
 print(f"instance {inst.n}/{inst.m} in {time.time() - t0:.1f} s", flush=True)
 for setting in a.settings.split(","):
-    f = setting.split(":") + ["0"] * 6
-    lanes, tiles, sets, nb, tablg, park = f[:6]
+    f = setting.split(":") + ["0"] * 7
+    lanes, tiles, sets, nb, tablg, park, l2f = f[:7]
+    if l2f != "0":
+        os.environ["SMSGPU_L2_FETCH"] = l2f
+    else:
+        os.environ.pop("SMSGPU_L2_FETCH", None)
     os.environ["SMSGPU_LANES_NB"] = nb if nb != "0" else "2048"
     os.environ["SMSGPU_LANES_TABLG"] = tablg
     os.environ["SMSGPU_LANES_PARK"] = park if park != "0" else "8192"
@@ -43,7 +47,7 @@ for setting in a.settings.split(","):
         ctx.fetch()
         wall = time.time() - t1
         st = ctx.stats()
-        print(f"lanes={lanes} tiles={tiles} sets={sets} nb={nb} tablg={tablg} park={park} round {r}: search {st['ms_search']:.1f} ms tiers {[round(v, 1) for v in st['ms_tier']]} "
+        print(f"lanes={lanes} tiles={tiles} sets={sets} nb={nb} tablg={tablg} park={park} l2fetch={l2f} round {r}: search {st['ms_search']:.1f} ms tiers {[round(v, 1) for v in st['ms_tier']]} "
               f"wall {wall * 1e3:.0f} ms tier_sources {st['tier_sources']} cuts {st['unique_cuts']} arcs {st['arcs_scanned']} "
               f"settled {st['settled']} mirrored {st['mirrored_sources']}", flush=True)
     ctx.close()

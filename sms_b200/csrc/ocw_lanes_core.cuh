@@ -168,9 +168,45 @@ __host__ __device__ __forceinline__ LanesEntryRegs lnLoadEntry(const Entry *p) {
     e.b = lnLoad4(reinterpret_cast<const uint4 *>(p) + 1);
     return e;
 }
+// The bucket words are read and updated at L2 only (ld.cg / atomics): an atomic does not update a line in L1.
+__host__ __device__ __forceinline__ uint4 lnLoadCnt4(const uint32_t *p) {
+#ifdef __CUDA_ARCH__
+    return __ldcg(reinterpret_cast<const uint4 *>(p));
+#else
+    return *reinterpret_cast<const uint4 *>(p);
+#endif
+}
+__host__ __device__ __forceinline__ uint32_t lnCntAdd(uint32_t *p, const uint32_t v) { // returns the old word
+#ifdef __CUDA_ARCH__
+    return atomicAdd(p, v);
+#else
+    const uint32_t o = *p;
+    *p = o + v;
+    return o;
+#endif
+}
+__host__ __device__ __forceinline__ void lnCntOr(uint32_t *p, const uint32_t v) { // no result: a reduction, nothing to wait for
+#ifdef __CUDA_ARCH__
+    atomicOr(p, v);
+#else
+    *p |= v;
+#endif
+}
+
+#ifndef SMSGPU_LANES_GROUP
+#define SMSGPU_LANES_GROUP 8
+#endif
+constexpr int kLanesG = SMSGPU_LANES_GROUP; // arcs per group: their loads, probes and queue-position atomics travel together
 
 // The search of one source.  `srow` = {first arc, degree} of the source's vertex.  Fills `rec` (src, flags bits 0-1,
 // best, histN, touchedN, arcs, settled, stamp, parkN); srcIdx / twinIdx / flag bit 2 belong to the caller.
+//
+// A thread is a chain of dependent memory round trips, so the arcs of a settled node are handled in GROUPS of kLanesG:
+//   (1) the group's arc records, one round trip; (2) the label entries at their home slots, one round trip (further probes
+//   of a collision chain on demand); (3) the reference's sequential logic over the group, in registers: accept tests, running
+//   bestDist / history (:59-84), and for every accepted label the ISSUE of the atomic that appends to its bucket (its result
+//   is not looked at yet) and of the reduction that kills a superseded key; (4) one wait for the atomics, then the stores of
+//   the queue entries and labels.
 __host__ __device__ inline void lanesSearch(const Arc *__restrict__ arcs, const uint2 *__restrict__ rowinfo, const LanesCfg &C,
                                             const LanesTile &T, const uint32_t src, const uint2 srow, const uint32_t stamp,
                                             const double bestInit, LanesRec &rec) {
@@ -179,7 +215,8 @@ __host__ __device__ inline void lanesSearch(const Arc *__restrict__ arcs, const 
     {
         uint4 *c4 = reinterpret_cast<uint4 *>(T.cnt);
         const uint4 z = make_uint4(0u, 0u, 0u, 0u);
-        for (uint32_t i = 0; i < (NB >> 2); ++i) c4[i] = z;
+        for (uint32_t i = 1; i < (NB >> 2); ++i) lnStore4(c4 + i, z);
+        lnStore4(c4, make_uint4(1u << 16, 0u, 0u, 0u)); // bucket 0: one entry appended
         const uint32_t s = ((src >> 1) * 0x9E3779B1u) >> C.tabShift;
         const unsigned long long un = lnDoubleBits(kUnlabelled);
         uint4 a = make_uint4((uint32_t)un, (uint32_t)(un >> 32), (uint32_t)un, (uint32_t)(un >> 32));
@@ -195,9 +232,8 @@ __host__ __device__ inline void lanesSearch(const Arc *__restrict__ arcs, const 
         }
         lnStore4(reinterpret_cast<uint4 *>(T.tab + s), a);
         lnStore4(reinterpret_cast<uint4 *>(T.tab + s) + 1, b);
-        lnStore4(T.q, make_uint4(0u, 0u, src, 0u));         // dist 0, id src, 0 hops
+        lnStore4(T.q, make_uint4(0u, 0u, src, 0u));             // dist 0, id src, 0 hops
         lnStore4(T.q + 1, make_uint4(srow.x, srow.y, src, 0u)); // row, predecessor: itself (never followed)
-        T.cnt[0] = 1u << 16;
     }
     double best = bestInit;
     uint32_t bestHop = 0; // bestHopDist: a double in the reference (:52) that only ever holds small integers
@@ -206,13 +242,21 @@ __host__ __device__ inline void lanesSearch(const Arc *__restrict__ arcs, const 
     uint32_t lo = 0; // bucket of the last extraction: keys never decrease
 
     while (!overflow) {
-        // ---- first bucket at or after `lo` with a live key -------------------------------------------------------
-        uint32_t b = lo, word = 0, live = 0, app = 0;
-        for (; b < NB; ++b) {
-            word = T.cnt[b];
-            app = word >> 16;
-            live = ((1u << app) - 1u) & ~word;
-            if (live) break;
+        // ---- first bucket at or after `lo` with a live key: eight bucket words (one sector) per round trip -----------
+        uint32_t b = NB, word = 0, live = 0, app = 0;
+        for (uint32_t b0 = lo & ~7u; b0 < NB && b >= NB; b0 += 8) {
+            const uint4 w0 = lnLoadCnt4(T.cnt + b0), w1 = lnLoadCnt4(T.cnt + b0 + 4);
+            const uint32_t ws[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const uint32_t ap = ws[j] >> 16, lv = ((1u << ap) - 1u) & ~ws[j];
+                if (b >= NB && b0 + j >= lo && lv) {
+                    b = b0 + j;
+                    word = ws[j];
+                    app = ap;
+                    live = lv;
+                }
+            }
         }
         if (b >= NB) break; // queue empty (:88)
         // ---- its minimum live key, (dist, hops, id) lexicographic; four entries per round trip ---------------------
@@ -221,6 +265,7 @@ __host__ __device__ inline void lanesSearch(const Arc *__restrict__ arcs, const 
         bool mtie = false;
         const uint4 *qb = T.q + 2 * (size_t)(b * kLanesC);
         for (uint32_t p0 = 0; p0 < app; p0 += 4) {
+            if (!((live >> p0) & 0xFu)) continue;
             uint4 k[4], r[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
@@ -252,7 +297,8 @@ __host__ __device__ inline void lanesSearch(const Arc *__restrict__ arcs, const 
         const double dc = lnBitsToDouble((uint32_t)mhi, (uint32_t)(mhi >> 32));
         // loop condition of ocw_seperator.cpp:88-90
         if (cur == (src ^ 1u) || 2 * dc > best) break;
-        T.cnt[b] = word | (1u << mpos); // extract_top: the position is dead from now on
+        lnCntOr(T.cnt + b, 1u << mpos); // extract_top: the position is dead from now on
+        (void)word;
         settledN++;
         lo = b;
         const uint32_t side = cur & 1u, hNew = hc + 1u;
@@ -261,27 +307,36 @@ __host__ __device__ inline void lanesSearch(const Arc *__restrict__ arcs, const 
             break;
         }
 
-        // ---- relax the arcs of the settled node in adjacency order, four per round trip ----------------------------
-        for (uint32_t a0 = 0; a0 < mdeg && !overflow; a0 += 4) {
-            uint4 av[4];
-            LanesEntryRegs pe[4];
-            uint32_t home[4], wslot[4];
-            const uint32_t nb = (mdeg - a0) < 4u ? (mdeg - a0) : 4u;
+        // ---- relax the arcs of the settled node in adjacency order, kLanesG per group -------------------------------
+        for (uint32_t a0 = 0; a0 < mdeg && !overflow; a0 += kLanesG) {
+            const uint32_t nb = (mdeg - a0) < (uint32_t)kLanesG ? (mdeg - a0) : (uint32_t)kLanesG;
+            uint4 av[kLanesG];
+            LanesEntryRegs pe[kLanesG];
+            // what phase (4) needs of every arc
+            uint32_t slotOf[kLanesG];  // its label's slot, 0xFFFFFFFF: nothing to store
+            uint4 labA[kLanesG];       // the new distances {d0, d1} as stored
+            uint32_t hopA[kLanesG], hopB[kLanesG]; // new hop words of the stay side / the other side (queue position pending)
+            uint32_t retA[kLanesG], retB[kLanesG]; // old bucket word returned by the append (admitted), or the parked position
+            uint32_t how[kLanesG];     // bit 0 / 1: stay / cross side accepted; bit 2 / 3: admitted to a bucket (else parked)
+            // (1) the arc records
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
+            for (int j = 0; j < kLanesG; ++j) {
                 av[j] = make_uint4(0x80000000u, 0u, 0u, 0u);
                 if ((uint32_t)j < nb) av[j] = lnLoadRO4(reinterpret_cast<const uint4 *>(arcs + mfirst + a0 + j));
             }
+            // (2) the labels at their home slots (speculative: nothing of this group has been stored yet)
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                home[j] = ((av[j].x & 0x7FFFFFFFu) * 0x9E3779B1u) >> C.tabShift;
-                wslot[j] = 0xFFFFFFFFu;
+            for (int j = 0; j < kLanesG; ++j) {
                 pe[j].a = make_uint4(0u, 0u, 0u, 0u);
                 pe[j].b = make_uint4(0u, 0u, 0u, 0u);
-                if ((uint32_t)j < nb && !(av[j].x & 0x80000000u)) pe[j] = lnLoadEntry(T.tab + home[j]); // first probe, speculative
+                slotOf[j] = 0xFFFFFFFFu;
+                how[j] = 0u;
+                if ((uint32_t)j < nb && !(av[j].x & 0x80000000u))
+                    pe[j] = lnLoadEntry(T.tab + (((av[j].x & 0x7FFFFFFFu) * 0x9E3779B1u) >> C.tabShift));
             }
+            // (3) the reference's sequential logic over the group
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
+            for (int j = 0; j < kLanesG; ++j) {
                 if ((uint32_t)j >= nb || overflow) continue;
                 if (av[j].x & 0x80000000u) continue; // blacklisted neighbours are skipped (:98-99)
                 const uint32_t nbr = av[j].x & 0x7FFFFFFFu;
@@ -295,31 +350,30 @@ __host__ __device__ inline void lanesSearch(const Arc *__restrict__ arcs, const 
                 const double dX = dc + (1.0 - w); // totalCrossDist (:107-108)
                 // label pruning (header of ocw_search.cuh) against the running bestDist
                 const bool creatS = dS + dc <= best, creatX = dX + dc <= best;
-                // ---- label table ----------------------------------------------------------------------------------
-                uint32_t s = home[j];
+                // ---- label table: slots claimed by earlier arcs of this group are not in memory yet ------------------
+                uint32_t s = (nbr * 0x9E3779B1u) >> C.tabShift;
                 LanesEntryRegs e = pe[j];
-                {
-                    bool stale = false; // an earlier arc of this group wrote the slot after the speculative load
-#pragma unroll
-                    for (int jj = 0; jj < 4; ++jj)
-                        if (jj < j && wslot[jj] == s) stale = true;
-                    if (stale) e = lnLoadEntry(T.tab + s);
-                }
                 bool found = false, isNew = false;
                 while (true) {
-                    if (e.b.w != stamp) { // free slot
-                        isNew = creatS || creatX;
-                        break;
-                    }
-                    if (e.b.x == nbr) {
-                        found = true;
-                        break;
+                    bool claimed = false;
+#pragma unroll
+                    for (int jj = 0; jj < kLanesG; ++jj)
+                        if (jj < j && slotOf[jj] == s) claimed = true; // by another vertex (a row holds a vertex once)
+                    if (!claimed) {
+                        if (e.b.w != stamp) { // free slot
+                            isNew = creatS || creatX;
+                            break;
+                        }
+                        if (e.b.x == nbr) {
+                            found = true;
+                            break;
+                        }
                     }
                     s = (s + 1u) & tabMask;
                     e = lnLoadEntry(T.tab + s);
                 }
                 if (!found && !isNew) continue; // no label, and none may be created
-                double dA = kUnlabelled, dB = kUnlabelled;           // label of the side the stay arc reaches / of the other side
+                double dA = kUnlabelled, dB = kUnlabelled;             // label of the side the stay arc reaches / of the other side
                 uint32_t pA = kLanesPackedNone, pB = kLanesPackedNone; // hops | queue position << 16
                 if (found) {
                     const double e0 = lnBitsToDouble(e.a.x, e.a.y), e1 = lnBitsToDouble(e.a.z, e.a.w);
@@ -330,7 +384,7 @@ __host__ __device__ inline void lanesSearch(const Arc *__restrict__ arcs, const 
                 }
                 const bool hadA = dA < kUnlabelled, hadB = dB < kUnlabelled;
                 uint32_t hA = pA & 0xFFFFu, hB = pB & 0xFFFFu;
-                bool anyAcc = false;
+                uint32_t hw = 0u;
 #pragma unroll
                 for (int k = 0; k < 2; ++k) { // updatePaths(stayNeighbor, ...) then updatePaths(crossNeighbor, ...)  (:59-84)
                     const double d = k ? dX : dS;
@@ -343,52 +397,30 @@ __host__ __device__ inline void lanesSearch(const Arc *__restrict__ arcs, const 
                     else
                         acc = (dOld == d) ? (hNew < hOld) : (d < dOld);
                     if (!acc || overflow) continue;
-                    anyAcc = true;
-                    const uint32_t sd = k ? (side ^ 1u) : side;
-                    // a superseded key leaves the queue (its position sits in the label's hop word)
+                    hw |= 1u << k;
+                    // a superseded key leaves the queue (its position sits in the label's hop word): a reduction, no wait
                     const uint32_t oldq = (k ? pB : pA) >> 16;
-                    if (had && oldq < parkBase) T.cnt[oldq / kLanesC] |= 1u << (oldq % kLanesC);
+                    if (had && oldq < parkBase) lnCntOr(T.cnt + oldq / kLanesC, 1u << (oldq % kLanesC));
                     // the new queue entry; only nodes that can still be extracted enter a bucket
-                    uint32_t qpos;
-                    uint4 kv = make_uint4(0u, 0u, 0u, 0u), rv = make_uint4(0u, 0u, cur, 0u);
+                    uint32_t ret;
                     if (2 * d <= best) {
-                        const uint32_t bk = lnBucketOf(d, C.scaleU, C.scaleB, NB - 1u);
-                        const uint32_t cw = T.cnt[bk];
-                        const uint32_t pos = cw >> 16;
-                        if (pos >= kLanesC) {
-                            overflow = true; // a bucket is full
-                            continue;
-                        }
-                        T.cnt[bk] = cw + (1u << 16);
-                        qpos = bk * kLanesC + pos;
-                        const unsigned long long db = lnDoubleBits(d);
-                        kv = make_uint4((uint32_t)db, (uint32_t)(db >> 32), 2u * nbr + sd, hNew);
-                        uint32_t first = av[j].y & ((1u << C.rowShift) - 1u), deg = av[j].y >> C.rowShift;
-                        if (deg == (0xFFFFFFFFu >> C.rowShift)) { // saturated degree field: read the row record
-                            const uint2 ri = rowinfo[nbr];
-                            first = ri.x;
-                            deg = ri.y;
-                        }
-                        rv.x = first;
-                        rv.y = deg;
+                        ret = lnCntAdd(T.cnt + lnBucketOf(d, C.scaleU, C.scaleB, NB - 1u), 1u << 16); // looked at in (4)
+                        hw |= 4u << k;
                     } else {
-                        if (parkN >= C.parkCap) {
+                        ret = parkBase + parkN++;
+                        if (parkN > C.parkCap) {
                             overflow = true;
                             continue;
                         }
-                        qpos = parkBase + parkN++;
                     }
-                    lnStore4(T.q + 2 * (size_t)qpos, kv);
-                    lnStore4(T.q + 2 * (size_t)qpos + 1, rv);
-                    const uint32_t pw = hNew | (qpos << 16);
                     if (k) {
                         dB = d;
                         hB = hNew;
-                        pB = pw;
+                        retB[j] = ret;
                     } else {
                         dA = d;
                         hA = hNew;
-                        pA = pw;
+                        retA[j] = ret;
                     }
                     // record logic (:71-82)
                     const double D = d + dTw;
@@ -406,16 +438,60 @@ __host__ __device__ inline void lanesSearch(const Arc *__restrict__ arcs, const 
                             overflow = true;
                             continue;
                         }
-                        T.hist[histN++] = 2u * nbr + sd;
+                        T.hist[histN++] = 2u * nbr + (k ? (side ^ 1u) : side);
                     }
                 }
-                if (anyAcc) {
+                if (hw) {
                     const unsigned long long a0b = lnDoubleBits(side ? dB : dA), a1b = lnDoubleBits(side ? dA : dB);
-                    lnStore4(reinterpret_cast<uint4 *>(T.tab + s), make_uint4((uint32_t)a0b, (uint32_t)(a0b >> 32), (uint32_t)a1b, (uint32_t)(a1b >> 32)));
-                    lnStore4(reinterpret_cast<uint4 *>(T.tab + s) + 1, make_uint4(nbr, side ? pB : pA, side ? pA : pB, stamp));
-                    wslot[j] = s;
+                    labA[j] = make_uint4((uint32_t)a0b, (uint32_t)(a0b >> 32), (uint32_t)a1b, (uint32_t)(a1b >> 32));
+                    hopA[j] = (hw & 1u) ? hNew : pA; // an untouched side keeps its word (hops and queue position)
+                    hopB[j] = (hw & 2u) ? hNew : pB;
+                    how[j] = hw;
+                    slotOf[j] = s;
                     if (isNew) touchedN++;
                 }
+            }
+            // (4) the appends have answered: queue entries and labels
+#pragma unroll
+            for (int j = 0; j < kLanesG; ++j) {
+                if (slotOf[j] == 0xFFFFFFFFu) continue;
+                const uint32_t nbr = av[j].x & 0x7FFFFFFFu;
+                uint32_t first = av[j].y & ((1u << C.rowShift) - 1u), deg = av[j].y >> C.rowShift;
+                if ((how[j] & 12u) && deg == (0xFFFFFFFFu >> C.rowShift)) { // saturated degree field: read the row record
+                    const uint2 ri = rowinfo[nbr];
+                    first = ri.x;
+                    deg = ri.y;
+                }
+#pragma unroll
+                for (int k = 0; k < 2; ++k) {
+                    if (!((how[j] >> k) & 1u)) continue;
+                    const uint32_t sd = k ? (side ^ 1u) : side;
+                    // the distance just stored for this side
+                    const uint32_t dlo = (sd ? labA[j].z : labA[j].x), dhi = (sd ? labA[j].w : labA[j].y);
+                    const uint32_t ret = k ? retB[j] : retA[j];
+                    uint32_t qpos = ret; // parked
+                    uint4 kv = make_uint4(0u, 0u, 0u, 0u), rv = make_uint4(0u, 0u, cur, 0u);
+                    if ((how[j] >> (2 + k)) & 1u) {
+                        const uint32_t pos = ret >> 16;
+                        if (pos >= kLanesC) {
+                            overflow = true; // the bucket is full
+                            continue;
+                        }
+                        const uint32_t bk = lnBucketOf(lnBitsToDouble(dlo, dhi), C.scaleU, C.scaleB, NB - 1u);
+                        qpos = bk * kLanesC + pos;
+                        kv = make_uint4(dlo, dhi, 2u * nbr + sd, hNew);
+                        rv.x = first;
+                        rv.y = deg;
+                    }
+                    lnStore4(T.q + 2 * (size_t)qpos, kv);
+                    lnStore4(T.q + 2 * (size_t)qpos + 1, rv);
+                    if (k)
+                        hopB[j] = hNew | (qpos << 16);
+                    else
+                        hopA[j] = hNew | (qpos << 16);
+                }
+                lnStore4(reinterpret_cast<uint4 *>(T.tab + slotOf[j]), labA[j]);
+                lnStore4(reinterpret_cast<uint4 *>(T.tab + slotOf[j]) + 1, make_uint4(nbr, side ? hopB[j] : hopA[j], side ? hopA[j] : hopB[j], stamp));
             }
         }
     }

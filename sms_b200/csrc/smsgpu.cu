@@ -755,6 +755,16 @@ int smsgpu_create(smsgpu_ctx **out, int64_t n, int64_t m, const int64_t *rowptr,
             }
         }
     }
+    // L2 fetch granularity (a device-wide hint, default 64 B): the searches read isolated 32-byte sectors
+    if (const char *eg = std::getenv("SMSGPU_L2_FETCH")) {
+        const int g = std::atoi(eg);
+        if (g == 32 || g == 64 || g == 128) {
+            if (cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)g) != cudaSuccess) (void)cudaGetLastError();
+            size_t got = 0;
+            if (cudaDeviceGetLimit(&got, cudaLimitMaxL2FetchGranularity) != cudaSuccess) (void)cudaGetLastError();
+            if (std::getenv("SMSGPU_DEBUG_OVF")) std::fprintf(stderr, "[smsgpu] L2 fetch granularity: asked %d, now %zu\n", g, got);
+        }
+    }
     if (const char *el = std::getenv("SMSGPU_LANES")) ctx->lanesMode = el[0] == '1' ? 1 : (el[0] == '2' ? 2 : 0);
     if (const char *el = std::getenv("SMSGPU_LANES_MIN")) ctx->lanesMinSources = std::atoll(el);
     if (const char *el = std::getenv("SMSGPU_LANES_TILES")) ctx->lanesMaxTiles = std::max<long long>(128, std::atoll(el));
