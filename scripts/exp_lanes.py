@@ -33,7 +33,7 @@ for setting in a.settings.split(","):
         os.environ.pop("SMSGPU_L2_FETCH", None)
     os.environ["SMSGPU_LANES_NB"] = nb if nb != "0" else "2048"
     os.environ["SMSGPU_LANES_TABLG"] = tablg
-    os.environ["SMSGPU_LANES_PARK"] = park if park != "0" else "8192"
+    os.environ["SMSGPU_LANES_QCAP"] = park if park != "0" else "8192"
     os.environ["SMSGPU_LANES"] = lanes
     os.environ["SMSGPU_LANES_TILES"] = tiles if tiles != "0" else "40960"
     os.environ["SMSGPU_LANES_SETS"] = sets if sets != "0" else "2"
@@ -47,7 +47,7 @@ for setting in a.settings.split(","):
         ctx.fetch()
         wall = time.time() - t1
         st = ctx.stats()
-        print(f"lanes={lanes} tiles={tiles} sets={sets} nb={nb} tablg={tablg} park={park} l2fetch={l2f} round {r}: search {st['ms_search']:.1f} ms tiers {[round(v, 1) for v in st['ms_tier']]} "
+        print(f"lanes={lanes} tiles={tiles} sets={sets} nb={nb} tablg={tablg} qcap={park} l2fetch={l2f} round {r}: search {st['ms_search']:.1f} ms tiers {[round(v, 1) for v in st['ms_tier']]} "
               f"wall {wall * 1e3:.0f} ms tier_sources {st['tier_sources']} cuts {st['unique_cuts']} arcs {st['arcs_scanned']} "
               f"settled {st['settled']} mirrored {st['mirrored_sources']}", flush=True)
     ctx.close()

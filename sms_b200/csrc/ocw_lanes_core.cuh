@@ -9,18 +9,19 @@
 // per source needs no cross-lane instruction at all, puts 32 independent searches behind every memory instruction, and
 // tens of thousands in flight; the round then is bound by DRAM sectors.
 //
-// Working memory of one search (a "tile", thread private, in HBM; bytes: lanesTileBytes):
+// Working memory of one search (a "tile", thread private, in HBM; bytes: lanesTileBytes -- what limits the searches in
+// flight is memory CAPACITY, so the tile is compact):
 //   tab   Entry[tabCap]        label table, open addressing; a slot is occupied iff its `flags` word carries the stamp of
-//                              the search (nothing is cleared between searches); hop words = hops | queue position << 16
-//   q     32 B x (NB * 16 + park)  queue entries {dist, id, hops | first arc, degree, PREDECESSOR, -}: written once with
-//                              two 16-byte stores (a full sector: no read-modify-write in the memory system), never
-//                              moved, never overwritten -- the entry a label points to also holds its predecessor, so
-//                              there is no predecessor array (a 4-byte store into a random sector costs a sector read and
-//                              a sector write).  Labels that may not enter the queue (2 d > bestDist) get a "parked"
-//                              entry behind the buckets, for their predecessor.
-//   cnt   uint32[NB]           per bucket: entries appended << 16 | dead mask (bit i: position i extracted / superseded)
+//                              the search (nothing is cleared between searches);
+//                              hop words = hops (12 bits) | queue entry << 12 (13 bits) | position in its bucket << 25
+//   q     32 B x qCap          queue entries {dist, id, hops | first arc, degree, PREDECESSOR, -}, allocated in push order,
+//                              written once with two 16-byte stores (a full sector: no read-modify-write in the memory
+//                              system), never moved -- the entry a label points to also holds its predecessor, so there is
+//                              no predecessor array.  Labels that may not enter a bucket (2 d > bestDist) get an entry too.
+//   bk    32 B x NB            one sector per bucket: word 0 = entries appended << 16 | dead mask (bit i: position i
+//                              extracted / superseded), then 14 half-words: the queue entries of its positions
 //   hist  uint32[histCap]      intermediateVertices_ in push order
-// This header is the engine's sequential core and compiles for the host as well (tests/cpp/lanes_host.cu runs it on
+// This header is the engine's sequential core and compiles for the host as well (tests/cpp/lanes_host.cpp runs it on
 // the CPU against the oracle); the kernels around it are in ocw_search_lanes.cuh.
 #pragma once
 #include "ocw_types.cuh"
@@ -28,16 +29,18 @@
 
 namespace smsgpu {
 
-constexpr uint32_t kLanesC = 16;               // queue positions per bucket (the dead mask has 16 bits)
-constexpr uint32_t kLanesNoQpos = 0xFFFFu;     // hop word >> 16: the label has no queue entry
+constexpr uint32_t kLanesC = 14;               // queue positions per bucket
+constexpr uint32_t kLanesHopBits = 12, kLanesHopMask = 0xFFFu;
+constexpr uint32_t kLanesQBits = 13, kLanesQMask = 0x1FFFu; // queue entry of a label: (hop word >> 12) & mask
+constexpr uint32_t kLanesNoPos = 15;           // hop word >> 25: the label's entry sits in no bucket
 constexpr uint32_t kLanesPackedNone = 0xFFFFFFFFu;
 
 struct LanesCfg {
     uint32_t tabCap, tabShift;  // label table slots (power of two), 32 - log2(tabCap)
     uint32_t touchedCap;        // labels a search may create
     uint32_t histCap;
-    uint32_t nbuckets;          // NB (multiple of 4); NB * kLanesC + parkCap <= 0xFFFF
-    uint32_t parkCap;
+    uint32_t nbuckets;          // NB (multiple of 4)
+    uint32_t qCap;              // queue entries (<= 8192)
     float scaleU, scaleB;       // bucket map of the pairs engine (ocw_search_pairs.cuh: bucketOf)
     uint32_t rowShift;          // Arc::row = first arc | degree << rowShift
 };
@@ -51,7 +54,7 @@ struct __align__(16) LanesRec {
                         // (dist, hops) tie by id (the twin is not the mirror image); bit 2: the second source is the twin
     double best;
     uint32_t histN, touchedN, arcs, settled;
-    uint32_t stamp, parkN;
+    uint32_t stamp, qN;
     uint32_t pad[4];
 };
 static_assert(sizeof(LanesRec) == 64, "LanesRec is two sectors");
@@ -59,15 +62,15 @@ static_assert(sizeof(LanesRec) == 64, "LanesRec is two sectors");
 struct LanesTile {
     Entry *tab;
     uint4 *q;       // two uint4 per entry
-    uint32_t *cnt;
+    uint4 *bk;      // two uint4 per bucket
     uint32_t *hist;
     LanesRec *rec;
 };
 
 __host__ __device__ inline size_t lanesTileBytes(const LanesCfg &c) {
     size_t b = (size_t)c.tabCap * sizeof(Entry);
-    b += ((size_t)c.nbuckets * kLanesC + c.parkCap) * 32;
-    b += (size_t)c.nbuckets * sizeof(uint32_t);
+    b += (size_t)c.qCap * 32;
+    b += (size_t)c.nbuckets * 32;
     b += (size_t)c.histCap * sizeof(uint32_t);
     b = (b + 31) & ~(size_t)31;
     b += sizeof(LanesRec);
@@ -79,9 +82,9 @@ __host__ __device__ inline LanesTile lanesCarve(unsigned char *base, const Lanes
     T.tab = reinterpret_cast<Entry *>(p);
     p += (size_t)c.tabCap * sizeof(Entry);
     T.q = reinterpret_cast<uint4 *>(p);
-    p += ((size_t)c.nbuckets * kLanesC + c.parkCap) * 32;
-    T.cnt = reinterpret_cast<uint32_t *>(p);
-    p += (size_t)c.nbuckets * sizeof(uint32_t);
+    p += (size_t)c.qCap * 32;
+    T.bk = reinterpret_cast<uint4 *>(p);
+    p += (size_t)c.nbuckets * 32;
     T.hist = reinterpret_cast<uint32_t *>(p);
     p += (size_t)c.histCap * sizeof(uint32_t);
     p = base + (((size_t)(p - base) + 31) & ~(size_t)31);
@@ -168,12 +171,26 @@ __host__ __device__ __forceinline__ LanesEntryRegs lnLoadEntry(const Entry *p) {
     e.b = lnLoad4(reinterpret_cast<const uint4 *>(p) + 1);
     return e;
 }
-// The bucket words are read and updated at L2 only (ld.cg / atomics): an atomic does not update a line in L1.
-__host__ __device__ __forceinline__ uint4 lnLoadCnt4(const uint32_t *p) {
+// The bucket sectors are read and updated at L2 only (ld.cg / st.cg / atomics): an atomic does not update a line in L1.
+__host__ __device__ __forceinline__ uint4 lnLoadBk(const uint4 *p) {
 #ifdef __CUDA_ARCH__
-    return __ldcg(reinterpret_cast<const uint4 *>(p));
+    return __ldcg(p);
 #else
-    return *reinterpret_cast<const uint4 *>(p);
+    return *p;
+#endif
+}
+__host__ __device__ __forceinline__ void lnStoreBk(uint4 *p, const uint4 v) {
+#ifdef __CUDA_ARCH__
+    __stcg(p, v);
+#else
+    *p = v;
+#endif
+}
+__host__ __device__ __forceinline__ void lnStoreBkHalf(unsigned short *p, const unsigned short v) {
+#ifdef __CUDA_ARCH__
+    __stcg(p, v);
+#else
+    *p = v;
 #endif
 }
 __host__ __device__ __forceinline__ uint32_t lnCntAdd(uint32_t *p, const uint32_t v) { // returns the old word
@@ -199,24 +216,24 @@ __host__ __device__ __forceinline__ void lnCntOr(uint32_t *p, const uint32_t v) 
 constexpr int kLanesG = SMSGPU_LANES_GROUP; // arcs per group: their loads, probes and queue-position atomics travel together
 
 // The search of one source.  `srow` = {first arc, degree} of the source's vertex.  Fills `rec` (src, flags bits 0-1,
-// best, histN, touchedN, arcs, settled, stamp, parkN); srcIdx / twinIdx / flag bit 2 belong to the caller.
+// best, histN, touchedN, arcs, settled, stamp, qN); srcIdx / twinIdx / flag bit 2 belong to the caller.
 //
 // A thread is a chain of dependent memory round trips, so the arcs of a settled node are handled in GROUPS of kLanesG:
 //   (1) the group's arc records, one round trip; (2) the label entries at their home slots, one round trip (further probes
 //   of a collision chain on demand); (3) the reference's sequential logic over the group, in registers: accept tests, running
-//   bestDist / history (:59-84), and for every accepted label the ISSUE of the atomic that appends to its bucket (its result
-//   is not looked at yet) and of the reduction that kills a superseded key; (4) one wait for the atomics, then the stores of
-//   the queue entries and labels.
+//   bestDist / history (:59-84), and for every accepted label its queue entry (stored at once: its place is the push
+//   counter), the ISSUE of the atomic that appends it to its bucket (the result is not looked at yet) and of the reduction
+//   that kills a superseded key; (4) one wait for the atomics, then the bucket's index half-words and the labels.
 __host__ __device__ inline void lanesSearch(const Arc *__restrict__ arcs, const uint2 *__restrict__ rowinfo, const LanesCfg &C,
                                             const LanesTile &T, const uint32_t src, const uint2 srow, const uint32_t stamp,
                                             const double bestInit, LanesRec &rec) {
-    const uint32_t NB = C.nbuckets, tabMask = C.tabCap - 1u, parkBase = NB * kLanesC;
-    // ---- reset the bucket words, label and enqueue the source (:54-57) ---------------------------------------------
+    const uint32_t NB = C.nbuckets, tabMask = C.tabCap - 1u;
+    // ---- reset the bucket sectors, label and enqueue the source (:54-57) -------------------------------------------
     {
-        uint4 *c4 = reinterpret_cast<uint4 *>(T.cnt);
         const uint4 z = make_uint4(0u, 0u, 0u, 0u);
-        for (uint32_t i = 1; i < (NB >> 2); ++i) lnStore4(c4 + i, z);
-        lnStore4(c4, make_uint4(1u << 16, 0u, 0u, 0u)); // bucket 0: one entry appended
+        for (uint32_t i = 2; i < 2 * NB; ++i) lnStoreBk(T.bk + i, z);
+        lnStoreBk(T.bk, make_uint4(1u << 16, 0u, 0u, 0u)); // bucket 0: one entry appended, position 0 = queue entry 0
+        lnStoreBk(T.bk + 1, z);
         const uint32_t s = ((src >> 1) * 0x9E3779B1u) >> C.tabShift;
         const unsigned long long un = lnDoubleBits(kUnlabelled);
         uint4 a = make_uint4((uint32_t)un, (uint32_t)(un >> 32), (uint32_t)un, (uint32_t)(un >> 32));
@@ -224,7 +241,7 @@ __host__ __device__ inline void lanesSearch(const Arc *__restrict__ arcs, const 
         if (src & 1u) {
             a.z = 0u;
             a.w = 0u;
-            b.z = 0u; // 0 hops, queue position 0
+            b.z = 0u; // 0 hops, queue entry 0, position 0
         } else {
             a.x = 0u;
             a.y = 0u;
@@ -237,24 +254,38 @@ __host__ __device__ inline void lanesSearch(const Arc *__restrict__ arcs, const 
     }
     double best = bestInit;
     uint32_t bestHop = 0; // bestHopDist: a double in the reference (:52) that only ever holds small integers
-    uint32_t histN = 0, touchedN = 1, arcsN = 0, settledN = 0, parkN = 0;
+    uint32_t histN = 0, touchedN = 1, arcsN = 0, settledN = 0, qN = 1;
     bool overflow = false, tie = false;
     uint32_t lo = 0; // bucket of the last extraction: keys never decrease
 
     while (!overflow) {
-        // ---- first bucket at or after `lo` with a live key: eight bucket words (one sector) per round trip -----------
-        uint32_t b = NB, word = 0, live = 0, app = 0;
-        for (uint32_t b0 = lo & ~7u; b0 < NB && b >= NB; b0 += 8) {
-            const uint4 w0 = lnLoadCnt4(T.cnt + b0), w1 = lnLoadCnt4(T.cnt + b0 + 4);
-            const uint32_t ws[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+        // ---- first bucket at or after `lo` with a live key: four bucket sectors per round trip ------------------------
+        uint32_t b = NB, live = 0;
+        uint32_t ix[7] = {0, 0, 0, 0, 0, 0, 0}; // its 14 index half-words
+        for (uint32_t b0 = lo; b0 < NB && b >= NB; b0 += 4) {
+            uint4 ra[4], rb[4];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const uint32_t ap = ws[j] >> 16, lv = ((1u << ap) - 1u) & ~ws[j];
-                if (b >= NB && b0 + j >= lo && lv) {
+            for (int j = 0; j < 4; ++j) {
+                ra[j] = make_uint4(0u, 0u, 0u, 0u);
+                rb[j] = make_uint4(0u, 0u, 0u, 0u);
+                if (b0 + j < NB) {
+                    ra[j] = lnLoadBk(T.bk + 2 * (size_t)(b0 + j));
+                    rb[j] = lnLoadBk(T.bk + 2 * (size_t)(b0 + j) + 1);
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint32_t ap = ra[j].x >> 16, lv = ((1u << ap) - 1u) & ~ra[j].x;
+                if (b >= NB && lv) {
                     b = b0 + j;
-                    word = ws[j];
-                    app = ap;
                     live = lv;
+                    ix[0] = ra[j].y;
+                    ix[1] = ra[j].z;
+                    ix[2] = ra[j].w;
+                    ix[3] = rb[j].x;
+                    ix[4] = rb[j].y;
+                    ix[5] = rb[j].z;
+                    ix[6] = rb[j].w;
                 }
             }
         }
@@ -263,22 +294,23 @@ __host__ __device__ inline void lanesSearch(const Arc *__restrict__ arcs, const 
         unsigned long long mhi = ~0ull, mlo = ~0ull;
         uint32_t mpos = 0, mfirst = 0, mdeg = 0;
         bool mtie = false;
-        const uint4 *qb = T.q + 2 * (size_t)(b * kLanesC);
-        for (uint32_t p0 = 0; p0 < app; p0 += 4) {
+#pragma unroll
+        for (int p0 = 0; p0 < 16; p0 += 4) {
             if (!((live >> p0) & 0xFu)) continue;
             uint4 k[4], r[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
                 k[j] = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
                 r[j] = make_uint4(0u, 0u, 0u, 0u);
-                if ((live >> (p0 + j)) & 1u) {
-                    k[j] = lnLoad4(qb + 2 * (p0 + j));
-                    r[j] = lnLoad4(qb + 2 * (p0 + j) + 1);
+                if (p0 + j < (int)kLanesC && ((live >> (p0 + j)) & 1u)) {
+                    const uint32_t n = (ix[(p0 + j) >> 1] >> (((p0 + j) & 1) * 16)) & 0xFFFFu;
+                    k[j] = lnLoad4(T.q + 2 * (size_t)n);
+                    r[j] = lnLoad4(T.q + 2 * (size_t)n + 1);
                 }
             }
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-                if (!((live >> (p0 + j)) & 1u)) continue;
+                if (p0 + j >= (int)kLanesC || !((live >> (p0 + j)) & 1u)) continue;
                 const unsigned long long hi = ((unsigned long long)k[j].y << 32) | k[j].x;
                 const unsigned long long lw = ((unsigned long long)k[j].w << 32) | k[j].z; // hops << 32 | id
                 if (hi == mhi && (uint32_t)(lw >> 32) == (uint32_t)(mlo >> 32)) mtie = true; // equal (dist, hops): the id decides
@@ -286,7 +318,7 @@ __host__ __device__ inline void lanesSearch(const Arc *__restrict__ arcs, const 
                     if (hi != mhi || (uint32_t)(lw >> 32) != (uint32_t)(mlo >> 32)) mtie = false;
                     mhi = hi;
                     mlo = lw;
-                    mpos = p0 + j;
+                    mpos = (uint32_t)(p0 + j);
                     mfirst = r[j].x;
                     mdeg = r[j].y;
                 }
@@ -297,12 +329,11 @@ __host__ __device__ inline void lanesSearch(const Arc *__restrict__ arcs, const 
         const double dc = lnBitsToDouble((uint32_t)mhi, (uint32_t)(mhi >> 32));
         // loop condition of ocw_seperator.cpp:88-90
         if (cur == (src ^ 1u) || 2 * dc > best) break;
-        lnCntOr(T.cnt + b, 1u << mpos); // extract_top: the position is dead from now on
-        (void)word;
+        lnCntOr(reinterpret_cast<uint32_t *>(T.bk + 2 * (size_t)b), 1u << mpos); // extract_top: the position is dead from now on
         settledN++;
         lo = b;
         const uint32_t side = cur & 1u, hNew = hc + 1u;
-        if (hNew >= 0xFFFFu) { // hops share a word with the queue position
+        if (hNew >= kLanesHopMask) { // hops share a word with the queue entry
             overflow = true;
             break;
         }
@@ -315,9 +346,10 @@ __host__ __device__ inline void lanesSearch(const Arc *__restrict__ arcs, const 
             // what phase (4) needs of every arc
             uint32_t slotOf[kLanesG];  // its label's slot, 0xFFFFFFFF: nothing to store
             uint4 labA[kLanesG];       // the new distances {d0, d1} as stored
-            uint32_t hopA[kLanesG], hopB[kLanesG]; // new hop words of the stay side / the other side (queue position pending)
-            uint32_t retA[kLanesG], retB[kLanesG]; // old bucket word returned by the append (admitted), or the parked position
-            uint32_t how[kLanesG];     // bit 0 / 1: stay / cross side accepted; bit 2 / 3: admitted to a bucket (else parked)
+            uint32_t hopA[kLanesG], hopB[kLanesG]; // new hop words of the stay side / the other side (bucket position pending)
+            uint32_t retA[kLanesG], retB[kLanesG]; // old bucket word returned by the append
+            uint32_t bkA[kLanesG], bkB[kLanesG];   // the bucket appended to
+            uint32_t how[kLanesG];     // bit 0 / 1: stay / cross side accepted; bit 2 / 3: appended to a bucket
             // (1) the arc records
 #pragma unroll
             for (int j = 0; j < kLanesG; ++j) {
@@ -374,7 +406,7 @@ __host__ __device__ inline void lanesSearch(const Arc *__restrict__ arcs, const 
                 }
                 if (!found && !isNew) continue; // no label, and none may be created
                 double dA = kUnlabelled, dB = kUnlabelled;             // label of the side the stay arc reaches / of the other side
-                uint32_t pA = kLanesPackedNone, pB = kLanesPackedNone; // hops | queue position << 16
+                uint32_t pA = kLanesPackedNone, pB = kLanesPackedNone; // hop words
                 if (found) {
                     const double e0 = lnBitsToDouble(e.a.x, e.a.y), e1 = lnBitsToDouble(e.a.z, e.a.w);
                     dA = side ? e1 : e0;
@@ -383,8 +415,10 @@ __host__ __device__ inline void lanesSearch(const Arc *__restrict__ arcs, const 
                     pB = side ? e.b.y : e.b.z;
                 }
                 const bool hadA = dA < kUnlabelled, hadB = dB < kUnlabelled;
-                uint32_t hA = pA & 0xFFFFu, hB = pB & 0xFFFFu;
+                uint32_t hA = pA & kLanesHopMask, hB = pB & kLanesHopMask;
                 uint32_t hw = 0u;
+                // the row of the neighbour, for its queue entries
+                uint32_t first = av[j].y & ((1u << C.rowShift) - 1u), deg = av[j].y >> C.rowShift;
 #pragma unroll
                 for (int k = 0; k < 2; ++k) { // updatePaths(stayNeighbor, ...) then updatePaths(crossNeighbor, ...)  (:59-84)
                     const double d = k ? dX : dS;
@@ -397,30 +431,45 @@ __host__ __device__ inline void lanesSearch(const Arc *__restrict__ arcs, const 
                     else
                         acc = (dOld == d) ? (hNew < hOld) : (d < dOld);
                     if (!acc || overflow) continue;
-                    hw |= 1u << k;
-                    // a superseded key leaves the queue (its position sits in the label's hop word): a reduction, no wait
-                    const uint32_t oldq = (k ? pB : pA) >> 16;
-                    if (had && oldq < parkBase) lnCntOr(T.cnt + oldq / kLanesC, 1u << (oldq % kLanesC));
-                    // the new queue entry; only nodes that can still be extracted enter a bucket
-                    uint32_t ret;
-                    if (2 * d <= best) {
-                        ret = lnCntAdd(T.cnt + lnBucketOf(d, C.scaleU, C.scaleB, NB - 1u), 1u << 16); // looked at in (4)
-                        hw |= 4u << k;
-                    } else {
-                        ret = parkBase + parkN++;
-                        if (parkN > C.parkCap) {
-                            overflow = true;
-                            continue;
-                        }
+                    if (qN >= C.qCap) {
+                        overflow = true;
+                        continue;
                     }
+                    hw |= 1u << k;
+                    const uint32_t sd = k ? (side ^ 1u) : side;
+                    // a superseded key leaves the queue (bucket from its distance, position from the hop word): a reduction, no wait
+                    const uint32_t oldPos = (k ? pB : pA) >> 25;
+                    if (had && oldPos < kLanesC)
+                        lnCntOr(reinterpret_cast<uint32_t *>(T.bk + 2 * (size_t)lnBucketOf(dOld, C.scaleU, C.scaleB, NB - 1u)), 1u << oldPos);
+                    // the new queue entry; only nodes that can still be extracted are appended to a bucket
+                    const uint32_t n = qN++;
+                    const unsigned long long db = lnDoubleBits(d);
+                    uint32_t ret = 0, bkt = 0;
+                    if (2 * d <= best) {
+                        if (deg == (0xFFFFFFFFu >> C.rowShift)) { // saturated degree field: read the row record
+                            const uint2 ri = rowinfo[nbr];
+                            first = ri.x;
+                            deg = ri.y;
+                        }
+                        bkt = lnBucketOf(d, C.scaleU, C.scaleB, NB - 1u);
+                        ret = lnCntAdd(reinterpret_cast<uint32_t *>(T.bk + 2 * (size_t)bkt), 1u << 16); // looked at in (4)
+                        hw |= 4u << k;
+                    }
+                    lnStore4(T.q + 2 * (size_t)n, make_uint4((uint32_t)db, (uint32_t)(db >> 32), 2u * nbr + sd, hNew));
+                    lnStore4(T.q + 2 * (size_t)n + 1, make_uint4(first, deg, cur, 0u));
+                    const uint32_t pw = hNew | (n << kLanesHopBits) | (kLanesNoPos << 25);
                     if (k) {
                         dB = d;
                         hB = hNew;
+                        pB = pw;
                         retB[j] = ret;
+                        bkB[j] = bkt;
                     } else {
                         dA = d;
                         hA = hNew;
+                        pA = pw;
                         retA[j] = ret;
+                        bkA[j] = bkt;
                     }
                     // record logic (:71-82)
                     const double D = d + dTw;
@@ -438,60 +487,43 @@ __host__ __device__ inline void lanesSearch(const Arc *__restrict__ arcs, const 
                             overflow = true;
                             continue;
                         }
-                        T.hist[histN++] = 2u * nbr + (k ? (side ^ 1u) : side);
+                        T.hist[histN++] = 2u * nbr + sd;
                     }
                 }
                 if (hw) {
                     const unsigned long long a0b = lnDoubleBits(side ? dB : dA), a1b = lnDoubleBits(side ? dA : dB);
                     labA[j] = make_uint4((uint32_t)a0b, (uint32_t)(a0b >> 32), (uint32_t)a1b, (uint32_t)(a1b >> 32));
-                    hopA[j] = (hw & 1u) ? hNew : pA; // an untouched side keeps its word (hops and queue position)
-                    hopB[j] = (hw & 2u) ? hNew : pB;
+                    hopA[j] = pA;
+                    hopB[j] = pB;
                     how[j] = hw;
                     slotOf[j] = s;
                     if (isNew) touchedN++;
                 }
             }
-            // (4) the appends have answered: queue entries and labels
+            // (4) the appends have answered: index half-words of the buckets, labels
 #pragma unroll
             for (int j = 0; j < kLanesG; ++j) {
                 if (slotOf[j] == 0xFFFFFFFFu) continue;
-                const uint32_t nbr = av[j].x & 0x7FFFFFFFu;
-                uint32_t first = av[j].y & ((1u << C.rowShift) - 1u), deg = av[j].y >> C.rowShift;
-                if ((how[j] & 12u) && deg == (0xFFFFFFFFu >> C.rowShift)) { // saturated degree field: read the row record
-                    const uint2 ri = rowinfo[nbr];
-                    first = ri.x;
-                    deg = ri.y;
-                }
 #pragma unroll
                 for (int k = 0; k < 2; ++k) {
-                    if (!((how[j] >> k) & 1u)) continue;
-                    const uint32_t sd = k ? (side ^ 1u) : side;
-                    // the distance just stored for this side
-                    const uint32_t dlo = (sd ? labA[j].z : labA[j].x), dhi = (sd ? labA[j].w : labA[j].y);
-                    const uint32_t ret = k ? retB[j] : retA[j];
-                    uint32_t qpos = ret; // parked
-                    uint4 kv = make_uint4(0u, 0u, 0u, 0u), rv = make_uint4(0u, 0u, cur, 0u);
-                    if ((how[j] >> (2 + k)) & 1u) {
-                        const uint32_t pos = ret >> 16;
-                        if (pos >= kLanesC) {
-                            overflow = true; // the bucket is full
-                            continue;
-                        }
-                        const uint32_t bk = lnBucketOf(lnBitsToDouble(dlo, dhi), C.scaleU, C.scaleB, NB - 1u);
-                        qpos = bk * kLanesC + pos;
-                        kv = make_uint4(dlo, dhi, 2u * nbr + sd, hNew);
-                        rv.x = first;
-                        rv.y = deg;
+                    if (!((how[j] >> (2 + k)) & 1u)) continue;
+                    const uint32_t pos = (k ? retB[j] : retA[j]) >> 16;
+                    if (pos >= kLanesC) {
+                        overflow = true; // the bucket is full
+                        continue;
                     }
-                    lnStore4(T.q + 2 * (size_t)qpos, kv);
-                    lnStore4(T.q + 2 * (size_t)qpos + 1, rv);
+                    const uint32_t pw = k ? hopB[j] : hopA[j];
+                    lnStoreBkHalf(reinterpret_cast<unsigned short *>(T.bk + 2 * (size_t)(k ? bkB[j] : bkA[j])) + 2 + pos,
+                                  (unsigned short)((pw >> kLanesHopBits) & kLanesQMask));
+                    const uint32_t nw = (pw & ~(15u << 25)) | (pos << 25);
                     if (k)
-                        hopB[j] = hNew | (qpos << 16);
+                        hopB[j] = nw;
                     else
-                        hopA[j] = hNew | (qpos << 16);
+                        hopA[j] = nw;
                 }
                 lnStore4(reinterpret_cast<uint4 *>(T.tab + slotOf[j]), labA[j]);
-                lnStore4(reinterpret_cast<uint4 *>(T.tab + slotOf[j]) + 1, make_uint4(nbr, side ? hopB[j] : hopA[j], side ? hopA[j] : hopB[j], stamp));
+                lnStore4(reinterpret_cast<uint4 *>(T.tab + slotOf[j]) + 1,
+                         make_uint4(av[j].x & 0x7FFFFFFFu, side ? hopB[j] : hopA[j], side ? hopA[j] : hopB[j], stamp));
             }
         }
     }
@@ -503,7 +535,7 @@ __host__ __device__ inline void lanesSearch(const Arc *__restrict__ arcs, const 
     rec.arcs = arcsN;
     rec.settled = settledN;
     rec.stamp = stamp;
-    rec.parkN = parkN;
+    rec.qN = qN;
 }
 
 } // namespace smsgpu

@@ -88,6 +88,7 @@ struct TileMem {
     // predecessor of a label sits in the queue entry its hop word points to
     uint32_t stamp;
     const uint4 *lq;
+    uint32_t lqShift, lqMask; // queue entry of a label: (hop word >> lqShift) & lqMask
 };
 
 __device__ inline void carveTileMem(TileMem &M, unsigned char *base, const TileCaps &c, unsigned char *hot = nullptr) {
@@ -98,6 +99,8 @@ __device__ inline void carveTileMem(TileMem &M, unsigned char *base, const TileC
     M.qrow = nullptr;
     M.stamp = 0;
     M.lq = nullptr;
+    M.lqShift = 0;
+    M.lqMask = 0;
     M.hopMask = c.pairs ? 0xFFFFu : 0xFFFFFFFFu;
     if (c.nbuckets) {
         M.cl = reinterpret_cast<uint32_t *>(hot);
@@ -226,9 +229,9 @@ __device__ __forceinline__ bool keyLess(unsigned long long ahi, unsigned long lo
 }
 
 __device__ __forceinline__ uint32_t predOf(const TileMem &M, int slot, uint32_t side) {
-    if (M.lq) { // lanes engine: hop word = hops | queue position << 16; the entry there holds the predecessor
+    if (M.lq) { // lanes engine: the hop word names the label's queue entry, which holds the predecessor
         const uint32_t hw = side ? M.tab[slot].h1 : M.tab[slot].h0;
-        return M.lq[2 * (size_t)(hw >> 16) + 1].z;
+        return M.lq[2 * (size_t)((hw >> M.lqShift) & M.lqMask) + 1].z;
     }
     return M.pq ? M.pq[2 * slot + side].x : M.pred[2 * slot + side];
 }

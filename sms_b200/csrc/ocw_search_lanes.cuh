@@ -36,8 +36,11 @@ struct LanesArgs {
 #ifndef SMSGPU_LANES_BLOCK
 #define SMSGPU_LANES_BLOCK 64
 #endif
+#ifndef SMSGPU_LANES_MINB // resident CTAs per SM the search kernel is compiled for (caps its registers)
+#define SMSGPU_LANES_MINB 1
+#endif
 
-__global__ void __launch_bounds__(SMSGPU_LANES_BLOCK) ocwLanesSearchKernel(const GraphDev G, const SearchParams P, const LanesArgs A) {
+__global__ void __launch_bounds__(SMSGPU_LANES_BLOCK, SMSGPU_LANES_MINB) ocwLanesSearchKernel(const GraphDev G, const SearchParams P, const LanesArgs A) {
     const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= A.count) return;
     if (A.debugFence) __threadfence();
@@ -50,7 +53,7 @@ __global__ void __launch_bounds__(SMSGPU_LANES_BLOCK) ocwLanesSearchKernel(const
     rec.flags = 0;
     rec.src = 0;
     rec.best = 0.0;
-    rec.histN = rec.touchedN = rec.arcs = rec.settled = rec.stamp = rec.parkN = 0;
+    rec.histN = rec.touchedN = rec.arcs = rec.settled = rec.stamp = rec.qN = 0;
     rec.pad[0] = rec.pad[1] = rec.pad[2] = rec.pad[3] = 0;
     // the entries of the item that are to be searched (same rules as the pairs engine's fetch)
     int32_t idx[2] = {-1, -1};
@@ -110,9 +113,11 @@ __global__ void __launch_bounds__(128) ocwLanesFinishKernel(const LanesArgs A) {
         M.hist = T.hist;
         M.pred = nullptr;
         M.touched = nullptr;
-        M.hopMask = 0xFFFFu;
+        M.hopMask = kLanesHopMask;
         M.stamp = rec.stamp;
         M.lq = T.q;
+        M.lqShift = kLanesHopBits;
+        M.lqMask = kLanesQMask;
         const int overflow = (int)(rec.flags & 1u);
         const bool isTwin = (rec.flags & 4u) != 0;
         const int mirrorOk = (isTwin && !(rec.flags & 2u)) ? 1 : 0;

@@ -136,7 +136,7 @@ struct smsgpu_ctx {
     long long lanesMaxTiles = 40960;      // SMSGPU_LANES_TILES: tiles (searches in flight) over all sets
     int lanesSetsWanted = 2;              // SMSGPU_LANES_SETS: tile sets = streams that alternate batches
     int lanesSets = 0;
-    int lanesTabLg = 0, lanesBuckets = SMSGPU_PAIRS_BUCKETS, lanesPark = 8192; // SMSGPU_LANES_TABLG / _NB / _PARK
+    int lanesTabLg = 0, lanesBuckets = SMSGPU_PAIRS_BUCKETS, lanesQCap = 8192; // SMSGPU_LANES_TABLG / _NB / _QCAP
     long long lanesTilesPerSet = 0, lanesAllocWant = 0;
     LanesCfg lanesCfg{};
     TileCaps lanesFcaps{};
@@ -455,7 +455,7 @@ int ensureLanes(smsgpu_ctx *ctx, long long items) {
     }
     C.histCap = pc.histCap;
     C.nbuckets = (uint32_t)ctx->lanesBuckets;
-    C.parkCap = std::min<uint32_t>((uint32_t)ctx->lanesPark, 0xFFFFu - C.nbuckets * kLanesC - 1u);
+    C.qCap = (uint32_t)ctx->lanesQCap;
     C.scaleU = ctx->pairsScaleU;
     C.scaleB = ctx->pairsScaleB * ((float)ctx->lanesBuckets / (float)SMSGPU_PAIRS_BUCKETS); // the pairs engine's map over this engine's buckets
     C.rowShift = ctx->rowShift;
@@ -770,7 +770,7 @@ int smsgpu_create(smsgpu_ctx **out, int64_t n, int64_t m, const int64_t *rowptr,
     if (const char *el = std::getenv("SMSGPU_LANES_TILES")) ctx->lanesMaxTiles = std::max<long long>(128, std::atoll(el));
     if (const char *el = std::getenv("SMSGPU_LANES_TABLG")) ctx->lanesTabLg = std::atoi(el) > 0 ? std::max(6, std::min(20, std::atoi(el))) : 0;
     if (const char *el = std::getenv("SMSGPU_LANES_NB")) ctx->lanesBuckets = std::max(64, std::min(2048, std::atoi(el) & ~3));
-    if (const char *el = std::getenv("SMSGPU_LANES_PARK")) ctx->lanesPark = std::max(16, std::min(16384, std::atoi(el)));
+    if (const char *el = std::getenv("SMSGPU_LANES_QCAP")) ctx->lanesQCap = std::max(64, std::min(8192, std::atoi(el)));
     if (const char *el = std::getenv("SMSGPU_LANES_SETS")) ctx->lanesSetsWanted = std::max(1, std::min(4, std::atoi(el)));
     if (const char *eh = std::getenv("SMSGPU_NO_HISTORY")) ctx->useHistory = !(eh[0] == '1');
     if (const char *eo = std::getenv("SMSGPU_NO_OVERLAP")) ctx->overlapHeavy = !(eo[0] == '1');

@@ -46,7 +46,7 @@ extern "C" int lanes_host_sweep(int64_t n, int64_t m, const int64_t *rowptr, con
     C.touchedCap = std::min<uint32_t>(C.tabCap / 4 * 3, touchedMax);
     C.histCap = 1u << 12;
     C.nbuckets = (uint32_t)nbuckets;
-    C.parkCap = (uint32_t)parkCap;
+    C.qCap = (uint32_t)parkCap; // the queue-entry capacity takes the place of the old parking capacity
     C.rowShift = shift;
     {
         const double half = 0.5 * bestInit, L = 7.0, NBd = (double)nbuckets;
@@ -84,8 +84,8 @@ extern "C" int lanes_host_sweep(int64_t n, int64_t m, const int64_t *rowptr, con
                 const uint32_t hw = sd ? e.h1 : e.h0;
                 labNode[nlab] = (int32_t)(2 * e.key + sd);
                 labDist[nlab] = d;
-                labHops[nlab] = (int32_t)(hw & 0xFFFFu);
-                labPred[nlab] = (int32_t)T.q[2 * (size_t)(hw >> 16) + 1].z;
+                labHops[nlab] = (int32_t)(hw & kLanesHopMask);
+                labPred[nlab] = (int32_t)T.q[2 * (size_t)((hw >> kLanesHopBits) & kLanesQMask) + 1].z;
                 ++nlab;
             }
         }

@@ -29,7 +29,7 @@ def lanes():
     return ctypes.CDLL(LIB)
 
 
-def run_core(lib, inst, x, bl, src, tab_lg=13, nbuckets=2048, park=8192):
+def run_core(lib, inst, x, bl, src, tab_lg=13, nbuckets=2048, park=8192):  # park: queue entries
     nsrc = len(src)
     arcs = np.zeros(nsrc, np.int64)
     settled = np.zeros(nsrc, np.int64)
@@ -104,7 +104,7 @@ def test_lanes_core_small_table_overflows_cleanly(lanes, orc):
     bl = inst.root_blacklist()
     src = inst.handler_sources()[::40]
     exp = orc.sweep(inst, x, blacklist=bl, sources=src, mode="I", want_labels=False, canonical=True)
-    for kw in (dict(tab_lg=6), dict(park=4), dict(nbuckets=64)):
+    for kw in (dict(tab_lg=6), dict(park=64), dict(nbuckets=64)):
         arcs, settled, histn, flags, *_ = run_core(lanes, inst, x, bl, src, **kw)
         done = (flags >= 0) & ((flags & 1) == 0)
         assert (flags[flags >= 0] & 1).any(), kw
