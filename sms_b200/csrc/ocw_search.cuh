@@ -233,6 +233,12 @@ __device__ __forceinline__ uint32_t predOf(const TileMem &M, int slot, uint32_t 
         const uint32_t hw = side ? M.tab[slot].h1 : M.tab[slot].h0;
         return M.lq[2 * (size_t)((hw >> M.lqShift) & M.lqMask) + 1].z;
     }
+#ifndef SMSGPU_PAIRS_PRED_ARRAY
+    if (M.qrow) { // pairs engine: the predecessor sits in the label's queue entry, in the array only when it has none
+        const uint32_t q = (side ? M.tab[slot].h1 : M.tab[slot].h0) >> 16;
+        if (q != 0xFFFFu) return M.qrow[2 * (size_t)q + 1].z;
+    }
+#endif
     return M.pq ? M.pq[2 * slot + side].x : M.pred[2 * slot + side];
 }
 

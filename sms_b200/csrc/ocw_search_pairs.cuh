@@ -402,7 +402,7 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
                     __stcs(&PQP(2 * s + (src & 1u))->x, src);
                     const uint2 srow = Q.rowinfo[src >> 1];
                     __stcs(QP(0), make_uint4(0u, 0u, src, 0u)); // dist 0, id src, 0 hops
-                    __stcs(QP(0) + 1, make_uint4(srow.x, srow.y, 0u, 0u));
+                    __stcs(QP(0) + 1, make_uint4(srow.x, srow.y, src, 0u)); // row, predecessor: itself (never followed)
                     cl[0] = 0x11u; // bucket 0: one appended, one live
                 }
                 st = 1;
@@ -812,14 +812,25 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
                             qpos = bk * C + pos;
                             const unsigned long long dbits = (unsigned long long)__double_as_longlong(d);
                             __stcs(QP(qpos), make_uint4((uint32_t)dbits, (uint32_t)(dbits >> 32), 2 * nbr + sd, hNew));
+#ifdef SMSGPU_PAIRS_PRED_ARRAY
                             __stcs(QP(qpos) + 1, make_uint4(nrow.x, nrow.y, 0u, 0u));
+#else
+                            // the predecessor rides in the queue entry (never overwritten: tombstones touch its first 8 bytes
+                            // only), which is a full-sector store anyway; a 4-byte store into the predecessor array costs the
+                            // memory system a sector read and a sector write
+                            __stcs(QP(qpos) + 1, make_uint4(nrow.x, nrow.y, cur, 0u));
+#endif
                         }
                     }
                     if (k)
                         pB = (hNew & 0xFFFFu) | (qpos << 16);
                     else
                         pA = (hNew & 0xFFFFu) | (qpos << 16);
+#ifdef SMSGPU_PAIRS_PRED_ARRAY
                     __stcs(&PQP(2 * slot + sd)->x, cur); // predecessor
+#else
+                    if (qpos == 0xFFFFu) __stcs(&PQP(2 * slot + sd)->x, cur); // predecessor of a label that has no queue entry
+#endif
                 }
                 Entry e;
                 e.d0 = side ? dB : dA;
