@@ -4,7 +4,8 @@
 //                             both = violatedOddSelectionClosedWalk   (src/graph/odd_closed_walk.cpp:8-65) on a fixed cycle
 //   resolveCycleEidsKernel <- the per-call lpWeightedGraph_.weight(u, v) adjacency scans, done ONCE when the
 //                             list is registered (addTriangle / addFourHole): the scan then gathers x* by edge id.
-// One thread per cycle; K edge ids (12 or 16 B) in, one flag word out; violated cycles are compacted in list order.
+// One thread per four consecutive cycles; K edge ids (12 or 16 B) per cycle in, one code byte out; violated cycles are
+// compacted in list order by the second pass.
 #pragma once
 #include "ocw_types.cuh"
 
@@ -84,23 +85,124 @@ __device__ __forceinline__ unsigned oddSelectionCode(const double (&w)[K], doubl
 //   pass 2  re-reads the code bytes, ranks the violated cycles inside the CTA (list order) and writes their walks.
 constexpr int kSmallBlock = 256, kSmallItems = 4, kSmallTile = kSmallBlock * kSmallItems;
 
+// The same decision without data-dependent branches (the scan's form: 32 cycles per warp take 32 different paths through the
+// reference's loop).  Identical arithmetic in identical order: the reference's early `return {}` at the first prefix with
+// curLength >= 1 equals one test of every prefix (nothing computed after it is used), and its running minimum / maximum with
+// strict comparisons become selects.
 template <int K>
+__device__ __forceinline__ unsigned oddSelectionCodeFlat(const double (&w)[K]) {
+    double cur = 0, lightestCross = 1, heaviestStay = 0;
+    unsigned cross = 0;
+    int li = -1, hi = -1;
+    bool none = false;
+#pragma unroll
+    for (int i = 0; i < K; ++i) {
+        const bool c = w[i] > 0.5;
+        cur += c ? 1 - w[i] : w[i];
+        cross |= (c ? 1u : 0u) << i;
+        const bool lt = c && w[i] < lightestCross, gt = !c && w[i] > heaviestStay;
+        lightestCross = lt ? w[i] : lightestCross;
+        li = lt ? i : li;
+        heaviestStay = gt ? w[i] : heaviestStay;
+        hi = gt ? i : hi;
+        none |= cur >= 1;
+    }
+    const bool even = !(__popc(cross) & 1);
+    const bool fixL = li >= 0 && (cur + 2 * lightestCross - 1 < 1);
+    const bool fixH = hi >= 0 && (cur - 2 * heaviestStay + 1 < 1);
+    const unsigned crossL = cross & ~(1u << (li & 31)), crossH = cross | (1u << (hi & 31));
+    cross = even ? (fixL ? crossL : (fixH ? crossH : cross)) : cross;
+    none |= even && !fixL && !fixH;
+    return none ? 0u : (0x80u | (~cross & ((1u << K) - 1u)));
+}
+
+// K = 3: the running minimum / maximum as a tournament over the three pairwise comparisons -- predicates and 32-bit selects
+// only; the two values are picked once at the end.
+__device__ __forceinline__ unsigned oddSelectionCodeFlat3(const double w0, const double w1, const double w2) {
+    const bool c0 = w0 > 0.5, c1 = w1 > 0.5, c2 = w2 > 0.5;
+    double cur = c0 ? 1 - w0 : w0;
+    bool none = cur >= 1;
+    cur += c1 ? 1 - w1 : w1;
+    none |= cur >= 1;
+    cur += c2 ? 1 - w2 : w2;
+    none |= cur >= 1;
+    const unsigned cross = (c0 ? 1u : 0u) | (c1 ? 2u : 0u) | (c2 ? 4u : 0u);
+    // lightest cross edge: first index attaining the minimum among cross edges below the initial 1 (strict <)
+    const bool l0 = c0 && w0 < 1, l1 = c1 && w1 < 1, l2 = c2 && w2 < 1;
+    int li = l0 ? 0 : -1;
+    li = (l1 && (li < 0 || w1 < w0)) ? 1 : li;
+    li = (l2 && (li < 0 || (li == 1 ? w2 < w1 : w2 < w0))) ? 2 : li;
+    // heaviest stay edge: first index attaining the maximum among stay edges above the initial 0 (strict >)
+    const bool h0 = !c0 && w0 > 0, h1 = !c1 && w1 > 0, h2 = !c2 && w2 > 0;
+    int hi = h0 ? 0 : -1;
+    hi = (h1 && (hi < 0 || w1 > w0)) ? 1 : hi;
+    hi = (h2 && (hi < 0 || (hi == 1 ? w2 > w1 : w2 > w0))) ? 2 : hi;
+    const double lightestCross = li == 0 ? w0 : (li == 1 ? w1 : w2), heaviestStay = hi == 0 ? w0 : (hi == 1 ? w1 : w2);
+    const bool even = !(__popc(cross) & 1);
+    const bool fixL = li >= 0 && (cur + 2 * lightestCross - 1 < 1);
+    const bool fixH = hi >= 0 && (cur - 2 * heaviestStay + 1 < 1);
+    const unsigned crossL = cross & ~(1u << (li & 31)), crossH = cross | (1u << (hi & 31));
+    const unsigned fin = even ? (fixL ? crossL : (fixH ? crossH : cross)) : cross;
+    none |= even && !fixL && !fixH;
+    return none ? 0u : (0x80u | (~fin & 7u));
+}
+template <int K>
+__device__ __forceinline__ unsigned oddSelectionCodeScan(const double (&w)[K]) {
+    if (K == 3) return oddSelectionCodeFlat3(w[0], w[1], w[2]);
+    return oddSelectionCodeFlat<K>(w);
+}
+__global__ void __launch_bounds__(256) clampWeightsKernel(const long long m, const double *__restrict__ x, double *__restrict__ xc) {
+    for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < m; e += (long long)gridDim.x * blockDim.x) xc[e] = clamp01(x[e]);
+}
+
+// One thread scans kSmallItems = 4 CONSECUTIVE cycles: their K * 4 edge ids arrive as K 128-bit loads, the four code bytes
+// leave as one 32-bit store (round 2: 264 -> ~100 instructions per cycle; the kernel is bound by instruction issue, not by
+// DRAM).  Lists whose edge ids / code bytes are not 16 / 4-byte aligned, and the last partial quad, take the scalar path.
+// CLAMPED: x holds clamp01(x*) already (clampWeightsKernel; the context's scan), else the clamp is applied per gather.
+template <int K, bool CLAMPED>
 __global__ void __launch_bounds__(kSmallBlock) smallCycleScanKernel(const long long T, const int32_t *__restrict__ eids,
                                                                     const double *__restrict__ x, uint8_t *__restrict__ code,
                                                                     int32_t *__restrict__ tileCount) {
-    const long long base = (long long)blockIdx.x * kSmallTile;
+    const long long t0 = (long long)blockIdx.x * kSmallTile + (long long)threadIdx.x * kSmallItems;
     int mine = 0;
+    const bool aligned = ((reinterpret_cast<uintptr_t>(eids) & 15u) == 0) && ((reinterpret_cast<uintptr_t>(code) & 3u) == 0);
+    if (aligned && t0 + kSmallItems <= T) {
+        int32_t e[K * kSmallItems];
+        const int4 *src = reinterpret_cast<const int4 *>(eids + K * t0);
 #pragma unroll
-    for (int it = 0; it < kSmallItems; ++it) {
-        const long long t = base + it * kSmallBlock + threadIdx.x;
-        if (t >= T) continue;
-        double w[K];
+        for (int q = 0; q < K; ++q) {
+            const int4 v = src[q];
+            e[4 * q] = v.x;
+            e[4 * q + 1] = v.y;
+            e[4 * q + 2] = v.z;
+            e[4 * q + 3] = v.w;
+        }
+        double wv[K * kSmallItems];
 #pragma unroll
-        for (int i = 0; i < K; ++i) w[i] = clamp01(__ldg(x + eids[K * t + i]));
-        double len;
-        const unsigned c = oddSelectionCode<K>(w, len);
-        code[t] = (uint8_t)c;
-        mine += c ? 1 : 0;
+        for (int i = 0; i < K * kSmallItems; ++i) wv[i] = CLAMPED ? __ldg(x + e[i]) : clamp01(__ldg(x + e[i]));
+        unsigned packed = 0;
+#pragma unroll
+        for (int it = 0; it < kSmallItems; ++it) {
+            double w[K];
+#pragma unroll
+            for (int i = 0; i < K; ++i) w[i] = wv[K * it + i];
+            const unsigned c = oddSelectionCodeScan<K>(w);
+            packed |= c << (8 * it);
+            mine += c ? 1 : 0;
+        }
+        *reinterpret_cast<uint32_t *>(code + t0) = packed;
+    } else {
+#pragma unroll
+        for (int it = 0; it < kSmallItems; ++it) {
+            const long long t = t0 + it;
+            if (t >= T) continue;
+            double w[K];
+#pragma unroll
+            for (int i = 0; i < K; ++i) w[i] = CLAMPED ? __ldg(x + eids[K * t + i]) : clamp01(__ldg(x + eids[K * t + i]));
+            const unsigned c = oddSelectionCodeScan<K>(w);
+            code[t] = (uint8_t)c;
+            mine += c ? 1 : 0;
+        }
     }
     // CTA total
     __shared__ int warpSum[kSmallBlock / 32];

@@ -196,7 +196,7 @@ struct smsgpu_ctx {
     bool haveLabels = false, haveSrcStats = false;
 
     // small cycles (k = 3, 4)
-    DevBuf scNodes[2], scEids[2], scCode;
+    DevBuf scNodes[2], scEids[2], scCode, scXc;
     cudaEvent_t scEv[4]{};
     double scMs[3] = {0, 0, 0}; // last scan: scan kernel, (count scan +) gather kernels, D2H of the walks
     long long scCount[2] = {0, 0};
@@ -800,7 +800,7 @@ void smsgpu_destroy(smsgpu_ctx *ctx) {
                      &ctx->fin.src, &ctx->fin.seq, &ctx->fin.viol, &ctx->scFin.off, &ctx->scFin.node, &ctx->scFin.eid,
                      &ctx->scFin.stay, &ctx->scFin.ncross, &ctx->scFin.src, &ctx->scFin.viol, &ctx->scNodes[0], &ctx->scNodes[1], &ctx->scEids[0],
                      &ctx->scEids[1], &ctx->gCounts,
-                     &ctx->pBlock, &ctx->mBlocks, &ctx->dArcSrc, &ctx->dColSorted, &ctx->eHoleBase, &ctx->scCode, &ctx->vStampA, &ctx->vStampB, &ctx->vStampC, &ctx->vIota, &ctx->vEmpty, &ctx->vEmptyB0, &ctx->vActive, &ctx->vFlags, &ctx->mNode, &ctx->mEid, &ctx->mStay, &ctx->mOff, &ctx->mLen, &ctx->mSrc,
+                     &ctx->pBlock, &ctx->mBlocks, &ctx->dArcSrc, &ctx->dColSorted, &ctx->eHoleBase, &ctx->scCode, &ctx->scXc, &ctx->vStampA, &ctx->vStampB, &ctx->vStampC, &ctx->vIota, &ctx->vEmpty, &ctx->vEmptyB0, &ctx->vActive, &ctx->vFlags, &ctx->mNode, &ctx->mEid, &ctx->mStay, &ctx->mOff, &ctx->mLen, &ctx->mSrc,
                      &ctx->mSeq, &ctx->mValid};
     for (auto *b : dev) b->release();
     PinBuf *pin[] = {&ctx->hX, &ctx->hBl, &ctx->hCounters, &ctx->hHeavy, &ctx->host.off, &ctx->host.node, &ctx->host.eid,
@@ -1907,13 +1907,16 @@ static int smallCyclesScanDevice(smsgpu_ctx *ctx, int k, long long *Uout) {
     CU(ctx->scCode.ensure((size_t)T));
     CU(ctx->wCnt.ensure((size_t)(ntiles + 1) * 4));
     CU(ctx->wBase.ensure((size_t)(ntiles + 2) * 8));
+    CU(ctx->scXc.ensure((size_t)std::max<long long>(ctx->m, 1) * 8));
     CU(cudaEventRecord(ctx->scEv[0], st));
+    // clamp(x*) once per edge (m values) instead of once per gather (k T values)
+    clampWeightsKernel<<<std::min<unsigned>(gridFor(ctx->m, 256), (unsigned)ctx->smCount * 8), 256, 0, st>>>(ctx->m, ctx->xPtr, ctx->scXc.as<double>());
     if (k == 3)
-        smallCycleScanKernel<3><<<(unsigned)ntiles, kSmallBlock, 0, st>>>(T, ctx->scEids[s].as<int32_t>(), ctx->xPtr, ctx->scCode.as<uint8_t>(),
-                                                                        ctx->wCnt.as<int32_t>());
+        smallCycleScanKernel<3, true><<<(unsigned)ntiles, kSmallBlock, 0, st>>>(T, ctx->scEids[s].as<int32_t>(), ctx->scXc.as<double>(),
+                                                                              ctx->scCode.as<uint8_t>(), ctx->wCnt.as<int32_t>());
     else
-        smallCycleScanKernel<4><<<(unsigned)ntiles, kSmallBlock, 0, st>>>(T, ctx->scEids[s].as<int32_t>(), ctx->xPtr, ctx->scCode.as<uint8_t>(),
-                                                                        ctx->wCnt.as<int32_t>());
+        smallCycleScanKernel<4, true><<<(unsigned)ntiles, kSmallBlock, 0, st>>>(T, ctx->scEids[s].as<int32_t>(), ctx->scXc.as<double>(),
+                                                                              ctx->scCode.as<uint8_t>(), ctx->wCnt.as<int32_t>());
     CU(cudaGetLastError());
     CU(cudaEventRecord(ctx->scEv[1], st));
     if (int rc = exclusiveScan(ctx, ctx->wCnt.as<int32_t>(), ntiles, ctx->wBase.as<long long>())) return rc;
@@ -2448,9 +2451,9 @@ extern "C" int smsgpu_small_cycles_scan_noalloc(int device, void *stream, int k,
     // writes tileBase[0, ntiles], and only those ranges are read afterwards -- what an earlier call left behind is never seen.
     if (ntiles > 0) {
         if (k == 3)
-            smallCycleScanKernel<3><<<(unsigned)ntiles, kSmallBlock, 0, st>>>(T, d_cycle_eids, d_x, code, tileCount);
+            smallCycleScanKernel<3, false><<<(unsigned)ntiles, kSmallBlock, 0, st>>>(T, d_cycle_eids, d_x, code, tileCount);
         else
-            smallCycleScanKernel<4><<<(unsigned)ntiles, kSmallBlock, 0, st>>>(T, d_cycle_eids, d_x, code, tileCount);
+            smallCycleScanKernel<4, false><<<(unsigned)ntiles, kSmallBlock, 0, st>>>(T, d_cycle_eids, d_x, code, tileCount);
         NA_CU(cudaGetLastError());
     }
     noallocTileScanKernel<<<1, 1024, 0, st>>>((int)ntiles, tileCount, tileBase, out_capacity, k, reinterpret_cast<long long *>(d_off),
