@@ -3,11 +3,16 @@
 // Same search as every other engine -- runDijsktra of the reference (src/graph/ocw_seperator.cpp:37-112) in the
 // canonical order (dist, hops, doubled id), event for event -- written as plain sequential code: the statement of the
 // reference, with the reference's dense arrays replaced by a hashed label table and its heap by a monotone bucket queue.
-// Why: the warp-cooperative engines spend ~400 warp instructions per settled node on ballots, shuffles and predication
-// to keep 16 lanes busy with the ~9 arcs of a node, and have 7 000 searches in flight; the round is bound by the issue
-// slots and by two to three dependent DRAM round trips per step (profiles/r02_pairs_tier1_random1m_256k.md).  A thread
-// per source needs no cross-lane instruction at all, puts 32 independent searches behind every memory instruction, and
-// tens of thousands in flight; the round then is bound by DRAM sectors.
+// Why it was built: the warp-cooperative engines spend ~400 warp instructions per settled node on ballots, shuffles and
+// predication to keep 16 lanes busy with the ~9 arcs of a node, and have 7 000 searches in flight
+// (profiles/r02_pairs_tier1_random1m_256k.md).  A thread per source needs no cross-lane instruction and puts up to 100 000
+// searches in flight.
+// What was measured (config 5, B200, profiles/r02_lanes_experiments.md): it is SLOWER -- 824 ms per round at 98 304
+// searches in flight against 475 ms for the pairs engine -- so it is OFF by default (SMSGPU_LANES=1 turns it on; the parity
+// tests run it).  Without shared memory there is no presence bitmap and no bucket counter on chip: every probe, every
+// bucket word is a DRAM access, 3.6 KB of DRAM traffic per settled node against 1.0 KB (every isolated access costs a
+// 128-byte line, scripts/sector_flavors.cu), and the 32 lanes of a warp take 32 different paths (6.7 of 32 threads active
+// per instruction).  More searches in flight did not help beyond ~65 000 (profiles/r02_lanes_search_v3.md).
 //
 // Working memory of one search (a "tile", thread private, in HBM; bytes: lanesTileBytes -- what limits the searches in
 // flight is memory CAPACITY, so the tile is compact):
@@ -211,9 +216,10 @@ __host__ __device__ __forceinline__ void lnCntOr(uint32_t *p, const uint32_t v) 
 }
 
 #ifndef SMSGPU_LANES_GROUP
-#define SMSGPU_LANES_GROUP 8
+#define SMSGPU_LANES_GROUP 4
 #endif
 constexpr int kLanesG = SMSGPU_LANES_GROUP; // arcs per group: their loads, probes and queue-position atomics travel together
+                                            // (measured: 4 beats 8 -- 163 against 232 registers -- and 2)
 
 // The search of one source.  `srow` = {first arc, degree} of the source's vertex.  Fills `rec` (src, flags bits 0-1,
 // best, histN, touchedN, arcs, settled, stamp, qN); srcIdx / twinIdx / flag bit 2 belong to the caller.

@@ -13,7 +13,6 @@
 #pragma once
 #include "ocw_lanes_core.cuh"
 #include "ocw_search_pairs.cuh"
-#include <cstdio>
 
 namespace smsgpu {
 
@@ -30,7 +29,6 @@ struct LanesArgs {
     unsigned char *warpScratch; // walk scratch of the finishing warps
     size_t warpScratchStride;
     TileCaps fcaps;        // capacities as the finishing code sees them
-    int debugFence;        // SMSGPU_LANES_FENCE (debugging): gpu-scope fences in front of the reads of a tile
 };
 
 #ifndef SMSGPU_LANES_BLOCK
@@ -43,7 +41,6 @@ struct LanesArgs {
 __global__ void __launch_bounds__(SMSGPU_LANES_BLOCK, SMSGPU_LANES_MINB) ocwLanesSearchKernel(const GraphDev G, const SearchParams P, const LanesArgs A) {
     const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= A.count) return;
-    if (A.debugFence) __threadfence();
     const LanesTile T = lanesCarve(A.tiles + (size_t)t * A.tileStride, A.cfg);
     const long long total = P.worklist ? P.nwork : P.nsrc;
     const long long w0 = (A.first + t) * A.itemSize;
@@ -94,10 +91,7 @@ __global__ void __launch_bounds__(128) ocwLanesFinishKernel(const LanesArgs A) {
     const PairsKArgs *K = A.kargs;
     for (long long t = warp; t < A.count; t += nwarps) {
         const LanesTile T = lanesCarve(A.tiles + (size_t)t * A.tileStride, A.cfg);
-        if (A.debugFence) __threadfence();
         const LanesRec rec = *T.rec;
-        if (rec.srcIdx >= 0 && rec.stamp != A.stamp && lane == 0)
-            printf("[smsgpu] lanes finish: tile %lld carries stamp %u, batch stamp %u (srcIdx %d)\n", t, rec.stamp, A.stamp, rec.srcIdx);
         if (rec.srcIdx < 0) continue; // every entry of the item was skipped
         TileMem M;
         {

@@ -564,7 +564,6 @@ int runLanes(smsgpu_ctx *ctx, const GraphDev &G, SearchParams P, const RawOut &R
         A.warpScratch = ctx->lanesWarpScratch.as<unsigned char>() + (size_t)set * (size_t)ctx->lanesFinishCtas * 4 * ctx->lanesWarpStride;
         A.warpScratchStride = ctx->lanesWarpStride;
         A.fcaps = ctx->lanesFcaps;
-        A.debugFence = std::getenv("SMSGPU_LANES_FENCE") ? 1 : 0;
         ocwLanesSearchKernel<<<(unsigned)((A.count + SMSGPU_LANES_BLOCK - 1) / SMSGPU_LANES_BLOCK), SMSGPU_LANES_BLOCK, 0, s>>>(G, P, A);
         CU(cudaGetLastError());
         ocwLanesFinishKernel<<<(unsigned)std::min<long long>((A.count + 3) / 4, ctx->lanesFinishCtas), 128, 0, s>>>(A);

@@ -16,7 +16,8 @@ def test_lanes_engine_equals_oracle(gpu, orc, monkeypatch, mirror):
     pairs / runs engines take those sources), a degree-40 graph (several groups of four arcs per row), a lattice"""
     monkeypatch.setenv("SMSGPU_LANES", "1")
     monkeypatch.setenv("SMSGPU_MIRROR", mirror)
-    for inst in (I.random_graph(3000, 12000, seed=11), I.random_graph(200, 4000, seed=12), I.torus3d(7)):
+    insts = (I.random_graph(3000, 12000, seed=11), I.random_graph(200, 4000, seed=12), I.torus3d(7))
+    for inst in (insts if mirror == "1" else insts[:1]):
         for xf in (I.xstar_uniform, I.xstar_lp_like, I.xstar_half_integral):
             _, _, st, tiers = check_raw(inst, xf(inst.m, seed=6), orc, start_tier=1)
             assert st["tier_sources"][0] == 0
