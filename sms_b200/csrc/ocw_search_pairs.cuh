@@ -58,8 +58,13 @@ __device__ __forceinline__ Entry loadEntryCS(const Entry *p) {
     Entry e;
     const uint4 *q = reinterpret_cast<const uint4 *>(p);
     uint4 *s = reinterpret_cast<uint4 *>(&e);
+#ifdef SMSGPU_PAIRS_PLAIN_LD // experiment: default loads (33.9 G isolated accesses/s against 30.0 G with ld.cs, profiles/r02_sector_flavors.md)
+    s[0] = q[0];
+    s[1] = q[1];
+#else
     s[0] = __ldcs(q);
     s[1] = __ldcs(q + 1);
+#endif
     return e;
 }
 __device__ __forceinline__ void storeEntryCS(Entry *p, const Entry &e) {
