@@ -59,3 +59,31 @@ def test_lanes_engine_rounds_with_history(gpu, orc, monkeypatch):
             assert st["sources_run"] == int((tier >= 0).sum()) == sum(st["tier_sources"])
     finally:
         sep.close()
+
+
+def test_lanes_and_pairs_engines_agree_at_scale(gpu, monkeypatch):
+    """Two engines that share no search code (two sources per warp in lock step / one source per thread) on a whole round
+    of a 100 000-node graph, all sources, dedup on: the same cut list byte for byte, the same arcs scanned and nodes settled
+    per source.  (The full 1M-source round of config 5 agrees as well: scripts/exp_lanes.py, profiles/r02_lanes_experiments.md.)"""
+    from sms_b200.separator import GpuOcwSeparator
+    inst = I.random_graph(100000, 400000, seed=21)
+    x = I.xstar_uniform(inst.m, seed=22)
+    bl = inst.root_blacklist()
+    src = inst.handler_sources()
+    out = []
+    for lanes in ("0", "1"):
+        monkeypatch.setenv("SMSGPU_LANES", lanes)
+        monkeypatch.setenv("SMSGPU_LANES_TILES", "16384")
+        sep = GpuOcwSeparator(inst.n, inst.rowptr, inst.col, inst.eid)
+        try:
+            sep.setRoundInput(x, bl)
+            got = sep.separateRound(sources=src, dedup=True, start_tier=1, export_src_stats=1)
+            arcs, settled, tier = sep.ctx.src_stats()
+            st = sep.ctx.stats()
+            out.append((got.walks(), arcs.copy(), settled.copy(), st["unique_cuts"], st["mirrored_sources"]))
+        finally:
+            sep.close()
+    a, b = out
+    assert a[3] == b[3] > 1000 and a[0] == b[0]
+    assert np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2])
+    assert b[4] > 0.4 * len(src)
