@@ -54,7 +54,7 @@ REF_SAMPLE = {"random1m": 2048, "torus100": 10_000, "torus3d20": 8_000, "random2
 
 
 # dram bytes of the search of one full round, from the committed ncu capture (per launch; see roofline.traffic_note)
-TRAFFIC_NCU = {"random1m": round(165.588185e9 * 1254134233 / 329005693)}  # 165.59 GB for the capture's 329.0 M (reference-equivalent) settled nodes
+TRAFFIC_NCU = {"random1m": round(150.746169e9 * 1254134233 / 329005693)}  # 150.75 GB for the capture's 329.0 M (reference-equivalent) settled nodes
 
 
 XSTAR_NOTE = {"fixed": "", "fresh": "; a NEW iid U(0,1) x* every step", "replay": "; x* sequence from the cutting loop (HiGHS root LP iterates, one per step)"}
@@ -653,9 +653,10 @@ def main():
             "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                          "traffic": TRAFFIC_NCU.get(args.workload), "peak_source": peak_src,
                          "kernel": "ocwSearchPairsKernel (tier 1; tiers 0/2: ocwSearchKernel)",
-                         "traffic_note": "dram__bytes_read+write of the tier-1 launch from profiles/r01_pairs_tier1_random1m_256k.md "
-                                         "(ncu --set full, 262144 sources), scaled to the round by settled nodes; the path is bound by "
-                                         "dependent random 32-byte accesses, not by bytes (DESIGN.md section 5)",
+                         "traffic_note": "dram__bytes_read+write of the tier-1 launch from profiles/r02_pairs_tier1_random1m_256k_final.md "
+                                         "(ncu --set full, 262144 sources), scaled to the round by settled nodes; every isolated 32-byte "
+                                         "access brings a 128-byte line from DRAM (profiles/r02_sector_flavors.md); the path is bound by the "
+                                         "latency of dependent accesses, not by bytes (DESIGN.md section 5)",
                          "algorithmic_bytes": alg_bytes, "per_gpu": True},
             "e2e": {"value": args.steps / res["e2e_dt"], "unit": "rounds/s", "h2d_bytes_per_step": res["h2d"],
                     "d2h_bytes_per_step": res["d2h"]},
