@@ -17,7 +17,7 @@ namespace smsgpu {
 __global__ void __launch_bounds__(256) dcWeightsKernel(const long long narcs, const int32_t *__restrict__ col,
                                                        const int32_t *__restrict__ eid, const uint32_t *__restrict__ rowpack,
                                                        const double *__restrict__ x, const uint8_t *__restrict__ bl,
-                                                       Arc *__restrict__ arcs) {
+                                                       Arc *__restrict__ arcs, uint32_t *__restrict__ arcs12) {
     const long long nquads = narcs >> 2;
     const long long stride = (long long)gridDim.x * blockDim.x;
     for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < nquads; q += stride) {
@@ -41,6 +41,12 @@ __global__ void __launch_bounds__(256) dcWeightsKernel(const long long narcs, co
             a.row = rs[k];
             a.w = clamp01(ws[k]);
             arcs[4 * q + k] = a;
+            if (arcs12) { // 12-byte copy {nbr, w} for the pairs engine (SMSGPU_ARCS12: 96 instead of 128 MB at config 5)
+                const unsigned long long wb = (unsigned long long)__double_as_longlong(a.w);
+                arcs12[3 * (4 * q + k)] = (uint32_t)a.nbr;
+                arcs12[3 * (4 * q + k) + 1] = (uint32_t)wb;
+                arcs12[3 * (4 * q + k) + 2] = (uint32_t)(wb >> 32);
+            }
         }
     }
     // tail
@@ -52,6 +58,12 @@ __global__ void __launch_bounds__(256) dcWeightsKernel(const long long narcs, co
         a.row = rowpack[t];
         a.w = clamp01(x[eid[t]]);
         arcs[t] = a;
+        if (arcs12) {
+            const unsigned long long wb = (unsigned long long)__double_as_longlong(a.w);
+            arcs12[3 * t] = (uint32_t)a.nbr;
+            arcs12[3 * t + 1] = (uint32_t)wb;
+            arcs12[3 * t + 2] = (uint32_t)(wb >> 32);
+        }
     }
 }
 

@@ -49,6 +49,7 @@ struct PairsParams {
     float scaleB;         // bucket = (2^u - 1) * scaleB   (linear map: dist * scaleB)
     int mirror;           // 1: twin sources (v,0)/(v,1) are searched once when no id tie-break occurred
     uint32_t rowShift;    // Arc::row = first arc | degree << rowShift; a saturated degree field means "read rowinfo"
+    const uint32_t *arcs12; // optional 12-byte copy of the arc records {nbr, w} (SMSGPU_ARCS12=1), else null
 };
 
 // The per-source working memory (label table, predecessors, queue) is touched once or twice per source and is far
@@ -535,8 +536,13 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
         // them towards L2 now (the row of the key just extracted is being loaded anyway)
         if (freshB) {
             if (run && khi != kDeadKey && deg) {
+#ifdef SMSGPU_PAIRS_ARCS12
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(Q.arcs12 + 3 * (size_t)rowB));
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(Q.arcs12 + 3 * (size_t)(rowB + deg - 1)));
+#else
                 asm volatile("prefetch.global.L2 [%0];" ::"l"(G.arcs + rowB));
                 asm volatile("prefetch.global.L2 [%0];" ::"l"(G.arcs + rowB + deg - 1));
+#endif
             }
             freshB = false;
         }
@@ -619,7 +625,14 @@ __global__ void __launch_bounds__(128, SMSGPU_PAIRS_MIN_CTAS)
             double w = 0.0;
             uint2 nrow = make_uint2(0u, 0u);
             if (act) {
+#ifdef SMSGPU_PAIRS_ARCS12 // experiment: the 12-byte copy of the arc records (96 MB at config 5: inside the 126 MB of L2)
+                const uint32_t *ap = Q.arcs12 + 3 * (size_t)(rb + c0 + tl);
+                Arc arc;
+                arc.nbr = (int32_t)__ldg(ap);
+                arc.w = __hiloint2double((int)__ldg(ap + 2), (int)__ldg(ap + 1));
+#else
                 const Arc arc = G.arcs[rb + c0 + tl];
+#endif
                 nbr = (uint32_t)arc.nbr & 0x7FFFFFFFu;
 #ifdef SMSGPU_PAIRS_ROW_IN_ARC
                 rowp = arc.row;

@@ -122,6 +122,7 @@ struct smsgpu_ctx {
 
     // graph (uploaded once)
     DevBuf dRowptr, dCol, dEid, dArcs;
+    DevBuf dArcs12;           // optional 12-byte copy of the arc records (experiment build -DSMSGPU_PAIRS_ARCS12)
     DevBuf dPairsArgs;        // PairsKArgs of the launch in flight
     DevBuf dRowinfo;          // uint2[n] {first arc, degree}: pairs engine (tier 1)
     DevBuf dRowpack;          // uint32[2m] Arc::row of every adjacency entry (static; K1 copies it into the arc records)
@@ -303,7 +304,8 @@ cudaError_t launchSearch(smsgpu_ctx *c, int tierIdx, const GraphDev &G, const Se
         if (e != cudaSuccess) return e;
         e = cudaMemcpyAsync(c->dPairsArgs.p, &K, sizeof K, cudaMemcpyHostToDevice, st); // pageable source: staged before return
         if (e != cudaSuccess) return e;
-        const PairsParams Q{c->dPairsArgs.as<PairsKArgs>(), c->dRowinfo.as<uint2>(), c->pairsScaleU, c->pairsScaleB, c->pairsMirror ? 1 : 0, c->rowShift};
+        const PairsParams Q{c->dPairsArgs.as<PairsKArgs>(), c->dRowinfo.as<uint2>(), c->pairsScaleU, c->pairsScaleB, c->pairsMirror ? 1 : 0, c->rowShift,
+                            c->dArcs12.as<uint32_t>()};
         kern<<<ctas, 128, t.smemBytes, st>>>(G, Q, P, R, t.caps, t.scratch.as<unsigned char>());
         return cudaGetLastError();
     }
@@ -670,6 +672,9 @@ int smsgpu_create(smsgpu_ctx **out, int64_t n, int64_t m, const int64_t *rowptr,
     CUB(ctx->dCol.ensure((size_t)std::max<int64_t>(2 * m, 4) * sizeof(int32_t)));
     CUB(ctx->dEid.ensure((size_t)std::max<int64_t>(2 * m, 4) * sizeof(int32_t)));
     CUB(ctx->dArcs.ensure((size_t)std::max<int64_t>(2 * m, 4) * sizeof(Arc)));
+#ifdef SMSGPU_PAIRS_ARCS12
+    CUB(ctx->dArcs12.ensure((size_t)std::max<int64_t>(2 * m, 4) * 12));
+#endif
     CUB(cudaMemcpyAsync(ctx->dRowptr.p, rowptr, (size_t)(n + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, ctx->stream));
     if (m > 0) {
         CUB(cudaMemcpyAsync(ctx->dCol.p, col, (size_t)2 * m * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
@@ -788,7 +793,7 @@ void smsgpu_destroy(smsgpu_ctx *ctx) {
     smsgpu_comm_destroy(ctx);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     if (ctx->stream2) cudaStreamSynchronize(ctx->stream2);
-    DevBuf *dev[] = {&ctx->dPairsArgs, &ctx->dRowinfo, &ctx->dRowpack, &ctx->dRowptr, &ctx->dCol, &ctx->dEid, &ctx->dArcs, &ctx->dX, &ctx->dBl, &ctx->dSources,
+    DevBuf *dev[] = {&ctx->dArcs12, &ctx->dPairsArgs, &ctx->dRowinfo, &ctx->dRowpack, &ctx->dRowptr, &ctx->dCol, &ctx->dEid, &ctx->dArcs, &ctx->dX, &ctx->dBl, &ctx->dSources,
                      &ctx->tier[0].scratch, &ctx->tier[1].scratch, &ctx->tier[2].scratch, &ctx->tier[3].scratch, &ctx->rNode, &ctx->rEid,
                      &ctx->rStay, &ctx->rCutOff, &ctx->rCutLen, &ctx->rCutSrc, &ctx->rCutSeq, &ctx->rCutTier, &ctx->rValid,
                      &ctx->labSrc, &ctx->labNode, &ctx->labHops, &ctx->labDist, &ctx->srcTier, &ctx->srcArcs,
@@ -1140,7 +1145,7 @@ int separateLocal(smsgpu_ctx *ctx, const smsgpu_params &P) {
     if (ctx->arcsDirty && ctx->m > 0) {
         dcWeightsKernel<<<std::min<unsigned>(gridFor((2 * ctx->m + 3) / 4, 256), (unsigned)ctx->smCount * 16), 256, 0, st>>>(
             2 * ctx->m, ctx->dCol.as<int32_t>(), ctx->dEid.as<int32_t>(), ctx->dRowpack.as<uint32_t>(), ctx->xPtr, ctx->blPtr,
-            ctx->dArcs.as<Arc>());
+            ctx->dArcs.as<Arc>(), ctx->dArcs12.as<uint32_t>());
         CU(cudaGetLastError());
         ctx->stats.total_launches += 1;
     }
