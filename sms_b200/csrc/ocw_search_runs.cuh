@@ -40,7 +40,6 @@ constexpr int kRunThreads = 256;
 constexpr uint32_t kRunOfferCap = 1024; // arcs per chunk (sort buffers in shared memory)
 
 #ifdef SMSGPU_RUNS_CLOCKS // instrumentation build: cycles per phase of a chunk, accumulated by thread 0 of CTA 0
-__device__ unsigned long long g_runClk[16];
 #define RCLK(i_)                                                                     \
     do {                                                                             \
         if (threadIdx.x == 0 && blockIdx.x == 0) {                                   \
@@ -923,6 +922,7 @@ __global__ void __launch_bounds__(kRunThreads, SMSGPU_RUNS_MIN_CTAS) ocwSearchRu
         if (threadIdx.x < 32) {
             if (!S.overflow && S.histN > 0) {
                 const int nsel = selectIntermediates<32>(T, M, S, maxInter, sel);
+                RCLK(10);
                 if (!S.overflow) {
                     Emitter E;
                     E.R = &R;
@@ -932,6 +932,7 @@ __global__ void __launch_bounds__(kRunThreads, SMSGPU_RUNS_MIN_CTAS) ocwSearchRu
 #pragma unroll
                     for (int r = 0; r < 16; ++r) sel[r] = T.shfl(sel[r], 0); // lane 0 holds the selection
                     walksOfSource(G, M, S, E, sel, nsel, src, srcIdx);
+                    RCLK_RESET;
                 }
                 S.overflow = T.shfl(S.overflow, 0);
             }

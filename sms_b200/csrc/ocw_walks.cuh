@@ -12,6 +12,22 @@
 
 namespace smsgpu {
 
+#ifdef SMSGPU_RUNS_CLOCKS // instrumentation build (ocw_search_runs.cuh): cycles of CTA 0 per phase
+__device__ unsigned long long g_runClk[16];
+#define WCLK(i_)                                                                         \
+    do {                                                                                 \
+        if (threadIdx.x == 0 && blockIdx.x == 0) {                                       \
+            const long long now_ = clock64();                                            \
+            atomicAdd(&g_runClk[i_], (unsigned long long)(now_ - wclkLast));             \
+            wclkLast = now_;                                                             \
+        }                                                                                \
+    } while (0)
+#define WCLK_DECL long long wclkLast = clock64()
+#else
+#define WCLK(i_) ((void)0)
+#define WCLK_DECL ((void)0)
+#endif
+
 struct Emitter {
     const RawOut *R;
     int32_t srcIdx;
@@ -113,7 +129,7 @@ __device__ inline int tracePath(const TileMem &M, uint32_t t, uint32_t src, int3
     p[0] = (int32_t)cur;
     while (cur != src) {
         if (len >= (int)M.caps.walkCap) return -1;
-        const int slot = findSlot(M, cur >> 1);
+        const int slot = M.caps.dense ? (int)(cur >> 1) : findSlot(M, cur >> 1); // dense table: slot = vertex, nothing to probe
         SMS_CHK(slot >= 0);
         SMS_CHK(((cur & 1u) ? M.tab[slot].d1 : M.tab[slot].d0) < kUnlabelled);
         cur = predOf(M, slot, cur & 1u);
@@ -123,10 +139,14 @@ __device__ inline int tracePath(const TileMem &M, uint32_t t, uint32_t src, int3
 }
 
 // extractCycles (:229-328) on the closed walk c[0..len] (c[len] == c[0]) with stay flags st[0..len).
-// Called by all 32 lanes of the warp with identical arguments (E and the serial parts belong to lane 0): the arcs of the
-// walk's edges and the chord search -- for every position i, every arc of c[i], the first earlier position of its end
-// point: O(len^2 deg) loads -- are spread over the lanes; the candidates come out in the reference's order (position,
-// adjacency position, inner before outer) through a warp prefix sum.  Lane 0 then sorts and emits as before.
+// Called by all 32 lanes of the warp with identical arguments (E and the serial parts belong to lane 0).  Everything that needs
+// the graph is done with the lanes over INDEPENDENT items, so that a walk costs a handful of memory round trips instead of
+// two or three per position (measured on the root-LP iterates of the 100x100 torus: 90 000 cycles per 18-edge walk, more
+// than half of the round, profiles/README.md): (1) lanes over the positions: the arc of the edge entering the position, its
+// weight and edge id, the row of the position's vertex; (2) lane 0: the reference's prefix sums (same order of additions);
+// (3) lanes over ALL arcs of all positions, flattened: the chord test -- for every position i, every arc of c[i], the first
+// earlier position of its end point -- with the candidates written in the reference's order (position, adjacency position,
+// inner before outer) through a warp prefix sum.  Lane 0 then sorts and emits as before, from what (1) left in scratch.
 __device__ inline void extractCycles(const GraphDev &G, TileMem &M, SrcState &S, Emitter &E, const int32_t *c,
                                      const int32_t *st, const int len) {
     constexpr unsigned FULL = 0xFFFFFFFFu;
@@ -134,104 +154,138 @@ __device__ inline void extractCycles(const GraphDev &G, TileMem &M, SrcState &S,
     int32_t *warc = M.warc; // warc[i]: arc (in the row of c[i]) of the edge c[i-1] - c[i], i = 1..len
     int32_t *crs = M.crs;
     double *plen = M.plen;
-    // prefix sums (:242-250): the arcs in parallel, the sums serially (the order of the additions is the reference's)
+    // scratch in the queue memory (idle once the intermediates are selected): per position the edge id of the entering
+    // edge, the first arc of its vertex' row, and the exclusive prefix of the degrees of the positions 2 .. len-1
+    if ((size_t)3 * (size_t)(len + 2) * sizeof(int32_t) > (size_t)M.caps.heapCap * sizeof(HeapEnt)) {
+        S.overflow = 1;
+        return;
+    }
+    int32_t *weid = reinterpret_cast<int32_t *>(M.heap);
+    int32_t *rowB = weid + (len + 2);
+    int32_t *degP = rowB + (len + 2);
+    // (1) lanes over the positions
     for (int i = 1 + lane; i <= len; i += 32) {
-        const long long a = findArc(G, c[i], c[i - 1]);
+        const int32_t u = c[i], from = c[i - 1];
+        const long long rb = G.rowptr[u], re = G.rowptr[u + 1];
+        long long a = -1; // Graph::indexInOutEdgeArray (NetworKit Graph.cpp:119-127): first adjacency position of u holding `from`
+        for (long long q = rb; q < re; ++q)
+            if ((G.arcs[q].nbr & 0x7FFFFFFF) == from) {
+                a = q;
+                break;
+            }
         SMS_CHK(a >= 0);
         SMS_CHK(i <= 2 * (int)M.caps.walkCap + 1);
         warc[i] = (int32_t)a;
         plen[i] = G.arcs[a].w; // the edge's weight for now, the prefix sum below
+        weid[i] = G.eid[a];
+        rowB[i] = (int32_t)rb; // 2m < 2^30 checked at create
+        degP[i] = (i >= 2 && i < len) ? (int32_t)(re - rb) : 0;
     }
     __syncwarp(FULL);
+    // (2) prefix sums (:242-250), serially: the order of the additions is the reference's
     if (lane == 0) {
-        int numCross = 0;
+        int numCross = 0, arcsBefore = 0;
         double pathLength = 0.;
         crs[0] = 0;
         plen[0] = 0.;
+        degP[0] = 0;
         for (int i = 1; i <= len; ++i) {
             numCross += st[i - 1] ? 0 : 1;
             const double w = plen[i];
             pathLength += st[i - 1] ? w : 1 - w;
             crs[i] = numCross;
             plen[i] = pathLength;
+            const int dg = degP[i];
+            degP[i] = arcsBefore;
+            arcsBefore += dg;
         }
+        degP[len + 1] = arcsBefore;
     }
     __syncwarp(FULL);
-    // good chords (:254-306)
+    // (3) good chords (:254-306): lanes over the arcs of the positions 2 .. len-1, in (position, adjacency position) order
     int nch = 0;
     const double total = plen[len];
-    for (int i = 2; i < len; ++i) {
-        const int32_t cur = c[i], prv = c[i - 1], nxt = c[i + 1];
-        const long long rb = G.rowptr[cur], re = G.rowptr[cur + 1];
-        for (long long base = rb; base < re; base += 32) {
-            const long long a = base + lane;
-            int f0 = -1, l0 = 0, f1 = -1, l1 = 0; // flags: bit0 crossing, bit1 inner
-            if (a < re) {
-                const Arc arc = G.arcs[a];
-                const int32_t nb = arc.nbr & 0x7FFFFFFF;
-                if (nb != prv && nb != nxt) {
-                    int j = -1;
-                    for (int k = 0; k < i; ++k)
-                        if (c[k] == nb) {
-                            j = k;
-                            break;
-                        }
-                    if (j >= 0) {
-                        const int innerCrossingDif = crs[i] - crs[j];
-                        const double innerLen = plen[i] - plen[j];
-                        const double outerLen = total - innerLen;
-                        // weights_[edgeId(c[i], c[j])]: the first arc of c[i] towards c[j] -- this one, the graph is simple
-                        const double x = arc.w;
-                        if ((innerCrossingDif % 2) == 0) {
-                            if (innerLen - x < 0) {
-                                f0 = 1 | 2;
-                                l0 = i - j + 1;
-                            }
-                            if (outerLen + x < 1) {
-                                f1 = 0;
-                                l1 = len - i + j + 1;
-                            }
-                        } else {
-                            if (innerLen + x < 1) {
-                                f0 = 2;
-                                l0 = i - j + 1;
-                            }
-                            if (outerLen - x < 0) {
-                                f1 = 1;
-                                l1 = len - i + j + 1;
-                            }
-                        }
-                        // the chord's start position j rides in the flags' high bits until the candidate is written
-                        if (f0 >= 0) f0 |= j << 8;
-                        if (f1 >= 0) f1 |= j << 8;
+    const int T = degP[len + 1];
+    for (int f0 = 0; f0 < T; f0 += 32) {
+        const int f = f0 + lane;
+        int f0c = -1, l0 = 0, f1c = -1, l1 = 0; // flags: bit0 crossing, bit1 inner
+        int i = 0;
+        long long a = 0;
+        if (f < T) {
+            int lo = 2, hi = len - 1; // the position of flat arc f: the largest i with degP[i] <= f
+            while (lo < hi) {
+                const int mid = (lo + hi + 1) >> 1;
+                if (degP[mid] <= f)
+                    lo = mid;
+                else
+                    hi = mid - 1;
+            }
+            i = lo;
+            a = (long long)rowB[i] + (f - degP[i]);
+            const Arc arc = G.arcs[a];
+            const int32_t nb = arc.nbr & 0x7FFFFFFF;
+            if (nb != c[i - 1] && nb != c[i + 1]) {
+                int j = -1;
+                for (int k = 0; k < i; ++k)
+                    if (c[k] == nb) {
+                        j = k;
+                        break;
                     }
+                if (j >= 0) {
+                    const int innerCrossingDif = crs[i] - crs[j];
+                    const double innerLen = plen[i] - plen[j];
+                    const double outerLen = total - innerLen;
+                    // weights_[edgeId(c[i], c[j])]: the first arc of c[i] towards c[j] -- this one, the graph is simple
+                    const double x = arc.w;
+                    if ((innerCrossingDif % 2) == 0) {
+                        if (innerLen - x < 0) {
+                            f0c = 1 | 2;
+                            l0 = i - j + 1;
+                        }
+                        if (outerLen + x < 1) {
+                            f1c = 0;
+                            l1 = len - i + j + 1;
+                        }
+                    } else {
+                        if (innerLen + x < 1) {
+                            f0c = 2;
+                            l0 = i - j + 1;
+                        }
+                        if (outerLen - x < 0) {
+                            f1c = 1;
+                            l1 = len - i + j + 1;
+                        }
+                    }
+                    // the chord's start position j rides in the flags' high bits until the candidate is written
+                    if (f0c >= 0) f0c |= j << 8;
+                    if (f1c >= 0) f1c |= j << 8;
                 }
             }
-            const int cnt = (f0 >= 0 ? 1 : 0) + (f1 >= 0 ? 1 : 0);
-            int incl = cnt;
-#pragma unroll
-            for (int off = 1; off < 32; off <<= 1) {
-                const int o = __shfl_up_sync(FULL, incl, off);
-                if (lane >= off) incl += o;
-            }
-            const int tot = __shfl_sync(FULL, incl, 31);
-            if (tot == 0) continue;
-            if (nch + tot > (int)M.caps.chordCap) {
-                S.overflow = 1;
-                return;
-            }
-            int pos = nch + incl - cnt;
-            for (int q = 0; q < 2; ++q) {
-                const int f = q ? f1 : f0;
-                if (f < 0) continue;
-                int32_t *ch = M.chords + 4 * pos++;
-                ch[0] = f >> 8;
-                ch[1] = i;
-                ch[2] = q ? l1 : l0;
-                ch[3] = (int32_t)((uint32_t)(f & 3) | ((uint32_t)a << 2)); // 2m < 2^30 checked at create
-            }
-            nch += tot;
         }
+        const int cnt = (f0c >= 0 ? 1 : 0) + (f1c >= 0 ? 1 : 0);
+        int incl = cnt;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const int o = __shfl_up_sync(FULL, incl, off);
+            if (lane >= off) incl += o;
+        }
+        const int tot = __shfl_sync(FULL, incl, 31);
+        if (tot == 0) continue;
+        if (nch + tot > (int)M.caps.chordCap) {
+            S.overflow = 1;
+            return;
+        }
+        int pos = nch + incl - cnt;
+        for (int q = 0; q < 2; ++q) {
+            const int fl = q ? f1c : f0c;
+            if (fl < 0) continue;
+            int32_t *ch = M.chords + 4 * pos++;
+            ch[0] = fl >> 8;
+            ch[1] = i;
+            ch[2] = q ? l1 : l0;
+            ch[3] = (int32_t)((uint32_t)(fl & 3) | ((uint32_t)a << 2)); // 2m < 2^30 checked at create
+        }
+        nch += tot;
     }
     __syncwarp(FULL);
     if (lane != 0) return; // the rest is serial: lane 0 (the caller re-converges the warp)
@@ -282,12 +336,12 @@ __device__ inline void extractCycles(const GraphDev &G, TileMem &M, SrcState &S,
             pos++;
         };
         if (inner) {
-            for (int k = start; k < end; ++k) put(c[k], G.eid[warc[k + 1]], st[k]);
+            for (int k = start; k < end; ++k) put(c[k], weid[k + 1], st[k]);
             put(c[end], chordEid, crossing ? 0 : 1);
         } else {
-            for (int k = 0; k < start; ++k) put(c[k], G.eid[warc[k + 1]], st[k]);
+            for (int k = 0; k < start; ++k) put(c[k], weid[k + 1], st[k]);
             put(c[start], chordEid, crossing ? 0 : 1);
-            for (int k = end; k < len; ++k) put(c[k], G.eid[warc[k + 1]], st[k]);
+            for (int k = end; k < len; ++k) put(c[k], weid[k + 1], st[k]);
         }
         if (ncov > covCap) {
             S.overflow = 1;
@@ -300,7 +354,7 @@ __device__ inline void extractCycles(const GraphDev &G, TileMem &M, SrcState &S,
         if (emitReserve(E, len, cut, off))
             for (int k = 0; k < len; ++k) {
                 E.R->node[off + k] = c[k];
-                E.R->eid[off + k] = G.eid[warc[k + 1]];
+                E.R->eid[off + k] = weid[k + 1];
                 E.R->stay[off + k] = (uint8_t)st[k];
             }
     }
@@ -380,16 +434,26 @@ __device__ inline int buildWalk(const GraphDev &G, const TileMem &M, uint32_t t,
 __device__ inline void walksOfSource(const GraphDev &G, TileMem &M, SrcState &S, Emitter &E, const uint32_t *sel, const int nsel,
                                      const uint32_t src, const int32_t now) {
     constexpr unsigned FULL = 0xFFFFFFFFu;
+    WCLK_DECL;
     for (int r = 0; r < nsel; ++r) {
         int W = 0;
         if ((threadIdx.x & 31) == 0) W = buildWalk(G, M, sel[r], src, now);
         __syncwarp(FULL);
         W = __shfl_sync(FULL, W, 0);
+        WCLK(11);
+#ifdef SMSGPU_RUNS_CLOCKS
+        if (threadIdx.x == 0 && blockIdx.x == 0 && W > 0) {
+            atomicAdd(&g_runClk[13], (unsigned long long)W);
+            atomicAdd(&g_runClk[14], 1ull);
+            atomicMax(&g_runClk[15], (unsigned long long)W);
+        }
+#endif
         if (W < 0) {
             S.overflow = 1;
             return;
         }
         simpleOddCyclesAndExtract(G, M, S, E, W);
+        WCLK(12);
         if (S.overflow) return;
     }
 }
