@@ -156,7 +156,7 @@ __device__ __forceinline__ int finishSourceBody(const PairsKArgs *K, TileMem &M,
                         }
                     break;
                 }
-                walksOfSource(G, M, S, E, sel, nsel, src, srcIdx);
+                walksOfSource<true>(G, M, S, E, sel, nsel, src, srcIdx);
                 nlogged = T.shfl(E.nlog, 0);
             }
         }

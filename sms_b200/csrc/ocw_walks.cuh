@@ -13,7 +13,7 @@
 namespace smsgpu {
 
 #ifdef SMSGPU_RUNS_CLOCKS // instrumentation build (ocw_search_runs.cuh): cycles of CTA 0 per phase
-__device__ unsigned long long g_runClk[16];
+__device__ unsigned long long g_runClk[24];
 #define WCLK(i_)                                                                         \
     do {                                                                                 \
         if (threadIdx.x == 0 && blockIdx.x == 0) {                                       \
@@ -147,8 +147,8 @@ __device__ inline int tracePath(const TileMem &M, uint32_t t, uint32_t src, int3
 // (3) lanes over ALL arcs of all positions, flattened: the chord test -- for every position i, every arc of c[i], the first
 // earlier position of its end point -- with the candidates written in the reference's order (position, adjacency position,
 // inner before outer) through a warp prefix sum.  Lane 0 then sorts and emits as before, from what (1) left in scratch.
-__device__ inline void extractCycles(const GraphDev &G, TileMem &M, SrcState &S, Emitter &E, const int32_t *c,
-                                     const int32_t *st, const int len) {
+__device__ __forceinline__ void extractCyclesBody(const GraphDev &G, TileMem &M, SrcState &S, Emitter &E, const int32_t *c,
+                                                  const int32_t *st, const int len) {
     constexpr unsigned FULL = 0xFFFFFFFFu;
     const int lane = threadIdx.x & 31;
     int32_t *warc = M.warc; // warc[i]: arc (in the row of c[i]) of the edge c[i-1] - c[i], i = 1..len
@@ -163,6 +163,7 @@ __device__ inline void extractCycles(const GraphDev &G, TileMem &M, SrcState &S,
     int32_t *weid = reinterpret_cast<int32_t *>(M.heap);
     int32_t *rowB = weid + (len + 2);
     int32_t *degP = rowB + (len + 2);
+    WCLK_DECL;
     // (1) lanes over the positions
     for (int i = 1 + lane; i <= len; i += 32) {
         const int32_t u = c[i], from = c[i - 1];
@@ -182,6 +183,7 @@ __device__ inline void extractCycles(const GraphDev &G, TileMem &M, SrcState &S,
         degP[i] = (i >= 2 && i < len) ? (int32_t)(re - rb) : 0;
     }
     __syncwarp(FULL);
+    WCLK(16);
     // (2) prefix sums (:242-250), serially: the order of the additions is the reference's
     if (lane == 0) {
         int numCross = 0, arcsBefore = 0;
@@ -202,6 +204,7 @@ __device__ inline void extractCycles(const GraphDev &G, TileMem &M, SrcState &S,
         degP[len + 1] = arcsBefore;
     }
     __syncwarp(FULL);
+    WCLK(17);
     // (3) good chords (:254-306): lanes over the arcs of the positions 2 .. len-1, in (position, adjacency position) order
     int nch = 0;
     const double total = plen[len];
@@ -288,97 +291,140 @@ __device__ inline void extractCycles(const GraphDev &G, TileMem &M, SrcState &S,
         nch += tot;
     }
     __syncwarp(FULL);
-    if (lane != 0) return; // the rest is serial: lane 0 (the caller re-converges the warp)
-    // stable sort by resulting length (:309; canonical: stable)
-    for (int a = 1; a < nch; ++a) {
-        int32_t t0 = M.chords[4 * a], t1 = M.chords[4 * a + 1], t2 = M.chords[4 * a + 2], t3 = M.chords[4 * a + 3];
-        int b = a - 1;
-        while (b >= 0 && M.chords[4 * b + 2] > t2) {
-            for (int q = 0; q < 4; ++q) M.chords[4 * (b + 1) + q] = M.chords[4 * b + q];
-            --b;
+    WCLK(18);
+    // stable sort by resulting length (:309; canonical: stable): a handful of candidates, lane 0
+    if (lane == 0) {
+        for (int a = 1; a < nch; ++a) {
+            int32_t t0 = M.chords[4 * a], t1 = M.chords[4 * a + 1], t2 = M.chords[4 * a + 2], t3 = M.chords[4 * a + 3];
+            int b = a - 1;
+            while (b >= 0 && M.chords[4 * b + 2] > t2) {
+                for (int q = 0; q < 4; ++q) M.chords[4 * (b + 1) + q] = M.chords[4 * b + q];
+                --b;
+            }
+            M.chords[4 * (b + 1)] = t0;
+            M.chords[4 * (b + 1) + 1] = t1;
+            M.chords[4 * (b + 1) + 2] = t2;
+            M.chords[4 * (b + 1) + 3] = t3;
         }
-        M.chords[4 * (b + 1)] = t0;
-        M.chords[4 * (b + 1) + 1] = t1;
-        M.chords[4 * (b + 1) + 2] = t2;
-        M.chords[4 * (b + 1) + 3] = t3;
     }
-    // greedy, non-overlapping (:312-323).  coveredNodes is READ by position and WRITTEN by node id (quirk A.7.3)
+    __syncwarp(FULL);
+    WCLK(19);
+    // greedy, non-overlapping (:312-323).  coveredNodes is READ by position and WRITTEN by node id (quirk A.7.3).  The decisions
+    // are sequential over the candidates; the lanes share the test against the covered list and the writing of a new walk
+    // (lane 0 owns the emitter and reserves its place).
     int ncov = 0, emitted = 0;
     const int covCap = 4 * (int)M.caps.walkCap + 8;
     for (int q = 0; q < nch; ++q) {
         const int32_t *ch = M.chords + 4 * q;
-        const int start = ch[0], end = ch[1];
-        bool cs = false, ce = false;
-        for (int k = 0; k < ncov; ++k) {
-            cs |= M.covered[k] == start;
-            ce |= M.covered[k] == end;
-        }
-        if (cs || ce) continue;
-        const bool crossing = ch[3] & 1, inner = (ch[3] & 2) != 0;
-        const long long ca = (long long)((uint32_t)ch[3] >> 2);
+        const int start = ch[0], end = ch[1], wlen = ch[2];
+        const uint32_t info = (uint32_t)ch[3];
+        bool hit = false;
+        for (int k = lane; k < min(ncov, covCap); k += 32) hit |= (M.covered[k] == start) || (M.covered[k] == end);
+        if (__any_sync(FULL, hit)) continue;
+        const bool crossing = info & 1u, inner = (info & 2u) != 0;
+        const long long ca = (long long)(info >> 2);
         const int32_t chordEid = G.eid[ca];
-        const int wlen = ch[2];
-        long long cut, off;
-        const bool ok = emitReserve(E, wlen, cut, off);
-        // splitOnChord (odd_closed_walk.cpp:67-90)
-        int pos = 0;
-        auto put = [&](int32_t node, int32_t eid, int32_t stay) {
+        long long cut = 0, off = 0;
+        int ok = 0;
+        if (lane == 0) ok = emitReserve(E, wlen, cut, off) ? 1 : 0;
+        ok = __shfl_sync(FULL, ok, 0);
+        off = __shfl_sync(FULL, off, 0);
+        // splitOnChord (odd_closed_walk.cpp:67-90): position p of the new walk
+        for (int p = lane; p < wlen; p += 32) {
+            int k = -1; // position in the old walk, -1: the chord
+            if (inner) {
+                if (p < end - start) k = start + p;
+            } else {
+                if (p < start)
+                    k = p;
+                else if (p > start)
+                    k = end + (p - start - 1);
+            }
+            const int32_t node = k >= 0 ? c[k] : (inner ? c[end] : c[start]);
+            const int32_t eid = k >= 0 ? weid[k + 1] : chordEid;
+            const int32_t stay = k >= 0 ? st[k] : (crossing ? 0 : 1);
             if (ok) {
-                E.R->node[off + pos] = node;
-                E.R->eid[off + pos] = eid;
-                E.R->stay[off + pos] = (uint8_t)stay;
+                E.R->node[off + p] = node;
+                E.R->eid[off + p] = eid;
+                E.R->stay[off + p] = (uint8_t)stay;
             }
             // covered: positions 1 .. size-2 of the new walk, by node id
-            if (pos >= 1 && pos <= wlen - 2) {
-                if (ncov < covCap) M.covered[ncov] = node;
-                ncov++;
-            }
-            pos++;
-        };
-        if (inner) {
-            for (int k = start; k < end; ++k) put(c[k], weid[k + 1], st[k]);
-            put(c[end], chordEid, crossing ? 0 : 1);
-        } else {
-            for (int k = 0; k < start; ++k) put(c[k], weid[k + 1], st[k]);
-            put(c[start], chordEid, crossing ? 0 : 1);
-            for (int k = end; k < len; ++k) put(c[k], weid[k + 1], st[k]);
+            if (p >= 1 && p <= wlen - 2 && ncov + p - 1 < covCap) M.covered[ncov + p - 1] = node;
         }
+        ncov += max(0, wlen - 2);
         if (ncov > covCap) {
             S.overflow = 1;
             return;
         }
         emitted++;
+        __syncwarp(FULL); // the covered list is read by the next candidate
     }
     if (emitted == 0) { // :325-326: no chord cycle -> the cycle itself
-        long long cut, off;
-        if (emitReserve(E, len, cut, off))
-            for (int k = 0; k < len; ++k) {
+        long long cut = 0, off = 0;
+        int ok = 0;
+        if (lane == 0) ok = emitReserve(E, len, cut, off) ? 1 : 0;
+        ok = __shfl_sync(FULL, ok, 0);
+        off = __shfl_sync(FULL, off, 0);
+        if (ok)
+            for (int k = lane; k < len; k += 32) {
                 E.R->node[off + k] = c[k];
                 E.R->eid[off + k] = weid[k + 1];
                 E.R->stay[off + k] = (uint8_t)st[k];
             }
     }
+    WCLK(20);
+#ifdef SMSGPU_RUNS_CLOCKS
+    if (threadIdx.x == 0 && blockIdx.x == 0) atomicAdd(&g_runClk[21], 1ull);
+#endif
 }
+
+// Two instantiations: inlined (kernels with registers to spare: the runs engine measured 58.5 against 53.1 rounds/s on the LP
+// replay of the 100x100 torus) and out of line (the pairs kernel is compiled for 80 registers, and everything inlined into its
+// finishing code moves the allocation of its hot loop: 503.8 against 472.2 ms on config 5).
+template <bool OUTLINE>
+struct ExtractCycles;
+template <>
+struct ExtractCycles<false> {
+    static __device__ __forceinline__ void run(const GraphDev &G, TileMem &M, SrcState &S, Emitter &E, const int32_t *c, const int32_t *st,
+                                               const int len) {
+        extractCyclesBody(G, M, S, E, c, st, len);
+    }
+};
+__device__ __noinline__ void extractCyclesOutOfLine(const GraphDev &G, TileMem &M, SrcState &S, Emitter &E, const int32_t *c, const int32_t *st,
+                                                    const int len) {
+    extractCyclesBody(G, M, S, E, c, st, len);
+}
+template <>
+struct ExtractCycles<true> {
+    static __device__ __forceinline__ void run(const GraphDev &G, TileMem &M, SrcState &S, Emitter &E, const int32_t *c, const int32_t *st,
+                                               const int len) {
+        extractCyclesOutOfLine(G, M, S, E, c, st, len);
+    }
+};
 
 // simpleOddCycles (:202-227) on the closed walk wn[0..W], then extractCycles on every piece.  All 32 lanes, identical
 // control flow (every lane reads the same walk); S.overflow is made uniform after every piece.
+template <bool OUTLINE>
 __device__ inline void simpleOddCyclesAndExtract(const GraphDev &G, TileMem &M, SrcState &S, Emitter &E, const int W) {
     constexpr unsigned FULL = 0xFFFFFFFFu;
     const int32_t *wn = M.wn, *ws = M.ws;
     int lastLeft = -1;
     bool any = false;
+    const int lane = threadIdx.x & 31;
+    const int32_t w32 = lane <= W ? wn[lane] : -1; // the first 32 positions in registers (most walks are shorter)
     for (int i = 0; i <= W; ++i) {
-        const int32_t v = wn[i];
-        int pp = -1; // prevPos[v]: last earlier position of v
-        for (int k = i - 1; k >= 0; --k)
-            if (wn[k] == v) {
-                pp = k;
-                break;
-            }
+        const int32_t v = i < 32 ? __shfl_sync(FULL, w32, i) : wn[i];
+        int pp = -1; // prevPos[v]: last earlier position of v -- the lanes share the scan
+        for (int b = 0; b < i; b += 32) {
+            const int k = b + lane;
+            const int32_t wk = b == 0 ? w32 : (k < i ? wn[k] : -1);
+            const unsigned m = __ballot_sync(FULL, k < i && wk == v);
+            if (m) pp = b + 31 - __clz(m);
+        }
         if (lastLeft < pp) {
             lastLeft = pp;
             if (i - lastLeft > 2) {
-                extractCycles(G, M, S, E, wn + lastLeft, ws + lastLeft, i - lastLeft);
+                ExtractCycles<OUTLINE>::run(G, M, S, E, wn + lastLeft, ws + lastLeft, i - lastLeft);
                 __syncwarp(FULL);
                 S.overflow = __shfl_sync(FULL, S.overflow, 0);
                 if (S.overflow) return;
@@ -387,7 +433,7 @@ __device__ inline void simpleOddCyclesAndExtract(const GraphDev &G, TileMem &M, 
         }
     }
     if (!any) {
-        extractCycles(G, M, S, E, wn, ws, W);
+        ExtractCycles<OUTLINE>::run(G, M, S, E, wn, ws, W);
         __syncwarp(FULL);
         S.overflow = __shfl_sync(FULL, S.overflow, 0);
     }
@@ -431,6 +477,7 @@ __device__ inline int buildWalk(const GraphDev &G, const TileMem &M, uint32_t t,
 
 // The walks of one source: intermediateVertexToOcw -> simpleOddCycles -> extractCycles for each selected intermediate
 // (ocw_seperator.cpp:341-358).  All 32 lanes; lane 0 owns the emitter.  Leaves S.overflow uniform.
+template <bool OUTLINE = false>
 __device__ inline void walksOfSource(const GraphDev &G, TileMem &M, SrcState &S, Emitter &E, const uint32_t *sel, const int nsel,
                                      const uint32_t src, const int32_t now) {
     constexpr unsigned FULL = 0xFFFFFFFFu;
@@ -452,7 +499,7 @@ __device__ inline void walksOfSource(const GraphDev &G, TileMem &M, SrcState &S,
             S.overflow = 1;
             return;
         }
-        simpleOddCyclesAndExtract(G, M, S, E, W);
+        simpleOddCyclesAndExtract<OUTLINE>(G, M, S, E, W);
         WCLK(12);
         if (S.overflow) return;
     }

@@ -1600,12 +1600,14 @@ int separateLocal(smsgpu_ctx *ctx, const smsgpu_params &P) {
               rawCuts};
 #ifdef SMSGPU_RUNS_CLOCKS
     {
-        unsigned long long h[16];
+        unsigned long long h[24];
         if (cudaMemcpyFromSymbol(h, g_runClk, sizeof h) == cudaSuccess) {
             std::fprintf(stderr, "[smsgpu] runs engine, CTA 0, cycles: offers + grouping %llu | apply %llu | record logic %llu | rollback %llu || pool minimum %llu | "
                                  "collect %llu | member sort %llu | chunk set-up %llu | rest of the tail %llu | table reset %llu || selection %llu | buildWalk %llu | "
-                                 "simple cycles + chords %llu | walks %llu of mean length %.1f, max %llu\n",
-                         h[0], h[1], h[2], h[3], h[4], h[5], h[6], h[7], h[8], h[9], h[10], h[11], h[12], h[14], h[14] ? (double)h[13] / (double)h[14] : 0.0, h[15]);
+                                 "simple cycles + chords %llu | walks %llu of mean length %.1f, max %llu || extractCycles x %llu: positions %llu | prefix sums %llu | "
+                                 "chord test %llu | sort %llu | greedy + emission %llu\n",
+                         h[0], h[1], h[2], h[3], h[4], h[5], h[6], h[7], h[8], h[9], h[10], h[11], h[12], h[14], h[14] ? (double)h[13] / (double)h[14] : 0.0, h[15],
+                         h[21], h[16], h[17], h[18], h[19], h[20]);
             std::memset(h, 0, sizeof h);
             cudaMemcpyToSymbol(g_runClk, h, sizeof h);
         }
