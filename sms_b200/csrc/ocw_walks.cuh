@@ -5,8 +5,10 @@
 //   simpleOddCycles      <- OcwSeparator::simpleOddCycles                  (ocw_seperator.cpp:202-227)
 //   extractCycles        <- OcwSeparator::extractCycles + OddClosedWalk::splitOnChord
 //                                                   (ocw_seperator.cpp:229-328, odd_closed_walk.cpp:67-90)
-// Walks are a handful of edges long, so everything after the selection is plain sequential code on lane 0;
-// the reference's O(n) scratch vectors (prevPos[n_], coveredNodes(n_)) become scans over the walk itself.
+// The predecessor chains are followed by lane 0 (buildWalk); everything that needs the graph afterwards is done with the
+// lanes of the warp over independent items (extractCycles), because one warp visiting the positions of a 20-edge cycle
+// one after the other pays two or three memory round trips per position.  The reference's O(n)
+// scratch vectors (prevPos[n_], coveredNodes(n_)) become scans over the walk itself.
 #pragma once
 #include "ocw_search.cuh"
 
@@ -115,13 +117,6 @@ __device__ int selectIntermediates(const Tile<TW> &T, TileMem &M, SrcState &S, i
 }
 
 // ---- sequential helpers (lane 0) ------------------------------------------------------------------------------
-// Graph::indexInOutEdgeArray (NetworKit Graph.cpp:119-127): first adjacency position of u holding v
-__device__ __forceinline__ long long findArc(const GraphDev &G, int32_t u, int32_t v) {
-    for (long long a = G.rowptr[u]; a < G.rowptr[u + 1]; ++a)
-        if ((G.arcs[a].nbr & 0x7FFFFFFF) == v) return a;
-    return -1;
-}
-
 // getShortestPath (:120-136): doubled ids t = p[0], previous_[p[0]] = p[1], ..., p[len] = source.  -1 on overflow.
 __device__ inline int tracePath(const TileMem &M, uint32_t t, uint32_t src, int32_t *p) {
     int len = 0;
