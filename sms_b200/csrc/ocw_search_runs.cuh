@@ -628,12 +628,21 @@ __global__ void __launch_bounds__(kRunThreads, SMSGPU_RUNS_MIN_CTAS) ocwSearchRu
             // ---- the minimal key of the pool: 128-bit lexicographic minimum over the live keys -------------------------------
             const uint32_t poolN = sh.poolN;
             unsigned long long mhi = ~0ull, mlo = ~0ull;
-            for (uint32_t i = threadIdx.x; i < poolN; i += blockDim.x) {
-                const HeapEnt k = M.heap[i];
-                if (k.hi != kDeadKey && keyLess(k.hi, k.lo, mhi, mlo)) {
-                    mhi = k.hi;
-                    mlo = k.lo;
+            for (uint32_t i0 = threadIdx.x; i0 < poolN; i0 += 4 * kRunThreads) { // four keys per thread in flight: the scan is latency
+                HeapEnt k[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const uint32_t i = i0 + j * kRunThreads;
+                    k[j].hi = kDeadKey;
+                    k[j].lo = ~0ull;
+                    if (i < poolN) k[j] = M.heap[i];
                 }
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    if (k[j].hi != kDeadKey && keyLess(k[j].hi, k[j].lo, mhi, mlo)) {
+                        mhi = k[j].hi;
+                        mlo = k[j].lo;
+                    }
             }
 #pragma unroll
             for (int off = 16; off > 0; off >>= 1) {
@@ -670,13 +679,24 @@ __global__ void __launch_bounds__(kRunThreads, SMSGPU_RUNS_MIN_CTAS) ocwSearchRu
             {
                 const unsigned long long dhi = sh.minHi;
                 const uint32_t hmin = sh.runH;
-                for (uint32_t i = threadIdx.x; i < poolN; i += blockDim.x) {
-                    const HeapEnt k = M.heap[i];
-                    if (k.hi == dhi && (uint32_t)(k.lo >> 32) == hmin) {
-                        const uint32_t pos = atomicAdd(&sh.runLen, 1u);
-                        if (pos < X.runCap) X.run[pos] = (uint32_t)k.lo;
-                        M.heap[i].hi = kDeadKey;
-                        X.qpos[(uint32_t)k.lo] = kNoQpos;
+                for (uint32_t i0 = threadIdx.x; i0 < poolN; i0 += 4 * kRunThreads) {
+                    HeapEnt k[4];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const uint32_t i = i0 + j * kRunThreads;
+                        k[j].hi = kDeadKey;
+                        k[j].lo = ~0ull;
+                        if (i < poolN) k[j] = M.heap[i];
+                    }
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const uint32_t i = i0 + j * kRunThreads;
+                        if (i < poolN && k[j].hi == dhi && (uint32_t)(k[j].lo >> 32) == hmin) {
+                            const uint32_t pos = atomicAdd(&sh.runLen, 1u);
+                            if (pos < X.runCap) X.run[pos] = (uint32_t)k[j].lo;
+                            M.heap[i].hi = kDeadKey;
+                            X.qpos[(uint32_t)k[j].lo] = kNoQpos;
+                        }
                     }
                 }
             }
