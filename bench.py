@@ -55,6 +55,10 @@ REF_SAMPLE = {"random1m": 2048, "torus100": 10_000, "torus3d20": 8_000, "random2
 
 # dram bytes of the search of one full round, from the committed ncu capture (per launch; see roofline.traffic_note)
 TRAFFIC_NCU = {"random1m": round(150.746169e9 * 1254134233 / 329005693)}  # 150.75 GB for the capture's 329.0 M (reference-equivalent) settled nodes
+# the same capture's dram__bytes_read alone (120.31 GB), and what the microbenchmark of isolated accesses measured on this part
+# (profiles/r02_sector_flavors.md: every isolated load brings a 128-byte line from DRAM; 33.9 G of them per second at most)
+TRAFFIC_READ_NCU = {"random1m": round(120.307265e9 * 1254134233 / 329005693)}
+ISOLATED_LINE_BYTES, ISOLATED_READS_PER_S = 128, 33.9e9
 
 
 XSTAR_NOTE = {"fixed": "", "fresh": "; a NEW iid U(0,1) x* every step", "replay": "; x* sequence from the cutting loop (HiGHS root LP iterates, one per step)"}
@@ -657,7 +661,15 @@ def main():
                                          "(ncu --set full, 262144 sources), scaled to the round by settled nodes; every isolated 32-byte "
                                          "access brings a 128-byte line from DRAM (profiles/r02_sector_flavors.md); the path is bound by the "
                                          "latency of dependent accesses, not by bytes (DESIGN.md section 5)",
-                         "algorithmic_bytes": alg_bytes, "per_gpu": True},
+                         "algorithmic_bytes": alg_bytes, "per_gpu": True,
+                         # second view (not the contract's `frac`): line fetches per second against the measured rate of isolated reads
+                         "access_rate": ({"unit": "128-byte DRAM line fetches per second per GPU",
+                                          "achieved": TRAFFIC_READ_NCU[args.workload] / ISOLATED_LINE_BYTES / (res["ms_search"] * 1e-3) / world,
+                                          "ceiling": ISOLATED_READS_PER_S,
+                                          "frac": TRAFFIC_READ_NCU[args.workload] / ISOLATED_LINE_BYTES / (res["ms_search"] * 1e-3) / world / ISOLATED_READS_PER_S,
+                                          "source": "dram__bytes_read of profiles/r02_pairs_tier1_random1m_256k_final.md scaled to the round; "
+                                                    "ceiling: scripts/sector_flavors.cu, profiles/r02_sector_flavors.md"}
+                                         if args.workload in TRAFFIC_READ_NCU and res["ms_search"] > 0 and args.mode == 0 else None)},
             "e2e": {"value": args.steps / res["e2e_dt"], "unit": "rounds/s", "h2d_bytes_per_step": res["h2d"],
                     "d2h_bytes_per_step": res["d2h"]},
             "gpu_launches": int(res["stats"]["total_launches"]) * args.steps,
