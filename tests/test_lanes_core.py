@@ -1,7 +1,7 @@
 """The sequential core of the lanes engine (sms_b200/csrc/ocw_lanes_core.cuh: one source per thread) compiled for the
 HOST and run on the CPU against the oracle: labels (dist, hops) bit for bit, arcs scanned / settled / number of
 intermediates per source, and predecessors that are consistent with the labels.  The same code runs per thread on the
-GPU (tests/test_gpu_parity.py::test_lanes_engine_equals_oracle compares its walks)."""
+GPU (tests/test_lanes_gpu.py compares its walks with the oracle and its whole round with the pairs engine's)."""
 import ctypes
 import os
 import subprocess
